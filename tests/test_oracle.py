@@ -1,0 +1,126 @@
+"""Pins the oracle (CPU checker): C restatement vs golden vectors vs the genuine libswscale.
+
+No GPU, no product code: this file is what lets the `-m gpu` parity tests trust oracle/.
+"""
+import hashlib
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+from oracle import port, ref_swscale
+from thinvids_b200 import frames as F
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+HASHES = json.load(open(os.path.join(GOLD, "swscale_hashes.json")))["cases"]
+SMALL = json.load(open(os.path.join(GOLD, "small_cases.json")))
+TABLES = json.load(open(os.path.join(GOLD, "survey_tables.json")))
+
+
+def _make_input(spec, fmt, w, h):
+    kind, arg = spec.split(":")
+    return F.random_frame(fmt, w, h, int(arg)) if kind == "seed" else F.pattern_frame(fmt, w, h, arg)
+
+
+def _port(c):
+    return port.PortScaler(c["src_w"], c["src_h"], F.FMT_BY_NAME[c["src_fmt"]], c["dst_w"], c["dst_h"],
+                           F.FMT_BY_NAME[c["dst_fmt"]], F.ALG_BY_NAME[c["alg"]])
+
+
+def _case_id(c):
+    return "%s_%dx%d-%s_%dx%d-%s-%s" % (c["src_fmt"], c["src_w"], c["src_h"], c["dst_fmt"], c["dst_w"], c["dst_h"],
+                                        c["alg"], c.get("input", c.get("seed")))
+
+
+@pytest.mark.parametrize("name", sorted(TABLES["configs"]))
+def test_port_tables_match_survey_hashes(name):
+    ent = TABLES["configs"][name]
+    sf, sw, sh, df, dw, dh, alg = ent["args"]
+    p = port.PortScaler(sw, sh, F.FMT_BY_NAME[sf], dw, dh, F.FMT_BY_NAME[df], F.ALG_BY_NAME[alg])
+    for which in range(4):
+        coef, pos = p.table(which)
+        assert coef.shape[1] == ent["taps"][which]
+        digest = hashlib.sha256(coef.astype(np.int16).tobytes() + pos.astype(np.int32).tobytes()).hexdigest()
+        assert digest == ent["sha256"][which], (name, which)
+
+
+def test_port_table_spot_values():
+    p = port.PortScaler(720, 480, 0, 1920, 1080, 0, F.SWS_LANCZOS)
+    h, hpos = p.table(0)
+    v, vpos = p.table(2)
+    s = TABLES["spot"]
+    assert h[:10].tolist() == s["C1_hLum_first10"] and h[-3:].tolist() == s["C1_hLum_last3"]
+    assert v[:10].tolist() == s["C1_vLum_first10"] and v[-3:].tolist() == s["C1_vLum_last3"]
+    assert (h.sum(axis=1) == 16384).all() and (v.sum(axis=1) == 4096).all()
+    assert hpos[-1] == 714 and vpos[-1] == 474
+    p2 = port.PortScaler(1920, 1080, 0, 3840, 2160, 0, F.SWS_BICUBIC)
+    h2, _ = p2.table(0)
+    assert h2[:6].tolist() == s["C2_hLum_first6"] and h2[-2:].tolist() == s["C2_hLum_last2"]
+
+
+@pytest.mark.parametrize("case", HASHES, ids=_case_id)
+def test_port_matches_golden_hashes(case):
+    src = _make_input(case["input"], case["src_fmt"], case["src_w"], case["src_h"])
+    assert F.frame_sha256(_port(case).scale(src)) == case["sha256"]
+
+
+def test_port_matches_small_golden_outputs():
+    blobs = np.load(os.path.join(GOLD, "small_cases.npz"))
+    for i, c in enumerate(SMALL):
+        src = F.random_frame(c["src_fmt"], c["src_w"], c["src_h"], c["seed"])
+        got = _port(c).scale(src)
+        for k in range(c["n_dst_planes"]):
+            assert np.array_equal(got[k], blobs[f"case{i}_dst{k}"]), (_case_id(c), k)
+
+
+needs_ref = pytest.mark.skipif(not ref_swscale.available(), reason="genuine libswscale not loadable here")
+
+
+@needs_ref
+def test_reference_library_is_the_pinned_build():
+    assert ref_swscale.version().startswith("libswscale 9.1.100")
+
+
+@needs_ref
+def test_port_equals_genuine_library_on_random_shapes():
+    rnd = random.Random(11)
+    algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
+    for i in range(80):
+        sf, df = rnd.randrange(4), rnd.randrange(4)
+        sw, sh = rnd.randrange(8, 160), rnd.randrange(8, 100)
+        dw = sw if rnd.random() < 0.2 else rnd.randrange(8, 240)
+        dh = sh if rnd.random() < 0.2 else rnd.randrange(8, 160)
+        alg = rnd.choice(algs)
+        src = F.random_frame(sf, sw, sh, i)
+        a = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        b = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg).scale_into(src, a)
+        port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale_into(src, b)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), (sf, df, sw, sh, dw, dh, hex(alg))
+
+
+@needs_ref
+def test_port_equals_genuine_library_unscaled_all_format_pairs():
+    for sf in range(4):
+        for df in range(4):
+            for w, h in [(64, 48), (67, 35), (76, 20), (2, 2)]:
+                src = F.random_frame(sf, w, h, 7)
+                a = [np.full_like(p, 77) for p in F.alloc_frame(df, w, h)]
+                b = [np.full_like(p, 77) for p in F.alloc_frame(df, w, h)]
+                ref_swscale.RefScaler(w, h, sf, w, h, df, F.SWS_BICUBIC).scale_into(src, a)
+                port.PortScaler(w, h, sf, w, h, df, F.SWS_BICUBIC).scale_into(src, b)
+                for x, y in zip(a, b):
+                    assert np.array_equal(x, y), (sf, df, w, h)
+
+
+@needs_ref
+def test_port_equals_genuine_library_with_explicit_chroma_siting():
+    for cp in [(0, -513, 0, -513), (0, 128, 0, 128), (0, 0, 0, 0), (0, 128, 128, 128)]:
+        src = F.random_frame(0, 320, 240, 5)
+        a = ref_swscale.RefScaler(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, chr_pos=cp).scale(src)
+        b = port.PortScaler(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, chr_pos=cp).scale(src)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), cp
