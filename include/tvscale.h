@@ -1,0 +1,135 @@
+/*
+ * tvscale.h — C ABI of the B200-native scale / pixel-format stage for thinvids.
+ *
+ * What it replaces.  The reference's `encode` task (worker/tasks.py:1354) spawns one ffmpeg child per
+ * segment with `-vf setpts=PTS-STARTPTS,[bwdif,]scale=-2:H[,format=nv12,hwupload]`
+ * (worker/tasks.py:62-65,436-449,1558-1586); tools/upscale_benchmark.py:163,182 does the same with
+ * `scale=-2:H:flags=lanczos,format=yuv420p|nv12`.  Inside ffmpeg that filter is libswscale's public trio
+ * sws_getContext / sws_scale / sws_freeContext (libswscale/swscale.h; third-party, not vendored under
+ * /root/reference).  The entry points below are that trio re-cut for device memory and batches of
+ * frames; a binding that used to call libswscale binds these instead.
+ *
+ * Semantics.  Output bytes are identical to libswscale 9.1.100 run with
+ * flags = alg | SWS_ACCURATE_RND | SWS_BITEXACT, for 4:2:0 8- and 10-bit planar and
+ * semi-planar formats.  There is no CPU fallback: every pixel is produced by sm_100a CUDA kernels, and
+ * every call fails with a negative code when no usable device is present.
+ *
+ * Conventions.  All functions return 0 (or a positive count where stated) on success and a negative
+ * errno-style code on failure; tvs_last_error() then holds a human-readable message for the calling
+ * thread.  A context belongs to one device and, like a SwsContext, must not be used by two threads at
+ * once.  Plain C types only: no CUDA or torch types appear in any signature (streams travel as void*).
+ */
+#ifndef TVSCALE_H
+#define TVSCALE_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Pixel formats (the 4:2:0 subset of AVPixelFormat the reference's filter strings produce). */
+enum {
+    TVS_FMT_YUV420P     = 0, /* AV_PIX_FMT_YUV420P      planes Y, U, V            8 bit  */
+    TVS_FMT_NV12        = 1, /* AV_PIX_FMT_NV12         planes Y, UV interleaved  8 bit  */
+    TVS_FMT_YUV420P10LE = 2, /* AV_PIX_FMT_YUV420P10LE  planes Y, U, V            10 bit in the low bits of LE16  */
+    TVS_FMT_P010LE      = 3  /* AV_PIX_FMT_P010LE       planes Y, UV interleaved  10 bit in the high bits of LE16 */
+};
+
+/* Scaler flags: numerically equal to libswscale's SWS_* so ffmpeg `flags=` values pass through. */
+enum {
+    TVS_BILINEAR     = 2,
+    TVS_BICUBIC      = 4,      /* ffmpeg's default when the filter string has no flags= (worker/tasks.py:448) */
+    TVS_AREA         = 0x20,
+    TVS_LANCZOS      = 0x200,  /* tools/upscale_benchmark.py:163,182 */
+    TVS_ACCURATE_RND = 0x40000,/* accepted; results are always accurate_rnd+bitexact */
+    TVS_BITEXACT     = 0x80000
+};
+
+/* Chroma siting sentinel: "use libswscale's default" (centre), as sws_getContext does. */
+#define TVS_CHR_POS_DEFAULT (-513)
+
+typedef struct tvs_ctx tvs_ctx;
+
+/*
+ * Replaces sws_getContext(srcW, srcH, srcFormat, dstW, dstH, dstFormat, flags, NULL, NULL, NULL)
+ * (libswscale/swscale.h), i.e. what ffmpeg's vf_scale does for `scale=W:H:flags=...` at
+ * worker/tasks.py:1565-1567,1580.  Builds the four fixed-point coefficient tables on the host
+ * (SURVEY.md A.2), uploads them to `device`, and plans the kernel launches.
+ * chr_pos = {src_h, src_v, dst_h, dst_v} in 1/256 luma-pixel units (ffmpeg's *_chr_pos options) or NULL.
+ * Returns NULL on failure.
+ */
+tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt,
+                    int flags, const int chr_pos[4]);
+
+/* Replaces sws_freeContext(). */
+void tvs_destroy(tvs_ctx *ctx);
+
+/*
+ * Replaces sws_scale(ctx, src, srcStride, 0, srcH, dst, dstStride) for `n_frames` frames that are
+ * already in DEVICE memory (decoder surfaces, or a previous filter's output).
+ *   src[i] / dst[i]          device pointer to plane i of frame 0 (2 planes for NV12/P010, else 3)
+ *   *_pitch[i]               bytes between rows of plane i (any value >= the row size; NVDEC pitches fit)
+ *   *_frame_stride[i]        bytes between the same plane of consecutive frames
+ *   stream                   a cudaStream_t passed as void* (NULL = default stream)
+ * Asynchronous with respect to the host: returns once the work is enqueued on `stream`.
+ * Returns dst_h (like sws_scale) or a negative error code.
+ */
+int tvs_scale_batch(tvs_ctx *ctx,
+                    const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                    void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                    int n_frames, void *stream);
+
+/*
+ * The literal drop-in for sws_scale(): HOST planes in, HOST planes out, same plane/stride meaning,
+ * `n_frames` frames spaced by *_frame_stride bytes.  Copies the frames to the context's device,
+ * scales them there and copies the result back, in chunks that overlap copies with kernels on two
+ * streams; returns after the last byte has landed in dst.  Host buffers may be pageable; pinned
+ * buffers (cudaHostAlloc / torch pin_memory) are copied without an intermediate staging step.
+ * Returns dst_h or a negative error code.
+ */
+int tvs_scale_host(tvs_ctx *ctx,
+                   const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                   void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                   int n_frames);
+
+/*
+ * Host-only: one axis of libswscale's initFilter.  No device needed.
+ *   inc = ((src_len << 16) + (dst_len >> 1)) / dst_len, one = 1<<14 (horizontal) or 1<<12 (vertical),
+ *   src_pos / dst_pos = 128 for luma and centred chroma.
+ * Writes taps*dst_len int16 coefficients and dst_len int32 start positions when the buffers are large
+ * enough (coef_cap / pos_cap count elements); returns the tap count, or a negative error code.
+ * Calling with coef == NULL just returns the tap count.
+ */
+int tvs_filter_table(int src_len, int dst_len, int alg, int one, int src_pos, int dst_pos,
+                     int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap);
+
+/* Read back a context's table: which = 0 hLum, 1 hChr, 2 vLum, 3 vChr.  Same buffer rules as above. */
+int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap);
+
+/*
+ * Plan introspection for benchmarks and tests.
+ *   TVS_INFO_KERNEL_LAUNCHES  kernels launched by this context so far (monotonic)
+ *   TVS_INFO_PATH             0 = fused tile kernel, 1 = two-pass kernels through device scratch,
+ *                             2 = same-size repack only
+ *   TVS_INFO_SCRATCH_BYTES    device scratch currently owned by the context
+ *   TVS_INFO_SRC_FRAME_BYTES / TVS_INFO_DST_FRAME_BYTES   tightly packed frame sizes
+ */
+enum { TVS_INFO_KERNEL_LAUNCHES = 0, TVS_INFO_PATH = 1, TVS_INFO_SCRATCH_BYTES = 2,
+       TVS_INFO_SRC_FRAME_BYTES = 3, TVS_INFO_DST_FRAME_BYTES = 4 };
+long long tvs_info(const tvs_ctx *ctx, int what);
+
+/* Force a kernel path for testing: -1 = automatic, 0 = fused, 1 = two-pass.  Returns 0 or -EINVAL. */
+int tvs_set_path(tvs_ctx *ctx, int path);
+
+/* Message describing the last failure on the calling thread ("" if none). */
+const char *tvs_last_error(void);
+
+/* Library version string, e.g. "tvscale 0.1 (sm_100a)". */
+const char *tvs_version(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* TVSCALE_H */
