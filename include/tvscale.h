@@ -25,6 +25,12 @@
 #include <stddef.h>
 #include <stdint.h>
 
+#if defined(__GNUC__)
+#define TVS_API __attribute__((visibility("default")))
+#else
+#define TVS_API
+#endif
+
 #ifdef __cplusplus
 extern "C" {
 #endif
@@ -60,11 +66,11 @@ typedef struct tvs_ctx tvs_ctx;
  * chr_pos = {src_h, src_v, dst_h, dst_v} in 1/256 luma-pixel units (ffmpeg's *_chr_pos options) or NULL.
  * Returns NULL on failure.
  */
-tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt,
+TVS_API tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt,
                     int flags, const int chr_pos[4]);
 
 /* Replaces sws_freeContext(). */
-void tvs_destroy(tvs_ctx *ctx);
+TVS_API void tvs_destroy(tvs_ctx *ctx);
 
 /*
  * Replaces sws_scale(ctx, src, srcStride, 0, srcH, dst, dstStride) for `n_frames` frames that are
@@ -76,7 +82,7 @@ void tvs_destroy(tvs_ctx *ctx);
  * Asynchronous with respect to the host: returns once the work is enqueued on `stream`.
  * Returns dst_h (like sws_scale) or a negative error code.
  */
-int tvs_scale_batch(tvs_ctx *ctx,
+TVS_API int tvs_scale_batch(tvs_ctx *ctx,
                     const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
                     void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
                     int n_frames, void *stream);
@@ -89,7 +95,7 @@ int tvs_scale_batch(tvs_ctx *ctx,
  * buffers (cudaHostAlloc / torch pin_memory) are copied without an intermediate staging step.
  * Returns dst_h or a negative error code.
  */
-int tvs_scale_host(tvs_ctx *ctx,
+TVS_API int tvs_scale_host(tvs_ctx *ctx,
                    const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
                    void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
                    int n_frames);
@@ -102,11 +108,11 @@ int tvs_scale_host(tvs_ctx *ctx,
  * enough (coef_cap / pos_cap count elements); returns the tap count, or a negative error code.
  * Calling with coef == NULL just returns the tap count.
  */
-int tvs_filter_table(int src_len, int dst_len, int alg, int one, int src_pos, int dst_pos,
+TVS_API int tvs_filter_table(int src_len, int dst_len, int alg, int one, int src_pos, int dst_pos,
                      int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap);
 
 /* Read back a context's table: which = 0 hLum, 1 hChr, 2 vLum, 3 vChr.  Same buffer rules as above. */
-int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap);
+TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap);
 
 /*
  * Plan introspection for benchmarks and tests.
@@ -118,16 +124,16 @@ int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size_t coef_
  */
 enum { TVS_INFO_KERNEL_LAUNCHES = 0, TVS_INFO_PATH = 1, TVS_INFO_SCRATCH_BYTES = 2,
        TVS_INFO_SRC_FRAME_BYTES = 3, TVS_INFO_DST_FRAME_BYTES = 4 };
-long long tvs_info(const tvs_ctx *ctx, int what);
+TVS_API long long tvs_info(const tvs_ctx *ctx, int what);
 
 /* Force a kernel path for testing: -1 = automatic, 0 = fused, 1 = two-pass.  Returns 0 or -EINVAL. */
-int tvs_set_path(tvs_ctx *ctx, int path);
+TVS_API int tvs_set_path(tvs_ctx *ctx, int path);
 
 /* Message describing the last failure on the calling thread ("" if none). */
-const char *tvs_last_error(void);
+TVS_API const char *tvs_last_error(void);
 
 /* Library version string, e.g. "tvscale 0.1 (sm_100a)". */
-const char *tvs_version(void);
+TVS_API const char *tvs_version(void);
 
 #ifdef __cplusplus
 }

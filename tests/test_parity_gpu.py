@@ -1,0 +1,206 @@
+"""Parity proper: the sm_100a kernels, called through the C ABI, against the oracle (oracle/port.py, itself
+pinned to the genuine libswscale by tests/test_oracle.py) and against the committed golden vectors.
+Bit-exact: every comparison is array equality or a SHA-256 match."""
+import json
+import os
+import random
+
+import numpy as np
+import pytest
+
+from thinvids_b200 import frames as F
+
+pytestmark = pytest.mark.gpu
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+HASHES = json.load(open(os.path.join(GOLD, "swscale_hashes.json")))["cases"]
+SMALL = json.load(open(os.path.join(GOLD, "small_cases.json")))
+PATHS = ("auto", "two-pass")
+
+
+def _scaler(c, **kw):
+    from thinvids_b200.swscale import Scaler
+    return Scaler(c["src_w"], c["src_h"], c["src_fmt"], c["dst_w"], c["dst_h"], c["dst_fmt"], c["alg"], **kw)
+
+
+def _input(spec, fmt, w, h):
+    kind, arg = spec.split(":")
+    return F.random_frame(fmt, w, h, int(arg)) if kind == "seed" else F.pattern_frame(fmt, w, h, arg)
+
+
+def _id(c):
+    return "%s_%dx%d-%s_%dx%d-%s-%s" % (c["src_fmt"], c["src_w"], c["src_h"], c["dst_fmt"], c["dst_w"], c["dst_h"],
+                                        c["alg"], c.get("input", c.get("seed")))
+
+
+@pytest.mark.parametrize("path", PATHS)
+@pytest.mark.parametrize("case", HASHES, ids=_id)
+def test_golden_hashes(case, path):
+    """Every golden vector of SURVEY.md Appendix B.2 (+ the extras) through tvs_scale_host."""
+    with _scaler(case) as s:
+        if path != "auto":
+            s.set_path(path)
+        out = s.scale(_input(case["input"], case["src_fmt"], case["src_w"], case["src_h"]))
+        assert F.frame_sha256(out) == case["sha256"], s.path
+
+
+@pytest.mark.parametrize("path", PATHS)
+def test_small_golden_outputs(path):
+    blobs = np.load(os.path.join(GOLD, "small_cases.npz"))
+    for i, c in enumerate(SMALL):
+        with _scaler(c) as s:
+            if path != "auto":
+                s.set_path(path)
+            got = s.scale(F.random_frame(c["src_fmt"], c["src_w"], c["src_h"], c["seed"]))
+        for k in range(c["n_dst_planes"]):
+            assert np.array_equal(got[k], blobs[f"case{i}_dst{k}"]), (_id(c), k, path)
+
+
+def test_random_shapes_against_oracle():
+    """Seeded random sizes/formats/algorithms, oracle port as the checker (it finishes these in milliseconds)."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    rnd = random.Random(2026)
+    algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
+    for i in range(120):
+        sf, df = rnd.randrange(4), rnd.randrange(4)
+        sw, sh = rnd.randrange(2, 400), rnd.randrange(2, 300)
+        dw = sw if rnd.random() < 0.15 else rnd.randrange(2, 500)
+        dh = sh if rnd.random() < 0.15 else rnd.randrange(2, 400)
+        alg = rnd.choice(algs)
+        src = F.random_frame(sf, sw, sh, 1000 + i)
+        want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+        port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale_into(src, want)
+        for path in PATHS:
+            got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                if path != "auto":
+                    s.set_path(path)
+                s.scale(src, got)
+            for k, (a, b) in enumerate(zip(got, want)):
+                assert np.array_equal(a, b), (i, path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
+
+
+def test_unscaled_all_format_pairs_against_oracle():
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    for sf in range(4):
+        for df in range(4):
+            for w, h in [(64, 48), (67, 35), (76, 20), (2, 2), (1620, 8)]:
+                src = F.random_frame(sf, w, h, 7)
+                want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, w, h)]
+                got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, w, h)]
+                port.PortScaler(w, h, sf, w, h, df, F.SWS_BICUBIC).scale_into(src, want)
+                with Scaler(w, h, sf, w, h, df, F.SWS_BICUBIC) as s:
+                    s.scale(src, got)
+                for a, b in zip(got, want):
+                    assert np.array_equal(a, b), (sf, df, w, h)
+
+
+def test_chroma_siting_against_oracle():
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    for cp in [(0, -513, 0, -513), (0, 128, 0, 128), (0, 0, 0, 0), (0, 128, 128, 128)]:
+        src = F.random_frame(0, 320, 240, 5)
+        want = port.PortScaler(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, chr_pos=cp).scale(src)
+        with Scaler(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, chr_pos=cp) as s:
+            got = s.scale(src)
+        for a, b in zip(got, want):
+            assert np.array_equal(a, b), cp
+
+
+def test_pitched_and_strided_device_surfaces():
+    """NVDEC-style pitched planes (pitch > row, odd pitches too) through tvs_scale_batch directly."""
+    import torch
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    for sf, df, sw, sh, dw, dh, alg, spitch_extra, dpitch_extra in [
+        (1, 1, 320, 180, 480, 270, F.SWS_LANCZOS, 192, 32), (0, 0, 322, 182, 161, 91, F.SWS_BICUBIC, 3, 5),
+        (3, 3, 128, 72, 256, 144, F.SWS_BICUBIC, 64, 2), (2, 0, 130, 74, 99, 55, F.SWS_AREA, 6, 1)]:
+        n = 3
+        frames = [F.random_frame(sf, sw, sh, 50 + i) for i in range(n)]
+        want = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(fr) for fr in frames]
+
+        def surfaces(fmt, w, h, extra, fill_from=None):
+            bufs, ptrs, pitches, fstrides = [], [], [], []
+            bps = 1 if F.bit_depth(fmt) == 8 else 2
+            for k, (rows, cols) in enumerate(F.plane_shapes(fmt, w, h)):
+                pitch = cols * bps + extra * bps
+                host = np.full((n, rows + 1, pitch), 0xEE, dtype=np.uint8)
+                if fill_from is not None:
+                    for i in range(n):
+                        host[i, :rows, :cols * bps] = np.ascontiguousarray(fill_from[i][k]).view(np.uint8).reshape(rows, cols * bps)
+                t = torch.from_numpy(host).cuda()
+                bufs.append(t); ptrs.append(t.data_ptr()); pitches.append(pitch); fstrides.append((rows + 1) * pitch)
+            return bufs, ptrs, pitches, fstrides
+
+        sb, sp, spi, sfs = surfaces(sf, sw, sh, spitch_extra, frames)
+        db, dp, dpi, dfs = surfaces(df, dw, dh, dpitch_extra)
+        with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+            for path in PATHS:
+                if path != "auto":
+                    s.set_path(path)
+                s.scale_device_planes(sp, spi, sfs, dp, dpi, dfs, n, torch.cuda.current_stream().cuda_stream)
+                torch.cuda.synchronize()
+                bps = 1 if F.bit_depth(df) == 8 else 2
+                for k, (rows, cols) in enumerate(F.plane_shapes(df, dw, dh)):
+                    host = db[k].cpu().numpy()
+                    for i in range(n):
+                        got = host[i, :rows, :cols * bps]
+                        exp = np.ascontiguousarray(want[i][k]).view(np.uint8).reshape(rows, cols * bps)
+                        assert np.array_equal(got, exp), (sf, df, path, k, i)
+                        assert (host[i, :rows, cols * bps:] == 0xEE).all(), "wrote into the pitch padding"
+                        assert (host[i, rows, :] == 0xEE).all(), "wrote past the last row"
+                    db[k].fill_(0xEE)
+
+
+def test_full_size_batch_properties():
+    """BASELINE sizes, whole batches: every frame of a C1 batch equals the single-frame result (frames are
+    independent), constant frames stay constant (rows of every table sum to one), device and host entry points agree."""
+    import torch
+    from thinvids_b200.swscale import Scaler
+    c = F.CONFIGS["C1"]
+    n = 12
+    with Scaler(c.src_w, c.src_h, c.src_fmt, c.dst_w, c.dst_h, c.dst_fmt, c.alg) as s:
+        frames = [F.random_frame(c.src_fmt, c.src_w, c.src_h, 1234 + (i % 2)) for i in range(n)]
+        packed = s.src_layout.pack(frames)
+        out_host = s.scale_packed_host(packed)
+        d_src = torch.from_numpy(packed).cuda()
+        d_dst = torch.empty((n, s.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+        s.scale_packed_device(d_src, d_dst)
+        torch.cuda.synchronize()
+        assert np.array_equal(d_dst.cpu().numpy(), out_host)
+        outs = s.dst_layout.unpack(out_host)
+        golden = {h["input"]: h["sha256"] for h in HASHES if h["src_w"] == 720 and h["dst_w"] == 1920 and h["alg"] == "lanczos"
+                  and h["src_fmt"] == "yuv420p"}
+        for i, fr in enumerate(outs):
+            assert F.frame_sha256(fr) == golden["seed:%d" % (1234 + (i % 2))]
+        for v in (0, 16, 128, 235, 255):
+            const = [np.full(sh, v, dtype=np.uint8) for sh in F.plane_shapes(c.src_fmt, c.src_w, c.src_h)]
+            got = s.scale(const)
+            assert all((p == v).all() for p in got), v
+
+
+def test_error_paths():
+    import ctypes
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler, PtrArr3, DiffArr3
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 64, 9, 32, 32, 0, F.SWS_BICUBIC)            # unknown format
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC | F.SWS_LANCZOS)  # two algorithms
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(4000, 64, 0, 8, 64, 0, F.SWS_LANCZOS)           # would need cascaded contexts
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC, device=99)
+    with Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC) as s:
+        src = F.random_frame(0, 64, 64, 1)
+        bad = [src[0][:, :32], src[1], src[2]]   # luma pitch fine but a too-narrow plane via strides trick
+        lib = tv_lib.load()
+        sp = PtrArr3(src[0].ctypes.data, src[1].ctypes.data, None)   # missing V plane
+        z = DiffArr3(64, 32, 32)
+        rc = lib.tvs_scale_host(s._ctx, sp, z, DiffArr3(0, 0, 0), sp, z, DiffArr3(0, 0, 0), 1)
+        assert rc == -22 and "NULL" in tv_lib.last_error()
+        rc = lib.tvs_scale_host(s._ctx, PtrArr3(*[p.ctypes.data for p in src]), DiffArr3(10, 32, 32), DiffArr3(0, 0, 0),
+                                PtrArr3(*[p.ctypes.data for p in src]), z, DiffArr3(0, 0, 0), 1)
+        assert rc == -22 and "pitch" in tv_lib.last_error()

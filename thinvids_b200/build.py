@@ -1,0 +1,63 @@
+"""Builds thinvids_b200/libtvscale.so (the C-ABI library of include/tvscale.h) in-tree with nvcc for sm_100a.
+
+    python -m thinvids_b200.build [--force]
+
+The library is git-ignored but travels with the tree (it is what the GPU box loads).  nvcc cross-compiles
+without a GPU, so this also runs on CPU-only machines.
+"""
+from __future__ import annotations
+
+import os
+import subprocess
+import sys
+
+PKG = os.path.dirname(os.path.abspath(__file__))
+CSRC = os.path.join(PKG, "csrc")
+LIB = os.path.join(PKG, "libtvscale.so")
+SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused.cu", "tvscale_abi.cu"]
+HEADERS = ["filter_tables.h", "tvs_internal.h", os.path.join("..", "..", "include", "tvscale.h")]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
+              "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "--fmad=true"]
+
+
+def _nvcc() -> str:
+    for cand in (os.environ.get("NVCC"), "/usr/local/cuda/bin/nvcc", "nvcc"):
+        if cand and (os.path.sep not in cand or os.path.exists(cand)):
+            return cand
+    raise RuntimeError("nvcc not found")
+
+
+def needs_build() -> bool:
+    if not os.path.exists(LIB):
+        return True
+    t = os.path.getmtime(LIB)
+    deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
+    return any(os.path.getmtime(d) > t for d in deps)
+
+
+def build(force: bool = False, verbose: bool = False) -> str:
+    if not force and not needs_build():
+        return LIB
+    objs = []
+    build_dir = os.path.join(PKG, "build")
+    os.makedirs(build_dir, exist_ok=True)
+    for s in SOURCES:
+        obj = os.path.join(build_dir, os.path.splitext(s)[0] + ".o")
+        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, s), "-o", obj]
+        if s.endswith(".cu"):
+            cmd += ["-Xptxas", "-v"] if verbose else []
+        else:
+            cmd += ["-x", "cu"] if False else []
+        if verbose:
+            print(" ".join(cmd))
+        subprocess.check_call(cmd)
+        objs.append(obj)
+    tmp = LIB + ".tmp.%d" % os.getpid()
+    subprocess.check_call([_nvcc(), "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
+                           "-cudart", "static"])
+    os.replace(tmp, LIB)
+    return LIB
+
+
+if __name__ == "__main__":
+    print(build(force="--force" in sys.argv, verbose="-v" in sys.argv))

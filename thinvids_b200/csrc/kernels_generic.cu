@@ -1,0 +1,144 @@
+// Two-pass reference-shaped kernels: a horizontal pass that writes libswscale's 15-bit intermediate to
+// device scratch, a vertical pass that reads it back, and the same-size repack kernels.
+//
+// This path handles every shape, format and tap count (up to 256 taps) and is what the fused tile
+// kernel (kernels_fused.cu) falls back to when a tile would not fit in shared memory.  It follows
+// SURVEY.md A.3 step by step: hScale8To15_c / hScale16To15_c, then yuv2planeX_8_c / yuv2planeX_10_c /
+// yuv2nv12cX_c, and A.4 for the unscaled converters (libswscale swscale_unscaled.c planarCopyWrapper).
+#include "tvs_internal.h"
+
+namespace tvs {
+namespace {
+
+__constant__ uint8_t kDither128[8][8] = {
+    {36, 68, 60, 92, 34, 66, 58, 90},  {100, 4, 124, 28, 98, 2, 122, 26},
+    {52, 84, 44, 76, 50, 82, 42, 74},  {116, 20, 108, 12, 114, 18, 106, 10},
+    {32, 64, 56, 88, 38, 70, 62, 94},  {96, 0, 120, 24, 102, 6, 126, 30},
+    {48, 80, 40, 72, 54, 86, 46, 78},  {112, 16, 104, 8, 118, 22, 110, 14},
+};
+
+template <typename T>
+__device__ __forceinline__ int load_sample(const uint8_t *p) {
+    return static_cast<int>(*reinterpret_cast<const T *>(p));
+}
+
+// One thread per intermediate sample: mid[frame][row][x] = min((sum_j src[pos[x]+j] * coef[x][j]) >> hshift, 32767).
+template <typename SrcT>
+__global__ void __launch_bounds__(256)
+hpass_generic_kernel(const uint8_t *__restrict__ src, ptrdiff_t pitch, ptrdiff_t frame_stride, int xstep, int src_shift,
+                     int sw, int dw, const int16_t *__restrict__ coef, const int32_t *__restrict__ pos, int taps,
+                     int hshift, int16_t *__restrict__ mid, size_t mid_frame_stride, int sh) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int r = blockIdx.y;
+    const int f = blockIdx.z;
+    if (x >= dw) return;
+    const uint8_t *row = src + f * frame_stride + r * pitch;
+    const int16_t *c = coef + static_cast<size_t>(x) * taps;
+    const int first = pos[x];
+    int acc = 0;
+    for (int j = 0; j < taps; ++j) {
+        const int sx = first + j;
+        if (sx < sw) acc += (load_sample<SrcT>(row + static_cast<ptrdiff_t>(sx) * xstep) >> src_shift) * c[j];
+    }
+    acc >>= hshift;
+    mid[f * mid_frame_stride + static_cast<size_t>(r) * dw + x] = static_cast<int16_t>(min(acc, 32767));
+}
+
+// One thread per output sample.
+template <typename DstT>
+__global__ void __launch_bounds__(256)
+vpass_generic_kernel(const int16_t *__restrict__ mid, size_t mid_frame_stride, int sh, int dw,
+                     const int16_t *__restrict__ coef, const int32_t *__restrict__ pos, int taps,
+                     uint8_t *__restrict__ dst, ptrdiff_t pitch, ptrdiff_t frame_stride, int xstep, int dst_shift,
+                     int rule, int dither_xoff) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    const int f = blockIdx.z;
+    if (x >= dw) return;
+    const int16_t *m = mid + f * mid_frame_stride + x;
+    const int16_t *c = coef + static_cast<size_t>(y) * taps;
+    const int first = pos[y];
+    int acc = 0;
+    for (int j = 0; j < taps; ++j) {
+        const int sr = first + j;
+        if (sr < sh) acc += static_cast<int>(m[static_cast<size_t>(sr) * dw]) * c[j];
+    }
+    int v;
+    if (rule == kOut10) {
+        v = min(max((acc + (1 << 16)) >> 17, 0), 1023) << dst_shift;
+    } else {
+        const int d = rule == kOut8 ? 64 : kDither128[y & 7][(x + dither_xoff) & 7];
+        v = min(max((acc + (d << 12)) >> 19, 0), 255);
+    }
+    *reinterpret_cast<DstT *>(dst + f * frame_stride + y * pitch + static_cast<ptrdiff_t>(x) * xstep) = static_cast<DstT>(v);
+}
+
+// Same-size converters.  kOpCopy moves a sample unchanged (dropping / restoring P010's padding bits);
+// kOpDither2 is libswscale's 10->8 bit copy: t = (p + d[y&1][x&7]) >> 2, out = t - (t >> 8), with
+// d = {1,2,1,2,..} on even rows and {3,0,3,0,..} on odd rows.  For P010 sources libswscale's scalar
+// tail loop (columns >= cols & ~7) forgets to drop the padding bits; `raw_tail_from` reproduces that.
+template <typename SrcT, typename DstT>
+__global__ void __launch_bounds__(256)
+repack_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, int sxstep, int src_shift,
+              uint8_t *__restrict__ dst, ptrdiff_t dpitch, ptrdiff_t dframe, int dxstep, int dst_shift,
+              int w, int kind, int raw_tail_from) {
+    const int x = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = blockIdx.y;
+    const int f = blockIdx.z;
+    if (x >= w) return;
+    unsigned v = load_sample<SrcT>(src + f * sframe + y * spitch + static_cast<ptrdiff_t>(x) * sxstep);
+    if (kind == kOpDither2) {
+        if (raw_tail_from < 0 || x < raw_tail_from) v >>= src_shift;
+        const unsigned d = (y & 1) ? ((x & 1) ? 0u : 3u) : ((x & 1) ? 2u : 1u);
+        const unsigned t = (v + d) >> 2;
+        v = (t - (t >> 8)) & 0xffu;
+    } else {
+        v = (v >> src_shift) << dst_shift;
+    }
+    *reinterpret_cast<DstT *>(dst + f * dframe + y * dpitch + static_cast<ptrdiff_t>(x) * dxstep) = static_cast<DstT>(v);
+}
+
+inline dim3 plane_grid(int w, int h, int n_frames) { return dim3((w + 255) / 256, h, n_frames); }
+
+}  // namespace
+
+int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceTable &h, int16_t *mid,
+                         size_t mid_frame_stride, int n_frames, cudaStream_t stream) {
+    const dim3 grid = plane_grid(op.dw, op.sh, n_frames);
+    int16_t *m = mid + op.mid_offset;
+    if (op.src_bits == 8)
+        hpass_generic_kernel<uint8_t><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep,
+            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh);
+    else
+        hpass_generic_kernel<uint16_t><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep,
+            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceTable &v, const int16_t *mid,
+                         size_t mid_frame_stride, int n_frames, cudaStream_t stream) {
+    const dim3 grid = plane_grid(op.dw, op.dh, n_frames);
+    const int16_t *m = mid + op.mid_offset;
+    if (op.dst_bits == 8)
+        vpass_generic_kernel<uint8_t><<<grid, 256, 0, stream>>>(m, mid_frame_stride, op.sh, op.dw, v.coef, v.pos, v.taps,
+            dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.rule, op.dither_xoff);
+    else
+        vpass_generic_kernel<uint16_t><<<grid, 256, 0, stream>>>(m, mid_frame_stride, op.sh, op.dw, v.coef, v.pos, v.taps,
+            dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.rule, op.dither_xoff);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream) {
+    const dim3 grid = plane_grid(op.dw, op.dh, n_frames);
+#define TVS_REPACK(S, D)                                                                                          \
+    repack_kernel<S, D><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep, op.src_shift, \
+        dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.dw, op.kind, op.raw_tail_from)
+    if (op.src_bits == 8 && op.dst_bits == 8) TVS_REPACK(uint8_t, uint8_t);
+    else if (op.src_bits == 8) TVS_REPACK(uint8_t, uint16_t);
+    else if (op.dst_bits == 8) TVS_REPACK(uint16_t, uint8_t);
+    else TVS_REPACK(uint16_t, uint16_t);
+#undef TVS_REPACK
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+}  // namespace tvs

@@ -1,0 +1,85 @@
+// Internal types shared by the C-ABI layer and the CUDA kernels.  Not installed; the public surface
+// is include/tvscale.h.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+#include <cstdint>
+#include <string>
+#include <vector>
+
+#include "filter_tables.h"
+
+namespace tvs {
+
+// Where the samples of ONE logical plane (Y, U or V) of frame 0 live.  NV12/P010 chroma is one stored
+// plane seen through two views that differ in `base` by one sample and step over the other component.
+struct SampleView {
+    uint8_t *base = nullptr;     // first sample of row 0, frame 0
+    ptrdiff_t pitch = 0;         // bytes between rows
+    ptrdiff_t frame_stride = 0;  // bytes between frames
+    int xstep = 1;               // bytes between consecutive samples of this logical plane
+};
+
+// Device-resident copy of one AxisTable.
+struct DeviceTable {
+    const int16_t *coef = nullptr;
+    const int32_t *pos = nullptr;
+    int taps = 0;
+    int length = 0;
+};
+
+// How the vertical pass turns its 32-bit sum into an output sample.
+enum OutputRule : int {
+    kOut8 = 0,        // 8-bit source -> 8-bit: (acc + (64<<12)) >> 19, clip to 0..255
+    kOut8Dither = 1,  // >8-bit source -> 8-bit: ordered 8x8 dither instead of the constant 64
+    kOut10 = 2        // -> 10-bit: (acc + (1<<16)) >> 17, clip to 0..1023 (P010 then shifts left by 6)
+};
+
+enum PlaneOpKind : int {
+    kOpScale = 0,   // horizontal + vertical filter (also used with 1-tap tables for depth changes)
+    kOpCopy = 1,    // same-size, same-depth sample copy (re-interleave / de-interleave)
+    kOpDither2 = 2  // same-size 10 -> 8 bit copy with libswscale's 2-bit ordered dither
+};
+
+// One unit of work of a frame: produce one logical (or, for the P010->NV12 copy, stored) plane.
+struct PlaneOp {
+    PlaneOpKind kind = kOpScale;
+    int src_plane = 0, dst_plane = 0;      // index into the caller's plane pointer arrays
+    int src_offset = 0, dst_offset = 0;    // byte offset of this component inside an interleaved sample group
+    int src_xstep = 1, dst_xstep = 1;      // bytes between samples
+    int src_bits = 8, dst_bits = 8;        // significant bits
+    int src_shift = 0, dst_shift = 0;      // P010 keeps its 10 bits in the top of the word
+    int sw = 0, sh = 0, dw = 0, dh = 0;    // logical plane sizes
+    int htable = 0, vtable = 0;            // which DeviceTable (0 hLum, 1 hChr, 2 vLum, 3 vChr)
+    int hshift = 7;                        // right shift after the horizontal sum
+    OutputRule rule = kOut8;
+    int dither_xoff = 0;                   // 3 for the V component when dithering
+    int raw_tail_from = -1;                // kOpDither2 only: columns >= this use the un-shifted P010 word
+    size_t mid_offset = 0;                 // element offset of this plane's intermediate inside a frame's scratch block
+};
+
+struct Plan {
+    std::vector<PlaneOp> ops;
+    size_t mid_elems_per_frame = 0;        // int16 elements of two-pass scratch per frame
+    bool any_scale = false;
+};
+
+// ---- kernel launchers (kernels_generic.cu) -------------------------------------------------------
+// Each returns the number of kernels it launched, or -1 after a launch error (cudaGetLastError kept).
+int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceTable &h, int16_t *mid,
+                         size_t mid_frame_stride, int n_frames, cudaStream_t stream);
+int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceTable &v, const int16_t *mid,
+                         size_t mid_frame_stride, int n_frames, cudaStream_t stream);
+int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
+
+// ---- fused tile kernel (kernels_fused.cu) --------------------------------------------------------
+struct FusedPlan;  // opaque, owned by the context
+FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);
+void fused_plan_destroy(FusedPlan *p);
+size_t fused_plan_device_bytes(const FusedPlan *p);
+// Launches the fused kernels for every scale op of the plan.  Returns kernels launched or -1.
+int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
+                 int n_frames, cudaStream_t stream);
+
+}  // namespace tvs

@@ -1,0 +1,532 @@
+// C ABI of the scale / pixel-format stage (include/tvscale.h): context life-cycle, launch planning,
+// the device-pointer batch call and the host-buffer drop-in for sws_scale().
+#include <cerrno>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+
+#include "../../include/tvscale.h"
+#include "tvs_internal.h"
+
+using namespace tvs;
+
+namespace {
+
+thread_local std::string g_last_error;
+
+int fail(int code, const char *fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof buf, fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+
+int cuda_fail(cudaError_t e, const char *what) {
+    return fail(-EIO, "%s: %s", what, cudaGetErrorString(e));
+}
+
+#define TVS_CUDA(call, what)                                    \
+    do {                                                        \
+        cudaError_t e_ = (call);                                \
+        if (e_ != cudaSuccess) return cuda_fail(e_, what);      \
+    } while (0)
+
+struct FormatInfo {
+    int bits;       // significant bits per sample
+    int bytes;      // bytes per sample
+    int shift;      // left shift of the significant bits inside the word (P010: 6)
+    bool semi;      // chroma interleaved in one plane
+    int planes;     // stored planes
+};
+
+bool format_info(int fmt, FormatInfo &fi) {
+    switch (fmt) {
+    case TVS_FMT_YUV420P: fi = {8, 1, 0, false, 3}; return true;
+    case TVS_FMT_NV12: fi = {8, 1, 0, true, 2}; return true;
+    case TVS_FMT_YUV420P10LE: fi = {10, 2, 0, false, 3}; return true;
+    case TVS_FMT_P010LE: fi = {10, 2, 6, true, 2}; return true;
+    default: return false;
+    }
+}
+
+size_t tight_frame_bytes(const FormatInfo &fi, int w, int h) {
+    const size_t cw = (w + 1) / 2, ch = (h + 1) / 2;
+    return (static_cast<size_t>(w) * h + 2 * cw * ch) * fi.bytes;
+}
+
+}  // namespace
+
+struct tvs_ctx {
+    int device = 0;
+    int src_w = 0, src_h = 0, dst_w = 0, dst_h = 0, src_fmt = 0, dst_fmt = 0, flags = 0;
+    FormatInfo sfi{}, dfi{};
+    AxisTable host_tables[4];
+    DeviceTable dev_tables[4];
+    void *dev_table_blob = nullptr;
+    Plan plan;
+    FusedPlan *fused = nullptr;
+    int forced_path = -1;
+    // two-pass scratch
+    int16_t *mid = nullptr;
+    size_t mid_capacity_elems = 0;
+    // host-buffer path
+    cudaStream_t copy_streams[2] = {nullptr, nullptr};
+    uint8_t *stage_src[2] = {nullptr, nullptr};
+    uint8_t *stage_dst[2] = {nullptr, nullptr};
+    size_t stage_src_bytes = 0, stage_dst_bytes = 0;
+    long long launches = 0;
+};
+
+namespace {
+
+// Logical plane `pl` (0 Y, 1 U, 2 V) of a format: which stored plane, byte offset inside the sample group,
+// bytes between samples.
+void logical_plane(const FormatInfo &fi, int pl, int &stored, int &offset, int &xstep) {
+    if (fi.semi && pl > 0) {
+        stored = 1;
+        offset = (pl - 1) * fi.bytes;
+        xstep = 2 * fi.bytes;
+    } else {
+        stored = pl;
+        offset = 0;
+        xstep = fi.bytes;
+    }
+}
+
+void build_plan(tvs_ctx *c) {
+    Plan &p = c->plan;
+    p.ops.clear();
+    const FormatInfo &s = c->sfi, &d = c->dfi;
+    const int sw = c->src_w, sh = c->src_h, dw = c->dst_w, dh = c->dst_h;
+    const int csw = (sw + 1) / 2, csh = (sh + 1) / 2, cdw = (dw + 1) / 2, cdh = (dh + 1) / 2;
+    const bool same = sw == dw && sh == dh;
+
+    auto logical_op = [&](int pl, PlaneOpKind kind) {
+        PlaneOp op;
+        op.kind = kind;
+        logical_plane(s, pl, op.src_plane, op.src_offset, op.src_xstep);
+        logical_plane(d, pl, op.dst_plane, op.dst_offset, op.dst_xstep);
+        op.src_bits = s.bits; op.dst_bits = d.bits; op.src_shift = s.shift; op.dst_shift = d.shift;
+        op.sw = pl ? csw : sw; op.sh = pl ? csh : sh; op.dw = pl ? cdw : dw; op.dh = pl ? cdh : dh;
+        op.htable = pl ? 1 : 0; op.vtable = pl ? 3 : 2;
+        op.hshift = s.bits == 8 ? 7 : s.bits - 1;
+        op.rule = d.bits > 8 ? kOut10 : (s.bits > 8 ? kOut8Dither : kOut8);
+        op.dither_xoff = pl == 2 ? 3 : 0;
+        // libswscale's same-size planar -> P010 converter writes floor(w/2) chroma pairs only.
+        if (same && pl > 0 && c->dst_fmt == TVS_FMT_P010LE && !s.semi) op.dw = dw >> 1;
+        return op;
+    };
+
+    if (same && s.bits == 10 && d.bits == 8 && s.semi && d.semi) {
+        // P010 -> NV12: each STORED plane is copied with the 2-bit dither, the UV plane as one plane of
+        // 2*cw samples (SURVEY.md A.4 as extended in oracle/swscale_port.c).
+        for (int st = 0; st < 2; ++st) {
+            PlaneOp op;
+            op.kind = kOpDither2;
+            op.src_plane = op.dst_plane = st;
+            op.src_xstep = 2; op.dst_xstep = 1;
+            op.src_bits = 10; op.dst_bits = 8; op.src_shift = 6; op.dst_shift = 0;
+            op.sw = op.dw = st ? 2 * cdw : dw;
+            op.sh = op.dh = st ? cdh : dh;
+            op.raw_tail_from = op.dw & ~7;
+            p.ops.push_back(op);
+        }
+    } else {
+        for (int pl = 0; pl < 3; ++pl) {
+            PlaneOpKind kind = kOpScale;
+            if (same) {
+                if (s.bits == d.bits) kind = kOpCopy;
+                else if (s.bits == 10 && !s.semi && !d.semi) kind = kOpDither2;        // yuv420p10le -> yuv420p
+                else if (s.bits == 10 && !s.semi && d.semi && pl == 0) kind = kOpDither2;  // -> nv12 luma
+            }
+            p.ops.push_back(logical_op(pl, kind));
+        }
+    }
+    size_t off = 0;
+    p.any_scale = false;
+    for (PlaneOp &op : p.ops) {
+        if (op.kind != kOpScale) continue;
+        p.any_scale = true;
+        op.mid_offset = off;
+        off += static_cast<size_t>(op.sh) * op.dw;
+    }
+    p.mid_elems_per_frame = off;
+}
+
+int upload_tables(tvs_ctx *c) {
+    size_t bytes = 0;
+    size_t coef_off[4], pos_off[4];
+    for (int i = 0; i < 4; ++i) {
+        coef_off[i] = bytes;
+        bytes += (c->host_tables[i].coef.size() * sizeof(int16_t) + 255) & ~static_cast<size_t>(255);
+        pos_off[i] = bytes;
+        bytes += (c->host_tables[i].pos.size() * sizeof(int32_t) + 255) & ~static_cast<size_t>(255);
+    }
+    TVS_CUDA(cudaMalloc(&c->dev_table_blob, bytes), "cudaMalloc(tables)");
+    uint8_t *base = static_cast<uint8_t *>(c->dev_table_blob);
+    for (int i = 0; i < 4; ++i) {
+        const AxisTable &t = c->host_tables[i];
+        TVS_CUDA(cudaMemcpy(base + coef_off[i], t.coef.data(), t.coef.size() * sizeof(int16_t), cudaMemcpyHostToDevice),
+                 "cudaMemcpy(coef)");
+        TVS_CUDA(cudaMemcpy(base + pos_off[i], t.pos.data(), t.pos.size() * sizeof(int32_t), cudaMemcpyHostToDevice),
+                 "cudaMemcpy(pos)");
+        c->dev_tables[i].coef = reinterpret_cast<const int16_t *>(base + coef_off[i]);
+        c->dev_tables[i].pos = reinterpret_cast<const int32_t *>(base + pos_off[i]);
+        c->dev_tables[i].taps = t.taps;
+        c->dev_tables[i].length = t.length;
+    }
+    return 0;
+}
+
+int check_planes(const FormatInfo &fi, int w, int h, const void *const planes[3], const ptrdiff_t pitch[3],
+                 const char *side) {
+    const int cw = (w + 1) / 2;
+    for (int i = 0; i < fi.planes; ++i) {
+        if (!planes[i]) return fail(-EINVAL, "%s plane %d is NULL", side, i);
+        const ptrdiff_t row = static_cast<ptrdiff_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
+        if (pitch[i] < row) return fail(-EINVAL, "%s pitch[%d]=%td is smaller than a row (%td bytes)", side, i, pitch[i], row);
+        if (fi.bytes == 2 && ((reinterpret_cast<uintptr_t>(planes[i]) | static_cast<uintptr_t>(pitch[i])) & 1))
+            return fail(-EINVAL, "%s plane %d: 16-bit samples need 2-byte aligned pointer and pitch", side, i);
+    }
+    return 0;
+}
+
+void bind_views(const tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
+                void *const dst[3], const ptrdiff_t dp[3], const ptrdiff_t df[3],
+                std::vector<SampleView> &sv, std::vector<SampleView> &dv) {
+    const size_t n = c->plan.ops.size();
+    sv.resize(n);
+    dv.resize(n);
+    for (size_t i = 0; i < n; ++i) {
+        const PlaneOp &op = c->plan.ops[i];
+        sv[i].base = const_cast<uint8_t *>(static_cast<const uint8_t *>(src[op.src_plane])) + op.src_offset;
+        sv[i].pitch = sp[op.src_plane];
+        sv[i].frame_stride = sf[op.src_plane];
+        sv[i].xstep = op.src_xstep;
+        dv[i].base = static_cast<uint8_t *>(dst[op.dst_plane]) + op.dst_offset;
+        dv[i].pitch = dp[op.dst_plane];
+        dv[i].frame_stride = df[op.dst_plane];
+        dv[i].xstep = op.dst_xstep;
+    }
+}
+
+int ensure_mid(tvs_ctx *c, size_t elems) {
+    if (c->mid_capacity_elems >= elems) return 0;
+    if (c->mid) {
+        TVS_CUDA(cudaFree(c->mid), "cudaFree(scratch)");
+        c->mid = nullptr;
+        c->mid_capacity_elems = 0;
+    }
+    TVS_CUDA(cudaMalloc(&c->mid, elems * sizeof(int16_t)), "cudaMalloc(scratch)");
+    c->mid_capacity_elems = elems;
+    return 0;
+}
+
+// Enqueue the whole batch on `stream`.  Pointers are device pointers.
+int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
+                  void *const dst[3], const ptrdiff_t dp[3], const ptrdiff_t df[3], int n_frames, cudaStream_t stream) {
+    std::vector<SampleView> sv, dv;
+    bind_views(c, src, sp, sf, dst, dp, df, sv, dv);
+    const Plan &plan = c->plan;
+
+    for (size_t i = 0; i < plan.ops.size(); ++i) {
+        if (plan.ops[i].kind == kOpScale) continue;
+        if (launch_repack(plan.ops[i], sv[i], dv[i], n_frames, stream) < 0)
+            return cuda_fail(cudaGetLastError(), "repack kernel launch");
+        ++c->launches;
+    }
+    if (!plan.any_scale) return 0;
+
+    const bool use_fused = c->fused && c->forced_path != 1;
+    if (c->forced_path == 0 && !c->fused) return fail(-ENOSYS, "fused path requested but this shape is not supported by it");
+    if (use_fused) {
+        const int n = fused_launch(c->fused, plan, sv.data(), dv.data(), n_frames, stream);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "fused kernel launch");
+        c->launches += n;
+        return 0;
+    }
+
+    // Two-pass: bound the scratch to ~256 MiB and walk the batch in chunks of frames.
+    const size_t per_frame = plan.mid_elems_per_frame;
+    size_t chunk = (static_cast<size_t>(256) << 20) / (per_frame * sizeof(int16_t));
+    if (chunk < 1) chunk = 1;
+    if (chunk > static_cast<size_t>(n_frames)) chunk = n_frames;
+    if (int rc = ensure_mid(c, per_frame * chunk)) return rc;
+    for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk)) {
+        const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
+        for (size_t i = 0; i < plan.ops.size(); ++i) {
+            const PlaneOp &op = plan.ops[i];
+            if (op.kind != kOpScale) continue;
+            SampleView s = sv[i], d = dv[i];
+            s.base += static_cast<ptrdiff_t>(f0) * s.frame_stride;
+            d.base += static_cast<ptrdiff_t>(f0) * d.frame_stride;
+            if (launch_hpass_generic(op, s, c->dev_tables[op.htable], c->mid, per_frame, nf, stream) < 0)
+                return cuda_fail(cudaGetLastError(), "horizontal kernel launch");
+            if (launch_vpass_generic(op, d, c->dev_tables[op.vtable], c->mid, per_frame, nf, stream) < 0)
+                return cuda_fail(cudaGetLastError(), "vertical kernel launch");
+            c->launches += 2;
+        }
+    }
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+const char *tvs_last_error(void) { return g_last_error.c_str(); }
+
+const char *tvs_version(void) { return "tvscale 0.1 (sm_100a)"; }
+
+int tvs_filter_table(int src_len, int dst_len, int alg, int one, int src_pos, int dst_pos,
+                     int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap) {
+    AxisTable t;
+    if (!build_axis_table(t, src_len, dst_len, static_cast<Algorithm>(alg), one, src_pos, dst_pos))
+        return fail(-EINVAL, "cannot build a filter table for %d -> %d with algorithm 0x%x", src_len, dst_len, alg);
+    if (coef) {
+        if (coef_cap < t.coef.size() || !pos || pos_cap < t.pos.size()) return fail(-ENOSPC, "table buffers too small");
+        memcpy(coef, t.coef.data(), t.coef.size() * sizeof(int16_t));
+        memcpy(pos, t.pos.data(), t.pos.size() * sizeof(int32_t));
+    }
+    return t.taps;
+}
+
+tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt, int flags,
+                    const int chr_pos[4]) {
+    FormatInfo sfi, dfi;
+    if (!format_info(src_fmt, sfi) || !format_info(dst_fmt, dfi)) {
+        fail(-EINVAL, "unsupported pixel format (src %d, dst %d)", src_fmt, dst_fmt);
+        return nullptr;
+    }
+    if (src_w < 1 || src_h < 1 || dst_w < 1 || dst_h < 1 || src_w > 32768 || src_h > 32768 || dst_w > 32768 || dst_h > 32768) {
+        fail(-EINVAL, "bad size %dx%d -> %dx%d", src_w, src_h, dst_w, dst_h);
+        return nullptr;
+    }
+    const int alg_bits = flags & (TVS_BILINEAR | TVS_BICUBIC | TVS_AREA | TVS_LANCZOS);
+    int alg = alg_bits ? alg_bits : TVS_BICUBIC;  // ffmpeg's default when flags= is absent
+    if (alg & (alg - 1)) {
+        fail(-EINVAL, "flags 0x%x select more than one scaling algorithm", flags);
+        return nullptr;
+    }
+    if (flags & ~(TVS_BILINEAR | TVS_BICUBIC | TVS_AREA | TVS_LANCZOS | TVS_ACCURATE_RND | TVS_BITEXACT)) {
+        fail(-ENOSYS, "flags 0x%x contain options this scaler does not implement", flags);
+        return nullptr;
+    }
+    int count = 0;
+    cudaError_t e = cudaGetDeviceCount(&count);
+    if (e != cudaSuccess || device < 0 || device >= count) {
+        fail(-ENODEV, "CUDA device %d not available (%s); this library has no CPU path", device,
+             e != cudaSuccess ? cudaGetErrorString(e) : "index out of range");
+        return nullptr;
+    }
+    if ((e = cudaSetDevice(device)) != cudaSuccess) {
+        cuda_fail(e, "cudaSetDevice");
+        return nullptr;
+    }
+
+    tvs_ctx *c = new tvs_ctx;
+    c->device = device;
+    c->src_w = src_w; c->src_h = src_h; c->dst_w = dst_w; c->dst_h = dst_h;
+    c->src_fmt = src_fmt; c->dst_fmt = dst_fmt; c->flags = flags;
+    c->sfi = sfi; c->dfi = dfi;
+    static const int centred[4] = {TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT};
+    if (!chr_pos) chr_pos = centred;
+    const int csw = (src_w + 1) / 2, csh = (src_h + 1) / 2, cdw = (dst_w + 1) / 2, cdh = (dst_h + 1) / 2;
+    const Algorithm a = static_cast<Algorithm>(alg);
+    const int luma = axis_position(TVS_CHR_POS_DEFAULT, 0);
+    const bool ok = build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma) &&
+                    build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], 1), axis_position(chr_pos[2], 1)) &&
+                    build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma) &&
+                    build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], 1), axis_position(chr_pos[3], 1));
+    if (!ok) {
+        fail(-ENOSYS, "%dx%d -> %dx%d needs a filter wider than 256 taps (libswscale would cascade); not supported",
+             src_w, src_h, dst_w, dst_h);
+        delete c;
+        return nullptr;
+    }
+    build_plan(c);
+    if (upload_tables(c) != 0) {
+        tvs_destroy(c);
+        return nullptr;
+    }
+    if (c->plan.any_scale) {
+        std::string why;
+        c->fused = fused_plan_create(c->plan, c->host_tables, device, why);  // nullptr = shape handled by the two-pass path
+    }
+    return c;
+}
+
+void tvs_destroy(tvs_ctx *c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    if (c->fused) fused_plan_destroy(c->fused);
+    if (c->dev_table_blob) cudaFree(c->dev_table_blob);
+    if (c->mid) cudaFree(c->mid);
+    for (int i = 0; i < 2; ++i) {
+        if (c->stage_src[i]) cudaFree(c->stage_src[i]);
+        if (c->stage_dst[i]) cudaFree(c->stage_dst[i]);
+        if (c->copy_streams[i]) cudaStreamDestroy(c->copy_streams[i]);
+    }
+    delete c;
+}
+
+int tvs_scale_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                    void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                    int n_frames, void *stream) {
+    if (!c) return fail(-EINVAL, "NULL context");
+    if (n_frames < 0) return fail(-EINVAL, "n_frames < 0");
+    if (n_frames > 65535) return fail(-EINVAL, "at most 65535 frames per call");
+    if (int rc = check_planes(c->sfi, c->src_w, c->src_h, src, src_pitch, "src")) return rc;
+    if (int rc = check_planes(c->dfi, c->dst_w, c->dst_h, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
+    if (n_frames == 0) return c->dst_h;
+    TVS_CUDA(cudaSetDevice(c->device), "cudaSetDevice");
+    if (int rc = enqueue_batch(c, src, src_pitch, src_frame_stride, dst, dst_pitch, dst_frame_stride, n_frames,
+                               static_cast<cudaStream_t>(stream)))
+        return rc;
+    return c->dst_h;
+}
+
+int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                   void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3], int n_frames) {
+    if (!c) return fail(-EINVAL, "NULL context");
+    if (n_frames < 0) return fail(-EINVAL, "n_frames < 0");
+    if (int rc = check_planes(c->sfi, c->src_w, c->src_h, src, src_pitch, "src")) return rc;
+    if (int rc = check_planes(c->dfi, c->dst_w, c->dst_h, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
+    if (n_frames == 0) return c->dst_h;
+    TVS_CUDA(cudaSetDevice(c->device), "cudaSetDevice");
+
+    // Device staging keeps planes tightly packed, frame after frame: [frame][plane].
+    const int cw_s = (c->src_w + 1) / 2, ch_s = (c->src_h + 1) / 2, cw_d = (c->dst_w + 1) / 2, ch_d = (c->dst_h + 1) / 2;
+    auto plane_rows = [](int i, int h, int ch) { return i == 0 ? h : ch; };
+    auto plane_row_bytes = [](const FormatInfo &fi, int i, int w, int cw) {
+        return static_cast<size_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
+    };
+    const size_t sframe = tight_frame_bytes(c->sfi, c->src_w, c->src_h);
+    const size_t dframe = tight_frame_bytes(c->dfi, c->dst_w, c->dst_h);
+    // Keep each chunk around 48 MiB so copies of one chunk overlap kernels of the other.
+    size_t chunk = (static_cast<size_t>(48) << 20) / (sframe + dframe);
+    if (chunk < 1) chunk = 1;
+    if (chunk > static_cast<size_t>(n_frames)) chunk = n_frames;
+    if (c->stage_src_bytes < chunk * sframe || c->stage_dst_bytes < chunk * dframe) {
+        for (int i = 0; i < 2; ++i) {
+            if (c->stage_src[i]) cudaFree(c->stage_src[i]);
+            if (c->stage_dst[i]) cudaFree(c->stage_dst[i]);
+            c->stage_src[i] = c->stage_dst[i] = nullptr;
+        }
+        c->stage_src_bytes = c->stage_dst_bytes = 0;
+        for (int i = 0; i < 2; ++i) {
+            TVS_CUDA(cudaMalloc(&c->stage_src[i], chunk * sframe), "cudaMalloc(src staging)");
+            TVS_CUDA(cudaMalloc(&c->stage_dst[i], chunk * dframe), "cudaMalloc(dst staging)");
+        }
+        c->stage_src_bytes = chunk * sframe;
+        c->stage_dst_bytes = chunk * dframe;
+    }
+    for (int i = 0; i < 2; ++i)
+        if (!c->copy_streams[i]) TVS_CUDA(cudaStreamCreateWithFlags(&c->copy_streams[i], cudaStreamNonBlocking), "cudaStreamCreate");
+
+    // Device-side plane table of a staged chunk.
+    ptrdiff_t s_pitch[3] = {0, 0, 0}, s_fs[3], d_pitch[3] = {0, 0, 0}, d_fs[3];
+    size_t s_off[3] = {0, 0, 0}, d_off[3] = {0, 0, 0};
+    {
+        size_t o = 0;
+        for (int i = 0; i < c->sfi.planes; ++i) {
+            s_off[i] = o;
+            s_pitch[i] = plane_row_bytes(c->sfi, i, c->src_w, cw_s);
+            o += s_pitch[i] * plane_rows(i, c->src_h, ch_s);
+        }
+        o = 0;
+        for (int i = 0; i < c->dfi.planes; ++i) {
+            d_off[i] = o;
+            d_pitch[i] = plane_row_bytes(c->dfi, i, c->dst_w, cw_d);
+            o += d_pitch[i] * plane_rows(i, c->dst_h, ch_d);
+        }
+        for (int i = 0; i < 3; ++i) { s_fs[i] = sframe; d_fs[i] = dframe; }
+    }
+    // A host frame that is itself tightly packed [Y|U|V] with frames back to back moves as ONE copy per chunk.
+    auto packed = [&](const void *const pl[3], const ptrdiff_t pitch[3], const ptrdiff_t fs[3], const FormatInfo &fi,
+                      const size_t off[3], const ptrdiff_t tp[3], size_t frame) {
+        for (int i = 0; i < fi.planes; ++i) {
+            if (pitch[i] != tp[i] || fs[i] != static_cast<ptrdiff_t>(frame)) return false;
+            if (static_cast<const uint8_t *>(pl[i]) != static_cast<const uint8_t *>(pl[0]) + off[i]) return false;
+        }
+        return true;
+    };
+    const bool src_packed = packed(src, src_pitch, src_frame_stride, c->sfi, s_off, s_pitch, sframe);
+    const bool dst_packed = packed(reinterpret_cast<const void *const *>(dst), dst_pitch, dst_frame_stride, c->dfi, d_off, d_pitch, dframe);
+
+    // The two-pass path owns ONE intermediate buffer, so its chunks must not overlap on the device.
+    const bool single_stream = c->plan.any_scale && !(c->fused && c->forced_path != 1);
+    int slot = 0;
+    for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk), slot = single_stream ? 0 : slot ^ 1) {
+        const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
+        cudaStream_t st = c->copy_streams[slot];
+        // The slot's previous chunk (two iterations ago) is ordered before us by the stream itself.
+        if (src_packed) {
+            TVS_CUDA(cudaMemcpyAsync(c->stage_src[slot], static_cast<const uint8_t *>(src[0]) + static_cast<size_t>(f0) * sframe,
+                                     static_cast<size_t>(nf) * sframe, cudaMemcpyHostToDevice, st), "H2D copy");
+        } else {
+            for (int f = 0; f < nf; ++f)
+                for (int i = 0; i < c->sfi.planes; ++i)
+                    TVS_CUDA(cudaMemcpy2DAsync(c->stage_src[slot] + f * sframe + s_off[i], s_pitch[i],
+                                               static_cast<const uint8_t *>(src[i]) + static_cast<ptrdiff_t>(f0 + f) * src_frame_stride[i],
+                                               src_pitch[i], s_pitch[i], plane_rows(i, c->src_h, ch_s), cudaMemcpyHostToDevice, st),
+                             "H2D plane copy");
+        }
+        const void *sp[3] = {c->stage_src[slot] + s_off[0], c->stage_src[slot] + s_off[1], c->stage_src[slot] + s_off[2]};
+        void *dp[3] = {c->stage_dst[slot] + d_off[0], c->stage_dst[slot] + d_off[1], c->stage_dst[slot] + d_off[2]};
+        if (int rc = enqueue_batch(c, sp, s_pitch, s_fs, dp, d_pitch, d_fs, nf, st)) return rc;
+        if (dst_packed) {
+            TVS_CUDA(cudaMemcpyAsync(static_cast<uint8_t *>(dst[0]) + static_cast<size_t>(f0) * dframe, c->stage_dst[slot],
+                                     static_cast<size_t>(nf) * dframe, cudaMemcpyDeviceToHost, st), "D2H copy");
+        } else {
+            for (int f = 0; f < nf; ++f)
+                for (int i = 0; i < c->dfi.planes; ++i)
+                    TVS_CUDA(cudaMemcpy2DAsync(static_cast<uint8_t *>(dst[i]) + static_cast<ptrdiff_t>(f0 + f) * dst_frame_stride[i], dst_pitch[i],
+                                               c->stage_dst[slot] + f * dframe + d_off[i], d_pitch[i], d_pitch[i],
+                                               plane_rows(i, c->dst_h, ch_d), cudaMemcpyDeviceToHost, st),
+                             "D2H plane copy");
+        }
+    }
+    TVS_CUDA(cudaStreamSynchronize(c->copy_streams[0]), "stream sync");
+    TVS_CUDA(cudaStreamSynchronize(c->copy_streams[1]), "stream sync");
+    return c->dst_h;
+}
+
+int tvs_context_table(const tvs_ctx *c, int which, int16_t *coef, size_t coef_cap, int32_t *pos, size_t pos_cap) {
+    if (!c || which < 0 || which > 3) return fail(-EINVAL, "bad table index");
+    const AxisTable &t = c->host_tables[which];
+    if (coef) {
+        if (coef_cap < t.coef.size() || !pos || pos_cap < t.pos.size()) return fail(-ENOSPC, "table buffers too small");
+        memcpy(coef, t.coef.data(), t.coef.size() * sizeof(int16_t));
+        memcpy(pos, t.pos.data(), t.pos.size() * sizeof(int32_t));
+    }
+    return t.taps;
+}
+
+long long tvs_info(const tvs_ctx *c, int what) {
+    if (!c) return fail(-EINVAL, "NULL context");
+    switch (what) {
+    case TVS_INFO_KERNEL_LAUNCHES: return c->launches;
+    case TVS_INFO_PATH:
+        if (!c->plan.any_scale) return 2;
+        return (c->fused && c->forced_path != 1) ? 0 : 1;
+    case TVS_INFO_SCRATCH_BYTES:
+        return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + 2 * (c->stage_src_bytes + c->stage_dst_bytes));
+    case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
+    case TVS_INFO_DST_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->dfi, c->dst_w, c->dst_h));
+    default: return fail(-EINVAL, "unknown info key %d", what);
+    }
+}
+
+int tvs_set_path(tvs_ctx *c, int path) {
+    if (!c || path < -1 || path > 1) return fail(-EINVAL, "bad path");
+    if (path == 0 && c->plan.any_scale && !c->fused) return fail(-ENOSYS, "this shape is not supported by the fused kernel");
+    c->forced_path = path;
+    return 0;
+}
+
+}  // extern "C"
