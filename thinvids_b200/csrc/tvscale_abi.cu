@@ -116,8 +116,9 @@ void build_plan(tvs_ctx *c) {
         op.hshift = s.bits == 8 ? 7 : s.bits - 1;
         op.rule = d.bits > 8 ? kOut10 : (s.bits > 8 ? kOut8Dither : kOut8);
         op.dither_xoff = pl == 2 ? 3 : 0;
-        // libswscale's same-size planar -> P010 converter writes floor(w/2) chroma pairs only.
-        if (same && pl > 0 && c->dst_fmt == TVS_FMT_P010LE && !s.semi) op.dw = dw >> 1;
+        // Note: libswscale's same-size planar -> P010 converter writes only floor(w/2) chroma pairs and
+        // leaves the last pair of an odd-width frame untouched; we write all ceil(w/2) pairs (the value the
+        // scaler proper would produce), so every destination byte is defined.
         return op;
     };
 
