@@ -1,9 +1,489 @@
-// Placeholder until the fused tile kernel lands: every shape uses the two-pass path.
+// Fused tile kernel: stage the source footprint of one output tile in shared memory, run libswscale's
+// horizontal pass into a shared-memory intermediate, then the vertical pass straight to global memory.
+// HBM sees each source byte once (plus the tile halo, which L2 absorbs) and each destination byte once.
+//
+// Arithmetic is bit-exact with SURVEY.md A.3 but runs on the FP32 FMA pipe, which on sm_100a issues twice
+// as many multiply-adds per clock as IMAD/IDP (profiles/r01_alu_rates.md):
+//   * H pass: pixels are exact small floats and coefficients are c * 2^-30, so the 6..24-term sum is an exact
+//     integer * 2^-30 (|sum| < 2^24).  One FMA with round-toward-minus-infinity by 2^-126 then yields
+//     floor(sum / 128) * 2^-149: a SUBNORMAL float whose bit pattern is the integer t itself (sign-magnitude
+//     for negative t).  FMNMX against the pattern 32767 is the upper clamp.  Subnormal operands run at full
+//     rate on this chip (profiles/r01_denorm_probe.txt).
+//   * V pass: acc' = sum t_d * (g * 2^107) = acc * 2^-42 accumulates with at most `e` absolute rounding error
+//     (|acc| < 2^28).  q = RN(acc' * 2^-126) is round(acc / 2^19) * 2^-149, again an integer bit pattern, which
+//     cvt.pack.sat.u8.s32 clamps and packs.  The residual r = acc' - q * 2^126 is exact; when |r| is within `e`
+//     of the rounding boundary (about 0.02 % of samples) the sample is recomputed in int32, so the result is
+//     exact by construction, not by luck.  RN ties are inside that band.
+// Tile geometry: 128 output columns (a lane owns 4 adjacent columns in both passes) by `th` output rows,
+// 256 threads.  Each lane keeps the dense coefficients of its 4 columns over their common source span in
+// registers for the life of the tile, and a ring of VT intermediate rows while it walks down its strip.
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
 #include "tvs_internal.h"
+
 namespace tvs {
-struct FusedPlan {};
-FusedPlan *fused_plan_create(const Plan &, const AxisTable[4], int, std::string &err) { err = "not built"; return nullptr; }
-void fused_plan_destroy(FusedPlan *p) { delete p; }
-size_t fused_plan_device_bytes(const FusedPlan *) { return 0; }
-int fused_launch(const FusedPlan *, const Plan &, const SampleView[], const SampleView[], int, cudaStream_t) { return -1; }
+namespace {
+
+constexpr int kTileW = 128;
+constexpr int kThreads = 256;
+constexpr int kWarps = kThreads / 32;
+constexpr int kGroup = 4;                 // adjacent output columns per lane
+constexpr int kMaxFusedOps = 3;
+constexpr size_t kSmemBudget = 100 * 1024;  // two CTAs per SM
+
+struct FusedOpParams {
+    const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
+    uint8_t *dst; ptrdiff_t dst_pitch, dst_fstride; int dst_xstep;
+    int sw, sh, dw, dh;
+    int th, tiles_x, tile_begin;
+    int n_groups;
+    const float *hdense;   // [n_groups][4][SPAN]  c * 2^-30, zero outside a column's own window
+    const int *hbase;      // [n_groups]           first source column of the group's span
+    const int *vpos;       // [dh]
+    const float *vring;    // [dh][VT]             g * 2^107, indexed by ring slot = source_row % VT
+    const int *vring_i;    // [dh][VT]             the same coefficients as integers (exact path)
+    int vtaps;
+    int s_pitch, m_rows;   // shared-memory geometry
+    float v_thr;           // |residual| at or above this needs the exact path
+};
+
+struct FusedLaunchParams {
+    FusedOpParams op[kMaxFusedOps];
+    int n_ops;
+};
+
+__device__ __forceinline__ float fma_rm(float a, float b, float c) {
+    float d;
+    asm("fma.rm.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ float fma_rn(float a, float b, float c) {
+    float d;
+    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+// (sat_u8(hi) << 8 | sat_u8(lo)) | upper << 16
+__device__ __forceinline__ unsigned pack_sat_u8(int hi, int lo, unsigned upper) {
+    unsigned d;
+    asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(upper));
+    return d;
+}
+__device__ __forceinline__ float byte_to_float(unsigned word, int k) {
+    // 0x4B0000bb is 2^23 + bb
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | k)) - 8388608.0f;
+}
+__device__ __forceinline__ int subnormal_to_int(float v) {
+    const int b = __float_as_int(v);
+    return b < 0 ? -(b & 0x7fffffff) : b;
+}
+
+// Pull intermediate rows [next_row, need_end) into the register ring.  Ring slot = row % VT, so the slot a
+// row lands in is a compile-time constant inside each case; the switch enters at the current slot and falls
+// through, which keeps `win` in registers (no dynamic indexing) at the cost of one uniform branch per call.
+template <int VT>
+__device__ __forceinline__ void load_ring_rows(float4 (&win)[VT], int &slot, int &next_row, int need_end,
+                                               const float *m_col, int r0, int r1) {
+#define TVS_RING_CASE(s)                                                                                     \
+    case s:                                                                                                  \
+        if constexpr (s < VT) {                                                                              \
+            win[s] = next_row < r1 ? *reinterpret_cast<const float4 *>(m_col + (next_row - r0) * kTileW)     \
+                                   : make_float4(0.f, 0.f, 0.f, 0.f);                                        \
+            if (++next_row >= need_end) { slot = (s + 1 == VT) ? 0 : s + 1; return; }                        \
+        }
+    for (;;) {
+        switch (slot) {
+            TVS_RING_CASE(0) TVS_RING_CASE(1) TVS_RING_CASE(2) TVS_RING_CASE(3) TVS_RING_CASE(4) TVS_RING_CASE(5)
+            TVS_RING_CASE(6) TVS_RING_CASE(7) TVS_RING_CASE(8) TVS_RING_CASE(9) TVS_RING_CASE(10) TVS_RING_CASE(11)
+        }
+        slot = 0;
+    }
+#undef TVS_RING_CASE
+}
+
+template <int SPAN, int VT>
+__global__ void __launch_bounds__(kThreads, 2)
+fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
+    extern __shared__ __align__(16) float smem[];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+
+    int t = blockIdx.x, oi = 0;
+    if (P.n_ops > 1 && t >= P.op[1].tile_begin) oi = 1;
+    if (P.n_ops > 2 && t >= P.op[2].tile_begin) oi = 2;
+    const FusedOpParams &op = P.op[oi];
+    t -= op.tile_begin;
+    const int ty = t / op.tiles_x, tx = t - ty * op.tiles_x;
+    const int f = blockIdx.y;
+
+    const int x0 = tx * kTileW;
+    const int y0 = ty * op.th, y1 = min(y0 + op.th, op.dh);
+    const int g0 = x0 / kGroup;
+    const int g_last = min(g0 + 31, op.n_groups - 1);
+    const int c0 = __ldg(op.hbase + g0);
+    const int ncols = __ldg(op.hbase + g_last) + SPAN - c0;
+    const int r0 = __ldg(op.vpos + y0);
+    const int r1 = min(__ldg(op.vpos + y1 - 1) + op.vtaps, op.sh);
+    const int nrows = r1 - r0;
+
+    float *M = smem;                                   // [m_rows][128]     intermediate t * 2^-149 (16-byte aligned rows)
+    float *S = smem + op.m_rows * kTileW;              // [m_rows][s_pitch] source samples as floats
+    const int s_pitch = op.s_pitch;
+
+    // ---- stage the source footprint ---------------------------------------------------------------
+    {
+        const int nv = min(ncols, op.sw - c0);         // samples that exist; the rest carry zero weight
+        const int xs = op.src_xstep;
+        const uint8_t *base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(r0) * op.src_pitch +
+                              static_cast<ptrdiff_t>(c0) * xs;
+        for (int row = warp; row < nrows; row += kWarps) {
+            const uint8_t *rp = base + row * op.src_pitch;
+            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
+            const unsigned *wp = reinterpret_cast<const unsigned *>(rp - mis);
+            const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
+            float *srow = S + row * s_pitch;
+            for (int w = lane; w < nwords; w += 32) {
+                const unsigned v = __ldg(wp + w);
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int off = 4 * w + k - static_cast<int>(mis);
+                    int s = off;
+                    bool ok = off >= 0;
+                    if (xs == 2) { ok = ok && !(off & 1); s = off >> 1; }
+                    if (ok && s < nv) srow[s] = byte_to_float(v, k);
+                }
+            }
+            for (int s = nv + lane; s < ncols; s += 32) srow[s] = 0.0f;
+        }
+    }
+    __syncthreads();
+
+    // ---- horizontal pass: S -> M --------------------------------------------------------------------
+    {
+        const int g = min(g0 + lane, op.n_groups - 1);
+        float cd[kGroup][SPAN];
+        const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+#pragma unroll
+        for (int k = 0; k < kGroup; ++k)
+#pragma unroll
+            for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
+        const int b = __ldg(op.hbase + g) - c0;
+        const float t_max = __int_as_float(32767);
+        for (int row = warp; row < nrows; row += kWarps) {
+            const float *sp = S + row * s_pitch + b;
+            float px[SPAN];
+#pragma unroll
+            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+            float4 o;
+            float *ov = reinterpret_cast<float *>(&o);
+#pragma unroll
+            for (int k = 0; k < kGroup; ++k) {
+                float acc = 0.0f;
+#pragma unroll
+                for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
+                ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
+            }
+            *reinterpret_cast<float4 *>(M + row * kTileW + 4 * lane) = o;
+        }
+    }
+    __syncthreads();
+
+    // ---- vertical pass: M -> destination ------------------------------------------------------------
+    {
+        const int strip = op.th / kWarps;
+        const int ya = y0 + warp * strip, yb = min(ya + strip, y1);
+        if (ya >= yb) return;
+        const int x = x0 + 4 * lane;
+        float4 win[VT];
+#pragma unroll
+        for (int s = 0; s < VT; ++s) win[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        int next_row = __ldg(op.vpos + ya);
+        int slot = next_row % VT;
+        const float v_thr = op.v_thr;
+        for (int y = ya; y < yb; ++y) {
+            const int first = __ldg(op.vpos + y);
+            if (next_row < first) { next_row = first; slot = first % VT; }   // steps larger than the ring
+            const int need_end = first + VT;
+            if (next_row < need_end)
+                load_ring_rows<VT>(win, slot, next_row, need_end, M + 4 * lane, r0, r1);
+            const float *cr = op.vring + static_cast<size_t>(y) * VT;
+            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int s = 0; s < VT; ++s) {
+                const float g = __ldg(cr + s);
+                acc[0] = fmaf(win[s].x, g, acc[0]);
+                acc[1] = fmaf(win[s].y, g, acc[1]);
+                acc[2] = fmaf(win[s].z, g, acc[2]);
+                acc[3] = fmaf(win[s].w, g, acc[3]);
+            }
+            float q[4], r[4];
+            float worst = 0.0f;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                q[k] = fma_rn(acc[k], 0x1p-126f, 0.0f);      // round(acc / 2^19) as a subnormal integer pattern
+                r[k] = fmaf(q[k], -0x1p126f, acc[k]);        // exact residual, scaled by 2^-42
+                worst = fmaxf(worst, fabsf(r[k]));
+            }
+            unsigned word = pack_sat_u8(__float_as_int(q[3]), __float_as_int(q[2]), 0u);
+            word = pack_sat_u8(__float_as_int(q[1]), __float_as_int(q[0]), word);
+            if (worst >= v_thr) {
+                // within the float error band of a rounding boundary: redo those samples in int32
+                const int *ci = op.vring_i + static_cast<size_t>(y) * VT;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    if (fabsf(r[k]) >= v_thr) {
+                        int a = 0;
+#pragma unroll
+                        for (int s = 0; s < VT; ++s) {
+                            const float wv = k == 0 ? win[s].x : k == 1 ? win[s].y : k == 2 ? win[s].z : win[s].w;
+                            a += subnormal_to_int(wv) * __ldg(ci + s);
+                        }
+                        const unsigned v = static_cast<unsigned>(min(max((a + (1 << 18)) >> 19, 0), 255));
+                        word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
+                    }
+                }
+            }
+            uint8_t *dp = op.dst + f * op.dst_fstride + static_cast<ptrdiff_t>(y) * op.dst_pitch;
+            if (op.dst_xstep == 1) {
+                uint8_t *p = dp + x;
+                if (x + 3 < op.dw && (reinterpret_cast<uintptr_t>(p) & 3u) == 0) {
+                    *reinterpret_cast<unsigned *>(p) = word;
+                } else {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k)
+                        if (x + k < op.dw) p[k] = static_cast<uint8_t>(word >> (8 * k));
+                }
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+                    if (x + k < op.dw) dp[static_cast<ptrdiff_t>(x + k) * op.dst_xstep] = static_cast<uint8_t>(word >> (8 * k));
+            }
+        }
+    }
+}
+
+using KernelFn = void (*)(const FusedLaunchParams);
+struct Instance { int span, vt; KernelFn fn; };
+#define TVS_INST(S, V) {S, V, fused_scale_kernel<S, V>}
+const Instance kInstances[] = {
+    TVS_INST(4, 1),  TVS_INST(8, 1),  TVS_INST(4, 2),  TVS_INST(8, 2),  TVS_INST(6, 4),  TVS_INST(8, 4),
+    TVS_INST(8, 6),  TVS_INST(12, 3), TVS_INST(12, 4), TVS_INST(12, 6), TVS_INST(16, 6), TVS_INST(16, 9),
+    TVS_INST(20, 12), TVS_INST(24, 12),
+};
+#undef TVS_INST
+
+}  // namespace
+
+struct FusedOp {
+    int op_index = 0;
+    int instance = -1;
+    int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, m_rows = 0;
+    size_t smem_bytes = 0;
+    float v_thr = 0;
+    // offsets (in bytes) into the device blob
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vring_off = 0, vring_i_off = 0;
+    int vtaps = 0;
+};
+
+struct FusedPlan {
+    std::vector<FusedOp> ops;
+    uint8_t *blob = nullptr;
+    size_t blob_bytes = 0;
+    int device = 0;
+};
+
+namespace {
+
+template <typename T>
+size_t append(std::vector<uint8_t> &blob, const std::vector<T> &v) {
+    size_t off = (blob.size() + 255) & ~static_cast<size_t>(255);
+    blob.resize(off + v.size() * sizeof(T));
+    memcpy(blob.data() + off, v.data(), v.size() * sizeof(T));
+    return off;
+}
+
+// Worst-case absolute rounding error of the float vertical sum, in units of the integer sum.
+double vertical_error_bound(const AxisTable &v, int vt_inst) {
+    long long worst = 0;
+    for (int y = 0; y < v.length; ++y) {
+        long long s = 0;
+        for (int j = 0; j < v.taps; ++j) s += std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+        worst = std::max(worst, s);
+    }
+    const double bound = 32767.0 * static_cast<double>(worst) + 1.0;
+    const double ulp = std::ldexp(1.0, static_cast<int>(std::floor(std::log2(bound))) - 23);
+    return 0.5 * ulp * vt_inst;
+}
+
+}  // namespace
+
+FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err) {
+    std::vector<uint8_t> blob;
+    auto fp = new FusedPlan;
+    fp->device = device;
+    for (size_t oi = 0; oi < plan.ops.size(); ++oi) {
+        const PlaneOp &op = plan.ops[oi];
+        if (op.kind != kOpScale) continue;
+        if (op.src_bits != 8 || op.dst_bits != 8 || op.rule != kOut8) { err = "only 8-bit to 8-bit so far"; delete fp; return nullptr; }
+        const AxisTable &h = host_tables[op.htable], &v = host_tables[op.vtable];
+
+        // float exactness of the horizontal sum: rows must sum to 2^14 and 255 * sum|c| must stay below 2^24
+        const int n_groups = (op.dw + kGroup - 1) / kGroup;
+        int span = 0;
+        long long worst_abs = 0;
+        for (int x = 0; x < op.dw; ++x) {
+            long long s = 0, a = 0;
+            for (int j = 0; j < h.taps; ++j) { const int c = h.coef[static_cast<size_t>(x) * h.taps + j]; s += c; a += std::abs(c); }
+            if (s != (1 << 14)) { err = "horizontal row does not sum to one"; delete fp; return nullptr; }
+            worst_abs = std::max(worst_abs, a);
+        }
+        if (255 * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete fp; return nullptr; }
+        for (int g = 0; g < n_groups; ++g) {
+            const int xa = g * kGroup, xb = std::min(xa + kGroup, op.dw) - 1;
+            span = std::max(span, h.pos[xb] + h.taps - h.pos[xa]);
+        }
+        int inst = -1;
+        for (size_t i = 0; i < sizeof(kInstances) / sizeof(kInstances[0]); ++i) {
+            if (kInstances[i].span < span || kInstances[i].vt < v.taps) continue;
+            if (inst < 0 || kInstances[i].span + kInstances[i].vt < kInstances[inst].span + kInstances[inst].vt) inst = static_cast<int>(i);
+        }
+        if (inst < 0) { err = "no kernel instance for this filter size"; delete fp; return nullptr; }
+        const int SPAN = kInstances[inst].span, VT = kInstances[inst].vt;
+        const double e = vertical_error_bound(v, VT);
+        if (e > 4096.0) { err = "vertical error bound too large"; delete fp; return nullptr; }
+
+        FusedOp fo;
+        fo.op_index = static_cast<int>(oi);
+        fo.instance = inst;
+        fo.n_groups = n_groups;
+        fo.vtaps = v.taps;
+        fo.tiles_x = (op.dw + kTileW - 1) / kTileW;
+        fo.v_thr = static_cast<float>(std::ldexp(static_cast<double>(1 << 18) - e - 1.0, -42));
+
+        // dense horizontal coefficients and span starts
+        std::vector<float> hdense(static_cast<size_t>(n_groups) * kGroup * SPAN, 0.0f);
+        std::vector<int> hbase(n_groups);
+        for (int g = 0; g < n_groups; ++g) {
+            const int xa = g * kGroup;
+            hbase[g] = h.pos[xa];
+            for (int k = 0; k < kGroup && xa + k < op.dw; ++k) {
+                const int x = xa + k;
+                for (int j = 0; j < h.taps; ++j) {
+                    const int c = h.coef[static_cast<size_t>(x) * h.taps + j];
+                    if (c) hdense[(static_cast<size_t>(g) * kGroup + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -30);
+                }
+            }
+        }
+        int s_pitch = 0;
+        for (int tx = 0; tx < fo.tiles_x; ++tx) {
+            const int ga = tx * (kTileW / kGroup), gb = std::min(ga + 31, n_groups - 1);
+            s_pitch = std::max(s_pitch, hbase[gb] + SPAN - hbase[ga]);
+        }
+        fo.s_pitch = s_pitch | 1;  // odd pitch spreads the staging stores over the banks
+
+        // vertical coefficients indexed by ring slot
+        std::vector<float> vring(static_cast<size_t>(op.dh) * VT, 0.0f);
+        std::vector<int> vring_i(static_cast<size_t>(op.dh) * VT, 0);
+        for (int y = 0; y < op.dh; ++y)
+            for (int j = 0; j < v.taps; ++j) {
+                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
+                const int slot = (v.pos[y] + j) % VT;
+                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
+                vring_i[static_cast<size_t>(y) * VT + slot] = c;
+            }
+
+        // tile height: as tall as shared memory allows (less vertical halo), a multiple of the warp count
+        auto rows_for = [&](int th, int &tiles_y) {
+            tiles_y = (op.dh + th - 1) / th;
+            int m = 0;
+            for (int ty = 0; ty < tiles_y; ++ty) {
+                const int ya = ty * th, yb = std::min(ya + th, op.dh);
+                m = std::max(m, std::min(v.pos[yb - 1] + v.taps, op.sh) - v.pos[ya]);
+            }
+            return m;
+        };
+        int th = 128;
+        while (th > kWarps && th / 2 >= op.dh) th /= 2;
+        for (;; th /= 2) {
+            fo.m_rows = rows_for(th, fo.tiles_y);
+            fo.smem_bytes = static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) * sizeof(float);
+            if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
+        }
+        if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
+        fo.th = th;
+
+        fo.hdense_off = append(blob, hdense);
+        fo.hbase_off = append(blob, hbase);
+        fo.vpos_off = append(blob, v.pos);
+        fo.vring_off = append(blob, vring);
+        fo.vring_i_off = append(blob, vring_i);
+        fp->ops.push_back(fo);
+    }
+    if (fp->ops.empty()) { err = "nothing to scale"; delete fp; return nullptr; }
+    if (cudaMalloc(&fp->blob, blob.size()) != cudaSuccess ||
+        cudaMemcpy(fp->blob, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        err = "device allocation for the fused tables failed";
+        cudaGetLastError();
+        if (fp->blob) cudaFree(fp->blob);
+        delete fp;
+        return nullptr;
+    }
+    fp->blob_bytes = blob.size();
+    for (const FusedOp &fo : fp->ops) {
+        if (fo.smem_bytes > 48 * 1024)
+            cudaFuncSetAttribute(reinterpret_cast<const void *>(kInstances[fo.instance].fn),
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024);
+    }
+    return fp;
+}
+
+void fused_plan_destroy(FusedPlan *p) {
+    if (!p) return;
+    if (p->blob) cudaFree(p->blob);
+    delete p;
+}
+
+size_t fused_plan_device_bytes(const FusedPlan *p) { return p ? p->blob_bytes : 0; }
+
+int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
+                 int n_frames, cudaStream_t stream) {
+    int launched = 0;
+    std::vector<bool> done(p->ops.size(), false);
+    for (size_t i = 0; i < p->ops.size(); ++i) {
+        if (done[i]) continue;
+        // one launch covers every plane that runs on the same kernel instance
+        FusedLaunchParams lp{};
+        int tiles = 0;
+        size_t smem = 0;
+        for (size_t j = i; j < p->ops.size() && lp.n_ops < kMaxFusedOps; ++j) {
+            const FusedOp &fo = p->ops[j];
+            if (done[j] || fo.instance != p->ops[i].instance) continue;
+            done[j] = true;
+            const PlaneOp &op = plan.ops[fo.op_index];
+            const SampleView &s = src_views[fo.op_index], &d = dst_views[fo.op_index];
+            FusedOpParams &q = lp.op[lp.n_ops++];
+            q.src = s.base; q.src_pitch = s.pitch; q.src_fstride = s.frame_stride; q.src_xstep = s.xstep;
+            q.dst = d.base; q.dst_pitch = d.pitch; q.dst_fstride = d.frame_stride; q.dst_xstep = d.xstep;
+            q.sw = op.sw; q.sh = op.sh; q.dw = op.dw; q.dh = op.dh;
+            q.th = fo.th; q.tiles_x = fo.tiles_x; q.tile_begin = tiles;
+            q.n_groups = fo.n_groups;
+            q.hdense = reinterpret_cast<const float *>(p->blob + fo.hdense_off);
+            q.hbase = reinterpret_cast<const int *>(p->blob + fo.hbase_off);
+            q.vpos = reinterpret_cast<const int *>(p->blob + fo.vpos_off);
+            q.vring = reinterpret_cast<const float *>(p->blob + fo.vring_off);
+            q.vring_i = reinterpret_cast<const int *>(p->blob + fo.vring_i_off);
+            q.vtaps = fo.vtaps;
+            q.s_pitch = fo.s_pitch; q.m_rows = fo.m_rows;
+            q.v_thr = fo.v_thr;
+            tiles += fo.tiles_x * fo.tiles_y;
+            smem = std::max(smem, fo.smem_bytes);
+        }
+        const dim3 grid(tiles, n_frames);
+        kInstances[p->ops[i].instance].fn<<<grid, kThreads, smem, stream>>>(lp);
+        if (cudaPeekAtLastError() != cudaSuccess) return -1;
+        ++launched;
+    }
+    return launched;
+}
+
 }  // namespace tvs
