@@ -14,9 +14,11 @@
 //     cvt.pack.sat.u8.s32 clamps and packs.  The residual r = acc' - q * 2^126 is exact; when |r| is within `e`
 //     of the rounding boundary (about 0.02 % of samples) the sample is recomputed in int32, so the result is
 //     exact by construction, not by luck.  RN ties are inside that band.
-// Tile geometry: 128 output columns (a lane owns 4 adjacent columns in both passes) by `th` output rows,
-// 256 threads.  Each lane keeps the dense coefficients of its 4 columns over their common source span in
-// registers for the life of the tile, and a ring of VT intermediate rows while it walks down its strip.
+// Tile geometry: 256 output columns (two halves of 128; a lane owns 4 adjacent columns of each half) by `th`
+// output rows, 256 threads.  In the H pass warps 0-3 / 4-7 take the left / right half and a lane keeps the dense
+// coefficients of its 4 columns over their common source span in registers for the life of the tile.  In the
+// V pass each warp walks down a strip of th/8 rows with a register ring of VT intermediate rows, producing
+// 8 samples per lane per row; row coefficients and start rows come from a shared-memory copy.
 #include <algorithm>
 #include <cmath>
 #include <cstring>
@@ -26,12 +28,14 @@
 namespace tvs {
 namespace {
 
-constexpr int kTileW = 128;
+constexpr int kHalfW = 128;               // columns per half tile: lane * 4 + k
+constexpr int kTileW = 2 * kHalfW;
 constexpr int kThreads = 256;
 constexpr int kWarps = kThreads / 32;
 constexpr int kGroup = 4;                 // adjacent output columns per lane
+constexpr int kGroupsPerHalf = kHalfW / kGroup;
 constexpr int kMaxFusedOps = 3;
-constexpr size_t kSmemBudget = 100 * 1024;  // two CTAs per SM
+constexpr size_t kSmemBudget = 112 * 1024;  // two CTAs per SM
 
 struct FusedOpParams {
     const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
@@ -45,7 +49,10 @@ struct FusedOpParams {
     const float *vring;    // [dh][VT]             g * 2^107, indexed by ring slot = source_row % VT
     const int *vring_i;    // [dh][VT]             the same coefficients as integers (exact path)
     int vtaps;
-    int s_pitch, m_rows;   // shared-memory geometry
+    int s_pitch;           // floats per staged source row
+    int s_words;           // 32-bit source words staged per row
+    int s_words_log2;      // log2 of the power of two >= s_words (index split in the staging loop)
+    int m_rows;            // rows of the shared-memory tiles
     float v_thr;           // |residual| at or above this needs the exact path
 };
 
@@ -70,27 +77,34 @@ __device__ __forceinline__ unsigned pack_sat_u8(int hi, int lo, unsigned upper) 
     asm("cvt.pack.sat.u8.s32.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(hi), "r"(lo), "r"(upper));
     return d;
 }
-__device__ __forceinline__ float byte_to_float(unsigned word, int k) {
-    // 0x4B0000bb is 2^23 + bb
-    return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7540u | k)) - 8388608.0f;
+__device__ __forceinline__ float byte_to_float(unsigned word, unsigned selector) {
+    // selector 0x754k moves byte k of `word` under the exponent of 2^23: 0x4B0000bb is 2^23 + bb
+    return __uint_as_float(__byte_perm(word, 0x4B000000u, selector)) - 8388608.0f;
 }
 __device__ __forceinline__ int subnormal_to_int(float v) {
     const int b = __float_as_int(v);
     return b < 0 ? -(b & 0x7fffffff) : b;
 }
+__device__ __forceinline__ float pick(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
 
-// Pull intermediate rows [next_row, need_end) into the register ring.  Ring slot = row % VT, so the slot a
-// row lands in is a compile-time constant inside each case; the switch enters at the current slot and falls
-// through, which keeps `win` in registers (no dynamic indexing) at the cost of one uniform branch per call.
+// Pull intermediate rows [next_row, need_end) into the register rings (left and right half).  Ring slot =
+// row % VT, so the slot a row lands in is a compile-time constant inside each case; the switch enters at the
+// current slot and falls through, which keeps the rings in registers (no dynamic indexing) at the cost of one
+// uniform branch per call.
 template <int VT>
-__device__ __forceinline__ void load_ring_rows(float4 (&win)[VT], int &slot, int &next_row, int need_end,
-                                               const float *m_col, int r0, int r1) {
-#define TVS_RING_CASE(s)                                                                                     \
-    case s:                                                                                                  \
-        if constexpr (s < VT) {                                                                              \
-            win[s] = next_row < r1 ? *reinterpret_cast<const float4 *>(m_col + (next_row - r0) * kTileW)     \
-                                   : make_float4(0.f, 0.f, 0.f, 0.f);                                        \
-            if (++next_row >= need_end) { slot = (s + 1 == VT) ? 0 : s + 1; return; }                        \
+__device__ __forceinline__ void load_ring_rows(float4 (&wa)[VT], float4 (&wb)[VT], int &slot, int &next_row,
+                                               int need_end, const float *m_col, int r0, int r1) {
+#define TVS_RING_CASE(s)                                                                           \
+    case s:                                                                                        \
+        if constexpr (s < VT) {                                                                    \
+            if (next_row < r1) {                                                                   \
+                const float *m = m_col + (next_row - r0) * kTileW;                                 \
+                wa[s] = *reinterpret_cast<const float4 *>(m);                                      \
+                wb[s] = *reinterpret_cast<const float4 *>(m + kHalfW);                             \
+            } else {                                                                               \
+                wa[s] = wb[s] = make_float4(0.f, 0.f, 0.f, 0.f);                                   \
+            }                                                                                      \
+            if (++next_row >= need_end) { slot = (s + 1 == VT) ? 0 : s + 1; return; }              \
         }
     for (;;) {
         switch (slot) {
@@ -102,161 +116,199 @@ __device__ __forceinline__ void load_ring_rows(float4 (&win)[VT], int &slot, int
 #undef TVS_RING_CASE
 }
 
+// One output row of 4 columns: float sum, rounded quotient, packed bytes, and the exact redo where needed.
+template <int VT>
+__device__ __forceinline__ unsigned vertical_quad(const float4 (&win)[VT], const float (&g)[VT], float v_thr,
+                                                  const int *exact_coef) {
+    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+#pragma unroll
+    for (int s = 0; s < VT; ++s) {
+        a0 = fmaf(win[s].x, g[s], a0);
+        a1 = fmaf(win[s].y, g[s], a1);
+        a2 = fmaf(win[s].z, g[s], a2);
+        a3 = fmaf(win[s].w, g[s], a3);
+    }
+    const float q0 = fma_rn(a0, 0x1p-126f, 0.f), q1 = fma_rn(a1, 0x1p-126f, 0.f);
+    const float q2 = fma_rn(a2, 0x1p-126f, 0.f), q3 = fma_rn(a3, 0x1p-126f, 0.f);
+    const float r0 = fmaf(q0, -0x1p126f, a0), r1 = fmaf(q1, -0x1p126f, a1);
+    const float r2 = fmaf(q2, -0x1p126f, a2), r3 = fmaf(q3, -0x1p126f, a3);
+    unsigned word = pack_sat_u8(__float_as_int(q3), __float_as_int(q2), 0u);
+    word = pack_sat_u8(__float_as_int(q1), __float_as_int(q0), word);
+    const float worst = fmaxf(fmaxf(fabsf(r0), fabsf(r1)), fmaxf(fabsf(r2), fabsf(r3)));
+    if (worst >= v_thr) {
+        // within the float error band of a rounding boundary: redo those samples in int32
+        const float r[4] = {r0, r1, r2, r3};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            if (fabsf(r[k]) >= v_thr) {
+                int a = 0;
+#pragma unroll
+                for (int s = 0; s < VT; ++s) a += subnormal_to_int(pick(win[s], k)) * __ldg(exact_coef + s);
+                const unsigned v = static_cast<unsigned>(min(max((a + (1 << 18)) >> 19, 0), 255));
+                word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
+            }
+        }
+    }
+    return word;
+}
+
+__device__ __forceinline__ void store_quad(uint8_t *row, int x, int dw, int xstep, bool aligned, unsigned word) {
+    if (xstep == 1) {
+        if (aligned && x + 3 < dw) {
+            *reinterpret_cast<unsigned *>(row + x) = word;
+        } else {
+#pragma unroll
+            for (int k = 0; k < 4; ++k)
+                if (x + k < dw) row[x + k] = static_cast<uint8_t>(word >> (8 * k));
+        }
+    } else {
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            if (x + k < dw) row[static_cast<ptrdiff_t>(x + k) * xstep] = static_cast<uint8_t>(word >> (8 * k));
+    }
+}
+
 template <int SPAN, int VT>
 __global__ void __launch_bounds__(kThreads, 2)
 fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
     int t = blockIdx.x, oi = 0;
     if (P.n_ops > 1 && t >= P.op[1].tile_begin) oi = 1;
     if (P.n_ops > 2 && t >= P.op[2].tile_begin) oi = 2;
     const FusedOpParams &op = P.op[oi];
     t -= op.tile_begin;
-    const int ty = t / op.tiles_x, tx = t - ty * op.tiles_x;
+    const int tiles_x = op.tiles_x;
+    const int ty = t / tiles_x, tx = t - ty * tiles_x;
     const int f = blockIdx.y;
+    const int th = op.th, dw = op.dw, dh = op.dh, n_groups = op.n_groups;
 
     const int x0 = tx * kTileW;
-    const int y0 = ty * op.th, y1 = min(y0 + op.th, op.dh);
+    const int y0 = ty * th, y1 = min(y0 + th, dh);
     const int g0 = x0 / kGroup;
-    const int g_last = min(g0 + 31, op.n_groups - 1);
+    const int g_last = min(g0 + 2 * kGroupsPerHalf - 1, n_groups - 1);
     const int c0 = __ldg(op.hbase + g0);
     const int ncols = __ldg(op.hbase + g_last) + SPAN - c0;
     const int r0 = __ldg(op.vpos + y0);
     const int r1 = min(__ldg(op.vpos + y1 - 1) + op.vtaps, op.sh);
     const int nrows = r1 - r0;
+    const int s_pitch = op.s_pitch, m_rows = op.m_rows;
+    const int xs = op.src_xstep;
 
-    float *M = smem;                                   // [m_rows][128]     intermediate t * 2^-149 (16-byte aligned rows)
-    float *S = smem + op.m_rows * kTileW;              // [m_rows][s_pitch] source samples as floats
-    const int s_pitch = op.s_pitch;
+    float *M = smem;                                  // [m_rows][256]   intermediate t * 2^-149
+    float *S = M + m_rows * kTileW;                   // [m_rows][s_pitch] source samples as floats
+    float *CV = S + m_rows * s_pitch;                 // [th][VT]        ring-ordered row coefficients
+    int *VP = reinterpret_cast<int *>(CV + th * VT);  // [th]            first source row of each output row
 
-    // ---- stage the source footprint ---------------------------------------------------------------
-    {
-        const int nv = min(ncols, op.sw - c0);         // samples that exist; the rest carry zero weight
-        const int xs = op.src_xstep;
-        const uint8_t *base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(r0) * op.src_pitch +
+    const uint8_t *src_base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(r0) * op.src_pitch +
                               static_cast<ptrdiff_t>(c0) * xs;
-        for (int row = warp; row < nrows; row += kWarps) {
-            const uint8_t *rp = base + row * op.src_pitch;
+    const ptrdiff_t src_pitch = op.src_pitch;
+
+    // ---- stage: per-row coefficients / start rows, and the source footprint as floats -----------------
+    for (int i = tid; i < th * VT; i += kThreads) {
+        const int y = y0 + i / VT;
+        CV[i] = y < dh ? __ldg(op.vring + static_cast<size_t>(y0) * VT + i) : 0.f;
+    }
+    for (int i = tid; i < th; i += kThreads) VP[i] = __ldg(op.vpos + min(y0 + i, dh - 1));
+    {
+        // A source row is read as aligned 32-bit words starting at the word that holds its first sample; the
+        // sample that lands in S[row][j] is therefore sample j - (mis / xs) of the footprint.
+        const int nv = min(ncols, op.sw - c0);        // samples that exist; the rest carry zero weight
+        const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
+        const int total = nrows << wlog;
+        for (int idx = tid; idx < total; idx += kThreads) {
+            const int row = idx >> wlog, w = idx & wmask;
+            if (w >= s_words) continue;
+            const uint8_t *rp = src_base + row * src_pitch;
             const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
-            const unsigned *wp = reinterpret_cast<const unsigned *>(rp - mis);
             const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
-            float *srow = S + row * s_pitch;
-            for (int w = lane; w < nwords; w += 32) {
-                const unsigned v = __ldg(wp + w);
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const int off = 4 * w + k - static_cast<int>(mis);
-                    int s = off;
-                    bool ok = off >= 0;
-                    if (xs == 2) { ok = ok && !(off & 1); s = off >> 1; }
-                    if (ok && s < nv) srow[s] = byte_to_float(v, k);
-                }
+            unsigned v = 0;
+            if (w < nwords) v = __ldg(reinterpret_cast<const unsigned *>(rp - mis) + w);
+            if (xs == 1) {
+                float4 o;
+                o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
+                o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
+                *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
+            } else {
+                const unsigned p = mis & 1u;
+                float2 o;
+                o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
+                *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
             }
-            for (int s = nv + lane; s < ncols; s += 32) srow[s] = 0.0f;
         }
     }
     __syncthreads();
 
     // ---- horizontal pass: S -> M --------------------------------------------------------------------
     {
-        const int g = min(g0 + lane, op.n_groups - 1);
-        float cd[kGroup][SPAN];
-        const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+        const int half = warp >> 2;
+        const int gb = g0 + half * kGroupsPerHalf;
+        if (gb < n_groups) {
+            const int g = min(gb + lane, n_groups - 1);
+            float cd[kGroup][SPAN];
+            const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
 #pragma unroll
-        for (int k = 0; k < kGroup; ++k)
+            for (int k = 0; k < kGroup; ++k)
 #pragma unroll
-            for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
-        const int b = __ldg(op.hbase + g) - c0;
-        const float t_max = __int_as_float(32767);
-        for (int row = warp; row < nrows; row += kWarps) {
-            const float *sp = S + row * s_pitch + b;
-            float px[SPAN];
+                for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
+            const int b = __ldg(op.hbase + g) - c0;
+            const float t_max = __int_as_float(32767);
+            float *mcol = M + half * kHalfW + 4 * lane;
+            for (int row = warp & 3; row < nrows; row += 4) {
+                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
+                const float *sp = S + row * s_pitch + b + (xs == 1 ? mis : (mis >> 1));
+                float px[SPAN];
 #pragma unroll
-            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
-            float4 o;
-            float *ov = reinterpret_cast<float *>(&o);
+                for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+                float4 o;
+                float *ov = reinterpret_cast<float *>(&o);
 #pragma unroll
-            for (int k = 0; k < kGroup; ++k) {
-                float acc = 0.0f;
+                for (int k = 0; k < kGroup; ++k) {
+                    float acc = 0.0f;
 #pragma unroll
-                for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
-                ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
+                    for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
+                    ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
+                }
+                *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
             }
-            *reinterpret_cast<float4 *>(M + row * kTileW + 4 * lane) = o;
         }
     }
     __syncthreads();
 
     // ---- vertical pass: M -> destination ------------------------------------------------------------
     {
-        const int strip = op.th / kWarps;
+        const int strip = th / kWarps;
         const int ya = y0 + warp * strip, yb = min(ya + strip, y1);
         if (ya >= yb) return;
-        const int x = x0 + 4 * lane;
-        float4 win[VT];
-#pragma unroll
-        for (int s = 0; s < VT; ++s) win[s] = make_float4(0.f, 0.f, 0.f, 0.f);
-        int next_row = __ldg(op.vpos + ya);
-        int slot = next_row % VT;
+        const bool right = x0 + kHalfW < dw;            // the right half of the last tile may be empty
+        const int xa = x0 + 4 * lane, xb = xa + kHalfW;
+        const int dst_xstep = op.dst_xstep;
+        const ptrdiff_t dst_pitch = op.dst_pitch;
         const float v_thr = op.v_thr;
-        for (int y = ya; y < yb; ++y) {
-            const int first = __ldg(op.vpos + y);
+        uint8_t *drow = op.dst + f * op.dst_fstride + static_cast<ptrdiff_t>(ya) * dst_pitch;
+        const int *exact = op.vring_i + static_cast<size_t>(ya) * VT;
+        const float *cv = CV + (ya - y0) * VT;
+        const int *vp = VP + (ya - y0);
+        const float *m_col = M + 4 * lane;
+        float4 wa[VT], wb[VT];
+#pragma unroll
+        for (int s = 0; s < VT; ++s) wa[s] = wb[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        int next_row = vp[0];
+        int slot = next_row % VT;
+        for (int y = ya; y < yb; ++y, drow += dst_pitch, exact += VT, cv += VT, ++vp) {
+            const int first = *vp;
             if (next_row < first) { next_row = first; slot = first % VT; }   // steps larger than the ring
-            const int need_end = first + VT;
-            if (next_row < need_end)
-                load_ring_rows<VT>(win, slot, next_row, need_end, M + 4 * lane, r0, r1);
-            const float *cr = op.vring + static_cast<size_t>(y) * VT;
-            float acc[4] = {0.f, 0.f, 0.f, 0.f};
+            if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, m_col, r0, r1);
+            float g[VT];
 #pragma unroll
-            for (int s = 0; s < VT; ++s) {
-                const float g = __ldg(cr + s);
-                acc[0] = fmaf(win[s].x, g, acc[0]);
-                acc[1] = fmaf(win[s].y, g, acc[1]);
-                acc[2] = fmaf(win[s].z, g, acc[2]);
-                acc[3] = fmaf(win[s].w, g, acc[3]);
-            }
-            float q[4], r[4];
-            float worst = 0.0f;
-#pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                q[k] = fma_rn(acc[k], 0x1p-126f, 0.0f);      // round(acc / 2^19) as a subnormal integer pattern
-                r[k] = fmaf(q[k], -0x1p126f, acc[k]);        // exact residual, scaled by 2^-42
-                worst = fmaxf(worst, fabsf(r[k]));
-            }
-            unsigned word = pack_sat_u8(__float_as_int(q[3]), __float_as_int(q[2]), 0u);
-            word = pack_sat_u8(__float_as_int(q[1]), __float_as_int(q[0]), word);
-            if (worst >= v_thr) {
-                // within the float error band of a rounding boundary: redo those samples in int32
-                const int *ci = op.vring_i + static_cast<size_t>(y) * VT;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    if (fabsf(r[k]) >= v_thr) {
-                        int a = 0;
-#pragma unroll
-                        for (int s = 0; s < VT; ++s) {
-                            const float wv = k == 0 ? win[s].x : k == 1 ? win[s].y : k == 2 ? win[s].z : win[s].w;
-                            a += subnormal_to_int(wv) * __ldg(ci + s);
-                        }
-                        const unsigned v = static_cast<unsigned>(min(max((a + (1 << 18)) >> 19, 0), 255));
-                        word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
-                    }
-                }
-            }
-            uint8_t *dp = op.dst + f * op.dst_fstride + static_cast<ptrdiff_t>(y) * op.dst_pitch;
-            if (op.dst_xstep == 1) {
-                uint8_t *p = dp + x;
-                if (x + 3 < op.dw && (reinterpret_cast<uintptr_t>(p) & 3u) == 0) {
-                    *reinterpret_cast<unsigned *>(p) = word;
-                } else {
-#pragma unroll
-                    for (int k = 0; k < 4; ++k)
-                        if (x + k < op.dw) p[k] = static_cast<uint8_t>(word >> (8 * k));
-                }
-            } else {
-#pragma unroll
-                for (int k = 0; k < 4; ++k)
-                    if (x + k < op.dw) dp[static_cast<ptrdiff_t>(x + k) * op.dst_xstep] = static_cast<uint8_t>(word >> (8 * k));
+            for (int s = 0; s < VT; ++s) g[s] = cv[s];
+            const bool aligned = ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0;
+            const unsigned word_a = vertical_quad<VT>(wa, g, v_thr, exact);
+            store_quad(drow, xa, dw, dst_xstep, aligned, word_a);
+            if (right) {
+                const unsigned word_b = vertical_quad<VT>(wb, g, v_thr, exact);
+                store_quad(drow, xb, dw, dst_xstep, aligned, word_b);
             }
         }
     }
@@ -277,7 +329,7 @@ const Instance kInstances[] = {
 struct FusedOp {
     int op_index = 0;
     int instance = -1;
-    int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, m_rows = 0;
+    int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, s_words = 0, s_words_log2 = 0, m_rows = 0;
     size_t smem_bytes = 0;
     float v_thr = 0;
     // offsets (in bytes) into the device blob
@@ -374,12 +426,17 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
                 }
             }
         }
-        int s_pitch = 0;
+        int ncols_max = 0;
         for (int tx = 0; tx < fo.tiles_x; ++tx) {
-            const int ga = tx * (kTileW / kGroup), gb = std::min(ga + 31, n_groups - 1);
-            s_pitch = std::max(s_pitch, hbase[gb] + SPAN - hbase[ga]);
+            const int ga = tx * 2 * kGroupsPerHalf, gb = std::min(ga + 2 * kGroupsPerHalf - 1, n_groups - 1);
+            ncols_max = std::max(ncols_max, hbase[gb] + SPAN - hbase[ga]);
         }
-        fo.s_pitch = s_pitch | 1;  // odd pitch spreads the staging stores over the banks
+        // words per staged row for the worst alignment, and the float pitch that holds them
+        fo.s_words = (3 + (ncols_max - 1) * op.src_xstep) / 4 + 1;
+        fo.s_words_log2 = 0;
+        while ((1 << fo.s_words_log2) < fo.s_words) ++fo.s_words_log2;
+        fo.s_pitch = fo.s_words * (4 / op.src_xstep);
+        if ((fo.s_pitch & 31) == 0) fo.s_pitch += 4;   // keep consecutive rows off the same banks
 
         // vertical coefficients indexed by ring slot
         std::vector<float> vring(static_cast<size_t>(op.dh) * VT, 0.0f);
@@ -406,7 +463,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         while (th > kWarps && th / 2 >= op.dh) th /= 2;
         for (;; th /= 2) {
             fo.m_rows = rows_for(th, fo.tiles_y);
-            fo.smem_bytes = static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) * sizeof(float);
+            fo.smem_bytes = (static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) + static_cast<size_t>(th) * (VT + 1)) * sizeof(float);
             if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
         }
         if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
@@ -473,7 +530,7 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             q.vring = reinterpret_cast<const float *>(p->blob + fo.vring_off);
             q.vring_i = reinterpret_cast<const int *>(p->blob + fo.vring_i_off);
             q.vtaps = fo.vtaps;
-            q.s_pitch = fo.s_pitch; q.m_rows = fo.m_rows;
+            q.s_pitch = fo.s_pitch; q.s_words = fo.s_words; q.s_words_log2 = fo.s_words_log2; q.m_rows = fo.m_rows;
             q.v_thr = fo.v_thr;
             tiles += fo.tiles_x * fo.tiles_y;
             smem = std::max(smem, fo.smem_bytes);
