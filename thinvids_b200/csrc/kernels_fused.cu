@@ -35,6 +35,7 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kGroup = 4;                 // adjacent output columns per lane
 constexpr int kGroupsPerHalf = kHalfW / kGroup;
 constexpr int kMaxFusedOps = 3;
+constexpr int kMaxTilesX = 64, kMaxTilesY = 160;   // tile descriptors travel in the kernel parameters
 constexpr size_t kSmemBudget = 112 * 1024;  // two CTAs per SM
 
 struct FusedOpParams {
@@ -54,6 +55,8 @@ struct FusedOpParams {
     int s_words_log2;      // log2 of the power of two >= s_words (index split in the staging loop)
     int m_rows;            // rows of the shared-memory tiles
     float v_thr;           // |residual| at or above this needs the exact path
+    // per tile column: first source column and column count of the footprint; per tile row: source row range
+    short tile_c0[kMaxTilesX], tile_nc[kMaxTilesX], tile_r0[kMaxTilesY], tile_r1[kMaxTilesY];
 };
 
 struct FusedLaunchParams {
@@ -187,11 +190,8 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     const int x0 = tx * kTileW;
     const int y0 = ty * th, y1 = min(y0 + th, dh);
     const int g0 = x0 / kGroup;
-    const int g_last = min(g0 + 2 * kGroupsPerHalf - 1, n_groups - 1);
-    const int c0 = __ldg(op.hbase + g0);
-    const int ncols = __ldg(op.hbase + g_last) + SPAN - c0;
-    const int r0 = __ldg(op.vpos + y0);
-    const int r1 = min(__ldg(op.vpos + y1 - 1) + op.vtaps, op.sh);
+    const int c0 = op.tile_c0[tx], ncols = op.tile_nc[tx];
+    const int r0 = op.tile_r0[ty], r1 = op.tile_r1[ty];
     const int nrows = r1 - r0;
     const int s_pitch = op.s_pitch, m_rows = op.m_rows;
     const int xs = op.src_xstep;
@@ -205,73 +205,99 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                               static_cast<ptrdiff_t>(c0) * xs;
     const ptrdiff_t src_pitch = op.src_pitch;
 
-    // ---- stage: per-row coefficients / start rows, and the source footprint as floats -----------------
-    for (int i = tid; i < th * VT; i += kThreads) {
-        const int y = y0 + i / VT;
-        CV[i] = y < dh ? __ldg(op.vring + static_cast<size_t>(y0) * VT + i) : 0.f;
-    }
-    for (int i = tid; i < th; i += kThreads) VP[i] = __ldg(op.vpos + min(y0 + i, dh - 1));
+    // ---- issue every global load of the tile up front, then fill shared memory -------------------------
+    // (1) this lane's dense horizontal coefficients (used after the first barrier)
+    const int half = warp >> 2;
+    const int gb = g0 + half * kGroupsPerHalf;
+    const bool h_active = gb < n_groups;
+    const int g = min(gb + lane, n_groups - 1);
+    float cd[kGroup][SPAN];
     {
-        // A source row is read as aligned 32-bit words starting at the word that holds its first sample; the
-        // sample that lands in S[row][j] is therefore sample j - (mis / xs) of the footprint.
+        const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+        if constexpr ((kGroup * SPAN) % 4 == 0) {
+            float *flat = &cd[0][0];
+#pragma unroll
+            for (int i = 0; i < kGroup * SPAN / 4; ++i) {
+                const float4 v = __ldg(reinterpret_cast<const float4 *>(hd) + i);
+                flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
+            }
+        } else {
+#pragma unroll
+            for (int k = 0; k < kGroup; ++k)
+#pragma unroll
+                for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
+        }
+    }
+    const int hb = __ldg(op.hbase + g) - c0;
+    // (2) row coefficients and start rows of this tile (tables are padded to whole tiles on the host)
+    {
+        const float4 *cvg = reinterpret_cast<const float4 *>(op.vring + static_cast<size_t>(y0) * VT);
+        const int n4 = th * VT / 4;                   // th is a multiple of 8
+        for (int i = tid; i < n4; i += kThreads) reinterpret_cast<float4 *>(CV)[i] = __ldg(cvg + i);
+        for (int i = tid; i < th; i += kThreads) VP[i] = __ldg(op.vpos + y0 + i);
+    }
+    // (3) the source footprint.  A source row is read as aligned 32-bit words starting at the word that holds
+    // its first sample; the sample that lands in S[row][j] is therefore sample j - (mis / xs) of the footprint.
+    {
         const int nv = min(ncols, op.sw - c0);        // samples that exist; the rest carry zero weight
         const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
         const int total = nrows << wlog;
-        for (int idx = tid; idx < total; idx += kThreads) {
-            const int row = idx >> wlog, w = idx & wmask;
-            if (w >= s_words) continue;
-            const uint8_t *rp = src_base + row * src_pitch;
-            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
-            const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
-            unsigned v = 0;
-            if (w < nwords) v = __ldg(reinterpret_cast<const unsigned *>(rp - mis) + w);
-            if (xs == 1) {
-                float4 o;
-                o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
-                o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
-                *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
-            } else {
-                const unsigned p = mis & 1u;
-                float2 o;
-                o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
-                *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
+        constexpr int U = 4;
+        for (int base = 0; base < total; base += kThreads * U) {
+            unsigned v[U];
+            unsigned mis_u[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int idx = base + u * kThreads + tid;
+                const int row = idx >> wlog, w = idx & wmask;
+                const uint8_t *rp = src_base + row * src_pitch;
+                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
+                const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
+                mis_u[u] = mis;
+                v[u] = 0;
+                if (idx < total && w < nwords) v[u] = __ldg(reinterpret_cast<const unsigned *>(rp - mis) + w);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                const int idx = base + u * kThreads + tid;
+                const int row = idx >> wlog, w = idx & wmask;
+                if (idx >= total || w >= s_words) continue;
+                if (xs == 1) {
+                    float4 o;
+                    o.x = byte_to_float(v[u], 0x7540u); o.y = byte_to_float(v[u], 0x7541u);
+                    o.z = byte_to_float(v[u], 0x7542u); o.w = byte_to_float(v[u], 0x7543u);
+                    *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
+                } else {
+                    const unsigned p = mis_u[u] & 1u;
+                    float2 o;
+                    o.x = byte_to_float(v[u], 0x7540u | p); o.y = byte_to_float(v[u], 0x7542u | p);
+                    *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
+                }
             }
         }
     }
     __syncthreads();
 
     // ---- horizontal pass: S -> M --------------------------------------------------------------------
-    {
-        const int half = warp >> 2;
-        const int gb = g0 + half * kGroupsPerHalf;
-        if (gb < n_groups) {
-            const int g = min(gb + lane, n_groups - 1);
-            float cd[kGroup][SPAN];
-            const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+    if (h_active) {
+        const float t_max = __int_as_float(32767);
+        float *mcol = M + half * kHalfW + 4 * lane;
+        for (int row = warp & 3; row < nrows; row += 4) {
+            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
+            const float *sp = S + row * s_pitch + hb + (xs == 1 ? mis : (mis >> 1));
+            float px[SPAN];
 #pragma unroll
-            for (int k = 0; k < kGroup; ++k)
+            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+            float4 o;
+            float *ov = reinterpret_cast<float *>(&o);
 #pragma unroll
-                for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
-            const int b = __ldg(op.hbase + g) - c0;
-            const float t_max = __int_as_float(32767);
-            float *mcol = M + half * kHalfW + 4 * lane;
-            for (int row = warp & 3; row < nrows; row += 4) {
-                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
-                const float *sp = S + row * s_pitch + b + (xs == 1 ? mis : (mis >> 1));
-                float px[SPAN];
+            for (int k = 0; k < kGroup; ++k) {
+                float acc = 0.0f;
 #pragma unroll
-                for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
-                float4 o;
-                float *ov = reinterpret_cast<float *>(&o);
-#pragma unroll
-                for (int k = 0; k < kGroup; ++k) {
-                    float acc = 0.0f;
-#pragma unroll
-                    for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
-                    ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
-                }
-                *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
+                for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
+                ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
             }
+            *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
         }
     }
     __syncthreads();
@@ -300,14 +326,28 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
             const int first = *vp;
             if (next_row < first) { next_row = first; slot = first % VT; }   // steps larger than the ring
             if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, m_col, r0, r1);
-            float g[VT];
+            float gv[VT];
+            if constexpr (VT % 4 == 0) {
 #pragma unroll
-            for (int s = 0; s < VT; ++s) g[s] = cv[s];
+                for (int s = 0; s < VT; s += 4) {
+                    const float4 c4 = *reinterpret_cast<const float4 *>(cv + s);
+                    gv[s] = c4.x; gv[s + 1] = c4.y; gv[s + 2] = c4.z; gv[s + 3] = c4.w;
+                }
+            } else if constexpr (VT % 2 == 0) {
+#pragma unroll
+                for (int s = 0; s < VT; s += 2) {
+                    const float2 c2 = *reinterpret_cast<const float2 *>(cv + s);
+                    gv[s] = c2.x; gv[s + 1] = c2.y;
+                }
+            } else {
+#pragma unroll
+                for (int s = 0; s < VT; ++s) gv[s] = cv[s];
+            }
             const bool aligned = ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0;
-            const unsigned word_a = vertical_quad<VT>(wa, g, v_thr, exact);
+            const unsigned word_a = vertical_quad<VT>(wa, gv, v_thr, exact);
             store_quad(drow, xa, dw, dst_xstep, aligned, word_a);
             if (right) {
-                const unsigned word_b = vertical_quad<VT>(wb, g, v_thr, exact);
+                const unsigned word_b = vertical_quad<VT>(wb, gv, v_thr, exact);
                 store_quad(drow, xb, dw, dst_xstep, aligned, word_b);
             }
         }
@@ -335,6 +375,7 @@ struct FusedOp {
     // offsets (in bytes) into the device blob
     size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vring_off = 0, vring_i_off = 0;
     int vtaps = 0;
+    std::vector<short> tile_c0, tile_nc, tile_r0, tile_r1;
 };
 
 struct FusedPlan {
@@ -435,19 +476,8 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         fo.s_words = (3 + (ncols_max - 1) * op.src_xstep) / 4 + 1;
         fo.s_words_log2 = 0;
         while ((1 << fo.s_words_log2) < fo.s_words) ++fo.s_words_log2;
-        fo.s_pitch = fo.s_words * (4 / op.src_xstep);
-        if ((fo.s_pitch & 31) == 0) fo.s_pitch += 4;   // keep consecutive rows off the same banks
-
-        // vertical coefficients indexed by ring slot
-        std::vector<float> vring(static_cast<size_t>(op.dh) * VT, 0.0f);
-        std::vector<int> vring_i(static_cast<size_t>(op.dh) * VT, 0);
-        for (int y = 0; y < op.dh; ++y)
-            for (int j = 0; j < v.taps; ++j) {
-                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
-                const int slot = (v.pos[y] + j) % VT;
-                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
-                vring_i[static_cast<size_t>(y) * VT + slot] = c;
-            }
+        fo.s_pitch = (fo.s_words * (4 / op.src_xstep) + 3) & ~3;   // rows stay 16-byte aligned
+        if ((fo.s_pitch & 31) == 0) fo.s_pitch += 4;                // keep consecutive rows off the same banks
 
         // tile height: as tall as shared memory allows (less vertical halo), a multiple of the warp count
         auto rows_for = [&](int th, int &tiles_y) {
@@ -468,10 +498,37 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         }
         if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
         fo.th = th;
+        if (fo.tiles_x > kMaxTilesX || fo.tiles_y > kMaxTilesY) { err = "too many tiles for the descriptor table"; delete fp; return nullptr; }
+
+        // vertical coefficients indexed by ring slot, and start rows; both padded to whole tiles so the kernel
+        // can copy a tile's worth without bounds checks
+        const int padded_rows = fo.tiles_y * th;
+        std::vector<float> vring(static_cast<size_t>(padded_rows) * VT, 0.0f);
+        std::vector<int> vring_i(static_cast<size_t>(padded_rows) * VT, 0);
+        std::vector<int> vpos_padded(padded_rows, v.pos[op.dh - 1]);
+        for (int y = 0; y < op.dh; ++y) {
+            vpos_padded[y] = v.pos[y];
+            for (int j = 0; j < v.taps; ++j) {
+                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
+                const int slot = (v.pos[y] + j) % VT;
+                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
+                vring_i[static_cast<size_t>(y) * VT + slot] = c;
+            }
+        }
+        for (int tx = 0; tx < fo.tiles_x; ++tx) {
+            const int ga = tx * 2 * kGroupsPerHalf, gb = std::min(ga + 2 * kGroupsPerHalf - 1, n_groups - 1);
+            fo.tile_c0.push_back(static_cast<short>(hbase[ga]));
+            fo.tile_nc.push_back(static_cast<short>(hbase[gb] + SPAN - hbase[ga]));
+        }
+        for (int ty = 0; ty < fo.tiles_y; ++ty) {
+            const int ya = ty * th, yb = std::min(ya + th, op.dh);
+            fo.tile_r0.push_back(static_cast<short>(v.pos[ya]));
+            fo.tile_r1.push_back(static_cast<short>(std::min(v.pos[yb - 1] + v.taps, op.sh)));
+        }
 
         fo.hdense_off = append(blob, hdense);
         fo.hbase_off = append(blob, hbase);
-        fo.vpos_off = append(blob, v.pos);
+        fo.vpos_off = append(blob, vpos_padded);
         fo.vring_off = append(blob, vring);
         fo.vring_i_off = append(blob, vring_i);
         fp->ops.push_back(fo);
@@ -532,6 +589,10 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             q.vtaps = fo.vtaps;
             q.s_pitch = fo.s_pitch; q.s_words = fo.s_words; q.s_words_log2 = fo.s_words_log2; q.m_rows = fo.m_rows;
             q.v_thr = fo.v_thr;
+            std::copy(fo.tile_c0.begin(), fo.tile_c0.end(), q.tile_c0);
+            std::copy(fo.tile_nc.begin(), fo.tile_nc.end(), q.tile_nc);
+            std::copy(fo.tile_r0.begin(), fo.tile_r0.end(), q.tile_r0);
+            std::copy(fo.tile_r1.begin(), fo.tile_r1.end(), q.tile_r1);
             tiles += fo.tiles_x * fo.tiles_y;
             smem = std::max(smem, fo.smem_bytes);
         }
