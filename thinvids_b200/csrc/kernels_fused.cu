@@ -64,14 +64,25 @@ struct FusedLaunchParams {
     int n_ops;
 };
 
+typedef unsigned long long f32x2;   // two floats in one 64-bit register pair (sm_100 packed FP32 ops)
+
 __device__ __forceinline__ float fma_rm(float a, float b, float c) {
     float d;
     asm("fma.rm.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
     return d;
 }
-__device__ __forceinline__ float fma_rn(float a, float b, float c) {
-    float d;
-    asm("fma.rn.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+__device__ __forceinline__ f32x2 pack2(float lo, float hi) {
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &lo, float &hi) {
+    asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v));
+}
+// FFMA2: one issue slot, two fused multiply-adds (same FMA-pipe time as two FFMAs)
+__device__ __forceinline__ f32x2 fma2(f32x2 a, f32x2 b, f32x2 c) {
+    f32x2 d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
     return d;
 }
 // (sat_u8(hi) << 8 | sat_u8(lo)) | upper << 16
@@ -88,25 +99,33 @@ __device__ __forceinline__ int subnormal_to_int(float v) {
     const int b = __float_as_int(v);
     return b < 0 ? -(b & 0x7fffffff) : b;
 }
-__device__ __forceinline__ float pick(const float4 &v, int k) { return k == 0 ? v.x : k == 1 ? v.y : k == 2 ? v.z : v.w; }
+
+// Four adjacent columns of one intermediate row, as two packed pairs.
+struct Quad { f32x2 lo, hi; };
+__device__ __forceinline__ Quad load_quad(const float *p) {
+    const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(p);
+    return Quad{v.x, v.y};
+}
+__device__ __forceinline__ float quad_elem(const Quad &q, int k) {
+    float a, b;
+    unpack2(k < 2 ? q.lo : q.hi, a, b);
+    return (k & 1) ? b : a;
+}
 
 // Pull intermediate rows [next_row, need_end) into the register rings (left and right half).  Ring slot =
 // row % VT, so the slot a row lands in is a compile-time constant inside each case; the switch enters at the
 // current slot and falls through, which keeps the rings in registers (no dynamic indexing) at the cost of one
-// uniform branch per call.
+// uniform branch per call.  Rows past the tile's last real row are zero-filled in shared memory, so the loads
+// need no guard.
 template <int VT>
-__device__ __forceinline__ void load_ring_rows(float4 (&wa)[VT], float4 (&wb)[VT], int &slot, int &next_row,
-                                               int need_end, const float *m_col, int r0, int r1) {
+__device__ __forceinline__ void load_ring_rows(Quad (&wa)[VT], Quad (&wb)[VT], int &slot, int &next_row,
+                                               int need_end, const float *&mp) {
 #define TVS_RING_CASE(s)                                                                           \
     case s:                                                                                        \
         if constexpr (s < VT) {                                                                    \
-            if (next_row < r1) {                                                                   \
-                const float *m = m_col + (next_row - r0) * kTileW;                                 \
-                wa[s] = *reinterpret_cast<const float4 *>(m);                                      \
-                wb[s] = *reinterpret_cast<const float4 *>(m + kHalfW);                             \
-            } else {                                                                               \
-                wa[s] = wb[s] = make_float4(0.f, 0.f, 0.f, 0.f);                                   \
-            }                                                                                      \
+            wa[s] = load_quad(mp);                                                                 \
+            wb[s] = load_quad(mp + kHalfW);                                                        \
+            mp += kTileW;                                                                          \
             if (++next_row >= need_end) { slot = (s + 1 == VT) ? 0 : s + 1; return; }              \
         }
     for (;;) {
@@ -120,21 +139,22 @@ __device__ __forceinline__ void load_ring_rows(float4 (&wa)[VT], float4 (&wb)[VT
 }
 
 // One output row of 4 columns: float sum, rounded quotient, packed bytes, and the exact redo where needed.
+// `gg` holds each ring coefficient twice, (g, g), so one FFMA2 serves two columns.
 template <int VT>
-__device__ __forceinline__ unsigned vertical_quad(const float4 (&win)[VT], const float (&g)[VT], float v_thr,
+__device__ __forceinline__ unsigned vertical_quad(const Quad (&win)[VT], const f32x2 (&gg)[VT], float v_thr,
                                                   const int *exact_coef) {
-    float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
+    f32x2 a01 = 0ull, a23 = 0ull;
 #pragma unroll
     for (int s = 0; s < VT; ++s) {
-        a0 = fmaf(win[s].x, g[s], a0);
-        a1 = fmaf(win[s].y, g[s], a1);
-        a2 = fmaf(win[s].z, g[s], a2);
-        a3 = fmaf(win[s].w, g[s], a3);
+        a01 = fma2(win[s].lo, gg[s], a01);
+        a23 = fma2(win[s].hi, gg[s], a23);
     }
-    const float q0 = fma_rn(a0, 0x1p-126f, 0.f), q1 = fma_rn(a1, 0x1p-126f, 0.f);
-    const float q2 = fma_rn(a2, 0x1p-126f, 0.f), q3 = fma_rn(a3, 0x1p-126f, 0.f);
-    const float r0 = fmaf(q0, -0x1p126f, a0), r1 = fmaf(q1, -0x1p126f, a1);
-    const float r2 = fmaf(q2, -0x1p126f, a2), r3 = fmaf(q3, -0x1p126f, a3);
+    const f32x2 scale = pack2(0x1p-126f, 0x1p-126f), back = pack2(-0x1p126f, -0x1p126f);
+    const f32x2 q01 = fma2(a01, scale, 0ull), q23 = fma2(a23, scale, 0ull);   // round(acc / 2^19) * 2^-149
+    const f32x2 r01 = fma2(q01, back, a01), r23 = fma2(q23, back, a23);       // exact residual * 2^-42
+    float q0, q1, q2, q3, r0, r1, r2, r3;
+    unpack2(q01, q0, q1); unpack2(q23, q2, q3);
+    unpack2(r01, r0, r1); unpack2(r23, r2, r3);
     unsigned word = pack_sat_u8(__float_as_int(q3), __float_as_int(q2), 0u);
     word = pack_sat_u8(__float_as_int(q1), __float_as_int(q0), word);
     const float worst = fmaxf(fmaxf(fabsf(r0), fabsf(r1)), fmaxf(fabsf(r2), fabsf(r3)));
@@ -146,7 +166,7 @@ __device__ __forceinline__ unsigned vertical_quad(const float4 (&win)[VT], const
             if (fabsf(r[k]) >= v_thr) {
                 int a = 0;
 #pragma unroll
-                for (int s = 0; s < VT; ++s) a += subnormal_to_int(pick(win[s], k)) * __ldg(exact_coef + s);
+                for (int s = 0; s < VT; ++s) a += subnormal_to_int(quad_elem(win[s], k)) * __ldg(exact_coef + s);
                 const unsigned v = static_cast<unsigned>(min(max((a + (1 << 18)) >> 19, 0), 255));
                 word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
             }
@@ -155,25 +175,16 @@ __device__ __forceinline__ unsigned vertical_quad(const float4 (&win)[VT], const
     return word;
 }
 
-__device__ __forceinline__ void store_quad(uint8_t *row, int x, int dw, int xstep, bool aligned, unsigned word) {
-    if (xstep == 1) {
-        if (aligned && x + 3 < dw) {
-            *reinterpret_cast<unsigned *>(row + x) = word;
-        } else {
+__device__ __forceinline__ void store_quad_slow(uint8_t *row, int x, int dw, int xstep, unsigned word) {
 #pragma unroll
-            for (int k = 0; k < 4; ++k)
-                if (x + k < dw) row[x + k] = static_cast<uint8_t>(word >> (8 * k));
-        }
-    } else {
-#pragma unroll
-        for (int k = 0; k < 4; ++k)
-            if (x + k < dw) row[static_cast<ptrdiff_t>(x + k) * xstep] = static_cast<uint8_t>(word >> (8 * k));
-    }
+    for (int k = 0; k < 4; ++k)
+        if (x + k < dw) row[static_cast<ptrdiff_t>(x + k) * xstep] = static_cast<uint8_t>(word >> (8 * k));
 }
 
 template <int SPAN, int VT>
 __global__ void __launch_bounds__(kThreads, 2)
 fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
+    static_assert(SPAN % 2 == 0, "the packed horizontal pass pairs up source samples");
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
 
@@ -185,10 +196,10 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     const int tiles_x = op.tiles_x;
     const int ty = t / tiles_x, tx = t - ty * tiles_x;
     const int f = blockIdx.y;
-    const int th = op.th, dw = op.dw, dh = op.dh, n_groups = op.n_groups;
+    const int th = op.th, dw = op.dw, n_groups = op.n_groups;
 
     const int x0 = tx * kTileW;
-    const int y0 = ty * th, y1 = min(y0 + th, dh);
+    const int y0 = ty * th, y1 = min(y0 + th, op.dh);
     const int g0 = x0 / kGroup;
     const int c0 = op.tile_c0[tx], ncols = op.tile_nc[tx];
     const int r0 = op.tile_r0[ty], r1 = op.tile_r1[ty];
@@ -196,44 +207,48 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     const int s_pitch = op.s_pitch, m_rows = op.m_rows;
     const int xs = op.src_xstep;
 
-    float *M = smem;                                  // [m_rows][256]   intermediate t * 2^-149
-    float *S = M + m_rows * kTileW;                   // [m_rows][s_pitch] source samples as floats
-    float *CV = S + m_rows * s_pitch;                 // [th][VT]        ring-ordered row coefficients
-    int *VP = reinterpret_cast<int *>(CV + th * VT);  // [th]            first source row of each output row
+    float *M = smem;                                        // [m_rows + VT][256] intermediate t * 2^-149
+    float *S = M + (m_rows + VT) * kTileW;                  // [m_rows][s_pitch]  source samples as floats
+    f32x2 *CV = reinterpret_cast<f32x2 *>(S + m_rows * s_pitch);   // [th][VT] ring-ordered (g, g) pairs
+    int *VP = reinterpret_cast<int *>(CV + th * VT);        // [th]               first source row per output row
 
     const uint8_t *src_base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(r0) * op.src_pitch +
                               static_cast<ptrdiff_t>(c0) * xs;
     const ptrdiff_t src_pitch = op.src_pitch;
 
     // ---- issue every global load of the tile up front, then fill shared memory -------------------------
-    // (1) this lane's dense horizontal coefficients (used after the first barrier)
+    // (1) this lane's dense horizontal coefficients, as (c[i], c[i+1]) pairs (used after the first barrier)
     const int half = warp >> 2;
     const int gb = g0 + half * kGroupsPerHalf;
     const bool h_active = gb < n_groups;
     const int g = min(gb + lane, n_groups - 1);
-    float cd[kGroup][SPAN];
+    f32x2 cd[kGroup][SPAN / 2];
     {
         const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+        f32x2 *flat = &cd[0][0];
         if constexpr ((kGroup * SPAN) % 4 == 0) {
-            float *flat = &cd[0][0];
 #pragma unroll
             for (int i = 0; i < kGroup * SPAN / 4; ++i) {
-                const float4 v = __ldg(reinterpret_cast<const float4 *>(hd) + i);
-                flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
+                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(hd) + i);
+                flat[2 * i] = v.x; flat[2 * i + 1] = v.y;
             }
         } else {
 #pragma unroll
-            for (int k = 0; k < kGroup; ++k)
-#pragma unroll
-                for (int i = 0; i < SPAN; ++i) cd[k][i] = __ldg(hd + k * SPAN + i);
+            for (int i = 0; i < kGroup * SPAN / 2; ++i) flat[i] = __ldg(reinterpret_cast<const f32x2 *>(hd) + i);
         }
     }
     const int hb = __ldg(op.hbase + g) - c0;
-    // (2) row coefficients and start rows of this tile (tables are padded to whole tiles on the host)
+    // (2) row coefficients (duplicated into pairs) and start rows of this tile; the tables are padded to whole
+    // tiles on the host
     {
         const float4 *cvg = reinterpret_cast<const float4 *>(op.vring + static_cast<size_t>(y0) * VT);
         const int n4 = th * VT / 4;                   // th is a multiple of 8
-        for (int i = tid; i < n4; i += kThreads) reinterpret_cast<float4 *>(CV)[i] = __ldg(cvg + i);
+        for (int i = tid; i < n4; i += kThreads) {
+            const float4 v = __ldg(cvg + i);
+            ulonglong2 *o = reinterpret_cast<ulonglong2 *>(CV + 4 * i);
+            o[0] = make_ulonglong2(pack2(v.x, v.x), pack2(v.y, v.y));
+            o[1] = make_ulonglong2(pack2(v.z, v.z), pack2(v.w, v.w));
+        }
         for (int i = tid; i < th; i += kThreads) VP[i] = __ldg(op.vpos + y0 + i);
     }
     // (3) the source footprint.  A source row is read as aligned 32-bit words starting at the word that holds
@@ -275,6 +290,9 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                 }
             }
         }
+        // rows the vertical ring may touch beyond the last real row read as zero
+        for (int i = tid; i < VT * (kTileW / 4); i += kThreads)
+            reinterpret_cast<float4 *>(M + nrows * kTileW)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     }
     __syncthreads();
 
@@ -285,17 +303,19 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         for (int row = warp & 3; row < nrows; row += 4) {
             const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
             const float *sp = S + row * s_pitch + hb + (xs == 1 ? mis : (mis >> 1));
-            float px[SPAN];
+            f32x2 px[SPAN / 2];
 #pragma unroll
-            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+            for (int i = 0; i < SPAN / 2; ++i) px[i] = pack2(sp[2 * i], sp[2 * i + 1]);
             float4 o;
             float *ov = reinterpret_cast<float *>(&o);
 #pragma unroll
             for (int k = 0; k < kGroup; ++k) {
-                float acc = 0.0f;
+                f32x2 acc = 0ull;
 #pragma unroll
-                for (int i = 0; i < SPAN; ++i) acc = fmaf(px[i], cd[k][i], acc);
-                ov[k] = fminf(fma_rm(acc, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
+                for (int i = 0; i < SPAN / 2; ++i) acc = fma2(px[i], cd[k][i], acc);
+                float even, odd;
+                unpack2(acc, even, odd);
+                ov[k] = fminf(fma_rm(even + odd, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
             }
             *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
         }
@@ -313,42 +333,43 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         const ptrdiff_t dst_pitch = op.dst_pitch;
         const float v_thr = op.v_thr;
         uint8_t *drow = op.dst + f * op.dst_fstride + static_cast<ptrdiff_t>(ya) * dst_pitch;
+        // 32-bit stores need every row of this tile column to start on a 4-byte boundary
+        const bool word_ok = dst_xstep == 1 && ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0 && (dst_pitch & 3) == 0;
+        const bool fast_a = word_ok && xa + 3 < dw, fast_b = word_ok && xb + 3 < dw;
         const int *exact = op.vring_i + static_cast<size_t>(ya) * VT;
-        const float *cv = CV + (ya - y0) * VT;
+        const f32x2 *cv = CV + (ya - y0) * VT;
         const int *vp = VP + (ya - y0);
         const float *m_col = M + 4 * lane;
-        float4 wa[VT], wb[VT];
+        Quad wa[VT], wb[VT];
 #pragma unroll
-        for (int s = 0; s < VT; ++s) wa[s] = wb[s] = make_float4(0.f, 0.f, 0.f, 0.f);
+        for (int s = 0; s < VT; ++s) wa[s] = wb[s] = Quad{0ull, 0ull};
         int next_row = vp[0];
         int slot = next_row % VT;
+        const float *mp = m_col + (next_row - r0) * kTileW;
         for (int y = ya; y < yb; ++y, drow += dst_pitch, exact += VT, cv += VT, ++vp) {
             const int first = *vp;
-            if (next_row < first) { next_row = first; slot = first % VT; }   // steps larger than the ring
-            if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, m_col, r0, r1);
-            float gv[VT];
-            if constexpr (VT % 4 == 0) {
-#pragma unroll
-                for (int s = 0; s < VT; s += 4) {
-                    const float4 c4 = *reinterpret_cast<const float4 *>(cv + s);
-                    gv[s] = c4.x; gv[s + 1] = c4.y; gv[s + 2] = c4.z; gv[s + 3] = c4.w;
-                }
-            } else if constexpr (VT % 2 == 0) {
+            if (next_row < first) {   // steps larger than the ring: skip rows nobody needs
+                next_row = first; slot = first % VT; mp = m_col + (first - r0) * kTileW;
+            }
+            if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, mp);
+            f32x2 gg[VT];
+            if constexpr (VT % 2 == 0) {
 #pragma unroll
                 for (int s = 0; s < VT; s += 2) {
-                    const float2 c2 = *reinterpret_cast<const float2 *>(cv + s);
-                    gv[s] = c2.x; gv[s + 1] = c2.y;
+                    const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(cv + s);
+                    gg[s] = c2.x; gg[s + 1] = c2.y;
                 }
             } else {
 #pragma unroll
-                for (int s = 0; s < VT; ++s) gv[s] = cv[s];
+                for (int s = 0; s < VT; ++s) gg[s] = cv[s];
             }
-            const bool aligned = ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0;
-            const unsigned word_a = vertical_quad<VT>(wa, gv, v_thr, exact);
-            store_quad(drow, xa, dw, dst_xstep, aligned, word_a);
+            const unsigned word_a = vertical_quad<VT>(wa, gg, v_thr, exact);
+            if (fast_a) *reinterpret_cast<unsigned *>(drow + xa) = word_a;
+            else store_quad_slow(drow, xa, dw, dst_xstep, word_a);
             if (right) {
-                const unsigned word_b = vertical_quad<VT>(wb, gv, v_thr, exact);
-                store_quad(drow, xb, dw, dst_xstep, aligned, word_b);
+                const unsigned word_b = vertical_quad<VT>(wb, gg, v_thr, exact);
+                if (fast_b) *reinterpret_cast<unsigned *>(drow + xb) = word_b;
+                else store_quad_slow(drow, xb, dw, dst_xstep, word_b);
             }
         }
     }
@@ -493,7 +514,8 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         while (th > kWarps && th / 2 >= op.dh) th /= 2;
         for (;; th /= 2) {
             fo.m_rows = rows_for(th, fo.tiles_y);
-            fo.smem_bytes = (static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) + static_cast<size_t>(th) * (VT + 1)) * sizeof(float);
+            fo.smem_bytes = (static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) + static_cast<size_t>(VT) * kTileW +
+                             static_cast<size_t>(th) * (2 * VT + 1)) * sizeof(float);
             if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
         }
         if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
