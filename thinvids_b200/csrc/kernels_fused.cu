@@ -42,12 +42,12 @@ struct FusedOpParams {
     const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
     uint8_t *dst; ptrdiff_t dst_pitch, dst_fstride; int dst_xstep;
     int sw, sh, dw, dh;
-    int th, tiles_x, tile_begin;
+    int th, tiles_x, tiles_y, tile_begin;
     int n_groups;
     const float *hdense;   // [n_groups][4][SPAN]  c * 2^-30, zero outside a column's own window
     const int *hbase;      // [n_groups]           first source column of the group's span
     const int *vpos;       // [dh]
-    const float *vring;    // [dh][VT]             g * 2^107, indexed by ring slot = source_row % VT
+    const float *vring;    // [rows][VT][2]        (g, g) * 2^107, indexed by ring slot = source_row % VT
     const int *vring_i;    // [dh][VT]             the same coefficients as integers (exact path)
     int vtaps;
     int s_pitch;           // floats per staged source row
@@ -62,6 +62,9 @@ struct FusedOpParams {
 struct FusedLaunchParams {
     FusedOpParams op[kMaxFusedOps];
     int n_ops;
+    int tiles_per_frame, total_tiles;
+    // shared-memory layout, sized for the largest plane of the launch (element counts)
+    int m_floats, s_floats, raw_words, cv_pairs, vp_ints;
 };
 
 typedef unsigned long long f32x2;   // two floats in one 64-bit register pair (sm_100 packed FP32 ops)
@@ -181,197 +184,258 @@ __device__ __forceinline__ void store_quad_slow(uint8_t *row, int x, int dw, int
         if (x + k < dw) row[static_cast<ptrdiff_t>(x + k) * xstep] = static_cast<uint8_t>(word >> (8 * k));
 }
 
+__device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"(static_cast<unsigned>(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async16(void *smem_dst, const void *gmem_src) {
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(static_cast<unsigned>(__cvta_generic_to_shared(smem_dst))), "l"(gmem_src));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+__device__ __forceinline__ void cp_async_wait_all() { asm volatile("cp.async.wait_all;" ::: "memory"); }
+
+struct TileCoord { int oi, f, tx, ty; };
+
+__device__ __forceinline__ TileCoord decode_tile(const FusedLaunchParams &P, int tile) {
+    TileCoord c;
+    c.f = tile / P.tiles_per_frame;
+    int rem = tile - c.f * P.tiles_per_frame;
+    c.oi = 0;
+    if (P.n_ops > 1 && rem >= P.op[1].tile_begin) c.oi = 1;
+    if (P.n_ops > 2 && rem >= P.op[2].tile_begin) c.oi = 2;
+    rem -= P.op[c.oi].tile_begin;
+    const int tiles_y = P.op[c.oi].tiles_y;     // tiles of one column are consecutive: they share coefficients and halo rows
+    c.tx = rem / tiles_y;
+    c.ty = rem - c.tx * tiles_y;
+    return c;
+}
+
+// First byte of the tile's source footprint (sample c0 of row r0 of frame f).
+__device__ __forceinline__ const uint8_t *tile_src_base(const FusedOpParams &op, const TileCoord &c) {
+    return op.src + c.f * op.src_fstride + static_cast<ptrdiff_t>(op.tile_r0[c.ty]) * op.src_pitch +
+           static_cast<ptrdiff_t>(op.tile_c0[c.tx]) * op.src_xstep;
+}
+
+// Start the asynchronous copy of everything tile `c` needs from global memory: the raw source footprint (as
+// aligned 32-bit words), the ring-ordered row coefficients and the row start positions.
+template <int VT>
+__device__ __forceinline__ void prefetch_tile(const FusedLaunchParams &P, const TileCoord &c, unsigned *raw, f32x2 *cv,
+                                              int *vp, int tid) {
+    const FusedOpParams &op = P.op[c.oi];
+    const int c0 = op.tile_c0[c.tx], ncols = op.tile_nc[c.tx];
+    const int nrows = op.tile_r1[c.ty] - op.tile_r0[c.ty];
+    const int xs = op.src_xstep;
+    const int nv = min(ncols, op.sw - c0);
+    const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
+    const uint8_t *src_base = tile_src_base(op, c);
+    const ptrdiff_t src_pitch = op.src_pitch;
+    const int total = nrows << wlog;
+    for (int idx = tid; idx < total; idx += kThreads) {
+        const int row = idx >> wlog, w = idx & wmask;
+        const uint8_t *rp = src_base + row * src_pitch;
+        const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
+        const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
+        if (w < nwords) cp_async4(raw + row * s_words + w, rp - mis + 4 * w);
+    }
+    const int y0 = c.ty * op.th;
+    const char *cvg = reinterpret_cast<const char *>(op.vring) + static_cast<size_t>(y0) * VT * sizeof(f32x2);
+    for (int i = tid; i < op.th * VT / 2; i += kThreads) cp_async16(reinterpret_cast<char *>(cv) + 16 * i, cvg + 16 * i);
+    const char *vpg = reinterpret_cast<const char *>(op.vpos + y0);
+    for (int i = tid; i < op.th / 4; i += kThreads) cp_async16(reinterpret_cast<char *>(vp) + 16 * i, vpg + 16 * i);
+    cp_async_commit();
+}
+
+// Persistent kernel: each CTA walks a contiguous range of tiles.  While tile i is filtered, the source bytes and
+// row tables of tile i+1 stream into the other half of a double buffer (cp.async), so no phase waits on HBM.
 template <int SPAN, int VT>
 __global__ void __launch_bounds__(kThreads, 2)
 fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     static_assert(SPAN % 2 == 0, "the packed horizontal pass pairs up source samples");
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-
-    int t = blockIdx.x, oi = 0;
-    if (P.n_ops > 1 && t >= P.op[1].tile_begin) oi = 1;
-    if (P.n_ops > 2 && t >= P.op[2].tile_begin) oi = 2;
-    const FusedOpParams &op = P.op[oi];
-    t -= op.tile_begin;
-    const int tiles_x = op.tiles_x;
-    const int ty = t / tiles_x, tx = t - ty * tiles_x;
-    const int f = blockIdx.y;
-    const int th = op.th, dw = op.dw, n_groups = op.n_groups;
-
-    const int x0 = tx * kTileW;
-    const int y0 = ty * th, y1 = min(y0 + th, op.dh);
-    const int g0 = x0 / kGroup;
-    const int c0 = op.tile_c0[tx], ncols = op.tile_nc[tx];
-    const int r0 = op.tile_r0[ty], r1 = op.tile_r1[ty];
-    const int nrows = r1 - r0;
-    const int s_pitch = op.s_pitch, m_rows = op.m_rows;
-    const int xs = op.src_xstep;
-
-    float *M = smem;                                        // [m_rows + VT][256] intermediate t * 2^-149
-    float *S = M + (m_rows + VT) * kTileW;                  // [m_rows][s_pitch]  source samples as floats
-    f32x2 *CV = reinterpret_cast<f32x2 *>(S + m_rows * s_pitch);   // [th][VT] ring-ordered (g, g) pairs
-    int *VP = reinterpret_cast<int *>(CV + th * VT);        // [th]               first source row per output row
-
-    const uint8_t *src_base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(r0) * op.src_pitch +
-                              static_cast<ptrdiff_t>(c0) * xs;
-    const ptrdiff_t src_pitch = op.src_pitch;
-
-    // ---- issue every global load of the tile up front, then fill shared memory -------------------------
-    // (1) this lane's dense horizontal coefficients, as (c[i], c[i+1]) pairs (used after the first barrier)
     const int half = warp >> 2;
-    const int gb = g0 + half * kGroupsPerHalf;
-    const bool h_active = gb < n_groups;
-    const int g = min(gb + lane, n_groups - 1);
-    f32x2 cd[kGroup][SPAN / 2];
-    {
-        const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
-        f32x2 *flat = &cd[0][0];
-        if constexpr ((kGroup * SPAN) % 4 == 0) {
-#pragma unroll
-            for (int i = 0; i < kGroup * SPAN / 4; ++i) {
-                const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(hd) + i);
-                flat[2 * i] = v.x; flat[2 * i + 1] = v.y;
-            }
-        } else {
-#pragma unroll
-            for (int i = 0; i < kGroup * SPAN / 2; ++i) flat[i] = __ldg(reinterpret_cast<const f32x2 *>(hd) + i);
-        }
-    }
-    const int hb = __ldg(op.hbase + g) - c0;
-    // (2) row coefficients (duplicated into pairs) and start rows of this tile; the tables are padded to whole
-    // tiles on the host
-    {
-        const float4 *cvg = reinterpret_cast<const float4 *>(op.vring + static_cast<size_t>(y0) * VT);
-        const int n4 = th * VT / 4;                   // th is a multiple of 8
-        for (int i = tid; i < n4; i += kThreads) {
-            const float4 v = __ldg(cvg + i);
-            ulonglong2 *o = reinterpret_cast<ulonglong2 *>(CV + 4 * i);
-            o[0] = make_ulonglong2(pack2(v.x, v.x), pack2(v.y, v.y));
-            o[1] = make_ulonglong2(pack2(v.z, v.z), pack2(v.w, v.w));
-        }
-        for (int i = tid; i < th; i += kThreads) VP[i] = __ldg(op.vpos + y0 + i);
-    }
-    // (3) the source footprint.  A source row is read as aligned 32-bit words starting at the word that holds
-    // its first sample; the sample that lands in S[row][j] is therefore sample j - (mis / xs) of the footprint.
-    {
-        const int nv = min(ncols, op.sw - c0);        // samples that exist; the rest carry zero weight
-        const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
-        const int total = nrows << wlog;
-        constexpr int U = 4;
-        for (int base = 0; base < total; base += kThreads * U) {
-            unsigned v[U];
-            unsigned mis_u[U];
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int idx = base + u * kThreads + tid;
-                const int row = idx >> wlog, w = idx & wmask;
-                const uint8_t *rp = src_base + row * src_pitch;
-                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
-                const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
-                mis_u[u] = mis;
-                v[u] = 0;
-                if (idx < total && w < nwords) v[u] = __ldg(reinterpret_cast<const unsigned *>(rp - mis) + w);
-            }
-#pragma unroll
-            for (int u = 0; u < U; ++u) {
-                const int idx = base + u * kThreads + tid;
-                const int row = idx >> wlog, w = idx & wmask;
-                if (idx >= total || w >= s_words) continue;
-                if (xs == 1) {
-                    float4 o;
-                    o.x = byte_to_float(v[u], 0x7540u); o.y = byte_to_float(v[u], 0x7541u);
-                    o.z = byte_to_float(v[u], 0x7542u); o.w = byte_to_float(v[u], 0x7543u);
-                    *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
-                } else {
-                    const unsigned p = mis_u[u] & 1u;
-                    float2 o;
-                    o.x = byte_to_float(v[u], 0x7540u | p); o.y = byte_to_float(v[u], 0x7542u | p);
-                    *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
-                }
-            }
-        }
-        // rows the vertical ring may touch beyond the last real row read as zero
-        for (int i = tid; i < VT * (kTileW / 4); i += kThreads)
-            reinterpret_cast<float4 *>(M + nrows * kTileW)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-    }
-    __syncthreads();
 
-    // ---- horizontal pass: S -> M --------------------------------------------------------------------
-    if (h_active) {
-        const float t_max = __int_as_float(32767);
-        float *mcol = M + half * kHalfW + 4 * lane;
-        for (int row = warp & 3; row < nrows; row += 4) {
-            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
-            const float *sp = S + row * s_pitch + hb + (xs == 1 ? mis : (mis >> 1));
-            f32x2 px[SPAN / 2];
-#pragma unroll
-            for (int i = 0; i < SPAN / 2; ++i) px[i] = pack2(sp[2 * i], sp[2 * i + 1]);
-            float4 o;
-            float *ov = reinterpret_cast<float *>(&o);
-#pragma unroll
-            for (int k = 0; k < kGroup; ++k) {
-                f32x2 acc = 0ull;
-#pragma unroll
-                for (int i = 0; i < SPAN / 2; ++i) acc = fma2(px[i], cd[k][i], acc);
-                float even, odd;
-                unpack2(acc, even, odd);
-                ov[k] = fminf(fma_rm(even + odd, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
-            }
-            *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
-        }
-    }
-    __syncthreads();
+    float *M = smem;                                             // [m_rows + VT][256] intermediate t * 2^-149
+    float *S = M + P.m_floats;                                   // [m_rows][s_pitch]  source samples as floats
+    unsigned *RAW = reinterpret_cast<unsigned *>(S + P.s_floats);   // 2 x [m_rows][s_words] raw source words
+    f32x2 *CVB = reinterpret_cast<f32x2 *>(RAW + 2 * P.raw_words);  // 2 x [th + 1][VT] ring-ordered (g, g) pairs
+    int *VPB = reinterpret_cast<int *>(CVB + 2 * P.cv_pairs);       // 2 x [th]      first source row per output row
 
-    // ---- vertical pass: M -> destination ------------------------------------------------------------
-    {
-        const int strip = th / kWarps;
-        const int ya = y0 + warp * strip, yb = min(ya + strip, y1);
-        if (ya >= yb) return;
-        const bool right = x0 + kHalfW < dw;            // the right half of the last tile may be empty
-        const int xa = x0 + 4 * lane, xb = xa + kHalfW;
-        const int dst_xstep = op.dst_xstep;
-        const ptrdiff_t dst_pitch = op.dst_pitch;
-        const float v_thr = op.v_thr;
-        uint8_t *drow = op.dst + f * op.dst_fstride + static_cast<ptrdiff_t>(ya) * dst_pitch;
-        // 32-bit stores need every row of this tile column to start on a 4-byte boundary
-        const bool word_ok = dst_xstep == 1 && ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0 && (dst_pitch & 3) == 0;
-        const bool fast_a = word_ok && xa + 3 < dw, fast_b = word_ok && xb + 3 < dw;
-        const int *exact = op.vring_i + static_cast<size_t>(ya) * VT;
-        const f32x2 *cv = CV + (ya - y0) * VT;
-        const int *vp = VP + (ya - y0);
-        const float *m_col = M + 4 * lane;
-        Quad wa[VT], wb[VT];
+    // contiguous share of the tile list
+    const int per = P.total_tiles / gridDim.x, extra = P.total_tiles % gridDim.x;
+    const int t_begin = blockIdx.x * per + min(static_cast<int>(blockIdx.x), extra);
+    const int t_end = t_begin + per + (static_cast<int>(blockIdx.x) < extra ? 1 : 0);
+    if (t_begin >= t_end) return;
+
+    f32x2 cd[kGroup][SPAN / 2];      // this lane's dense horizontal coefficients, (c[i], c[i+1]) pairs
+    int hb = 0;                      // first source column of this lane's span
+    bool h_active = false;
+    int cd_oi = -1, cd_tx = -1;
+
+    int buf = 0;
+    TileCoord cur = decode_tile(P, t_begin);
+    prefetch_tile<VT>(P, cur, RAW, CVB, VPB, tid);
+
+    for (int tile = t_begin; tile < t_end; ++tile, buf ^= 1) {
+        const FusedOpParams &op = P.op[cur.oi];
+        cp_async_wait_all();
+        __syncthreads();             // tile's inputs have landed; everyone is done with the previous tile's M / S
+        TileCoord nxt = cur;
+        if (tile + 1 < t_end) {
+            nxt = decode_tile(P, tile + 1);
+            prefetch_tile<VT>(P, nxt, RAW + (buf ^ 1) * P.raw_words, CVB + (buf ^ 1) * P.cv_pairs, VPB + (buf ^ 1) * P.vp_ints, tid);
+        }
+
+        const int th = op.th, dw = op.dw, n_groups = op.n_groups;
+        const int x0 = cur.tx * kTileW;
+        const int y0 = cur.ty * th, y1 = min(y0 + th, op.dh);
+        const int c0 = op.tile_c0[cur.tx], ncols = op.tile_nc[cur.tx];
+        const int r0 = op.tile_r0[cur.ty], r1 = op.tile_r1[cur.ty];
+        const int nrows = r1 - r0;
+        const int s_pitch = op.s_pitch, xs = op.src_xstep;
+        const uint8_t *src_base = tile_src_base(op, cur);
+        const ptrdiff_t src_pitch = op.src_pitch;
+        const unsigned *raw = RAW + buf * P.raw_words;
+        const f32x2 *CV = CVB + buf * P.cv_pairs;
+        const int *VP = VPB + buf * P.vp_ints;
+
+        // ---- a new tile column: fetch this lane's horizontal coefficients (kept across the column's tiles) ----
+        if (cur.oi != cd_oi || cur.tx != cd_tx) {
+            cd_oi = cur.oi; cd_tx = cur.tx;
+            const int gb = x0 / kGroup + half * kGroupsPerHalf;
+            h_active = gb < n_groups;
+            const int g = min(gb + lane, n_groups - 1);
+            const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
+            f32x2 *flat = &cd[0][0];
+            if constexpr ((kGroup * SPAN) % 4 == 0) {
 #pragma unroll
-        for (int s = 0; s < VT; ++s) wa[s] = wb[s] = Quad{0ull, 0ull};
-        int next_row = vp[0];
-        int slot = next_row % VT;
-        const float *mp = m_col + (next_row - r0) * kTileW;
-        for (int y = ya; y < yb; ++y, drow += dst_pitch, exact += VT, cv += VT, ++vp) {
-            const int first = *vp;
-            if (next_row < first) {   // steps larger than the ring: skip rows nobody needs
-                next_row = first; slot = first % VT; mp = m_col + (first - r0) * kTileW;
-            }
-            if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, mp);
-            f32x2 gg[VT];
-            if constexpr (VT % 2 == 0) {
-#pragma unroll
-                for (int s = 0; s < VT; s += 2) {
-                    const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(cv + s);
-                    gg[s] = c2.x; gg[s + 1] = c2.y;
+                for (int i = 0; i < kGroup * SPAN / 4; ++i) {
+                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(hd) + i);
+                    flat[2 * i] = v.x; flat[2 * i + 1] = v.y;
                 }
             } else {
 #pragma unroll
-                for (int s = 0; s < VT; ++s) gg[s] = cv[s];
+                for (int i = 0; i < kGroup * SPAN / 2; ++i) flat[i] = __ldg(reinterpret_cast<const f32x2 *>(hd) + i);
             }
-            const unsigned word_a = vertical_quad<VT>(wa, gg, v_thr, exact);
-            if (fast_a) *reinterpret_cast<unsigned *>(drow + xa) = word_a;
-            else store_quad_slow(drow, xa, dw, dst_xstep, word_a);
-            if (right) {
-                const unsigned word_b = vertical_quad<VT>(wb, gg, v_thr, exact);
-                if (fast_b) *reinterpret_cast<unsigned *>(drow + xb) = word_b;
-                else store_quad_slow(drow, xb, dw, dst_xstep, word_b);
+            hb = __ldg(op.hbase + g) - c0;
+        }
+
+        // ---- raw words -> float samples.  The sample that lands in S[row][j] is sample j - (mis / xs) of the footprint,
+        // where mis is the misalignment of the row's first byte (rows are read as aligned words). ----
+        {
+            const int nv = min(ncols, op.sw - c0);    // samples that exist; the rest carry zero weight
+            const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
+            const int total = nrows << wlog;
+            for (int idx = tid; idx < total; idx += kThreads) {
+                const int row = idx >> wlog, w = idx & wmask;
+                if (w >= s_words) continue;
+                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
+                const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
+                const unsigned v = w < nwords ? raw[row * s_words + w] : 0u;
+                if (xs == 1) {
+                    float4 o;
+                    o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
+                    o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
+                    *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
+                } else {
+                    const unsigned p = mis & 1u;
+                    float2 o;
+                    o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
+                    *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
+                }
+            }
+            // rows the vertical ring may touch beyond the last real row read as zero
+            for (int i = tid; i < VT * (kTileW / 4); i += kThreads)
+                reinterpret_cast<float4 *>(M + nrows * kTileW)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+        __syncthreads();
+
+        // ---- horizontal pass: S -> M ----------------------------------------------------------------
+        if (h_active) {
+            const float t_max = __int_as_float(32767);
+            float *mcol = M + half * kHalfW + 4 * lane;
+            for (int row = warp & 3; row < nrows; row += 4) {
+                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
+                const float *sp = S + row * s_pitch + hb + (xs == 1 ? mis : (mis >> 1));
+                f32x2 px[SPAN / 2];
+#pragma unroll
+                for (int i = 0; i < SPAN / 2; ++i) px[i] = pack2(sp[2 * i], sp[2 * i + 1]);
+                float4 o;
+                float *ov = reinterpret_cast<float *>(&o);
+#pragma unroll
+                for (int k = 0; k < kGroup; ++k) {
+                    f32x2 acc = 0ull;
+#pragma unroll
+                    for (int i = 0; i < SPAN / 2; ++i) acc = fma2(px[i], cd[k][i], acc);
+                    float even, odd;
+                    unpack2(acc, even, odd);
+                    ov[k] = fminf(fma_rm(even + odd, 0x1p-126f, 0.0f), t_max);   // floor(sum / 128), clamped above
+                }
+                *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
             }
         }
+        __syncthreads();
+
+        // ---- vertical pass: M -> destination --------------------------------------------------------
+        const int strip = th / kWarps;
+        const int ya = y0 + warp * strip, yb = min(ya + strip, y1);
+        if (ya < yb) {
+            const bool right = x0 + kHalfW < dw;        // the right half of the last tile may be empty
+            const int xa = x0 + 4 * lane, xb = xa + kHalfW;
+            const int dst_xstep = op.dst_xstep;
+            const ptrdiff_t dst_pitch = op.dst_pitch;
+            const float v_thr = op.v_thr;
+            uint8_t *drow = op.dst + cur.f * op.dst_fstride + static_cast<ptrdiff_t>(ya) * dst_pitch;
+            // 32-bit stores need every row of this tile column to start on a 4-byte boundary
+            const bool word_ok = dst_xstep == 1 && ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0 && (dst_pitch & 3) == 0;
+            const bool fast_a = word_ok && xa + 3 < dw, fast_b = word_ok && xb + 3 < dw;
+            const int *exact = op.vring_i + static_cast<size_t>(ya) * VT;
+            const f32x2 *cv = CV + (ya - y0) * VT;
+            const int *vp = VP + (ya - y0);
+            const float *m_col = M + 4 * lane;
+            Quad wa[VT], wb[VT];
+#pragma unroll
+            for (int s = 0; s < VT; ++s) wa[s] = wb[s] = Quad{0ull, 0ull};
+            int first = vp[0];
+            int next_row = first;
+            int slot = next_row % VT;
+            const float *mp = m_col + (next_row - r0) * kTileW;
+            f32x2 gg[VT];
+#pragma unroll
+            for (int s = 0; s < VT; ++s) gg[s] = cv[s];
+            for (int y = ya; y < yb; ++y, drow += dst_pitch, exact += VT) {
+                // next row's start position and coefficients are requested now and consumed next iteration
+                // (both tables carry one padding row)
+                ++vp; cv += VT;
+                const int first_next = *vp;
+                f32x2 gg_next[VT];
+                if constexpr (VT % 2 == 0) {
+#pragma unroll
+                    for (int s = 0; s < VT; s += 2) {
+                        const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(cv + s);
+                        gg_next[s] = c2.x; gg_next[s + 1] = c2.y;
+                    }
+                } else {
+#pragma unroll
+                    for (int s = 0; s < VT; ++s) gg_next[s] = cv[s];
+                }
+                if (next_row < first) {   // steps larger than the ring: skip rows nobody needs
+                    next_row = first; slot = first % VT; mp = m_col + (first - r0) * kTileW;
+                }
+                if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, mp);
+                const unsigned word_a = vertical_quad<VT>(wa, gg, v_thr, exact);
+                if (fast_a) *reinterpret_cast<unsigned *>(drow + xa) = word_a;
+                else store_quad_slow(drow, xa, dw, dst_xstep, word_a);
+                if (right) {
+                    const unsigned word_b = vertical_quad<VT>(wb, gg, v_thr, exact);
+                    if (fast_b) *reinterpret_cast<unsigned *>(drow + xb) = word_b;
+                    else store_quad_slow(drow, xb, dw, dst_xstep, word_b);
+                }
+                first = first_next;
+#pragma unroll
+                for (int s = 0; s < VT; ++s) gg[s] = gg_next[s];
+            }
+        }
+        cur = nxt;
     }
 }
 
@@ -404,6 +468,7 @@ struct FusedPlan {
     uint8_t *blob = nullptr;
     size_t blob_bytes = 0;
     int device = 0;
+    int sm_count = 148;
 };
 
 namespace {
@@ -414,6 +479,23 @@ size_t append(std::vector<uint8_t> &blob, const std::vector<T> &v) {
     blob.resize(off + v.size() * sizeof(T));
     memcpy(blob.data() + off, v.data(), v.size() * sizeof(T));
     return off;
+}
+
+struct SmemLayout { int m_floats, s_floats, raw_words, cv_pairs, vp_ints; };
+SmemLayout smem_layout(int m_rows, int s_pitch, int s_words, int th, int vt) {
+    SmemLayout l;
+    l.m_floats = (m_rows + vt) * kTileW;
+    l.s_floats = m_rows * s_pitch;
+    l.raw_words = (m_rows * s_words + 3) & ~3;
+    l.cv_pairs = ((th + 1) * vt + 1) & ~1;
+    l.vp_ints = (th + 1 + 3) & ~3;
+    return l;
+}
+size_t layout_bytes(const SmemLayout &l) {
+    return static_cast<size_t>(l.m_floats + l.s_floats + 2 * l.raw_words + 2 * l.vp_ints) * 4 + static_cast<size_t>(2 * l.cv_pairs) * 8;
+}
+size_t fused_smem_bytes(int m_rows, int s_pitch, int s_words, int th, int vt) {
+    return layout_bytes(smem_layout(m_rows, s_pitch, s_words, th, vt));
 }
 
 // Worst-case absolute rounding error of the float vertical sum, in units of the integer sum.
@@ -435,6 +517,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
     std::vector<uint8_t> blob;
     auto fp = new FusedPlan;
     fp->device = device;
+    cudaDeviceGetAttribute(&fp->sm_count, cudaDevAttrMultiProcessorCount, device);
     for (size_t oi = 0; oi < plan.ops.size(); ++oi) {
         const PlaneOp &op = plan.ops[oi];
         if (op.kind != kOpScale) continue;
@@ -511,11 +594,10 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
             return m;
         };
         int th = 128;
-        while (th > kWarps && th / 2 >= op.dh) th /= 2;
-        for (;; th /= 2) {
+        while (th > kWarps && th - kWarps >= op.dh) th -= kWarps;
+        for (;; th -= kWarps) {
             fo.m_rows = rows_for(th, fo.tiles_y);
-            fo.smem_bytes = (static_cast<size_t>(fo.m_rows) * (fo.s_pitch + kTileW) + static_cast<size_t>(VT) * kTileW +
-                             static_cast<size_t>(th) * (2 * VT + 1)) * sizeof(float);
+            fo.smem_bytes = fused_smem_bytes(fo.m_rows, fo.s_pitch, fo.s_words, th, VT);
             if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
         }
         if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
@@ -525,7 +607,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         // vertical coefficients indexed by ring slot, and start rows; both padded to whole tiles so the kernel
         // can copy a tile's worth without bounds checks
         const int padded_rows = fo.tiles_y * th;
-        std::vector<float> vring(static_cast<size_t>(padded_rows) * VT, 0.0f);
+        std::vector<float> vring(static_cast<size_t>(padded_rows) * VT * 2, 0.0f);   // (g, g) pairs
         std::vector<int> vring_i(static_cast<size_t>(padded_rows) * VT, 0);
         std::vector<int> vpos_padded(padded_rows, v.pos[op.dh - 1]);
         for (int y = 0; y < op.dh; ++y) {
@@ -533,7 +615,8 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
             for (int j = 0; j < v.taps; ++j) {
                 const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
                 const int slot = (v.pos[y] + j) % VT;
-                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
+                vring[(static_cast<size_t>(y) * VT + slot) * 2] = vring[(static_cast<size_t>(y) * VT + slot) * 2 + 1] =
+                    std::ldexp(static_cast<float>(c), 107);
                 vring_i[static_cast<size_t>(y) * VT + slot] = c;
             }
         }
@@ -590,7 +673,8 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
         // one launch covers every plane that runs on the same kernel instance
         FusedLaunchParams lp{};
         int tiles = 0;
-        size_t smem = 0;
+        SmemLayout lay{0, 0, 0, 0, 0};
+        const int vt = kInstances[p->ops[i].instance].vt;
         for (size_t j = i; j < p->ops.size() && lp.n_ops < kMaxFusedOps; ++j) {
             const FusedOp &fo = p->ops[j];
             if (done[j] || fo.instance != p->ops[i].instance) continue;
@@ -601,7 +685,7 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             q.src = s.base; q.src_pitch = s.pitch; q.src_fstride = s.frame_stride; q.src_xstep = s.xstep;
             q.dst = d.base; q.dst_pitch = d.pitch; q.dst_fstride = d.frame_stride; q.dst_xstep = d.xstep;
             q.sw = op.sw; q.sh = op.sh; q.dw = op.dw; q.dh = op.dh;
-            q.th = fo.th; q.tiles_x = fo.tiles_x; q.tile_begin = tiles;
+            q.th = fo.th; q.tiles_x = fo.tiles_x; q.tiles_y = fo.tiles_y; q.tile_begin = tiles;
             q.n_groups = fo.n_groups;
             q.hdense = reinterpret_cast<const float *>(p->blob + fo.hdense_off);
             q.hbase = reinterpret_cast<const int *>(p->blob + fo.hbase_off);
@@ -616,9 +700,20 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             std::copy(fo.tile_r0.begin(), fo.tile_r0.end(), q.tile_r0);
             std::copy(fo.tile_r1.begin(), fo.tile_r1.end(), q.tile_r1);
             tiles += fo.tiles_x * fo.tiles_y;
-            smem = std::max(smem, fo.smem_bytes);
+            const SmemLayout l = smem_layout(fo.m_rows, fo.s_pitch, fo.s_words, fo.th, vt);
+            lay.m_floats = std::max(lay.m_floats, l.m_floats);
+            lay.s_floats = std::max(lay.s_floats, l.s_floats);
+            lay.raw_words = std::max(lay.raw_words, l.raw_words);
+            lay.cv_pairs = std::max(lay.cv_pairs, l.cv_pairs);
+            lay.vp_ints = std::max(lay.vp_ints, l.vp_ints);
         }
-        const dim3 grid(tiles, n_frames);
+        lp.tiles_per_frame = tiles;
+        lp.total_tiles = tiles * n_frames;
+        lp.m_floats = lay.m_floats; lp.s_floats = lay.s_floats; lp.raw_words = lay.raw_words;
+        lp.cv_pairs = lay.cv_pairs; lp.vp_ints = lay.vp_ints;
+        const size_t smem = layout_bytes(lay);
+        // persistent CTAs: two per SM, each walking a contiguous share of the tiles
+        const int grid = std::min(lp.total_tiles, 2 * p->sm_count);
         kInstances[p->ops[i].instance].fn<<<grid, kThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
         ++launched;
