@@ -21,6 +21,7 @@
 // 8 samples per lane per row; row coefficients and start rows come from a shared-memory copy.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "tvs_internal.h"
@@ -65,6 +66,7 @@ struct FusedLaunchParams {
     int tiles_per_frame, total_tiles;
     // shared-memory layout, sized for the largest plane of the launch (element counts)
     int m_floats, s_floats, raw_words, cv_pairs, vp_ints;
+    int debug_skip;   // profiling aid (TVS_DEBUG_SKIP): bit 0 skips the conversion, bit 1 the H pass, bit 2 the V pass
 };
 
 typedef unsigned long long f32x2;   // two floats in one 64-bit register pair (sm_100 packed FP32 ops)
@@ -141,47 +143,157 @@ __device__ __forceinline__ void load_ring_rows(Quad (&wa)[VT], Quad (&wb)[VT], i
 #undef TVS_RING_CASE
 }
 
-// One output row of 4 columns: float sum, rounded quotient, packed bytes, and the exact redo where needed.
-// `gg` holds each ring coefficient twice, (g, g), so one FFMA2 serves two columns.
+// Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary.
+// Rare (about one warp-row in fifty), so it re-reads its VT intermediate rows from shared memory instead of
+// keeping the register ring alive across a call.  `m_first` points at this quad's columns in row `first`.
 template <int VT>
-__device__ __forceinline__ unsigned vertical_quad(const Quad (&win)[VT], const f32x2 (&gg)[VT], float v_thr,
-                                                  const int *exact_coef) {
-    f32x2 a01 = 0ull, a23 = 0ull;
-#pragma unroll
-    for (int s = 0; s < VT; ++s) {
-        a01 = fma2(win[s].lo, gg[s], a01);
-        a23 = fma2(win[s].hi, gg[s], a23);
+__device__ __noinline__ unsigned exact_fixup(const float *m_first, int first, const int *exact_coef, float v_thr,
+                                             float r0, float r1, float r2, float r3, unsigned word) {
+    const float r[4] = {r0, r1, r2, r3};
+    int slot = first % VT;
+    int a[4] = {0, 0, 0, 0};
+    for (int j = 0; j < VT; ++j) {
+        const float4 t = *reinterpret_cast<const float4 *>(m_first + j * kTileW);
+        const int c = __ldg(exact_coef + slot);
+        a[0] += subnormal_to_int(t.x) * c; a[1] += subnormal_to_int(t.y) * c;
+        a[2] += subnormal_to_int(t.z) * c; a[3] += subnormal_to_int(t.w) * c;
+        slot = slot + 1 == VT ? 0 : slot + 1;
     }
-    const f32x2 scale = pack2(0x1p-126f, 0x1p-126f), back = pack2(-0x1p126f, -0x1p126f);
-    const f32x2 q01 = fma2(a01, scale, 0ull), q23 = fma2(a23, scale, 0ull);   // round(acc / 2^19) * 2^-149
-    const f32x2 r01 = fma2(q01, back, a01), r23 = fma2(q23, back, a23);       // exact residual * 2^-42
-    float q0, q1, q2, q3, r0, r1, r2, r3;
-    unpack2(q01, q0, q1); unpack2(q23, q2, q3);
-    unpack2(r01, r0, r1); unpack2(r23, r2, r3);
-    unsigned word = pack_sat_u8(__float_as_int(q3), __float_as_int(q2), 0u);
-    word = pack_sat_u8(__float_as_int(q1), __float_as_int(q0), word);
-    const float worst = fmaxf(fmaxf(fabsf(r0), fabsf(r1)), fmaxf(fabsf(r2), fabsf(r3)));
-    if (worst >= v_thr) {
-        // within the float error band of a rounding boundary: redo those samples in int32
-        const float r[4] = {r0, r1, r2, r3};
 #pragma unroll
-        for (int k = 0; k < 4; ++k) {
-            if (fabsf(r[k]) >= v_thr) {
-                int a = 0;
-#pragma unroll
-                for (int s = 0; s < VT; ++s) a += subnormal_to_int(quad_elem(win[s], k)) * __ldg(exact_coef + s);
-                const unsigned v = static_cast<unsigned>(min(max((a + (1 << 18)) >> 19, 0), 255));
-                word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
-            }
+    for (int k = 0; k < 4; ++k) {
+        if (fabsf(r[k]) >= v_thr) {
+            const unsigned v = static_cast<unsigned>(min(max((a[k] + (1 << 18)) >> 19, 0), 255));
+            word = (word & ~(0xffu << (8 * k))) | (v << (8 * k));
         }
     }
     return word;
+}
+
+// One output row, 4 + 4 columns (left and right half of the tile): float sums, rounded quotients, packed bytes.
+// `gg` holds each ring coefficient twice, (g, g), so one FFMA2 serves two columns.  The four accumulator chains
+// are independent, which is what hides the FMA latency at 4 warps per scheduler.
+template <int VT, bool RIGHT>
+__device__ __forceinline__ void vertical_row(const Quad (&wa)[VT], const Quad (&wb)[VT], const f32x2 (&gg)[VT], float v_thr,
+                                             const int *exact_coef, const float *m_first, int first, unsigned &word_a,
+                                             unsigned &word_b) {
+    f32x2 a01 = 0ull, a23 = 0ull, b01 = 0ull, b23 = 0ull;
+#pragma unroll
+    for (int s = 0; s < VT; ++s) {
+        a01 = fma2(wa[s].lo, gg[s], a01);
+        a23 = fma2(wa[s].hi, gg[s], a23);
+        if (RIGHT) {
+            b01 = fma2(wb[s].lo, gg[s], b01);
+            b23 = fma2(wb[s].hi, gg[s], b23);
+        }
+    }
+    const f32x2 scale = pack2(0x1p-126f, 0x1p-126f), back = pack2(-0x1p126f, -0x1p126f);
+    // q = round(acc / 2^19) * 2^-149 (an integer bit pattern); r = exact residual * 2^-42
+    const f32x2 qa01 = fma2(a01, scale, 0ull), qa23 = fma2(a23, scale, 0ull);
+    const f32x2 ra01 = fma2(qa01, back, a01), ra23 = fma2(qa23, back, a23);
+    float q0, q1, q2, q3, r0, r1, r2, r3;
+    unpack2(qa01, q0, q1); unpack2(qa23, q2, q3);
+    unpack2(ra01, r0, r1); unpack2(ra23, r2, r3);
+    word_a = pack_sat_u8(__float_as_int(q3), __float_as_int(q2), 0u);
+    word_a = pack_sat_u8(__float_as_int(q1), __float_as_int(q0), word_a);
+    float worst = fmaxf(fmaxf(fabsf(r0), fabsf(r1)), fmaxf(fabsf(r2), fabsf(r3)));
+    float s0 = 0.f, s1 = 0.f, s2 = 0.f, s3 = 0.f;
+    if (RIGHT) {
+        const f32x2 qb01 = fma2(b01, scale, 0ull), qb23 = fma2(b23, scale, 0ull);
+        const f32x2 rb01 = fma2(qb01, back, b01), rb23 = fma2(qb23, back, b23);
+        unpack2(qb01, q0, q1); unpack2(qb23, q2, q3);
+        unpack2(rb01, s0, s1); unpack2(rb23, s2, s3);
+        word_b = pack_sat_u8(__float_as_int(q3), __float_as_int(q2), 0u);
+        word_b = pack_sat_u8(__float_as_int(q1), __float_as_int(q0), word_b);
+        worst = fmaxf(worst, fmaxf(fmaxf(fabsf(s0), fabsf(s1)), fmaxf(fabsf(s2), fabsf(s3))));
+    }
+    if (worst >= v_thr) {
+        word_a = exact_fixup<VT>(m_first, first, exact_coef, v_thr, r0, r1, r2, r3, word_a);
+        if (RIGHT) word_b = exact_fixup<VT>(m_first + kHalfW, first, exact_coef, v_thr, s0, s1, s2, s3, word_b);
+    }
 }
 
 __device__ __forceinline__ void store_quad_slow(uint8_t *row, int x, int dw, int xstep, unsigned word) {
 #pragma unroll
     for (int k = 0; k < 4; ++k)
         if (x + k < dw) row[static_cast<ptrdiff_t>(x + k) * xstep] = static_cast<uint8_t>(word >> (8 * k));
+}
+
+// Vertical pass of one warp over its strip of output rows [ya, yb).
+// MODE 0: the tile is full width and every destination row starts on a 4-byte boundary: each quad is one 32-bit
+// store and nothing is predicated.  MODE 1: the same for a tile whose right half is empty.  MODE 2: anything
+// else (partial quads, interleaved chroma, unaligned rows): bounds-checked byte stores.
+enum { kStoreBoth = 0, kStoreLeft = 1, kStoreGeneric = 2 };
+
+template <int VT>
+__device__ __forceinline__ void load_row_coefs(f32x2 (&gg)[VT], const f32x2 *cv) {
+    if constexpr (VT % 2 == 0) {
+#pragma unroll
+        for (int s = 0; s < VT; s += 2) {
+            const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(cv + s);
+            gg[s] = c2.x; gg[s + 1] = c2.y;
+        }
+    } else {
+#pragma unroll
+        for (int s = 0; s < VT; ++s) gg[s] = cv[s];
+    }
+}
+
+template <int VT, int MODE>
+__device__ __forceinline__ void vertical_strip(const float *M, const f32x2 *cv, const int *vp, const int *exact, int r0,
+                                               int ya, int yb, uint8_t *drow, ptrdiff_t dst_pitch, int dst_xstep, int dw,
+                                               int xa, bool right, float v_thr, int lane) {
+    const int xb = xa + kHalfW;
+    const float *m_col = M + 4 * lane;
+    Quad wa[VT], wb[VT];
+#pragma unroll
+    for (int s = 0; s < VT; ++s) wa[s] = wb[s] = Quad{0ull, 0ull};
+    int next_row = vp[0];
+    int slot = next_row % VT;
+    const float *mp = m_col + (next_row - r0) * kTileW;
+
+    // one output row; `gg` are this row's coefficients, `first` its first source row
+    auto emit = [&](const f32x2 (&gg)[VT], int first) {
+        if (next_row < first) {   // steps larger than the ring: skip rows nobody needs
+            next_row = first; slot = first % VT; mp = m_col + (first - r0) * kTileW;
+        }
+        if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, mp);
+        const float *m_first = m_col + (first - r0) * kTileW;
+        unsigned word_a, word_b = 0;
+        if (MODE == kStoreBoth) {
+            vertical_row<VT, true>(wa, wb, gg, v_thr, exact, m_first, first, word_a, word_b);
+            *reinterpret_cast<unsigned *>(drow + xa) = word_a;
+            *reinterpret_cast<unsigned *>(drow + xb) = word_b;
+        } else if (MODE == kStoreLeft) {
+            vertical_row<VT, false>(wa, wb, gg, v_thr, exact, m_first, first, word_a, word_b);
+            *reinterpret_cast<unsigned *>(drow + xa) = word_a;
+        } else if (right) {
+            vertical_row<VT, true>(wa, wb, gg, v_thr, exact, m_first, first, word_a, word_b);
+            store_quad_slow(drow, xa, dw, dst_xstep, word_a);
+            store_quad_slow(drow, xb, dw, dst_xstep, word_b);
+        } else {
+            vertical_row<VT, false>(wa, wb, gg, v_thr, exact, m_first, first, word_a, word_b);
+            store_quad_slow(drow, xa, dw, dst_xstep, word_a);
+        }
+        drow += dst_pitch;
+        exact += VT;
+    };
+
+    // Rows are taken two at a time so that each row's start position and coefficients are requested one row
+    // ahead of their use without register-to-register copies (both tables carry a padding row).
+    f32x2 g0[VT], g1[VT];
+    load_row_coefs<VT>(g0, cv);
+    int f0 = vp[0];
+    int y = ya;
+    for (; y + 1 < yb; y += 2) {
+        load_row_coefs<VT>(g1, cv + VT);
+        const int f1 = vp[1];
+        emit(g0, f0);
+        cv += 2 * VT; vp += 2;
+        load_row_coefs<VT>(g0, cv);
+        f0 = vp[0];
+        emit(g1, f1);
+    }
+    if (y < yb) emit(g0, f0);
 }
 
 __device__ __forceinline__ void cp_async4(void *smem_dst, const void *gmem_src) {
@@ -216,32 +328,57 @@ __device__ __forceinline__ const uint8_t *tile_src_base(const FusedOpParams &op,
 }
 
 // Start the asynchronous copy of everything tile `c` needs from global memory: the raw source footprint (as
-// aligned 32-bit words), the ring-ordered row coefficients and the row start positions.
+// aligned 32-bit words; words past the end of a row are zeroed here), the ring-ordered row coefficients and the
+// row start positions.  Rows are read as aligned words starting at the word that holds their first sample, so
+// the sample that ends up at word-relative position j is sample j - mis / xs of the footprint, mis being the
+// misalignment of the row's first byte.
 template <int VT>
 __device__ __forceinline__ void prefetch_tile(const FusedLaunchParams &P, const TileCoord &c, unsigned *raw, f32x2 *cv,
                                               int *vp, int tid) {
     const FusedOpParams &op = P.op[c.oi];
-    const int c0 = op.tile_c0[c.tx], ncols = op.tile_nc[c.tx];
+    const int c0 = op.tile_c0[c.tx];
     const int nrows = op.tile_r1[c.ty] - op.tile_r0[c.ty];
     const int xs = op.src_xstep;
-    const int nv = min(ncols, op.sw - c0);
-    const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
+    const int span_bytes = (min(static_cast<int>(op.tile_nc[c.tx]), op.sw - c0) - 1) * xs;   // offset of the last existing sample
+    const int wlog = min(op.s_words_log2, 8), wmask = (1 << wlog) - 1, s_words = op.s_words;
     const uint8_t *src_base = tile_src_base(op, c);
+    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base)) & 3u;
+    const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 3u;
     const ptrdiff_t src_pitch = op.src_pitch;
-    const int total = nrows << wlog;
-    for (int idx = tid; idx < total; idx += kThreads) {
-        const int row = idx >> wlog, w = idx & wmask;
-        const uint8_t *rp = src_base + row * src_pitch;
-        const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rp)) & 3u;
-        const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
-        if (w < nwords) cp_async4(raw + row * s_words + w, rp - mis + 4 * w);
+    // 256 threads cover 256 >> wlog rows per pass; a thread keeps its word index and steps down the rows
+    const int rstep = kThreads >> wlog;
+    for (int w = tid & wmask; w < s_words; w += 1 << wlog) {   // one pass unless a row is longer than 256 words
+        int row = tid >> wlog;
+        unsigned *dst = raw + row * s_words + w;
+        const uint8_t *src = src_base + row * src_pitch + 4 * w;
+        const int limit = span_bytes - 4 * w;          // the word holds data iff mis + limit >= 0
+        unsigned mis = (mis0 + row * pmod) & 3u;
+        const unsigned mstep = (rstep * pmod) & 3u;
+        for (; row < nrows; row += rstep, dst += rstep * s_words, src += rstep * src_pitch, mis = (mis + mstep) & 3u) {
+            if (static_cast<int>(mis) + limit >= 0) cp_async4(dst, src - mis);
+            else *dst = 0u;
+        }
     }
     const int y0 = c.ty * op.th;
     const char *cvg = reinterpret_cast<const char *>(op.vring) + static_cast<size_t>(y0) * VT * sizeof(f32x2);
     for (int i = tid; i < op.th * VT / 2; i += kThreads) cp_async16(reinterpret_cast<char *>(cv) + 16 * i, cvg + 16 * i);
     const char *vpg = reinterpret_cast<const char *>(op.vpos + y0);
     for (int i = tid; i < op.th / 4; i += kThreads) cp_async16(reinterpret_cast<char *>(vp) + 16 * i, vpg + 16 * i);
-    cp_async_commit();
+}
+
+// Horizontal coefficients of the 64 column groups of tile column `tx` (2 halves x 32 lanes), laid out so that a
+// warp's 128-bit reads are conflict free: CD[(half * N4 + i) * 32 + lane] as 16-byte units, N4 = 4 * SPAN / 4.
+template <int SPAN>
+__device__ __forceinline__ void prefetch_hcoef(const FusedOpParams &op, int tx, float4 *cd, int *hb, int tid) {
+    constexpr int N4 = kGroup * SPAN / 4;
+    const int g0 = tx * 2 * kGroupsPerHalf;
+    for (int i = tid; i < 2 * kGroupsPerHalf * N4; i += kThreads) {
+        const int grp = i / N4, part = i - grp * N4;     // consecutive threads read consecutive 16-byte pieces
+        const int g = min(g0 + grp, op.n_groups - 1);
+        const int half = grp >> 5, ln = grp & 31;
+        cp_async16(cd + (half * N4 + part) * 32 + ln, op.hdense + static_cast<size_t>(g) * (kGroup * SPAN) + 4 * part);
+    }
+    if (tid < 2 * kGroupsPerHalf) hb[tid] = __ldg(op.hbase + min(g0 + tid, op.n_groups - 1)) - op.tile_c0[tx];
 }
 
 // Persistent kernel: each CTA walks a contiguous range of tiles.  While tile i is filtered, the source bytes and
@@ -250,6 +387,7 @@ template <int SPAN, int VT>
 __global__ void __launch_bounds__(kThreads, 2)
 fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     static_assert(SPAN % 2 == 0, "the packed horizontal pass pairs up source samples");
+    constexpr int N4 = kGroup * SPAN / 4;
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int half = warp >> 2;
@@ -258,7 +396,9 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     float *S = M + P.m_floats;                                   // [m_rows][s_pitch]  source samples as floats
     unsigned *RAW = reinterpret_cast<unsigned *>(S + P.s_floats);   // 2 x [m_rows][s_words] raw source words
     f32x2 *CVB = reinterpret_cast<f32x2 *>(RAW + 2 * P.raw_words);  // 2 x [th + 1][VT] ring-ordered (g, g) pairs
-    int *VPB = reinterpret_cast<int *>(CVB + 2 * P.cv_pairs);       // 2 x [th]      first source row per output row
+    int *VPB = reinterpret_cast<int *>(CVB + 2 * P.cv_pairs);       // 2 x [th + 1]  first source row per output row
+    float4 *CD = reinterpret_cast<float4 *>(VPB + 2 * P.vp_ints);   // [2][N4][32]   horizontal coefficients of the column
+    int *HB = reinterpret_cast<int *>(CD + 2 * N4 * 32);            // [64]          span start of each column group
 
     // contiguous share of the tile list
     const int per = P.total_tiles / gridDim.x, extra = P.total_tiles % gridDim.x;
@@ -266,81 +406,59 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     const int t_end = t_begin + per + (static_cast<int>(blockIdx.x) < extra ? 1 : 0);
     if (t_begin >= t_end) return;
 
-    f32x2 cd[kGroup][SPAN / 2];      // this lane's dense horizontal coefficients, (c[i], c[i+1]) pairs
-    int hb = 0;                      // first source column of this lane's span
-    bool h_active = false;
-    int cd_oi = -1, cd_tx = -1;
-
     int buf = 0;
     TileCoord cur = decode_tile(P, t_begin);
     prefetch_tile<VT>(P, cur, RAW, CVB, VPB, tid);
+    prefetch_hcoef<SPAN>(P.op[cur.oi], cur.tx, CD, HB, tid);
+    cp_async_commit();
 
     for (int tile = t_begin; tile < t_end; ++tile, buf ^= 1) {
         const FusedOpParams &op = P.op[cur.oi];
         cp_async_wait_all();
-        __syncthreads();             // tile's inputs have landed; everyone is done with the previous tile's M / S
+        __syncthreads();             // this tile's inputs have landed; everyone is done with the previous tile's M / S
         TileCoord nxt = cur;
-        if (tile + 1 < t_end) {
+        const bool more = tile + 1 < t_end;
+        if (more) {
             nxt = decode_tile(P, tile + 1);
             prefetch_tile<VT>(P, nxt, RAW + (buf ^ 1) * P.raw_words, CVB + (buf ^ 1) * P.cv_pairs, VPB + (buf ^ 1) * P.vp_ints, tid);
+            cp_async_commit();
         }
 
-        const int th = op.th, dw = op.dw, n_groups = op.n_groups;
+        const int th = op.th, dw = op.dw;
         const int x0 = cur.tx * kTileW;
         const int y0 = cur.ty * th, y1 = min(y0 + th, op.dh);
-        const int c0 = op.tile_c0[cur.tx], ncols = op.tile_nc[cur.tx];
-        const int r0 = op.tile_r0[cur.ty], r1 = op.tile_r1[cur.ty];
-        const int nrows = r1 - r0;
+        const int r0 = op.tile_r0[cur.ty];
+        const int nrows = op.tile_r1[cur.ty] - r0;
         const int s_pitch = op.s_pitch, xs = op.src_xstep;
-        const uint8_t *src_base = tile_src_base(op, cur);
-        const ptrdiff_t src_pitch = op.src_pitch;
+        const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(tile_src_base(op, cur))) & 3u;
+        const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 3u;
         const unsigned *raw = RAW + buf * P.raw_words;
-        const f32x2 *CV = CVB + buf * P.cv_pairs;
-        const int *VP = VPB + buf * P.vp_ints;
 
-        // ---- a new tile column: fetch this lane's horizontal coefficients (kept across the column's tiles) ----
-        if (cur.oi != cd_oi || cur.tx != cd_tx) {
-            cd_oi = cur.oi; cd_tx = cur.tx;
-            const int gb = x0 / kGroup + half * kGroupsPerHalf;
-            h_active = gb < n_groups;
-            const int g = min(gb + lane, n_groups - 1);
-            const float *hd = op.hdense + static_cast<size_t>(g) * (kGroup * SPAN);
-            f32x2 *flat = &cd[0][0];
-            if constexpr ((kGroup * SPAN) % 4 == 0) {
-#pragma unroll
-                for (int i = 0; i < kGroup * SPAN / 4; ++i) {
-                    const ulonglong2 v = __ldg(reinterpret_cast<const ulonglong2 *>(hd) + i);
-                    flat[2 * i] = v.x; flat[2 * i + 1] = v.y;
-                }
-            } else {
-#pragma unroll
-                for (int i = 0; i < kGroup * SPAN / 2; ++i) flat[i] = __ldg(reinterpret_cast<const f32x2 *>(hd) + i);
-            }
-            hb = __ldg(op.hbase + g) - c0;
-        }
-
-        // ---- raw words -> float samples.  The sample that lands in S[row][j] is sample j - (mis / xs) of the footprint,
-        // where mis is the misalignment of the row's first byte (rows are read as aligned words). ----
-        {
-            const int nv = min(ncols, op.sw - c0);    // samples that exist; the rest carry zero weight
-            const int wlog = op.s_words_log2, wmask = (1 << wlog) - 1, s_words = op.s_words;
-            const int total = nrows << wlog;
-            for (int idx = tid; idx < total; idx += kThreads) {
-                const int row = idx >> wlog, w = idx & wmask;
-                if (w >= s_words) continue;
-                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
-                const int nwords = (static_cast<int>(mis) + (nv - 1) * xs) / 4 + 1;
-                const unsigned v = w < nwords ? raw[row * s_words + w] : 0u;
+        // ---- raw words -> float samples ----
+        if (!(P.debug_skip & 1)) {
+            const int wlog = min(op.s_words_log2, 8), wmask = (1 << wlog) - 1, s_words = op.s_words;
+            const int rstep = kThreads >> wlog;
+            for (int w = tid & wmask; w < s_words; w += 1 << wlog) {
+                int row = tid >> wlog;
+                const unsigned *rw = raw + row * s_words + w;
                 if (xs == 1) {
-                    float4 o;
-                    o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
-                    o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
-                    *reinterpret_cast<float4 *>(S + row * s_pitch + 4 * w) = o;
+                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + w;
+                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * (s_pitch / 4)) {
+                        const unsigned v = *rw;
+                        float4 o;
+                        o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
+                        o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
+                        *out = o;
+                    }
                 } else {
-                    const unsigned p = mis & 1u;
-                    float2 o;
-                    o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
-                    *reinterpret_cast<float2 *>(S + row * s_pitch + 2 * w) = o;
+                    float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
+                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * (s_pitch / 2)) {
+                        const unsigned p = (mis0 + row * pmod) & 1u;
+                        const unsigned v = *rw;
+                        float2 o;
+                        o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
+                        *out = o;
+                    }
                 }
             }
             // rows the vertical ring may touch beyond the last real row read as zero
@@ -350,11 +468,21 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         __syncthreads();
 
         // ---- horizontal pass: S -> M ----------------------------------------------------------------
-        if (h_active) {
+        if (x0 + half * kHalfW < dw && !(P.debug_skip & 2)) {
+            f32x2 cd[kGroup][SPAN / 2];      // this lane's dense coefficients, (c[i], c[i+1]) pairs
+            {
+                f32x2 *flat = &cd[0][0];
+#pragma unroll
+                for (int i = 0; i < N4; ++i) {
+                    const ulonglong2 v = *reinterpret_cast<const ulonglong2 *>(CD + (half * N4 + i) * 32 + lane);
+                    flat[2 * i] = v.x; flat[2 * i + 1] = v.y;
+                }
+            }
+            const int hb = HB[half * kGroupsPerHalf + lane];
             const float t_max = __int_as_float(32767);
             float *mcol = M + half * kHalfW + 4 * lane;
             for (int row = warp & 3; row < nrows; row += 4) {
-                const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base + row * src_pitch)) & 3u;
+                const unsigned mis = (mis0 + row * pmod) & 3u;
                 const float *sp = S + row * s_pitch + hb + (xs == 1 ? mis : (mis >> 1));
                 f32x2 px[SPAN / 2];
 #pragma unroll
@@ -375,65 +503,31 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         }
         __syncthreads();
 
+        // the next tile starts a new column: its horizontal coefficients can stream in under the vertical pass
+        if (more && (nxt.oi != cur.oi || nxt.tx != cur.tx)) {
+            prefetch_hcoef<SPAN>(P.op[nxt.oi], nxt.tx, CD, HB, tid);
+            cp_async_commit();
+        }
+
         // ---- vertical pass: M -> destination --------------------------------------------------------
         const int strip = th / kWarps;
         const int ya = y0 + warp * strip, yb = min(ya + strip, y1);
-        if (ya < yb) {
-            const bool right = x0 + kHalfW < dw;        // the right half of the last tile may be empty
-            const int xa = x0 + 4 * lane, xb = xa + kHalfW;
+        if (ya < yb && !(P.debug_skip & 4)) {
             const int dst_xstep = op.dst_xstep;
             const ptrdiff_t dst_pitch = op.dst_pitch;
-            const float v_thr = op.v_thr;
             uint8_t *drow = op.dst + cur.f * op.dst_fstride + static_cast<ptrdiff_t>(ya) * dst_pitch;
-            // 32-bit stores need every row of this tile column to start on a 4-byte boundary
-            const bool word_ok = dst_xstep == 1 && ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0 && (dst_pitch & 3) == 0;
-            const bool fast_a = word_ok && xa + 3 < dw, fast_b = word_ok && xb + 3 < dw;
+            const bool words = dst_xstep == 1 && (dst_pitch & 3) == 0 && ((reinterpret_cast<uintptr_t>(drow) + x0) & 3u) == 0;
             const int *exact = op.vring_i + static_cast<size_t>(ya) * VT;
-            const f32x2 *cv = CV + (ya - y0) * VT;
-            const int *vp = VP + (ya - y0);
-            const float *m_col = M + 4 * lane;
-            Quad wa[VT], wb[VT];
-#pragma unroll
-            for (int s = 0; s < VT; ++s) wa[s] = wb[s] = Quad{0ull, 0ull};
-            int first = vp[0];
-            int next_row = first;
-            int slot = next_row % VT;
-            const float *mp = m_col + (next_row - r0) * kTileW;
-            f32x2 gg[VT];
-#pragma unroll
-            for (int s = 0; s < VT; ++s) gg[s] = cv[s];
-            for (int y = ya; y < yb; ++y, drow += dst_pitch, exact += VT) {
-                // next row's start position and coefficients are requested now and consumed next iteration
-                // (both tables carry one padding row)
-                ++vp; cv += VT;
-                const int first_next = *vp;
-                f32x2 gg_next[VT];
-                if constexpr (VT % 2 == 0) {
-#pragma unroll
-                    for (int s = 0; s < VT; s += 2) {
-                        const ulonglong2 c2 = *reinterpret_cast<const ulonglong2 *>(cv + s);
-                        gg_next[s] = c2.x; gg_next[s + 1] = c2.y;
-                    }
-                } else {
-#pragma unroll
-                    for (int s = 0; s < VT; ++s) gg_next[s] = cv[s];
-                }
-                if (next_row < first) {   // steps larger than the ring: skip rows nobody needs
-                    next_row = first; slot = first % VT; mp = m_col + (first - r0) * kTileW;
-                }
-                if (next_row < first + VT) load_ring_rows<VT>(wa, wb, slot, next_row, first + VT, mp);
-                const unsigned word_a = vertical_quad<VT>(wa, gg, v_thr, exact);
-                if (fast_a) *reinterpret_cast<unsigned *>(drow + xa) = word_a;
-                else store_quad_slow(drow, xa, dw, dst_xstep, word_a);
-                if (right) {
-                    const unsigned word_b = vertical_quad<VT>(wb, gg, v_thr, exact);
-                    if (fast_b) *reinterpret_cast<unsigned *>(drow + xb) = word_b;
-                    else store_quad_slow(drow, xb, dw, dst_xstep, word_b);
-                }
-                first = first_next;
-#pragma unroll
-                for (int s = 0; s < VT; ++s) gg[s] = gg_next[s];
-            }
+            const f32x2 *cv = CVB + buf * P.cv_pairs + (ya - y0) * VT;
+            const int *vp = VPB + buf * P.vp_ints + (ya - y0);
+            const int xa = x0 + 4 * lane;
+            if (words && x0 + kTileW <= dw)
+                vertical_strip<VT, kStoreBoth>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, 1, dw, xa, true, op.v_thr, lane);
+            else if (words && x0 + kHalfW == dw)
+                vertical_strip<VT, kStoreLeft>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, 1, dw, xa, false, op.v_thr, lane);
+            else
+                vertical_strip<VT, kStoreGeneric>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, dst_xstep, dw, xa,
+                                                  x0 + kHalfW < dw, op.v_thr, lane);
         }
         cur = nxt;
     }
@@ -491,11 +585,12 @@ SmemLayout smem_layout(int m_rows, int s_pitch, int s_words, int th, int vt) {
     l.vp_ints = (th + 1 + 3) & ~3;
     return l;
 }
-size_t layout_bytes(const SmemLayout &l) {
-    return static_cast<size_t>(l.m_floats + l.s_floats + 2 * l.raw_words + 2 * l.vp_ints) * 4 + static_cast<size_t>(2 * l.cv_pairs) * 8;
+size_t layout_bytes(const SmemLayout &l, int span) {
+    const size_t hcoef = static_cast<size_t>(2 * kGroupsPerHalf) * (kGroup * span + 1) * 4;   // CD + HB
+    return static_cast<size_t>(l.m_floats + l.s_floats + 2 * l.raw_words + 2 * l.vp_ints) * 4 + static_cast<size_t>(2 * l.cv_pairs) * 8 + hcoef;
 }
-size_t fused_smem_bytes(int m_rows, int s_pitch, int s_words, int th, int vt) {
-    return layout_bytes(smem_layout(m_rows, s_pitch, s_words, th, vt));
+size_t fused_smem_bytes(int m_rows, int s_pitch, int s_words, int th, int vt, int span) {
+    return layout_bytes(smem_layout(m_rows, s_pitch, s_words, th, vt), span);
 }
 
 // Worst-case absolute rounding error of the float vertical sum, in units of the integer sum.
@@ -597,7 +692,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         while (th > kWarps && th - kWarps >= op.dh) th -= kWarps;
         for (;; th -= kWarps) {
             fo.m_rows = rows_for(th, fo.tiles_y);
-            fo.smem_bytes = fused_smem_bytes(fo.m_rows, fo.s_pitch, fo.s_words, th, VT);
+            fo.smem_bytes = fused_smem_bytes(fo.m_rows, fo.s_pitch, fo.s_words, th, VT, SPAN);
             if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
         }
         if (fo.smem_bytes > 220 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
@@ -711,7 +806,8 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
         lp.total_tiles = tiles * n_frames;
         lp.m_floats = lay.m_floats; lp.s_floats = lay.s_floats; lp.raw_words = lay.raw_words;
         lp.cv_pairs = lay.cv_pairs; lp.vp_ints = lay.vp_ints;
-        const size_t smem = layout_bytes(lay);
+        if (const char *dbg = getenv("TVS_DEBUG_SKIP")) lp.debug_skip = atoi(dbg);
+        const size_t smem = layout_bytes(lay, kInstances[p->ops[i].instance].span);
         // persistent CTAs: two per SM, each walking a contiguous share of the tiles
         const int grid = std::min(lp.total_tiles, 2 * p->sm_count);
         kInstances[p->ops[i].instance].fn<<<grid, kThreads, smem, stream>>>(lp);
