@@ -332,9 +332,7 @@ __device__ __forceinline__ const uint8_t *tile_src_base(const FusedOpParams &op,
 // row start positions.  Rows are read as aligned words starting at the word that holds their first sample, so
 // the sample that ends up at word-relative position j is sample j - mis / xs of the footprint, mis being the
 // misalignment of the row's first byte.
-template <int VT>
-__device__ __forceinline__ void prefetch_tile(const FusedLaunchParams &P, const TileCoord &c, unsigned *raw, f32x2 *cv,
-                                              int *vp, int tid) {
+__device__ __forceinline__ void prefetch_tile_source(const FusedLaunchParams &P, const TileCoord &c, unsigned *raw, int tid) {
     const FusedOpParams &op = P.op[c.oi];
     const int c0 = op.tile_c0[c.tx];
     const int nrows = op.tile_r1[c.ty] - op.tile_r0[c.ty];
@@ -359,6 +357,11 @@ __device__ __forceinline__ void prefetch_tile(const FusedLaunchParams &P, const 
             else *dst = 0u;
         }
     }
+}
+
+template <int VT>
+__device__ __forceinline__ void prefetch_tile_tables(const FusedLaunchParams &P, const TileCoord &c, f32x2 *cv, int *vp, int tid) {
+    const FusedOpParams &op = P.op[c.oi];
     const int y0 = c.ty * op.th;
     const char *cvg = reinterpret_cast<const char *>(op.vring) + static_cast<size_t>(y0) * VT * sizeof(f32x2);
     for (int i = tid; i < op.th * VT / 2; i += kThreads) cp_async16(reinterpret_cast<char *>(cv) + 16 * i, cvg + 16 * i);
@@ -408,19 +411,22 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
 
     int buf = 0;
     TileCoord cur = decode_tile(P, t_begin);
-    prefetch_tile<VT>(P, cur, RAW, CVB, VPB, tid);
+    prefetch_tile_source(P, cur, RAW, tid);
+    prefetch_tile_tables<VT>(P, cur, CVB, VPB, tid);
     prefetch_hcoef<SPAN>(P.op[cur.oi], cur.tx, CD, HB, tid);
     cp_async_commit();
 
     for (int tile = t_begin; tile < t_end; ++tile, buf ^= 1) {
         const FusedOpParams &op = P.op[cur.oi];
+        // No barrier here: a thread converts exactly the source words it prefetched itself, so its own
+        // cp.async completion is enough, and the conversion only writes S, which nobody reads during the vertical
+        // pass.  Warps that finish a tile early therefore run ahead into the next tile's conversion.
         cp_async_wait_all();
-        __syncthreads();             // this tile's inputs have landed; everyone is done with the previous tile's M / S
         TileCoord nxt = cur;
         const bool more = tile + 1 < t_end;
         if (more) {
             nxt = decode_tile(P, tile + 1);
-            prefetch_tile<VT>(P, nxt, RAW + (buf ^ 1) * P.raw_words, CVB + (buf ^ 1) * P.cv_pairs, VPB + (buf ^ 1) * P.vp_ints, tid);
+            prefetch_tile_source(P, nxt, RAW + (buf ^ 1) * P.raw_words, tid);
             cp_async_commit();
         }
 
@@ -461,11 +467,17 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                     }
                 }
             }
-            // rows the vertical ring may touch beyond the last real row read as zero
-            for (int i = tid; i < VT * (kTileW / 4); i += kThreads)
-                reinterpret_cast<float4 *>(M + nrows * kTileW)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
         }
-        __syncthreads();
+        __syncthreads();   // (A) S is complete, the tables copied a tile ago are visible, and the previous tile's M is free
+
+        // the other halves of the table buffers were last read by the previous tile's vertical pass: refill them now
+        if (more) {
+            prefetch_tile_tables<VT>(P, nxt, CVB + (buf ^ 1) * P.cv_pairs, VPB + (buf ^ 1) * P.vp_ints, tid);
+            cp_async_commit();
+        }
+        // rows the vertical ring may touch beyond the last real row read as zero
+        for (int i = tid; i < VT * (kTileW / 4); i += kThreads)
+            reinterpret_cast<float4 *>(M + nrows * kTileW)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
 
         // ---- horizontal pass: S -> M ----------------------------------------------------------------
         if (x0 + half * kHalfW < dw && !(P.debug_skip & 2)) {
@@ -501,7 +513,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                 *reinterpret_cast<float4 *>(mcol + row * kTileW) = o;
             }
         }
-        __syncthreads();
+        __syncthreads();   // (B) M is complete
 
         // the next tile starts a new column: its horizontal coefficients can stream in under the vertical pass
         if (more && (nxt.oi != cur.oi || nxt.tx != cur.tx)) {
