@@ -15,12 +15,26 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 HASHES = json.load(open(os.path.join(GOLD, "swscale_hashes.json")))["cases"]
 SMALL = json.load(open(os.path.join(GOLD, "small_cases.json")))
-PATHS = ("auto", "two-pass")
+PATHS = ("auto", "two-pass", "fused")
 
 
 def _scaler(c, **kw):
     from thinvids_b200.swscale import Scaler
     return Scaler(c["src_w"], c["src_h"], c["src_fmt"], c["dst_w"], c["dst_h"], c["dst_fmt"], c["alg"], **kw)
+
+
+def _use_path(s, path):
+    """Select a kernel path; False when `fused` is requested for a shape only the two-pass kernels handle."""
+    from thinvids_b200 import lib as tv_lib
+    if path == "auto":
+        return True
+    try:
+        s.set_path(path)
+    except tv_lib.TvscaleError:
+        if path == "fused":
+            return False
+        raise
+    return True
 
 
 def _input(spec, fmt, w, h):
@@ -38,8 +52,8 @@ def _id(c):
 def test_golden_hashes(case, path):
     """Every golden vector of SURVEY.md Appendix B.2 (+ the extras) through tvs_scale_host."""
     with _scaler(case) as s:
-        if path != "auto":
-            s.set_path(path)
+        if not _use_path(s, path):
+            pytest.skip("shape not handled by the fused kernel")
         out = s.scale(_input(case["input"], case["src_fmt"], case["src_w"], case["src_h"]))
         if (case["dst_fmt"] == "p010le" and case["src_fmt"] in ("yuv420p", "yuv420p10le") and case["src_w"] % 2
                 and (case["src_w"], case["src_h"]) == (case["dst_w"], case["dst_h"])):
@@ -52,8 +66,8 @@ def test_small_golden_outputs(path):
     blobs = np.load(os.path.join(GOLD, "small_cases.npz"))
     for i, c in enumerate(SMALL):
         with _scaler(c) as s:
-            if path != "auto":
-                s.set_path(path)
+            if not _use_path(s, path):
+                continue
             got = s.scale(F.random_frame(c["src_fmt"], c["src_w"], c["src_h"], c["seed"]))
         for k in range(c["n_dst_planes"]):
             assert np.array_equal(got[k], blobs[f"case{i}_dst{k}"]), (_id(c), k, path)
@@ -77,8 +91,8 @@ def test_random_shapes_against_oracle():
         for path in PATHS:
             got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
             with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
-                if path != "auto":
-                    s.set_path(path)
+                if not _use_path(s, path):
+                    continue
                 s.scale(src, got)
             for k, (a, b) in enumerate(zip(got, want)):
                 assert np.array_equal(a, b), (i, path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
@@ -146,8 +160,8 @@ def test_pitched_and_strided_device_surfaces():
         db, dp, dpi, dfs = surfaces(df, dw, dh, dpitch_extra)
         with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
             for path in PATHS:
-                if path != "auto":
-                    s.set_path(path)
+                if not _use_path(s, path):
+                    continue
                 s.scale_device_planes(sp, spi, sfs, dp, dpi, dfs, n, torch.cuda.current_stream().cuda_stream)
                 torch.cuda.synchronize()
                 bps = 1 if F.bit_depth(df) == 8 else 2

@@ -78,6 +78,7 @@ struct FusedPlan;  // opaque, owned by the context
 FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);
 void fused_plan_destroy(FusedPlan *p);
 size_t fused_plan_device_bytes(const FusedPlan *p);
+bool fused_plan_prefers_two_pass(const FusedPlan *p);
 // Launches the fused kernels for every scale op of the plan.  Returns kernels launched or -1.
 int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
                  int n_frames, cudaStream_t stream);

@@ -242,7 +242,7 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     }
     if (!plan.any_scale) return 0;
 
-    const bool use_fused = c->fused && c->forced_path != 1;
+    const bool use_fused = c->fused && (c->forced_path == 0 || (c->forced_path < 0 && !fused_plan_prefers_two_pass(c->fused)));
     if (c->forced_path == 0 && !c->fused) return fail(-ENOSYS, "fused path requested but this shape is not supported by it");
     if (use_fused) {
         const int n = fused_launch(c->fused, plan, sv.data(), dv.data(), n_frames, stream);
@@ -460,7 +460,8 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const bool dst_packed = packed(reinterpret_cast<const void *const *>(dst), dst_pitch, dst_frame_stride, c->dfi, d_off, d_pitch, dframe);
 
     // The two-pass path owns ONE intermediate buffer, so its chunks must not overlap on the device.
-    const bool single_stream = c->plan.any_scale && !(c->fused && c->forced_path != 1);
+    const bool single_stream = c->plan.any_scale &&
+                               !(c->fused && (c->forced_path == 0 || (c->forced_path < 0 && !fused_plan_prefers_two_pass(c->fused))));
     int slot = 0;
     for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk), slot = single_stream ? 0 : slot ^ 1) {
         const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
@@ -514,7 +515,7 @@ long long tvs_info(const tvs_ctx *c, int what) {
     case TVS_INFO_KERNEL_LAUNCHES: return c->launches;
     case TVS_INFO_PATH:
         if (!c->plan.any_scale) return 2;
-        return (c->fused && c->forced_path != 1) ? 0 : 1;
+        return (c->fused && (c->forced_path == 0 || (c->forced_path < 0 && !fused_plan_prefers_two_pass(c->fused)))) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
         return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + 2 * (c->stage_src_bytes + c->stage_dst_bytes));
     case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
