@@ -31,7 +31,13 @@ import numpy as np  # noqa: E402
 
 from thinvids_b200 import frames as F  # noqa: E402
 
-METRIC = "frames/s 720x480->1920x1080 lanczos (scale + pixel-format stage)"
+METRIC = "frames/s 720x480->1920x1080 lanczos (scale + pixel-format stage)"   # BASELINE.json's metric, quoted on C1
+
+
+def metric_name(cfg) -> str:
+    if cfg.name == "C1":
+        return METRIC
+    return f"frames/s {cfg.src_w}x{cfg.src_h}->{cfg.dst_w}x{cfg.dst_h} {cfg.alg} (scale + pixel-format stage)"
 DISTINCT_FRAMES = 8  # distinct synthetic frames generated on the host; the batch tiles them
 
 
@@ -163,7 +169,7 @@ def run_reference(args, cfg, rank, world):
     fps = statistics.mean(r["value"] for r in results)
     base = dict(results[-1], value=fps)
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
+        "impl": "reference", "metric": metric_name(cfg), "value": fps, "unit": "frames/s", "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step * 1e3, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8" if F.bit_depth(cfg.src_fmt) == 8 else "u16",
         "data": "synthetic", "config": {"workload": workload_name(cfg), "threads": threads,
@@ -179,7 +185,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--config", default="C1", choices=sorted(F.CONFIGS))
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
-    ap.add_argument("--frames", type=int, default=0, help="frames per step per GPU (default: the config's batch)")
+    ap.add_argument("--frames", type=int, default=0, help="frames per segment (default: the config's batch)")
+    ap.add_argument("--segments", type=int, default=0, help="segments per step (default: 1 per GPU; C5: 64 in total)")
     ap.add_argument("--path", default="auto", choices=("auto", "fused", "two-pass"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
@@ -216,7 +223,18 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
-    n = args.frames or cfg.n_frames          # per GPU: weak scaling, each rank owns its own segments
+    n = args.frames or cfg.n_frames          # frames per segment (one segment = one call = one kernel launch)
+    if cfg.name == "C5":
+        # the farm job of BASELINE.json: 64 segments of 240 frames striped over the GPUs (strong scaling)
+        from thinvids_b200.farm import shard_segments
+        my_segments = len(shard_segments(args.segments or 64, rank, world))
+        total_segments = args.segments or 64
+        scaling = "strong"
+    else:
+        # every GPU owns its own segment(s) of the same size (weak scaling)
+        my_segments = args.segments or 1
+        total_segments = my_segments * world
+        scaling = "weak"
     sc = Scaler(cfg.src_w, cfg.src_h, cfg.src_fmt, cfg.dst_w, cfg.dst_h, cfg.dst_fmt, cfg.alg, device=local)
     if args.path != "auto":
         sc.set_path(args.path)
@@ -227,8 +245,12 @@ def main():
     stream = torch.cuda.current_stream()
 
     # ---- device-resident throughput (`value`) ------------------------------------------------------------
+    def step():
+        for _ in range(my_segments):     # segments are independent; the synthetic segment buffer is reused
+            sc.scale_packed_device(d_src, d_dst, stream)
+
     for _ in range(args.warmup):
-        sc.scale_packed_device(d_src, d_dst, stream)
+        step()
     barrier()
     sampler = ClockSampler(local)
     sampler.start()
@@ -236,29 +258,31 @@ def main():
     evs = [torch.cuda.Event(enable_timing=True) for _ in range(args.steps + 1)]
     evs[0].record(stream)
     for k in range(args.steps):
-        sc.scale_packed_device(d_src, d_dst, stream)
+        step()
         evs[k + 1].record(stream)
     barrier()
     launches = sc.kernel_launches - launches0
     step_ms = [evs[k].elapsed_time(evs[k + 1]) for k in range(args.steps)]
     total_ms = max_over_ranks(evs[0].elapsed_time(evs[-1]))
     clocks = sampler.stop()
-    fps = world * n * args.steps / (total_ms * 1e-3)
+    fps = total_segments * n * args.steps / (total_ms * 1e-3)
 
     # ---- end to end through the host-buffer C-ABI call (`e2e`) ------------------------------------------
     e2e = None
     if not args.no_e2e:
+        e2e_segments = min(my_segments, 4)               # bounded: every segment crosses PCIe both ways
         for _ in range(2):
             sc.scale_packed_pinned(host_src, host_dst)
         barrier()
         t0 = time.perf_counter()
         for _ in range(args.steps):
-            sc.scale_packed_pinned(host_src, host_dst)   # returns after the last byte is back in host memory
-            _ = int(host_dst[-1, -1])                    # touch the result on the host
+            for _ in range(e2e_segments):
+                sc.scale_packed_pinned(host_src, host_dst)   # returns after the last byte is back in host memory
+                _ = int(host_dst[-1, -1])                    # touch the result on the host
         dt = max_over_ranks(time.perf_counter() - t0)
         barrier()
-        e2e = {"value": world * n * args.steps / dt, "unit": "frames/s",
-               "h2d_bytes_per_step": int(host_src.numel()), "d2h_bytes_per_step": int(host_dst.numel()),
+        e2e = {"value": world * e2e_segments * n * args.steps / dt, "unit": "frames/s",
+               "h2d_bytes_per_step": int(host_src.numel()) * e2e_segments, "d2h_bytes_per_step": int(host_dst.numel()) * e2e_segments,
                "ms_per_step": dt / args.steps * 1e3, "api": "tvs_scale_host (pinned host buffers)"}
         # the two entry points must agree byte for byte
         sc.scale_packed_device(d_src, d_dst, stream)
@@ -269,8 +293,8 @@ def main():
     # ---- roofline of the dominant kernel ----------------------------------------------------------------
     peak, peak_src = measured_peak_gbs()
     launches_per_step = launches // max(1, args.steps)
-    alg_bytes = cfg.algorithmic_bytes * n                      # per step == per launch when one kernel does the batch
-    kernel_ms = statistics.mean(step_ms)
+    alg_bytes = cfg.algorithmic_bytes * n                      # per launch: one kernel does one whole segment
+    kernel_ms = statistics.mean(step_ms) / max(1, launches_per_step)   # back-to-back launches of the same kernel
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     traffic = None
     prof = os.path.join(ROOT, "profiles", "traffic.json")    # written from an `ncu --set full` capture, per launch
@@ -281,7 +305,7 @@ def main():
             traffic = None
     roofline = {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                 "traffic": traffic, "peak_source": peak_src, "kernel": sc.path, "launches_per_step": launches_per_step,
-                "algorithmic_bytes_per_launch": alg_bytes if launches_per_step == 1 else None,
+                "algorithmic_bytes_per_launch": alg_bytes,
                 "kernel_ms": kernel_ms}
 
     # ---- CPU baseline on this box's host cores (rank 0, N = 1 only) -------------------------------------
@@ -292,11 +316,11 @@ def main():
     sc.close()
     if rank == 0:
         print(json.dumps({
-            "metric": METRIC, "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
+            "metric": metric_name(cfg), "value": fps, "unit": "frames/s", "n_gpus": world, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-            "scaling": "weak", "vs_baseline": None, "dtype": "u8" if F.bit_depth(cfg.src_fmt) == 8 else "u16",
+            "scaling": scaling, "vs_baseline": None, "dtype": "u8" if F.bit_depth(cfg.src_fmt) == 8 else "u16",
             "data": "synthetic",
-            "config": {"workload": workload_name(cfg), "frames_per_step_per_gpu": n,
+            "config": {"workload": workload_name(cfg), "frames_per_segment": n, "segments_per_step": total_segments,
                        "l2": f"batch of {(cfg.algorithmic_bytes * n) >> 20} MiB per step exceeds the 126 MB L2",
                        "sharding": "independent segments per GPU, no collective on the data path"},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches), "clocks": clocks}))

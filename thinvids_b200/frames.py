@@ -110,7 +110,7 @@ def scaled_width(src_w: int, src_h: int, dst_h: int) -> int:
     Matches the shapes the reference produces with ``scale=-2:{H}`` (worker/tasks.py:62-65,448):
     720x480 -> 1620x1080, 1920x1080 -> 1280x720.
     """
-    w = int(round(src_w * dst_h / src_h / 2.0)) * 2
+    w = int(src_w * dst_h / (src_h * 2.0) + 0.5) * 2
     return max(w, 2)
 
 
