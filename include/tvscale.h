@@ -101,6 +101,36 @@ TVS_API int tvs_scale_host(tvs_ctx *ctx,
                    int n_frames);
 
 /*
+ * No counterpart in the reference or in libswscale.
+ *
+ * tvs_scale_batch() for callers that must not allocate device memory when they scale.  Two kinds of caller are in
+ * that position: a worker whose GPU memory has been handed out in full before the first frame arrives (decoder
+ * surface pools, the encoder's buffers, another framework's arena), for whom a late cudaMalloc can simply fail; and
+ * a frame loop that cannot afford the device-wide synchronisation a cudaMalloc / cudaFree implies while its other
+ * streams are busy.  This call runs the two-pass kernels (horizontal launch, vertical launch) and keeps the int16
+ * intermediate between them in a fixed array that is part of the library image, TVS_STATIC_SCRATCH_BYTES long, so it
+ * performs no cudaMalloc, cudaFree or other allocating call.  Same arguments, result bytes and return value as
+ * tvs_scale_batch(); the caller still provides source and destination planes in device memory.
+ *
+ * Limits and rules:
+ *   - n_frames x (intermediate of one frame: 2 bytes x dst_w x src_h for luma plus the two chroma planes) must fit in
+ *     TVS_STATIC_SCRATCH_BYTES, e.g. 12 frames of 720x480 -> 1920x1080 or 2 frames of 1920x1080 -> 3840x2160.
+ *     Larger requests fail with -E2BIG and a message that states the per-call maximum; split the batch.
+ *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
+ *     current).  Make that first call before starting any stream capture.
+ *   - There is ONE array per device, shared by every context and every call in the process, and it keeps whatever
+ *     the last call left in it.  Nothing in it needs clearing (each call overwrites what it later reads), but two
+ *     calls whose kernels can run at the same time on one GPU - different streams, or different threads - race on
+ *     it.  Issue these calls on one stream, or order them with events.
+ *   - Every GPU that loads the library holds the array until the process exits.
+ */
+#define TVS_STATIC_SCRATCH_BYTES (32u << 20)
+TVS_API int tvs_scale_batch_static(tvs_ctx *ctx,
+                    const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                    void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                    int n_frames, void *stream);
+
+/*
  * Host-only: one axis of libswscale's initFilter.  No device needed.
  *   inc = ((src_len << 16) + (dst_len >> 1)) / dst_len, one = 1<<14 (horizontal) or 1<<12 (vertical),
  *   src_pos / dst_pos = 128 for luma and centred chroma.

@@ -4,6 +4,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 
 #include "../../include/tvscale.h"
@@ -275,6 +276,32 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     return 0;
 }
 
+// ---- fixed scratch for tvs_scale_batch_static ------------------------------------------------------------------
+// The two-pass kernels park libswscale's int16 intermediate in global memory between the horizontal and the
+// vertical launch.  tvs_scale_batch gets that buffer from cudaMalloc; the entry point below uses this array
+// instead, so it never has to ask the driver for memory.  Every GPU that loads the library carries the array
+// (TVS_STATIC_SCRATCH_BYTES) until the process exits.
+static __device__ __align__(256) int16_t g_static_mid[TVS_STATIC_SCRATCH_BYTES / sizeof(int16_t)];
+
+constexpr int kMaxStaticDevices = 64;
+std::mutex g_static_mid_mutex;
+int16_t *g_static_mid_ptr[kMaxStaticDevices];   // device address of g_static_mid, per device, once resolved
+
+// `g_static_mid` is only a host-side handle here; the kernels need the address the symbol has on `device`.
+// Resolved once per device, with that device current.
+int static_mid_for_device(int device, int16_t **out) {
+    if (device < 0 || device >= kMaxStaticDevices) return fail(-EINVAL, "device %d is outside the static-scratch table", device);
+    std::lock_guard<std::mutex> lock(g_static_mid_mutex);
+    if (!g_static_mid_ptr[device]) {
+        TVS_CUDA(cudaSetDevice(device), "cudaSetDevice");
+        void *p = nullptr;
+        TVS_CUDA(cudaGetSymbolAddress(&p, g_static_mid), "cudaGetSymbolAddress(static scratch)");
+        g_static_mid_ptr[device] = static_cast<int16_t *>(p);
+    }
+    *out = g_static_mid_ptr[device];
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -529,6 +556,49 @@ int tvs_set_path(tvs_ctx *c, int path) {
     if (path == 0 && c->plan.any_scale && !c->fused) return fail(-ENOSYS, "this shape is not supported by the fused kernel");
     c->forced_path = path;
     return 0;
+}
+
+int tvs_scale_batch_static(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                           void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                           int n_frames, void *stream) {
+    if (!c) return fail(-EINVAL, "NULL context");
+    if (n_frames < 0 || n_frames > 65535) return fail(-EINVAL, "n_frames must be 0..65535");
+    if (int rc = check_planes(c->sfi, c->src_w, c->src_h, src, src_pitch, "src")) return rc;
+    if (int rc = check_planes(c->dfi, c->dst_w, c->dst_h, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
+    const Plan &plan = c->plan;
+    const size_t need = plan.mid_elems_per_frame * static_cast<size_t>(n_frames) * sizeof(int16_t);
+    if (need > TVS_STATIC_SCRATCH_BYTES)
+        return fail(-E2BIG, "%d frame(s) of this shape need %zu bytes of intermediate, the static scratch holds %u "
+                            "(at most %zu frame(s) per call)", n_frames, need, static_cast<unsigned>(TVS_STATIC_SCRATCH_BYTES),
+                    plan.mid_elems_per_frame ? TVS_STATIC_SCRATCH_BYTES / (plan.mid_elems_per_frame * sizeof(int16_t)) : size_t(0));
+    if (n_frames == 0) return c->dst_h;
+    if (plan.ops.size() > 3) return fail(-EINVAL, "unexpected plan");
+    int16_t *mid = nullptr;
+    if (int rc = static_mid_for_device(c->device, &mid)) return rc;   // the first call on a device resolves the address
+    TVS_CUDA(cudaSetDevice(c->device), "cudaSetDevice");
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+
+    // Same launches as the two-pass branch of tvs_scale_batch, with the array above as the intermediate.  Nothing
+    // in it has to start at zero: the horizontal kernel writes every element the vertical kernel reads.
+    for (size_t i = 0; i < plan.ops.size(); ++i) {
+        const PlaneOp &op = plan.ops[i];
+        SampleView s, d;
+        s.base = const_cast<uint8_t *>(static_cast<const uint8_t *>(src[op.src_plane])) + op.src_offset;
+        s.pitch = src_pitch[op.src_plane]; s.frame_stride = src_frame_stride[op.src_plane]; s.xstep = op.src_xstep;
+        d.base = static_cast<uint8_t *>(dst[op.dst_plane]) + op.dst_offset;
+        d.pitch = dst_pitch[op.dst_plane]; d.frame_stride = dst_frame_stride[op.dst_plane]; d.xstep = op.dst_xstep;
+        if (op.kind != kOpScale) {
+            if (launch_repack(op, s, d, n_frames, st) < 0) return cuda_fail(cudaGetLastError(), "repack kernel launch");
+            ++c->launches;
+            continue;
+        }
+        if (launch_hpass_generic(op, s, c->dev_tables[op.htable], mid, plan.mid_elems_per_frame, n_frames, st) < 0)
+            return cuda_fail(cudaGetLastError(), "horizontal kernel launch");
+        if (launch_vpass_generic(op, d, c->dev_tables[op.vtable], mid, plan.mid_elems_per_frame, n_frames, st) < 0)
+            return cuda_fail(cudaGetLastError(), "vertical kernel launch");
+        c->launches += 2;
+    }
+    return c->dst_h;
 }
 
 }  // extern "C"

@@ -9,9 +9,10 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libtvscale.so")
 
 # Every symbol include/tvscale.h declares; tests check the built library exports each one.
-EXPORTS = ("tvs_create", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tvs_filter_table",
+EXPORTS = ("tvs_create", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tvs_scale_batch_static", "tvs_filter_table",
            "tvs_context_table", "tvs_info", "tvs_set_path", "tvs_last_error", "tvs_version")
 
+STATIC_SCRATCH_BYTES = 32 << 20   # TVS_STATIC_SCRATCH_BYTES
 INFO_KERNEL_LAUNCHES, INFO_PATH, INFO_SCRATCH_BYTES, INFO_SRC_FRAME_BYTES, INFO_DST_FRAME_BYTES = range(5)
 
 _lib = None
@@ -38,6 +39,8 @@ def load() -> ctypes.CDLL:
     lib.tvs_destroy.argtypes = [P]
     lib.tvs_scale_batch.restype = I
     lib.tvs_scale_batch.argtypes = [P, P, P, P, P, P, P, I, P]
+    lib.tvs_scale_batch_static.restype = I
+    lib.tvs_scale_batch_static.argtypes = [P, P, P, P, P, P, P, I, P]
     lib.tvs_scale_host.restype = I
     lib.tvs_scale_host.argtypes = [P, P, P, P, P, P, P, I]
     lib.tvs_filter_table.restype = I

@@ -158,6 +158,24 @@ class Scaler:
         _lib.check(self._lib.tvs_scale_batch(self._ctx, sp, ss, sf, dp, ds, df, n, ctypes.c_void_p(st)))
         return dst
 
+    def scale_packed_device_static(self, src, dst, stream=None):
+        """`scale_packed_device` through tvs_scale_batch_static: the variant for callers that cannot allocate device
+        memory while scaling (a GPU whose memory is already fully handed out, or a frame loop that must not take the
+        device-wide stall of cudaMalloc).  Runs the two-pass kernels with their intermediate in the library's fixed
+        array: at most `lib.STATIC_SCRATCH_BYTES` of intermediate per call (TvscaleError -E2BIG beyond that), one array
+        per GPU shared by all calls, so keep these calls on one stream.  Output bytes equal `scale_packed_device`."""
+        import torch
+
+        assert src.is_cuda and dst.is_cuda and src.dtype == torch.uint8 and dst.dtype == torch.uint8
+        assert src.is_contiguous() and dst.is_contiguous() and src.device.index == self.device
+        n = src.shape[0]
+        assert src.shape[1] == self.src_layout.frame_bytes and dst.shape == (n, self.dst_layout.frame_bytes)
+        st = (stream or torch.cuda.current_stream(src.device)).cuda_stream
+        sp, ss, sf = self.src_layout.pointer_args(src.data_ptr())
+        dp, ds, df = self.dst_layout.pointer_args(dst.data_ptr())
+        _lib.check(self._lib.tvs_scale_batch_static(self._ctx, sp, ss, sf, dp, ds, df, n, ctypes.c_void_p(st)))
+        return dst
+
     def scale_device_planes(self, src_ptrs, src_pitch, src_fstride, dst_ptrs, dst_pitch, dst_fstride, n_frames, stream=0):
         """Raw form of tvs_scale_batch for pitched surfaces (e.g. NVDEC output): lists of ints."""
         pad = lambda v, fill: list(v) + [fill] * (3 - len(v))
