@@ -294,7 +294,9 @@ def main():
     peak, peak_src = measured_peak_gbs()
     launches_per_step = launches // max(1, args.steps)
     alg_bytes = cfg.algorithmic_bytes * n                      # per launch: one kernel does one whole segment
-    kernel_ms = statistics.mean(step_ms) / max(1, launches_per_step)   # back-to-back launches of the same kernel
+    # one launch per segment on the fused path; the two-pass path needs several launches per segment, and the
+    # figure is then the time of the whole group of launches that processes one segment
+    kernel_ms = statistics.mean(step_ms) / max(1, my_segments)
     achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
     traffic = None
     prof = os.path.join(ROOT, "profiles", "traffic.json")    # written from an `ncu --set full` capture, per launch

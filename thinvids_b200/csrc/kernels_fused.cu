@@ -62,8 +62,10 @@ struct FusedOpParams {
     const int *vring_i;    // [dh][VT]             the same coefficients as integers (exact path)
     int vtaps;
     int s_pitch;           // floats per staged source row
-    int s_words;           // 32-bit source words staged per row
-    int s_words_log2;      // log2 of the power of two >= s_words (index split in the staging loop)
+    int s_chunks;          // 16-byte source chunks staged per row
+    int s_chunks_log2;     // log2 of the power of two >= s_chunks (index split in the staging loops)
+    const uint8_t *src_lo; // first byte of the stored source plane (frame 0) and its extent: bounds for 16-byte reads
+    size_t src_extent;
     int m_rows;            // rows of the shared-memory tiles
     float v_thr;           // |residual| at or above this needs the exact path
     int src_mode;          // kSrcU8 / kSrcU8Pair / kSrcU16 / kSrcU16Pair: sample width and spacing in the source plane
@@ -171,9 +173,10 @@ template <> struct OutRule<kOutU10>      { static constexpr int kShift = 17, kMa
 // keeping the register ring alive across a call.  `m_first` points at this quad's columns in row `first`;
 // `dither` are the four ordered-dither values (kOutU8Dither only).
 template <int VT, int OUT>
-__device__ __noinline__ void exact_fixup(const float *m_first, int first, const int *exact_coef, float v_thr,
-                                         float r0, float r1, float r2, float r3, int4 dither, int dst_shift,
-                                         unsigned (&word)[2]) {
+__device__ __noinline__ uint2 exact_fixup(const float *m_first, int first, const int *exact_coef, float v_thr,
+                                          float r0, float r1, float r2, float r3, int4 dither, int dst_shift,
+                                          uint2 packed) {
+    unsigned word[2] = {packed.x, packed.y};
     const float r[4] = {r0, r1, r2, r3};
     const int d[4] = {dither.x, dither.y, dither.z, dither.w};
     int slot = first % VT;
@@ -198,6 +201,7 @@ __device__ __noinline__ void exact_fixup(const float *m_first, int first, const 
             }
         }
     }
+    return make_uint2(word[0], word[1]);
 }
 
 // Per-row extras of the output rule: the accumulator start values (dither) for the lane's four columns.
@@ -255,8 +259,14 @@ __device__ __forceinline__ void vertical_row(const Quad (&wa)[VT], const Quad (&
     float worst = finish_quad<OUT>(a01, a23, dst_shift, word_a, ra);
     if (RIGHT) worst = fmaxf(worst, finish_quad<OUT>(b01, b23, dst_shift, word_b, rb));
     if (worst >= v_thr) {
-        exact_fixup<VT, OUT>(m_first, first, exact_coef, v_thr, ra[0], ra[1], ra[2], ra[3], ex.dither, dst_shift, word_a);
-        if (RIGHT) exact_fixup<VT, OUT>(m_first + kHalfW, first, exact_coef, v_thr, rb[0], rb[1], rb[2], rb[3], ex.dither, dst_shift, word_b);
+        const uint2 fa = exact_fixup<VT, OUT>(m_first, first, exact_coef, v_thr, ra[0], ra[1], ra[2], ra[3], ex.dither, dst_shift,
+                                              make_uint2(word_a[0], word_a[1]));
+        word_a[0] = fa.x; word_a[1] = fa.y;
+        if (RIGHT) {
+            const uint2 fb = exact_fixup<VT, OUT>(m_first + kHalfW, first, exact_coef, v_thr, rb[0], rb[1], rb[2], rb[3], ex.dither,
+                                                  dst_shift, make_uint2(word_b[0], word_b[1]));
+            word_b[0] = fb.x; word_b[1] = fb.y;
+        }
     }
 }
 
@@ -401,34 +411,47 @@ __device__ __forceinline__ const uint8_t *tile_src_base(const FusedOpParams &op,
            static_cast<ptrdiff_t>(op.tile_c0[c.tx]) * op.src_xstep;
 }
 
-// Start the asynchronous copy of everything tile `c` needs from global memory: the raw source footprint (as
-// aligned 32-bit words; words past the end of a row are zeroed here), the ring-ordered row coefficients and the
-// row start positions.  Rows are read as aligned words starting at the word that holds their first sample, so
-// the sample that ends up at word-relative position j is sample j - mis / xs of the footprint, mis being the
-// misalignment of the row's first byte.
+// Start the asynchronous copy of the raw source footprint of tile `c`.  Rows are read as aligned 16-byte chunks
+// starting at the chunk that holds the row's first sample, so byte i of the footprint row lands at position
+// mis + i of the staged row, mis (0..15) being the misalignment of the row's first byte; any pitch works.  A chunk
+// that would reach outside the plane (first / last bytes of the allocation) is fetched as 4-byte words that each
+// contain at least one needed byte; chunks and words past the end of the row are zeroed.
 __device__ __forceinline__ void prefetch_tile_source(const FusedLaunchParams &P, const TileCoord &c, unsigned *raw, int tid) {
     const FusedOpParams &op = P.op[c.oi];
     const int c0 = op.tile_c0[c.tx];
     const int nrows = op.tile_r1[c.ty] - op.tile_r0[c.ty];
     const int xs = op.src_xstep;
-    const int span_bytes = (min(static_cast<int>(op.tile_nc[c.tx]), op.sw - c0) - 1) * xs;   // offset of the last existing sample
-    const int wlog = min(op.s_words_log2, 8), wmask = (1 << wlog) - 1, s_words = op.s_words;
+    const int sample_bytes = op.src_mode >= kSrcU16 ? 2 : 1;
+    // offset of the last needed byte of a footprint row (samples past the plane's width carry zero weight)
+    const int last_byte = (min(static_cast<int>(op.tile_nc[c.tx]), op.sw - c0) - 1) * xs + sample_bytes - 1;
+    const int clog = min(op.s_chunks_log2, 8), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
     const uint8_t *src_base = tile_src_base(op, c);
-    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base)) & 3u;
-    const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 3u;
+    const uint8_t *lo = op.src_lo + c.f * op.src_fstride, *hi = lo + op.src_extent;
+    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base)) & 15u;
+    const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 15u;
     const ptrdiff_t src_pitch = op.src_pitch;
-    // 256 threads cover 256 >> wlog rows per pass; a thread keeps its word index and steps down the rows
-    const int rstep = kThreads >> wlog;
-    for (int w = tid & wmask; w < s_words; w += 1 << wlog) {   // one pass unless a row is longer than 256 words
-        int row = tid >> wlog;
-        unsigned *dst = raw + row * s_words + w;
-        const uint8_t *src = src_base + row * src_pitch + 4 * w;
-        const int limit = span_bytes - 4 * w;          // the word holds data iff mis + limit >= 0
-        unsigned mis = (mis0 + row * pmod) & 3u;
-        const unsigned mstep = (rstep * pmod) & 3u;
-        for (; row < nrows; row += rstep, dst += rstep * s_words, src += rstep * src_pitch, mis = (mis + mstep) & 3u) {
-            if (static_cast<int>(mis) + limit >= 0) cp_async4(dst, src - mis);
-            else *dst = 0u;
+    const int rstep = kThreads >> clog;
+    for (int ch = tid & cmask; ch < s_chunks; ch += 1 << clog) {   // one pass unless a row is longer than 256 chunks
+        int row = tid >> clog;
+        uint4 *dst = reinterpret_cast<uint4 *>(raw) + row * s_chunks + ch;
+        const uint8_t *src = src_base + row * src_pitch + 16 * ch;
+        unsigned mis = (mis0 + row * pmod) & 15u;
+        const unsigned mstep = (rstep * pmod) & 15u;
+        for (; row < nrows; row += rstep, dst += rstep * s_chunks, src += rstep * src_pitch, mis = (mis + mstep) & 15u) {
+            const int first = 16 * ch - static_cast<int>(mis);      // footprint-row offset of the chunk's first byte
+            const uint8_t *g = src - mis;
+            if (first > last_byte) {
+                *dst = make_uint4(0u, 0u, 0u, 0u);
+            } else if (g >= lo && g + 16 <= hi) {
+                cp_async16(dst, g);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+                    if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
+                    else *d = 0u;
+                }
+            }
         }
     }
 }
@@ -471,7 +494,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
 
     float *M = smem;                                             // [m_rows + VT][256] intermediate t * 2^-149
     float *S = M + P.m_floats;                                   // [m_rows][s_pitch]  source samples as floats
-    unsigned *RAW = reinterpret_cast<unsigned *>(S + P.s_floats);   // 2 x [m_rows][s_words] raw source words
+    unsigned *RAW = reinterpret_cast<unsigned *>(S + P.s_floats);   // 2 x [m_rows][s_chunks] raw 16-byte source chunks
     f32x2 *CVB = reinterpret_cast<f32x2 *>(RAW + 2 * P.raw_words);  // 2 x [th + 1][VT] ring-ordered (g, g) pairs
     int *VPB = reinterpret_cast<int *>(CVB + 2 * P.cv_pairs);       // 2 x [th + 1]  first source row per output row
     float4 *CD = reinterpret_cast<float4 *>(VPB + 2 * P.vp_ints);   // [2][N4][32]   horizontal coefficients of the column
@@ -510,51 +533,56 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         const int r0 = op.tile_r0[cur.ty];
         const int nrows = op.tile_r1[cur.ty] - r0;
         const int s_pitch = op.s_pitch, xs = op.src_xstep;
-        const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(tile_src_base(op, cur))) & 3u;
-        const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 3u;
+        const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(tile_src_base(op, cur))) & 15u;
+        const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 15u;
         const unsigned *raw = RAW + buf * P.raw_words;
 
         // ---- raw words -> float samples ----
         if (!(P.debug_skip & 1)) {
-            const int wlog = min(op.s_words_log2, 8), wmask = (1 << wlog) - 1, s_words = op.s_words;
-            const int rstep = kThreads >> wlog;
+            const int clog = min(op.s_chunks_log2, 8), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
+            const int rstep = kThreads >> clog;
             const int src_mode = op.src_mode;
             const float sscale = op.src_scale;
-            for (int w = tid & wmask; w < s_words; w += 1 << wlog) {
-                int row = tid >> wlog;
-                const unsigned *rw = raw + row * s_words + w;
-                if (src_mode == kSrcU8) {              // four samples per word
-                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + w;
-                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * (s_pitch / 4)) {
-                        const unsigned v = *rw;
-                        float4 o;
-                        o.x = byte_to_float(v, 0x7540u); o.y = byte_to_float(v, 0x7541u);
-                        o.z = byte_to_float(v, 0x7542u); o.w = byte_to_float(v, 0x7543u);
-                        *out = o;
+            // a thread converts the chunks it prefetched: byte p of a staged row is sample p / spacing of S
+            for (int ch = tid & cmask; ch < s_chunks; ch += 1 << clog) {
+                int row = tid >> clog;
+                const uint4 *rw = reinterpret_cast<const uint4 *>(raw) + row * s_chunks + ch;
+                if (src_mode == kSrcU8) {              // 16 samples per chunk
+                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + 4 * ch;
+                    for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
+                        const uint4 v = *rw;
+                        const unsigned w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            out[k] = make_float4(byte_to_float(w[k], 0x7540u), byte_to_float(w[k], 0x7541u),
+                                                 byte_to_float(w[k], 0x7542u), byte_to_float(w[k], 0x7543u));
                     }
                 } else if (src_mode == kSrcU8Pair) {   // interleaved 8-bit chroma: this plane is every other byte
-                    float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
-                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * (s_pitch / 2)) {
+                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + 2 * ch;
+                    for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
                         const unsigned p = (mis0 + row * pmod) & 1u;
-                        const unsigned v = *rw;
-                        float2 o;
-                        o.x = byte_to_float(v, 0x7540u | p); o.y = byte_to_float(v, 0x7542u | p);
-                        *out = o;
+                        const uint4 v = *rw;
+                        out[0] = make_float4(byte_to_float(v.x, 0x7540u | p), byte_to_float(v.x, 0x7542u | p),
+                                             byte_to_float(v.y, 0x7540u | p), byte_to_float(v.y, 0x7542u | p));
+                        out[1] = make_float4(byte_to_float(v.z, 0x7540u | p), byte_to_float(v.z, 0x7542u | p),
+                                             byte_to_float(v.w, 0x7540u | p), byte_to_float(v.w, 0x7542u | p));
                     }
-                } else if (src_mode == kSrcU16) {      // two 16-bit samples per word, centred on 512
-                    float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
-                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * (s_pitch / 2)) {
-                        const unsigned v = *rw;
-                        float2 o;
-                        o.x = fmaf(byte_to_float(v, 0x7410u), sscale, -512.0f);
-                        o.y = fmaf(byte_to_float(v, 0x7432u), sscale, -512.0f);
-                        *out = o;
+                } else if (src_mode == kSrcU16) {      // eight 16-bit samples per chunk, centred on 512
+                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + 2 * ch;
+                    for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
+                        const uint4 v = *rw;
+                        out[0] = make_float4(fmaf(byte_to_float(v.x, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.x, 0x7432u), sscale, -512.0f),
+                                             fmaf(byte_to_float(v.y, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.y, 0x7432u), sscale, -512.0f));
+                        out[1] = make_float4(fmaf(byte_to_float(v.z, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.z, 0x7432u), sscale, -512.0f),
+                                             fmaf(byte_to_float(v.w, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.w, 0x7432u), sscale, -512.0f));
                     }
-                } else {                               // interleaved 16-bit chroma: one sample of this plane per word
-                    float *out = S + row * s_pitch + w;
-                    for (; row < nrows; row += rstep, rw += rstep * s_words, out += rstep * s_pitch) {
-                        const unsigned hi = (mis0 + row * pmod) & 2u;
-                        *out = fmaf(byte_to_float(*rw, hi ? 0x7432u : 0x7410u), sscale, -512.0f);
+                } else {                               // interleaved 16-bit chroma: one sample of this plane per 4 bytes
+                    float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + ch;
+                    for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
+                        const unsigned sel = ((mis0 + row * pmod) & 2u) ? 0x7432u : 0x7410u;
+                        const uint4 v = *rw;
+                        *out = make_float4(fmaf(byte_to_float(v.x, sel), sscale, -512.0f), fmaf(byte_to_float(v.y, sel), sscale, -512.0f),
+                                           fmaf(byte_to_float(v.z, sel), sscale, -512.0f), fmaf(byte_to_float(v.w, sel), sscale, -512.0f));
                     }
                 }
             }
@@ -587,9 +615,9 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
             const float t_max = __int_as_float(32767);
             float *mcol = M + half * kHalfW + 4 * lane;
             for (int row = warp & 3; row < nrows; row += 4) {
-                const unsigned mis = (mis0 + row * pmod) & 3u;
-                // word-relative position of the row's first sample (see prefetch_tile_source)
-                const float *sp = S + row * s_pitch + hb + (src_mode_h == kSrcU8 ? mis : src_mode_h == kSrcU16Pair ? 0u : (mis >> 1));
+                const unsigned mis = (mis0 + row * pmod) & 15u;
+                // position of the row's first sample inside the staged row (see prefetch_tile_source)
+                const float *sp = S + row * s_pitch + hb + (src_mode_h == kSrcU8 ? mis : src_mode_h == kSrcU16Pair ? (mis >> 2) : (mis >> 1));
                 f32x2 px[SPAN / 2];
 #pragma unroll
                 for (int i = 0; i < SPAN / 2; ++i) px[i] = pack2(sp[2 * i], sp[2 * i + 1]);
@@ -672,7 +700,7 @@ const Instance kInstances[] = {
 struct FusedOp {
     int op_index = 0;
     int instance = -1;
-    int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, s_words = 0, s_words_log2 = 0, m_rows = 0;
+    int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0, m_rows = 0;
     size_t smem_bytes = 0;
     float v_thr = 0;
     // offsets (in bytes) into the device blob
@@ -703,11 +731,11 @@ size_t append(std::vector<uint8_t> &blob, const std::vector<T> &v) {
 }
 
 struct SmemLayout { int m_floats, s_floats, raw_words, cv_pairs, vp_ints; };
-SmemLayout smem_layout(int m_rows, int s_pitch, int s_words, int th, int vt) {
+SmemLayout smem_layout(int m_rows, int s_pitch, int s_chunks, int th, int vt) {
     SmemLayout l;
     l.m_floats = (m_rows + vt) * kTileW;
     l.s_floats = m_rows * s_pitch;
-    l.raw_words = (m_rows * s_words + 3) & ~3;
+    l.raw_words = m_rows * s_chunks * 4;
     l.cv_pairs = ((th + 1) * vt + 1) & ~1;
     l.vp_ints = (th + 1 + 3) & ~3;
     return l;
@@ -716,8 +744,8 @@ size_t layout_bytes(const SmemLayout &l, int span) {
     const size_t hcoef = static_cast<size_t>(2 * kGroupsPerHalf) * (kGroup * span + 1) * 4;   // CD + HB
     return static_cast<size_t>(l.m_floats + l.s_floats + 2 * l.raw_words + 2 * l.vp_ints) * 4 + static_cast<size_t>(2 * l.cv_pairs) * 8 + hcoef;
 }
-size_t fused_smem_bytes(int m_rows, int s_pitch, int s_words, int th, int vt, int span) {
-    return layout_bytes(smem_layout(m_rows, s_pitch, s_words, th, vt), span);
+size_t fused_smem_bytes(int m_rows, int s_pitch, int s_chunks, int th, int vt, int span) {
+    return layout_bytes(smem_layout(m_rows, s_pitch, s_chunks, th, vt), span);
 }
 
 // Worst-case absolute rounding error of the float vertical sum, in units of the integer sum.
@@ -810,11 +838,11 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
             const int ga = tx * 2 * kGroupsPerHalf, gb = std::min(ga + 2 * kGroupsPerHalf - 1, n_groups - 1);
             ncols_max = std::max(ncols_max, hbase[gb] + SPAN - hbase[ga]);
         }
-        // words per staged row for the worst alignment, and the float pitch that holds them
-        fo.s_words = (3 + (ncols_max - 1) * op.src_xstep) / 4 + 1;
-        fo.s_words_log2 = 0;
-        while ((1 << fo.s_words_log2) < fo.s_words) ++fo.s_words_log2;
-        fo.s_pitch = (fo.s_words * (4 / op.src_xstep) + 3) & ~3;   // samples per word = 4 / spacing; rows stay 16-byte aligned
+        // 16-byte chunks per staged row for the worst alignment, and the float pitch that holds their samples
+        fo.s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
+        fo.s_chunks_log2 = 0;
+        while ((1 << fo.s_chunks_log2) < fo.s_chunks) ++fo.s_chunks_log2;
+        fo.s_pitch = fo.s_chunks * (16 / op.src_xstep);            // samples per chunk = 16 / spacing (a multiple of 4)
         if ((fo.s_pitch & 31) == 0) fo.s_pitch += 4;                // keep consecutive rows off the same banks
 
         // tile height: as tall as shared memory allows (less vertical halo), a multiple of the warp count
@@ -831,7 +859,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         while (th > kWarps && th - kWarps >= op.dh) th -= kWarps;
         for (;; th -= kWarps) {
             fo.m_rows = rows_for(th, fo.tiles_y);
-            fo.smem_bytes = fused_smem_bytes(fo.m_rows, fo.s_pitch, fo.s_words, th, VT, SPAN);
+            fo.smem_bytes = fused_smem_bytes(fo.m_rows, fo.s_pitch, fo.s_chunks, th, VT, SPAN);
             if (fo.smem_bytes <= kSmemBudget || th == kWarps) break;
         }
         if (fo.smem_bytes > 226 * 1024) { err = "tile does not fit in shared memory"; delete fp; return nullptr; }
@@ -880,7 +908,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         SmemLayout lay{0, 0, 0, 0, 0};
         for (const FusedOp &b : fp->ops) {
             if (b.instance != a.instance || b.out_mode != a.out_mode) continue;
-            const SmemLayout l = smem_layout(b.m_rows, b.s_pitch, b.s_words, b.th, kInstances[b.instance].vt);
+            const SmemLayout l = smem_layout(b.m_rows, b.s_pitch, b.s_chunks, b.th, kInstances[b.instance].vt);
             lay.m_floats = std::max(lay.m_floats, l.m_floats); lay.s_floats = std::max(lay.s_floats, l.s_floats);
             lay.raw_words = std::max(lay.raw_words, l.raw_words); lay.cv_pairs = std::max(lay.cv_pairs, l.cv_pairs);
             lay.vp_ints = std::max(lay.vp_ints, l.vp_ints);
@@ -942,7 +970,9 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             q.vring = reinterpret_cast<const float *>(p->blob + fo.vring_off);
             q.vring_i = reinterpret_cast<const int *>(p->blob + fo.vring_i_off);
             q.vtaps = fo.vtaps;
-            q.s_pitch = fo.s_pitch; q.s_words = fo.s_words; q.s_words_log2 = fo.s_words_log2; q.m_rows = fo.m_rows;
+            q.s_pitch = fo.s_pitch; q.s_chunks = fo.s_chunks; q.s_chunks_log2 = fo.s_chunks_log2; q.m_rows = fo.m_rows;
+            q.src_lo = s.base - op.src_offset;
+            q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
             q.v_thr = fo.v_thr;
             q.src_mode = fo.src_mode; q.src_scale = fo.src_scale; q.h_addend = fo.h_addend;
             q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
@@ -951,7 +981,7 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
             std::copy(fo.tile_r0.begin(), fo.tile_r0.end(), q.tile_r0);
             std::copy(fo.tile_r1.begin(), fo.tile_r1.end(), q.tile_r1);
             tiles += fo.tiles_x * fo.tiles_y;
-            const SmemLayout l = smem_layout(fo.m_rows, fo.s_pitch, fo.s_words, fo.th, vt);
+            const SmemLayout l = smem_layout(fo.m_rows, fo.s_pitch, fo.s_chunks, fo.th, vt);
             lay.m_floats = std::max(lay.m_floats, l.m_floats);
             lay.s_floats = std::max(lay.s_floats, l.s_floats);
             lay.raw_words = std::max(lay.raw_words, l.raw_words);

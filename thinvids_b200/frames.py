@@ -149,3 +149,12 @@ CONFIGS = {
     "C4": ScaleConfig("C4", "yuv420p10le", 3840, 2160, "yuv420p10le", 1920, 1080, "lanczos", 64),
     "C5": ScaleConfig("C5", "yuv420p", 1920, 1080, "yuv420p", 3840, 2160, "lanczos", 240),
 }
+# Shapes the reference's worker produces by default (worker/tasks.py:62-65) and planar / 8-bit variants of the
+# named configs, for profiling; not BASELINE.json bench lines.
+EXTRA_CONFIGS = {
+    "W1080": ScaleConfig("W1080", "yuv420p", 720, 480, "nv12", 1620, 1080, "bicubic", 300),
+    "W720": ScaleConfig("W720", "yuv420p", 1920, 1080, "nv12", 1280, 720, "bicubic", 128),
+    "C3P": ScaleConfig("C3P", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "area", 64),
+    "C4P8": ScaleConfig("C4P8", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "lanczos", 64),
+}
+CONFIGS.update(EXTRA_CONFIGS)
