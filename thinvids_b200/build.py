@@ -14,10 +14,11 @@ import sys
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libtvscale.so")
-SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused.cu", "tvscale_abi.cu"]
-HEADERS = ["filter_tables.h", "tvs_internal.h", os.path.join("..", "..", "include", "tvscale.h")]
+SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused_w256.cu", "kernels_fused_w128.cu", "tvscale_abi.cu"]
+HEADERS = ["filter_tables.h", "tvs_internal.h", "kernels_fused_impl.cuh", os.path.join("..", "..", "include", "tvscale.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "--fmad=true"]
+NVCC_FLAGS += os.environ.get("TVS_NVCC_EXTRA", "").split()   # experiments, e.g. -DTVS_HALVES=1
 
 
 def _nvcc() -> str:
@@ -38,19 +39,28 @@ def needs_build() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not needs_build():
         return LIB
-    objs = []
     build_dir = os.path.join(PKG, "build")
     os.makedirs(build_dir, exist_ok=True)
-    for s in SOURCES:
-        obj = os.path.join(build_dir, os.path.splitext(s)[0] + ".o")
-        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, s), "-o", obj]
-        if s.endswith(".cu"):
-            cmd += ["-Xptxas", "-v"] if verbose else []
-        else:
-            cmd += ["-x", "cu"] if False else []
-        if verbose:
+
+    def compile_one(src):
+        obj = os.path.join(build_dir, os.path.splitext(src)[0] + ".o")
+        cmd = [_nvcc(), *NVCC_FLAGS, "-c", os.path.join(CSRC, src), "-o", obj]
+        if verbose and src.endswith(".cu"):
+            cmd += ["-Xptxas", "-v"]
+        proc = subprocess.run(cmd, capture_output=True, text=True)
+        return src, obj, cmd, proc
+
+    from concurrent.futures import ThreadPoolExecutor
+    with ThreadPoolExecutor(max_workers=min(len(SOURCES), os.cpu_count() or 1)) as pool:
+        results = list(pool.map(compile_one, SOURCES))
+    objs = []
+    for src, obj, cmd, proc in results:
+        if verbose or proc.returncode:
             print(" ".join(cmd))
-        subprocess.check_call(cmd)
+            sys.stdout.write(proc.stdout)
+            sys.stdout.write(proc.stderr)
+        if proc.returncode:
+            raise subprocess.CalledProcessError(proc.returncode, cmd)
         objs.append(obj)
     tmp = LIB + ".tmp.%d" % os.getpid()
     subprocess.check_call([_nvcc(), "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a",

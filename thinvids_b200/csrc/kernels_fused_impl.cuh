@@ -29,9 +29,24 @@
 namespace tvs {
 namespace {
 
+// This file is compiled twice (kernels_fused_w256.cu, kernels_fused_w128.cu) with TVS_HALVES = 2 and 1: 256-column
+// tiles with 2 CTAs of 256 threads per SM (best for up-scales: 8 samples per lane per row in the vertical pass) and
+// 128-column tiles with 4 CTAs of 128 threads per SM (best for down-scales, whose source footprint is what fills
+// shared memory).  TVS_FUSED_FN gives the entry points of each build their own names.
+#ifndef TVS_HALVES
+#error "include this file from kernels_fused_w256.cu / kernels_fused_w128.cu"
+#endif
+#ifndef TVS_CTAS_PER_SM
+#define TVS_CTAS_PER_SM (TVS_HALVES == 2 ? 2 : 4)
+#endif
+#define TVS_CAT2(a, b) a##b
+#define TVS_CAT(a, b) TVS_CAT2(a, b)
+#define TVS_FUSED_FN(name) TVS_CAT(name, TVS_FUSED_SUFFIX)
+constexpr int kHalves = TVS_HALVES;        // 128-column halves per tile: 4 warps each in the H pass
+constexpr int kCtasPerSM = TVS_CTAS_PER_SM;
 constexpr int kHalfW = 128;               // columns per half tile: lane * 4 + k
-constexpr int kTileW = 2 * kHalfW;
-constexpr int kThreads = 256;
+constexpr int kTileW = kHalves * kHalfW;
+constexpr int kThreads = 128 * kHalves;
 constexpr int kWarps = kThreads / 32;
 constexpr int kGroup = 4;                 // adjacent output columns per lane
 constexpr int kGroupsPerHalf = kHalfW / kGroup;
@@ -47,7 +62,7 @@ __constant__ int kDither128i[8][8] = {
     {32, 64, 56, 88, 38, 70, 62, 94},  {96, 0, 120, 24, 102, 6, 126, 30},
     {48, 80, 40, 72, 54, 86, 46, 78},  {112, 16, 104, 8, 118, 22, 110, 14},
 };
-constexpr size_t kSmemBudget = 112 * 1024;  // two CTAs per SM
+constexpr size_t kSmemBudget = (227 * 1024) / kCtasPerSM - 1536;   // shared memory per CTA so that kCtasPerSM fit on an SM
 
 struct FusedOpParams {
     const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
@@ -471,20 +486,20 @@ __device__ __forceinline__ void prefetch_tile_tables(const FusedLaunchParams &P,
 template <int SPAN>
 __device__ __forceinline__ void prefetch_hcoef(const FusedOpParams &op, int tx, float4 *cd, int *hb, int tid) {
     constexpr int N4 = kGroup * SPAN / 4;
-    const int g0 = tx * 2 * kGroupsPerHalf;
-    for (int i = tid; i < 2 * kGroupsPerHalf * N4; i += kThreads) {
+    const int g0 = tx * kHalves * kGroupsPerHalf;
+    for (int i = tid; i < kHalves * kGroupsPerHalf * N4; i += kThreads) {
         const int grp = i / N4, part = i - grp * N4;     // consecutive threads read consecutive 16-byte pieces
         const int g = min(g0 + grp, op.n_groups - 1);
         const int half = grp >> 5, ln = grp & 31;
         cp_async16(cd + (half * N4 + part) * 32 + ln, op.hdense + static_cast<size_t>(g) * (kGroup * SPAN) + 4 * part);
     }
-    if (tid < 2 * kGroupsPerHalf) hb[tid] = __ldg(op.hbase + min(g0 + tid, op.n_groups - 1)) - op.tile_c0[tx];
+    if (tid < kHalves * kGroupsPerHalf) hb[tid] = __ldg(op.hbase + min(g0 + tid, op.n_groups - 1)) - op.tile_c0[tx];
 }
 
 // Persistent kernel: each CTA walks a contiguous range of tiles.  While tile i is filtered, the source bytes and
 // row tables of tile i+1 stream into the other half of a double buffer (cp.async), so no phase waits on HBM.
 template <int SPAN, int VT, int OUT>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, kCtasPerSM)
 fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     static_assert(SPAN % 2 == 0, "the packed horizontal pass pairs up source samples");
     constexpr int N4 = kGroup * SPAN / 4;
@@ -498,7 +513,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
     f32x2 *CVB = reinterpret_cast<f32x2 *>(RAW + 2 * P.raw_words);  // 2 x [th + 1][VT] ring-ordered (g, g) pairs
     int *VPB = reinterpret_cast<int *>(CVB + 2 * P.cv_pairs);       // 2 x [th + 1]  first source row per output row
     float4 *CD = reinterpret_cast<float4 *>(VPB + 2 * P.vp_ints);   // [2][N4][32]   horizontal coefficients of the column
-    int *HB = reinterpret_cast<int *>(CD + 2 * N4 * 32);            // [64]          span start of each column group
+    int *HB = reinterpret_cast<int *>(CD + kHalves * N4 * 32);            // [64]          span start of each column group
 
     // contiguous share of the tile list
     const int per = P.total_tiles / gridDim.x, extra = P.total_tiles % gridDim.x;
@@ -658,7 +673,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
             const f32x2 *cv = CVB + buf * P.cv_pairs + (ya - y0) * VT;
             const int *vp = VPB + buf * P.vp_ints + (ya - y0);
             const int xa = x0 + 4 * lane;
-            constexpr bool kDual = VT <= 8;   // two register rings of VT rows x 4 columns only fit up to 8 taps
+            constexpr bool kDual = kHalves == 2 && VT <= 8;   // two register rings of VT rows x 4 columns only fit up to 8 taps
             if constexpr (kDual) {
                 if (words && x0 + kTileW <= dw)
                     vertical_strip<VT, kStoreBoth, OUT, true>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, kSample, dw, xa, true,
@@ -670,7 +685,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                     vertical_strip<VT, kStoreGeneric, OUT, true>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, dst_xstep, dw, xa,
                                                                  x0 + kHalfW < dw, op.v_thr, lane, op.dst_shift, op.dither_xoff);
             } else {
-                for (int h = 0; h < 2 && x0 + h * kHalfW < dw; ++h) {
+                for (int h = 0; h < kHalves && x0 + h * kHalfW < dw; ++h) {
                     const int xh = xa + h * kHalfW;
                     if (words && x0 + (h + 1) * kHalfW <= dw)
                         vertical_strip<VT, kStoreLeft, OUT, false>(M + h * kHalfW, cv, vp, exact, r0, ya, yb, drow, dst_pitch, kSample, dw,
@@ -741,7 +756,7 @@ SmemLayout smem_layout(int m_rows, int s_pitch, int s_chunks, int th, int vt) {
     return l;
 }
 size_t layout_bytes(const SmemLayout &l, int span) {
-    const size_t hcoef = static_cast<size_t>(2 * kGroupsPerHalf) * (kGroup * span + 1) * 4;   // CD + HB
+    const size_t hcoef = static_cast<size_t>(kHalves * kGroupsPerHalf) * (kGroup * span + 1) * 4;   // CD + HB
     return static_cast<size_t>(l.m_floats + l.s_floats + 2 * l.raw_words + 2 * l.vp_ints) * 4 + static_cast<size_t>(2 * l.cv_pairs) * 8 + hcoef;
 }
 size_t fused_smem_bytes(int m_rows, int s_pitch, int s_chunks, int th, int vt, int span) {
@@ -763,7 +778,7 @@ double vertical_error_bound(const AxisTable &v, int vt_inst) {
 
 }  // namespace
 
-FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err) {
+FusedPlan *TVS_FUSED_FN(fused_plan_create)(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err) {
     std::vector<uint8_t> blob;
     auto fp = new FusedPlan;
     fp->device = device;
@@ -835,7 +850,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
         }
         int ncols_max = 0;
         for (int tx = 0; tx < fo.tiles_x; ++tx) {
-            const int ga = tx * 2 * kGroupsPerHalf, gb = std::min(ga + 2 * kGroupsPerHalf - 1, n_groups - 1);
+            const int ga = tx * kHalves * kGroupsPerHalf, gb = std::min(ga + kHalves * kGroupsPerHalf - 1, n_groups - 1);
             ncols_max = std::max(ncols_max, hbase[gb] + SPAN - hbase[ga]);
         }
         // 16-byte chunks per staged row for the worst alignment, and the float pitch that holds their samples
@@ -883,7 +898,7 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
             }
         }
         for (int tx = 0; tx < fo.tiles_x; ++tx) {
-            const int ga = tx * 2 * kGroupsPerHalf, gb = std::min(ga + 2 * kGroupsPerHalf - 1, n_groups - 1);
+            const int ga = tx * kHalves * kGroupsPerHalf, gb = std::min(ga + kHalves * kGroupsPerHalf - 1, n_groups - 1);
             fo.tile_c0.push_back(static_cast<short>(hbase[ga]));
             fo.tile_nc.push_back(static_cast<short>(hbase[gb] + SPAN - hbase[ga]));
         }
@@ -931,17 +946,17 @@ FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], i
     return fp;
 }
 
-void fused_plan_destroy(FusedPlan *p) {
+void TVS_FUSED_FN(fused_plan_destroy)(FusedPlan *p) {
     if (!p) return;
     if (p->blob) cudaFree(p->blob);
     delete p;
 }
 
-size_t fused_plan_device_bytes(const FusedPlan *p) { return p ? p->blob_bytes : 0; }
+size_t TVS_FUSED_FN(fused_plan_device_bytes)(const FusedPlan *p) { return p ? p->blob_bytes : 0; }
 
-bool fused_plan_prefers_two_pass(const FusedPlan *p) { return p && p->prefer_two_pass; }
+bool TVS_FUSED_FN(fused_plan_prefers_two_pass)(const FusedPlan *p) { return p && p->prefer_two_pass; }
 
-int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
+int TVS_FUSED_FN(fused_launch)(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
                  int n_frames, cudaStream_t stream) {
     int launched = 0;
     std::vector<bool> done(p->ops.size(), false);
@@ -995,7 +1010,7 @@ int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_view
         if (const char *dbg = getenv("TVS_DEBUG_SKIP")) lp.debug_skip = atoi(dbg);
         const size_t smem = layout_bytes(lay, kInstances[p->ops[i].instance].span);
         // persistent CTAs: two per SM, each walking a contiguous share of the tiles
-        const int grid = std::min(lp.total_tiles, 2 * p->sm_count);
+        const int grid = std::min(lp.total_tiles, kCtasPerSM * p->sm_count);
         kInstances[p->ops[i].instance].fn[p->ops[i].out_mode]<<<grid, kThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
         ++launched;

@@ -73,14 +73,18 @@ int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceT
                          size_t mid_frame_stride, int n_frames, cudaStream_t stream);
 int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
 
-// ---- fused tile kernel (kernels_fused.cu) --------------------------------------------------------
+// ---- fused tile kernel (kernels_fused_impl.cuh, built as two variants) ---------------------------------
 struct FusedPlan;  // opaque, owned by the context
-FusedPlan *fused_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);
-void fused_plan_destroy(FusedPlan *p);
-size_t fused_plan_device_bytes(const FusedPlan *p);
-bool fused_plan_prefers_two_pass(const FusedPlan *p);
-// Launches the fused kernels for every scale op of the plan.  Returns kernels launched or -1.
-int fused_launch(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[],
-                 int n_frames, cudaStream_t stream);
+#define TVS_DECLARE_FUSED(SFX)                                                                                              \
+    FusedPlan *fused_plan_create##SFX(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);      \
+    void fused_plan_destroy##SFX(FusedPlan *p);                                                                             \
+    size_t fused_plan_device_bytes##SFX(const FusedPlan *p);                                                                \
+    bool fused_plan_prefers_two_pass##SFX(const FusedPlan *p);                                                              \
+    /* Launches the fused kernels for every scale op of the plan.  Returns kernels launched or -1. */                       \
+    int fused_launch##SFX(const FusedPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], \
+                          int n_frames, cudaStream_t stream);
+TVS_DECLARE_FUSED(_w256)   // 256-column tiles, 2 CTAs x 256 threads per SM
+TVS_DECLARE_FUSED(_w128)   // 128-column tiles, 4 CTAs x 128 threads per SM
+#undef TVS_DECLARE_FUSED
 
 }  // namespace tvs
