@@ -5,6 +5,8 @@
 // kernel (kernels_fused.cu) falls back to when a tile would not fit in shared memory.  It follows
 // SURVEY.md A.3 step by step: hScale8To15_c / hScale16To15_c, then yuv2planeX_8_c / yuv2planeX_10_c /
 // yuv2nv12cX_c, and A.4 for the unscaled converters (libswscale swscale_unscaled.c planarCopyWrapper).
+#include <algorithm>
+
 #include "tvs_internal.h"
 
 namespace tvs {
@@ -98,6 +100,68 @@ repack_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sfram
     *reinterpret_cast<DstT *>(dst + f * dframe + y * dpitch + static_cast<ptrdiff_t>(x) * dxstep) = static_cast<DstT>(v);
 }
 
+// ---- memcpy-class fast paths of the same-size converters (the DVD production shape: yuv420p -> nv12 at equal size,
+// worker/tasks.py:62-63) -------------------------------------------------------------------------------------------
+// Plain 2-D copy of `row_bytes` per row.  V = bytes per thread access (16, 4 or 1), chosen by the launcher from the
+// alignment of both sides; the row tail that does not fill a vector is copied bytewise by the last threads.
+template <int V>
+__global__ void __launch_bounds__(256)
+copy_rows_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, uint8_t *__restrict__ dst, ptrdiff_t dpitch,
+                 ptrdiff_t dframe, int row_bytes, int rows) {
+    // rows are short (a 720-byte DVD luma row is 45 vectors), so threads are spread over (row, vector) pairs
+    const int nvec = row_bytes / V, slots = nvec + (row_bytes % V ? 1 : 0);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, i = idx - y * slots;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const uint8_t *s = src + f * sframe + y * spitch;
+    uint8_t *d = dst + f * dframe + y * dpitch;
+    if (i < nvec) {
+        if (V == 16) reinterpret_cast<uint4 *>(d)[i] = __ldg(reinterpret_cast<const uint4 *>(s) + i);
+        else if (V == 4) reinterpret_cast<unsigned *>(d)[i] = __ldg(reinterpret_cast<const unsigned *>(s) + i);
+        else d[i] = __ldg(s + i);
+    } else {
+        for (int k = nvec * V; k < row_bytes; ++k) d[k] = s[k];   // the bytes that do not fill a vector
+    }
+}
+
+// Two planar chroma planes -> one interleaved plane (T = sample type).  Each thread reads 8 bytes of U and 8 of V and
+// writes 16 interleaved bytes when everything is aligned for it; otherwise one sample pair per thread.
+template <typename T, bool VEC>
+__global__ void __launch_bounds__(256)
+interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__restrict__ v, ptrdiff_t spitch_u, ptrdiff_t spitch_v,
+                  ptrdiff_t sframe_u, ptrdiff_t sframe_v, uint8_t *__restrict__ dst, ptrdiff_t dpitch, ptrdiff_t dframe, int w,
+                  int rows) {
+    constexpr int PER = VEC ? 8 / static_cast<int>(sizeof(T)) : 1;   // samples of each plane per thread
+    const int ngroups = w / PER, slots = ngroups + (w % PER ? 1 : 0);
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, i = idx - y * slots;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const T *us = reinterpret_cast<const T *>(u + f * sframe_u + y * spitch_u);
+    const T *vs = reinterpret_cast<const T *>(v + f * sframe_v + y * spitch_v);
+    T *d = reinterpret_cast<T *>(dst + f * dframe + y * dpitch);
+    if (i < ngroups) {
+        if (VEC) {
+            const uint2 a = __ldg(reinterpret_cast<const uint2 *>(us) + i), b = __ldg(reinterpret_cast<const uint2 *>(vs) + i);
+            uint4 o;
+            if (sizeof(T) == 1) {
+                o.x = __byte_perm(a.x, b.x, 0x5140); o.y = __byte_perm(a.x, b.x, 0x7362);
+                o.z = __byte_perm(a.y, b.y, 0x5140); o.w = __byte_perm(a.y, b.y, 0x7362);
+            } else {
+                o.x = __byte_perm(a.x, b.x, 0x5410); o.y = __byte_perm(a.x, b.x, 0x7632);
+                o.z = __byte_perm(a.y, b.y, 0x5410); o.w = __byte_perm(a.y, b.y, 0x7632);
+            }
+            reinterpret_cast<uint4 *>(d)[i] = o;
+        } else {
+            d[2 * i] = us[i];
+            d[2 * i + 1] = vs[i];
+        }
+    } else {
+        for (int k = ngroups * PER; k < w; ++k) { d[2 * k] = us[k]; d[2 * k + 1] = vs[k]; }   // samples that do not fill a vector
+    }
+}
+
 inline dim3 plane_grid(int w, int h, int n_frames) { return dim3((w + 255) / 256, h, n_frames); }
 
 }  // namespace
@@ -138,6 +202,38 @@ int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &ds
     else if (op.dst_bits == 8) TVS_REPACK(uint16_t, uint8_t);
     else TVS_REPACK(uint16_t, uint16_t);
 #undef TVS_REPACK
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+namespace {
+inline bool aligned_for(const void *p, ptrdiff_t pitch, ptrdiff_t frame, int n_frames, int a) {
+    return ((reinterpret_cast<uintptr_t>(p) | static_cast<uintptr_t>(pitch) | (n_frames > 1 ? static_cast<uintptr_t>(frame) : 0u)) & (a - 1)) == 0;
+}
+}  // namespace
+
+int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream) {
+    const int v = aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 16) && aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16) ? 16
+                : aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 4) && aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 4) ? 4 : 1;
+    const int slots = row_bytes / v + (row_bytes % v ? 1 : 0);
+    const dim3 grid((static_cast<unsigned>(slots) * rows + 255) / 256, 1, n_frames);
+    if (v == 16) copy_rows_kernel<16><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, row_bytes, rows);
+    else if (v == 4) copy_rows_kernel<4><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, row_bytes, rows);
+    else copy_rows_kernel<1><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, row_bytes, rows);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,
+                      cudaStream_t stream) {
+    const bool vec = aligned_for(u.base, u.pitch, u.frame_stride, n_frames, 8) && aligned_for(v.base, v.pitch, v.frame_stride, n_frames, 8) &&
+                     aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16);
+    const int per = vec ? 8 / sample_bytes : 1;
+    const int slots = w / per + (w % per ? 1 : 0);
+    const dim3 grid((static_cast<unsigned>(slots) * rows + 255) / 256, 1, n_frames);
+#define TVS_ILV(T, V) interleave_kernel<T, V><<<grid, 256, 0, stream>>>(u.base, v.base, u.pitch, v.pitch, u.frame_stride, v.frame_stride, \
+                                                                      dst.base, dst.pitch, dst.frame_stride, w, rows)
+    if (sample_bytes == 1) { if (vec) TVS_ILV(uint8_t, true); else TVS_ILV(uint8_t, false); }
+    else { if (vec) TVS_ILV(uint16_t, true); else TVS_ILV(uint16_t, false); }
+#undef TVS_ILV
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -72,6 +72,10 @@ int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceT
 int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceTable &v, const int16_t *mid,
                          size_t mid_frame_stride, int n_frames, cudaStream_t stream);
 int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
+// memcpy-class special cases of the same-size converters
+int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream);
+int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,
+                      cudaStream_t stream);
 
 // ---- fused tile kernel (kernels_fused_impl.cuh, built as two variants) ---------------------------------
 struct FusedPlan;  // opaque, owned by the context

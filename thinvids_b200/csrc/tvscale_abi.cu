@@ -245,9 +245,25 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     const Plan &plan = c->plan;
 
     for (size_t i = 0; i < plan.ops.size(); ++i) {
-        if (plan.ops[i].kind == kOpScale) continue;
-        if (launch_repack(plan.ops[i], sv[i], dv[i], n_frames, stream) < 0)
-            return cuda_fail(cudaGetLastError(), "repack kernel launch");
+        const PlaneOp &op = plan.ops[i];
+        if (op.kind == kOpScale) continue;
+        int rc;
+        const int bytes = op.src_bits > 8 ? 2 : 1;
+        const bool plain = op.kind == kOpCopy && op.src_bits == op.dst_bits && op.src_shift == op.dst_shift;
+        if (plain && op.src_xstep == bytes && op.dst_xstep == bytes) {
+            rc = launch_copy_rows(sv[i], dv[i], op.dw * bytes, op.dh, n_frames, stream);                 // plane -> plane
+        } else if (plain && op.src_xstep == bytes && op.dst_xstep == 2 * bytes && op.dst_offset == 0 && i + 1 < plan.ops.size() &&
+                   plan.ops[i + 1].kind == kOpCopy && plan.ops[i + 1].dst_plane == op.dst_plane && plan.ops[i + 1].src_xstep == bytes) {
+            rc = launch_interleave(sv[i], sv[i + 1], dv[i], bytes, op.dw, op.dh, n_frames, stream);       // U, V -> UV
+            ++i;                                                                                          // consumed the V op too
+        } else if (plain && op.src_xstep == 2 * bytes && op.dst_xstep == 2 * bytes && op.src_offset == 0 && op.dst_offset == 0 &&
+                   i + 1 < plan.ops.size() && plan.ops[i + 1].src_plane == op.src_plane && plan.ops[i + 1].dst_plane == op.dst_plane) {
+            rc = launch_copy_rows(sv[i], dv[i], 2 * op.dw * bytes, op.dh, n_frames, stream);              // UV -> UV as one byte plane
+            ++i;
+        } else {
+            rc = launch_repack(op, sv[i], dv[i], n_frames, stream);
+        }
+        if (rc < 0) return cuda_fail(cudaGetLastError(), "repack kernel launch");
         ++c->launches;
     }
     if (!plan.any_scale) return 0;
