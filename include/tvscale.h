@@ -148,7 +148,7 @@ TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size
  * Plan introspection for benchmarks and tests.
  *   TVS_INFO_KERNEL_LAUNCHES  kernels launched by this context so far (monotonic)
  *   TVS_INFO_PATH             0 = fused tile kernel, 1 = two-pass kernels through device scratch,
- *                             2 = same-size repack only
+ *                             2 = same-size repack only, 3 = streaming (line-buffer) kernel for vertical down-scales
  *   TVS_INFO_SCRATCH_BYTES    device scratch currently owned by the context
  *   TVS_INFO_SRC_FRAME_BYTES / TVS_INFO_DST_FRAME_BYTES   tightly packed frame sizes
  */
@@ -156,7 +156,8 @@ enum { TVS_INFO_KERNEL_LAUNCHES = 0, TVS_INFO_PATH = 1, TVS_INFO_SCRATCH_BYTES =
        TVS_INFO_SRC_FRAME_BYTES = 3, TVS_INFO_DST_FRAME_BYTES = 4 };
 TVS_API long long tvs_info(const tvs_ctx *ctx, int what);
 
-/* Force a kernel path for testing: -1 = automatic, 0 = fused, 1 = two-pass.  Returns 0 or -EINVAL. */
+/* Force a kernel path for testing: -1 = automatic, 0 = fused tiles, 1 = two-pass, 2 = streaming.
+ * Returns 0, -EINVAL, or -ENOSYS when the requested kernel does not handle this context's shape. */
 TVS_API int tvs_set_path(tvs_ctx *ctx, int path);
 
 /* Message describing the last failure on the calling thread ("" if none). */

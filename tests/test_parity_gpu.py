@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 HASHES = json.load(open(os.path.join(GOLD, "swscale_hashes.json")))["cases"]
 SMALL = json.load(open(os.path.join(GOLD, "small_cases.json")))
-PATHS = ("auto", "two-pass", "fused")
+PATHS = ("auto", "two-pass", "fused", "stream")
 
 
 def _scaler(c, **kw):
@@ -31,7 +31,7 @@ def _use_path(s, path):
     try:
         s.set_path(path)
     except tv_lib.TvscaleError:
-        if path == "fused":
+        if path in ("fused", "stream"):
             return False
         raise
     return True

@@ -1,0 +1,521 @@
+// Streaming ("line buffer") kernel for vertical down-scales.
+//
+// The tile kernel (kernels_fused_impl.cuh) pays for every tile with a vertical halo, a register-ring warm-up and
+// per-tile bookkeeping.  That is cheap when a tile's source footprint is small (up-scales) and expensive when the
+// source is the bulk of the data: a 1080p -> 720p tile only fits 16 output rows in shared memory.  Here a CTA owns
+// a 128-column strip of one plane of one frame and walks down the whole height instead:
+//
+//   for each block of KB source rows:   cp.async the raw rows (double buffered, one block ahead)
+//                                       convert to floats                          -> S      (own chunks, no barrier)
+//                                       horizontal pass of those rows              -> M ring (barrier before and after)
+//                                       vertical pass of every output row whose window is now complete -> HBM
+//
+// The intermediate lives in a shared-memory ring of RM rows (a power of two >= the live window + KB), so no source
+// row is ever filtered twice, the lane's horizontal coefficients stay in registers for the whole strip, and shared
+// memory per CTA is a few tens of KB (5+ CTAs per SM).  Vertical windows of consecutive output rows barely overlap
+// when down-scaling, so the vertical pass simply reads its VT rows from the ring (no register ring to maintain).
+// Arithmetic, exactness argument and output rules are those of the tile kernel (scale_device.cuh).
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+#include "scale_device.cuh"
+#include "tvs_internal.h"
+
+namespace tvs {
+namespace {
+
+constexpr int kStripW = 128;              // output columns per CTA: lane * 4 + k
+constexpr int kSThreads = 128;
+constexpr int kSWarps = kSThreads / 32;
+constexpr int kMaxStrips = 96;
+constexpr int kMaxStreamOps = 3;
+constexpr int kStreamCtasPerSM = 5;
+constexpr size_t kStreamSmemBudget = (227 * 1024) / kStreamCtasPerSM - 1536;
+
+struct StreamOpParams {
+    const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
+    uint8_t *dst; ptrdiff_t dst_pitch, dst_fstride; int dst_xstep;
+    int sw, sh, dw, dh;
+    int strips, strip_begin;
+    const float *hcoef;    // [dw][HT]             c * 2^-(23+hshift) in tap order (zero padded to HT)
+    const int *hpos;       // [dw]                 first source column of each output column
+    const int *vpos;       // [dh]
+    const float *vpair;    // [dh][VT][2]          (g, g) * 2^107 in tap order
+    const int *vint;       // [dh][VT]             the same coefficients as integers (exact path)
+    const int *block_yend; // [n_blocks]           output rows complete once source block b has been filtered
+    int kb, n_blocks;      // source rows per block
+    int rm_mask;           // rows of the intermediate ring - 1 (power of two)
+    int s_pitch, s_chunks, s_chunks_log2;
+    const uint8_t *src_lo; size_t src_extent;
+    float v_thr;
+    int src_mode; float src_scale, h_addend;
+    int dst_shift, dither_xoff;
+    short strip_c0[kMaxStrips], strip_nc[kMaxStrips];
+};
+
+struct StreamLaunchParams {
+    StreamOpParams op[kMaxStreamOps];
+    int n_ops;
+    int m_floats, s_floats, raw_words;   // shared-memory layout (element counts), maxima over the planes of the launch
+};
+
+template <int VT, int OUT>
+__device__ __noinline__ uint2 exact_fixup_ring(const float *m_col, int mask, int first, const int *coef, float v_thr, float r0,
+                                               float r1, float r2, float r3, int4 dither, int dst_shift, uint2 packed) {
+    unsigned word[2] = {packed.x, packed.y};
+    const float r[4] = {r0, r1, r2, r3};
+    const int d[4] = {dither.x, dither.y, dither.z, dither.w};
+    int a[4] = {0, 0, 0, 0};
+    for (int j = 0; j < VT; ++j) {
+        const float4 t = *reinterpret_cast<const float4 *>(m_col + ((first + j) & mask) * kStripW);
+        const int c = __ldg(coef + j);
+        a[0] += subnormal_to_int(t.x) * c; a[1] += subnormal_to_int(t.y) * c;
+        a[2] += subnormal_to_int(t.z) * c; a[3] += subnormal_to_int(t.w) * c;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (fabsf(r[k]) >= v_thr) {
+            const int bias = OUT == kOutU8 ? (64 << 12) : OUT == kOutU8Dither ? (d[k] << 12) : (1 << 16);
+            const unsigned v = static_cast<unsigned>(min(max((a[k] + bias) >> OutRule<OUT>::kShift, 0), OutRule<OUT>::kMax));
+            if (OUT == kOutU10) {
+                const int sh = 16 * (k & 1);
+                word[k >> 1] = (word[k >> 1] & ~(0xffffu << sh)) | ((v << dst_shift) << sh);
+            } else {
+                word[0] = (word[0] & ~(0xffu << (8 * k))) | (v << (8 * k));
+            }
+        }
+    }
+    return make_uint2(word[0], word[1]);
+}
+
+// cp.async the raw bytes of source rows [r_b, r_b + kb) of the strip's footprint (see prefetch_tile_source of the tile
+// kernel for the chunk / alignment rules; identical here).
+__device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const uint8_t *strip_base, const uint8_t *lo, const uint8_t *hi,
+                                               int r_b, int rows, int last_byte, unsigned *raw, int tid) {
+    const int clog = min(op.s_chunks_log2, 7), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
+    const ptrdiff_t pitch = op.src_pitch;
+    const uint8_t *base = strip_base + static_cast<ptrdiff_t>(r_b) * pitch;
+    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(base)) & 15u;
+    const unsigned pmod = static_cast<unsigned>(pitch) & 15u;
+    const int rstep = kSThreads >> clog;
+    for (int ch = tid & cmask; ch < s_chunks; ch += 1 << clog) {
+        int row = tid >> clog;
+        uint4 *dst = reinterpret_cast<uint4 *>(raw) + row * s_chunks + ch;
+        const uint8_t *src = base + row * pitch + 16 * ch;
+        unsigned mis = (mis0 + row * pmod) & 15u;
+        const unsigned mstep = (rstep * pmod) & 15u;
+        for (; row < rows; row += rstep, dst += rstep * s_chunks, src += rstep * pitch, mis = (mis + mstep) & 15u) {
+            const int first = 16 * ch - static_cast<int>(mis);
+            const uint8_t *g = src - mis;
+            if (first > last_byte) {
+                *dst = make_uint4(0u, 0u, 0u, 0u);
+            } else if (g >= lo && g + 16 <= hi) {
+                cp_async16(dst, g);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+                    if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
+                    else *d = 0u;
+                }
+            }
+        }
+    }
+}
+
+// Raw words -> float samples of S.  Consecutive threads take consecutive 4-byte words, so the 16-byte stores of a
+// warp land on consecutive banks (the caller has made the copied chunks visible with a barrier).
+__device__ __forceinline__ void convert_block(const StreamOpParams &op, const unsigned *raw, float *S, int rows, unsigned mis0, unsigned pmod,
+                                              int tid) {
+    const int words = op.s_chunks * 4, s_pitch = op.s_pitch;
+    const int wlog = min(op.s_chunks_log2 + 2, 7), wmask = (1 << wlog) - 1;
+    const int rstep = kSThreads >> wlog;
+    const int src_mode = op.src_mode;
+    const float sscale = op.src_scale;
+    for (int w = tid & wmask; w < words; w += 1 << wlog) {
+        int row = tid >> wlog;
+        const unsigned *rw = raw + row * words + w;
+        if (src_mode == kSrcU8) {              // four samples per word
+            float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + w;
+            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 4)) {
+                const unsigned v = *rw;
+                *out = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u), byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+            }
+        } else if (src_mode == kSrcU8Pair) {   // interleaved 8-bit chroma: this plane is every other byte
+            float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
+            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 2)) {
+                const unsigned p = (mis0 + row * pmod) & 1u;
+                const unsigned v = *rw;
+                *out = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
+            }
+        } else if (src_mode == kSrcU16) {      // two 16-bit samples per word, centred on 512
+            float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
+            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 2)) {
+                const unsigned v = *rw;
+                *out = make_float2(fmaf(byte_to_float(v, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v, 0x7432u), sscale, -512.0f));
+            }
+        } else {                               // interleaved 16-bit chroma: one sample of this plane per word
+            float *out = S + row * s_pitch + w;
+            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * s_pitch) {
+                const unsigned hi = (mis0 + row * pmod) & 2u;
+                *out = fmaf(byte_to_float(*rw, hi ? 0x7432u : 0x7410u), sscale, -512.0f);
+            }
+        }
+    }
+}
+
+template <int HT, int VT, int OUT>
+__global__ void __launch_bounds__(kSThreads, 4)
+stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
+    extern __shared__ __align__(16) float smem[];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+
+    int sx = blockIdx.x, oi = 0;
+    if (P.n_ops > 1 && sx >= P.op[1].strip_begin) oi = 1;
+    if (P.n_ops > 2 && sx >= P.op[2].strip_begin) oi = 2;
+    const StreamOpParams &op = P.op[oi];
+    sx -= op.strip_begin;
+    const int f = blockIdx.y;
+
+    float *M = smem;                                                // [rm_mask + 1][128] intermediate ring, t * 2^-149
+    float *S = M + P.m_floats;                                      // [kb][s_pitch]      float samples of the current block
+    unsigned *RAW = reinterpret_cast<unsigned *>(S + P.s_floats);   // 2 x [kb][s_chunks] raw 16-byte chunks
+
+    const int dw = op.dw, dh = op.dh, sh = op.sh, kb = op.kb, mask = op.rm_mask;
+    const int x0 = sx * kStripW;
+    const int c0 = op.strip_c0[sx], ncols = op.strip_nc[sx];
+    const int xs = op.src_xstep;
+    const int sample_bytes = op.src_mode >= kSrcU16 ? 2 : 1;
+    const int last_byte = (min(ncols, op.sw - c0) - 1) * xs + sample_bytes - 1;
+    const uint8_t *strip_base = op.src + f * op.src_fstride + static_cast<ptrdiff_t>(c0) * xs;   // row 0 of the footprint
+    const uint8_t *lo = op.src_lo + f * op.src_fstride, *hi = lo + op.src_extent;
+    const ptrdiff_t src_pitch = op.src_pitch;
+    const unsigned pmod = static_cast<unsigned>(src_pitch) & 15u;
+    const int raw_words = P.raw_words;
+
+    // Horizontal pass: a lane owns columns lane, lane + 32, lane + 64, lane + 96 of the strip.  When down-scaling,
+    // neighbouring output columns read windows that are a whole source step apart, so consecutive lanes touch
+    // consecutive shared-memory words (no bank conflicts) and every multiply-add is a real tap.  The coefficients of
+    // the four columns stay in registers for the whole strip.
+    float ck[4][HT];
+    int hstart[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int x = min(x0 + lane + 32 * k, dw - 1);
+        hstart[k] = __ldg(op.hpos + x) - c0;
+#pragma unroll
+        for (int j = 0; j < HT; ++j) ck[k][j] = __ldg(op.hcoef + static_cast<size_t>(x) * HT + j);
+    }
+    const int src_mode = op.src_mode;
+    const float h_addend = op.h_addend, t_max = __int_as_float(32767);
+
+    // rows the vertical pass may touch before they are produced (tap padding) must read as finite values
+    for (int i = tid; i < (mask + 1) * (kStripW / 4); i += kSThreads) reinterpret_cast<float4 *>(M)[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+
+    // vertical-pass constants
+    const int xq = x0 + 4 * lane;
+    const int dst_xstep = op.dst_xstep, dst_shift = op.dst_shift;
+    const ptrdiff_t dst_pitch = op.dst_pitch;
+    uint8_t *dst_base = op.dst + f * op.dst_fstride;
+    constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
+    const bool fast_store = dst_xstep == kSample && (dst_pitch & kAlign) == 0 && x0 + kStripW <= dw &&
+                            ((reinterpret_cast<uintptr_t>(dst_base) + static_cast<uintptr_t>(x0) * kSample) & kAlign) == 0;
+    const float v_thr = op.v_thr;
+    const int dcol = (xq + op.dither_xoff) & 7;
+    const float *m_col = M + 4 * lane;
+
+    prefetch_block(op, strip_base, lo, hi, 0, min(kb, sh), last_byte, RAW, tid);
+    cp_async_commit();
+    int y_next = 0;
+    for (int b = 0; b < op.n_blocks; ++b) {
+        const int r_b = b * kb, rows = min(kb, sh - r_b);
+        cp_async_wait_all();
+        if (b + 1 < op.n_blocks) {
+            prefetch_block(op, strip_base, lo, hi, r_b + kb, min(kb, sh - r_b - kb), last_byte, RAW + ((b + 1) & 1) * raw_words, tid);
+            cp_async_commit();
+        }
+        __syncthreads();   // the block's raw rows are visible to everyone; S is free (previous horizontal pass is over)
+        const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(strip_base + static_cast<ptrdiff_t>(r_b) * src_pitch)) & 15u;
+        convert_block(op, RAW + (b & 1) * raw_words, S, rows, mis0, pmod, tid);
+        __syncthreads();   // S holds the block
+
+        // ---- horizontal pass of the block's rows into the ring ----
+        for (int i = warp; i < rows; i += kSWarps) {
+            const unsigned mis = (mis0 + i * pmod) & 15u;
+            const float *srow = S + i * op.s_pitch + (src_mode == kSrcU8 ? mis : src_mode == kSrcU16Pair ? (mis >> 2) : (mis >> 1));
+            float *mrow = M + ((r_b + i) & mask) * kStripW + lane;
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const float *sp = srow + hstart[k];
+                float acc = 0.0f;
+#pragma unroll
+                for (int j = 0; j < HT; ++j) acc = fmaf(sp[j], ck[k][j], acc);
+                mrow[32 * k] = fminf(fma_rm(acc, 0x1p-126f, h_addend), t_max);   // floor(sum >> hshift), clamped above
+            }
+        }
+        __syncthreads();   // the ring holds every row up to r_b + rows
+
+        // ---- vertical pass of the output rows whose windows are now complete ----
+        const int y_end = __ldg(op.block_yend + b);
+        for (int y = y_next + warp; y < y_end; y += kSWarps) {
+            const int first = __ldg(op.vpos + y);
+            const f32x2 *gp = reinterpret_cast<const f32x2 *>(op.vpair) + static_cast<size_t>(y) * VT;
+            f32x2 a01 = 0ull, a23 = 0ull;
+            int4 dither = make_int4(0, 0, 0, 0);
+            if (OUT == kOutU8Dither) {
+                const int *tab = kDither128i[y & 7];
+                dither = make_int4(tab[dcol], tab[(dcol + 1) & 7], tab[(dcol + 2) & 7], tab[(dcol + 3) & 7]);
+                a01 = pack2(static_cast<float>(dither.x - 64) * 0x1p-30f, static_cast<float>(dither.y - 64) * 0x1p-30f);
+                a23 = pack2(static_cast<float>(dither.z - 64) * 0x1p-30f, static_cast<float>(dither.w - 64) * 0x1p-30f);
+            }
+#pragma unroll
+            for (int j = 0; j < VT; ++j) {
+                const Quad q = load_quad(m_col + ((first + j) & mask) * kStripW);
+                const f32x2 gg = __ldg(gp + j);
+                a01 = fma2(q.lo, gg, a01);
+                a23 = fma2(q.hi, gg, a23);
+            }
+            unsigned word[2];
+            float r[4];
+            const float worst = finish_quad<OUT>(a01, a23, dst_shift, word, r);
+            if (worst >= v_thr) {
+                const uint2 fx = exact_fixup_ring<VT, OUT>(m_col, mask, first, op.vint + static_cast<size_t>(y) * VT, v_thr, r[0], r[1], r[2],
+                                                           r[3], dither, dst_shift, make_uint2(word[0], word[1]));
+                word[0] = fx.x; word[1] = fx.y;
+            }
+            uint8_t *drow = dst_base + static_cast<ptrdiff_t>(y) * dst_pitch;
+            if (fast_store) store_quad_fast<OUT>(drow, xq, word);
+            else store_quad_slow<OUT>(drow, xq, dw, dst_xstep, word);
+        }
+        y_next = y_end;
+    }
+    (void)dh;
+}
+
+using StreamFn = void (*)(const StreamLaunchParams);
+struct StreamInstance { int ht, vt; StreamFn fn[3]; };   // horizontal taps, vertical taps; one kernel per output rule
+#define TVS_SINST(H, V) {H, V, {stream_scale_kernel<H, V, kOutU8>, stream_scale_kernel<H, V, kOutU8Dither>, stream_scale_kernel<H, V, kOutU10>}}
+const StreamInstance kStreamInstances[] = {
+    TVS_SINST(2, 2), TVS_SINST(4, 2), TVS_SINST(4, 3),  TVS_SINST(4, 4),  TVS_SINST(6, 4),  TVS_SINST(6, 6),   TVS_SINST(8, 6),
+    TVS_SINST(8, 8), TVS_SINST(9, 9), TVS_SINST(12, 9), TVS_SINST(12, 12), TVS_SINST(16, 12),
+};
+#undef TVS_SINST
+
+template <typename T>
+size_t append_blob(std::vector<uint8_t> &blob, const std::vector<T> &v) {
+    const size_t off = (blob.size() + 255) & ~static_cast<size_t>(255);
+    blob.resize(off + v.size() * sizeof(T));
+    memcpy(blob.data() + off, v.data(), v.size() * sizeof(T));
+    return off;
+}
+
+}  // namespace
+
+struct StreamOp {
+    int op_index = 0, instance = -1, out_mode = 0, src_mode = 0;
+    int strips = 0, vtaps = 0, kb = 0, n_blocks = 0, rm_rows = 0;
+    int s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0;
+    float v_thr = 0, src_scale = 1.f, h_addend = 0.f;
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vpair_off = 0, vint_off = 0, yend_off = 0;
+    std::vector<short> strip_c0, strip_nc;
+    size_t smem_bytes = 0;
+};
+
+struct StreamPlan {
+    std::vector<StreamOp> ops;
+    uint8_t *blob = nullptr;
+    size_t blob_bytes = 0;
+};
+
+namespace {
+size_t stream_smem_bytes(int rm_rows, int kb, int s_pitch, int s_chunks) {
+    return (static_cast<size_t>(rm_rows) * kStripW + static_cast<size_t>(kb) * s_pitch + 2 * static_cast<size_t>(kb) * s_chunks * 4) * 4;
+}
+}  // namespace
+
+StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err) {
+    (void)device;
+    std::vector<uint8_t> blob;
+    auto sp = new StreamPlan;
+    auto bail = [&](const char *why) { err = why; delete sp; return static_cast<StreamPlan *>(nullptr); };
+    for (size_t oi = 0; oi < plan.ops.size(); ++oi) {
+        const PlaneOp &op = plan.ops[oi];
+        if (op.kind != kOpScale) continue;
+        if (op.sh <= op.dh) return bail("not a vertical down-scale");
+        const AxisTable &h = host_tables[op.htable], &v = host_tables[op.vtable];
+        const bool wide_src = op.src_bits > 8;
+        const int sample_bytes = wide_src ? 2 : 1;
+        if (op.src_xstep != sample_bytes && op.src_xstep != 2 * sample_bytes) return bail("unexpected sample spacing");
+        StreamOp so;
+        so.op_index = static_cast<int>(oi);
+        so.src_mode = wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
+        so.out_mode = op.rule == kOut10 ? kOutU10 : op.rule == kOut8Dither ? kOutU8Dither : kOutU8;
+
+        // exactness preconditions of the float horizontal sum (see kernels_fused_impl.cuh)
+        long long worst_abs = 0;
+        for (int x = 0; x < op.dw; ++x) {
+            long long s = 0, a = 0;
+            for (int j = 0; j < h.taps; ++j) { const int c = h.coef[static_cast<size_t>(x) * h.taps + j]; s += c; a += std::abs(c); }
+            if (s != (1 << 14)) return bail("horizontal row does not sum to one");
+            worst_abs = std::max(worst_abs, a);
+        }
+        if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) return bail("horizontal sum not exact in fp32");
+        int inst = -1;
+        const int n_inst = static_cast<int>(sizeof(kStreamInstances) / sizeof(kStreamInstances[0]));
+        for (int i = 0; i < n_inst; ++i) {
+            if (kStreamInstances[i].ht < h.taps || kStreamInstances[i].vt < v.taps) continue;
+            if (inst < 0 || kStreamInstances[i].ht + kStreamInstances[i].vt < kStreamInstances[inst].ht + kStreamInstances[inst].vt) inst = i;
+        }
+        if (inst < 0) return bail("no streaming kernel instance for this filter size");
+        const int HT = kStreamInstances[inst].ht, VT = kStreamInstances[inst].vt;
+        so.instance = inst;
+        so.vtaps = v.taps;
+        so.strips = (op.dw + kStripW - 1) / kStripW;
+        if (so.strips > kMaxStrips) return bail("plane too wide for the strip table");
+
+        // float vertical sum: rounding-error bound and the residual threshold
+        long long vworst = 0;
+        for (int y = 0; y < v.length; ++y) {
+            long long s = 0;
+            for (int j = 0; j < v.taps; ++j) s += std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+            vworst = std::max(vworst, s);
+        }
+        const double bound = 32767.0 * static_cast<double>(vworst) + 1.0;
+        const double e = 0.5 * std::ldexp(1.0, static_cast<int>(std::floor(std::log2(bound))) - 23) * VT;
+        const double half_step = so.out_mode == kOutU10 ? 65536.0 : 262144.0;
+        if (e > half_step / 8) return bail("vertical error bound too large");
+        so.v_thr = static_cast<float>(std::ldexp(half_step - e - 1.0, -42));
+        so.src_scale = op.src_shift ? std::ldexp(1.0f, -op.src_shift) : 1.0f;
+        so.h_addend = wide_src ? std::ldexp(16384.0f, -149) : 0.0f;
+
+        std::vector<float> hcoef(static_cast<size_t>(op.dw) * HT, 0.0f);
+        for (int x = 0; x < op.dw; ++x)
+            for (int j = 0; j < h.taps; ++j)
+                hcoef[static_cast<size_t>(x) * HT + j] = std::ldexp(static_cast<float>(h.coef[static_cast<size_t>(x) * h.taps + j]), -(23 + op.hshift));
+        int ncols_max = 0;
+        for (int sx = 0; sx < so.strips; ++sx) {
+            const int xa = sx * kStripW, xb = std::min(xa + kStripW, op.dw) - 1;
+            so.strip_c0.push_back(static_cast<short>(h.pos[xa]));
+            so.strip_nc.push_back(static_cast<short>(h.pos[xb] + HT - h.pos[xa]));
+            ncols_max = std::max(ncols_max, h.pos[xb] + HT - h.pos[xa]);
+        }
+        so.s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
+        so.s_chunks_log2 = 0;
+        while ((1 << so.s_chunks_log2) < so.s_chunks) ++so.s_chunks_log2;
+        so.s_pitch = so.s_chunks * (16 / op.src_xstep);
+        if ((so.s_pitch & 31) == 0) so.s_pitch += 4;
+
+        // vertical tables in tap order, (g, g) pairs and integers
+        std::vector<float> vpair(static_cast<size_t>(op.dh) * VT * 2, 0.0f);
+        std::vector<int> vint(static_cast<size_t>(op.dh) * VT, 0);
+        for (int y = 0; y < op.dh; ++y)
+            for (int j = 0; j < v.taps; ++j) {
+                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
+                vpair[(static_cast<size_t>(y) * VT + j) * 2] = vpair[(static_cast<size_t>(y) * VT + j) * 2 + 1] = std::ldexp(static_cast<float>(c), 107);
+                vint[static_cast<size_t>(y) * VT + j] = c;
+            }
+
+        // block size: as many source rows per step as shared memory allows (fewer barriers), and the ring that holds
+        // the live window plus one block
+        for (int kb = 32;; kb /= 2) {
+            const int n_blocks = (op.sh + kb - 1) / kb;
+            std::vector<int> yend(n_blocks);
+            int y = 0, live = 0;
+            for (int b = 0; b < n_blocks; ++b) {
+                const int hr_end = std::min((b + 1) * kb, op.sh);
+                const int ystart = y;
+                while (y < op.dh && (std::min(v.pos[y] + v.taps, op.sh) <= hr_end)) ++y;
+                if (b == n_blocks - 1) y = op.dh;
+                yend[b] = y;
+                // rows alive while block b is being written: from the first row still needed to the end of the block
+                const int first_needed = ystart < op.dh ? v.pos[ystart] : hr_end;
+                live = std::max(live, b * kb + kb - std::min(first_needed, b * kb));
+            }
+            int rm = 1;
+            while (rm < live + VT) rm *= 2;   // + VT: tap padding may index a little past the window
+            so.kb = kb; so.n_blocks = n_blocks; so.rm_rows = rm;
+            so.smem_bytes = stream_smem_bytes(rm, kb, so.s_pitch, so.s_chunks);
+            if (so.smem_bytes <= kStreamSmemBudget || kb == 4) {
+                so.yend_off = append_blob(blob, yend);
+                break;
+            }
+        }
+        if (so.smem_bytes > 200 * 1024) return bail("strip does not fit in shared memory");
+        so.hdense_off = append_blob(blob, hcoef);
+        so.hbase_off = append_blob(blob, h.pos);
+        so.vpos_off = append_blob(blob, v.pos);
+        so.vpair_off = append_blob(blob, vpair);
+        so.vint_off = append_blob(blob, vint);
+        sp->ops.push_back(so);
+    }
+    if (sp->ops.empty()) return bail("nothing to scale");
+    if (cudaMalloc(&sp->blob, blob.size()) != cudaSuccess ||
+        cudaMemcpy(sp->blob, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        cudaGetLastError();
+        if (sp->blob) cudaFree(sp->blob);
+        return bail("device allocation for the streaming tables failed");
+    }
+    sp->blob_bytes = blob.size();
+    for (const StreamOp &so : sp->ops)
+        cudaFuncSetAttribute(reinterpret_cast<const void *>(kStreamInstances[so.instance].fn[so.out_mode]),
+                             cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    return sp;
+}
+
+void stream_plan_destroy(StreamPlan *p) {
+    if (!p) return;
+    if (p->blob) cudaFree(p->blob);
+    delete p;
+}
+
+int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
+                  cudaStream_t stream) {
+    int launched = 0;
+    std::vector<bool> done(p->ops.size(), false);
+    for (size_t i = 0; i < p->ops.size(); ++i) {
+        if (done[i]) continue;
+        StreamLaunchParams lp{};
+        int strips = 0, m_floats = 0, s_floats = 0, raw_words = 0;
+        for (size_t j = i; j < p->ops.size() && lp.n_ops < kMaxStreamOps; ++j) {
+            const StreamOp &so = p->ops[j];
+            if (done[j] || so.instance != p->ops[i].instance || so.out_mode != p->ops[i].out_mode) continue;
+            done[j] = true;
+            const PlaneOp &op = plan.ops[so.op_index];
+            const SampleView &s = src_views[so.op_index], &d = dst_views[so.op_index];
+            StreamOpParams &q = lp.op[lp.n_ops++];
+            q.src = s.base; q.src_pitch = s.pitch; q.src_fstride = s.frame_stride; q.src_xstep = s.xstep;
+            q.dst = d.base; q.dst_pitch = d.pitch; q.dst_fstride = d.frame_stride; q.dst_xstep = d.xstep;
+            q.sw = op.sw; q.sh = op.sh; q.dw = op.dw; q.dh = op.dh;
+            q.strips = so.strips; q.strip_begin = strips;
+            q.hcoef = reinterpret_cast<const float *>(p->blob + so.hdense_off);
+            q.hpos = reinterpret_cast<const int *>(p->blob + so.hbase_off);
+            q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
+            q.vpair = reinterpret_cast<const float *>(p->blob + so.vpair_off);
+            q.vint = reinterpret_cast<const int *>(p->blob + so.vint_off);
+            q.block_yend = reinterpret_cast<const int *>(p->blob + so.yend_off);
+            q.kb = so.kb; q.n_blocks = so.n_blocks; q.rm_mask = so.rm_rows - 1;
+            q.s_pitch = so.s_pitch; q.s_chunks = so.s_chunks; q.s_chunks_log2 = so.s_chunks_log2;
+            q.src_lo = s.base - op.src_offset;
+            q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
+            q.v_thr = so.v_thr; q.src_mode = so.src_mode; q.src_scale = so.src_scale; q.h_addend = so.h_addend;
+            q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
+            std::copy(so.strip_c0.begin(), so.strip_c0.end(), q.strip_c0);
+            std::copy(so.strip_nc.begin(), so.strip_nc.end(), q.strip_nc);
+            strips += so.strips;
+            m_floats = std::max(m_floats, so.rm_rows * kStripW);
+            s_floats = std::max(s_floats, so.kb * so.s_pitch);
+            raw_words = std::max(raw_words, so.kb * so.s_chunks * 4);
+        }
+        lp.m_floats = m_floats; lp.s_floats = s_floats; lp.raw_words = raw_words;
+        const size_t smem = static_cast<size_t>(m_floats + s_floats + 2 * raw_words) * 4;
+        if (smem > 200 * 1024) return -2;
+        const dim3 grid(strips, n_frames);
+        kStreamInstances[p->ops[i].instance].fn[p->ops[i].out_mode]<<<grid, kSThreads, smem, stream>>>(lp);
+        if (cudaPeekAtLastError() != cudaSuccess) return -1;
+        ++launched;
+    }
+    return launched;
+}
+
+}  // namespace tvs

@@ -91,4 +91,12 @@ TVS_DECLARE_FUSED(_w256)   // 256-column tiles, 2 CTAs x 256 threads per SM
 TVS_DECLARE_FUSED(_w128)   // 128-column tiles, 4 CTAs x 128 threads per SM
 #undef TVS_DECLARE_FUSED
 
+// ---- streaming down-scale kernel (kernels_stream.cu) ------------------------------------------------------
+struct StreamPlan;  // opaque, owned by the context
+StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);
+void stream_plan_destroy(StreamPlan *p);
+// Returns kernels launched, or a negative value after a launch error.
+int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
+                  cudaStream_t stream);
+
 }  // namespace tvs

@@ -71,6 +71,7 @@ struct tvs_ctx {
     Plan plan;
     FusedPlan *fused = nullptr;
     bool fused_narrow = false;   // which build of the fused kernel owns `fused`: 128-column (true) or 256-column tiles
+    StreamPlan *streaming = nullptr;   // vertical down-scales: the line-buffer kernel
     int forced_path = -1;
     // two-pass scratch
     int16_t *mid = nullptr;
@@ -89,7 +90,10 @@ namespace {
 bool fused_prefers_two_pass(const tvs_ctx *c) {
     return c->fused_narrow ? fused_plan_prefers_two_pass_w128(c->fused) : fused_plan_prefers_two_pass_w256(c->fused);
 }
+// forced_path: -1 automatic, 0 fused tile kernel, 1 two-pass kernels, 2 streaming kernel
+bool use_stream_path(const tvs_ctx *c) { return c->streaming && (c->forced_path == 2 || c->forced_path < 0); }
 bool use_fused_path(const tvs_ctx *c) {
+    if (use_stream_path(c)) return false;
     return c->fused && (c->forced_path == 0 || (c->forced_path < 0 && !fused_prefers_two_pass(c)));
 }
 
@@ -268,6 +272,13 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     }
     if (!plan.any_scale) return 0;
 
+    if (c->forced_path == 2 && !c->streaming) return fail(-ENOSYS, "streaming path requested but this shape is not supported by it");
+    if (use_stream_path(c)) {
+        const int n = stream_launch(c->streaming, plan, sv.data(), dv.data(), n_frames, stream);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "streaming kernel launch");
+        c->launches += n;
+        return 0;
+    }
     const bool use_fused = use_fused_path(c);
     if (c->forced_path == 0 && !c->fused) return fail(-ENOSYS, "fused path requested but this shape is not supported by it");
     if (use_fused) {
@@ -412,6 +423,7 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         // Down-scales stage a wide source footprint and do better with 128-column tiles; up-scales amortise the
         // vertical pass over 256 columns.  If the preferred build cannot take the shape, try the other one;
         // nullptr = the shape is handled by the two-pass kernels.
+        if (src_h > dst_h) c->streaming = stream_plan_create(c->plan, c->host_tables, device, why);
         c->fused_narrow = src_w > dst_w;
         for (int attempt = 0; attempt < 2 && !c->fused; ++attempt, c->fused_narrow = !c->fused_narrow) {
             c->fused = c->fused_narrow ? fused_plan_create_w128(c->plan, c->host_tables, device, why)
@@ -426,6 +438,7 @@ void tvs_destroy(tvs_ctx *c) {
     if (!c) return;
     cudaSetDevice(c->device);
     if (c->fused) { if (c->fused_narrow) fused_plan_destroy_w128(c->fused); else fused_plan_destroy_w256(c->fused); }
+    if (c->streaming) stream_plan_destroy(c->streaming);
     if (c->dev_table_blob) cudaFree(c->dev_table_blob);
     if (c->mid) cudaFree(c->mid);
     for (int i = 0; i < 2; ++i) {
@@ -521,7 +534,7 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const bool dst_packed = packed(reinterpret_cast<const void *const *>(dst), dst_pitch, dst_frame_stride, c->dfi, d_off, d_pitch, dframe);
 
     // The two-pass path owns ONE intermediate buffer, so its chunks must not overlap on the device.
-    const bool single_stream = c->plan.any_scale && !use_fused_path(c);
+    const bool single_stream = c->plan.any_scale && !use_fused_path(c) && !use_stream_path(c);
     int slot = 0;
     for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk), slot = single_stream ? 0 : slot ^ 1) {
         const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
@@ -575,7 +588,7 @@ long long tvs_info(const tvs_ctx *c, int what) {
     case TVS_INFO_KERNEL_LAUNCHES: return c->launches;
     case TVS_INFO_PATH:
         if (!c->plan.any_scale) return 2;
-        return use_fused_path(c) ? 0 : 1;
+        return use_stream_path(c) ? 3 : use_fused_path(c) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
         return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + 2 * (c->stage_src_bytes + c->stage_dst_bytes));
     case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
@@ -585,8 +598,9 @@ long long tvs_info(const tvs_ctx *c, int what) {
 }
 
 int tvs_set_path(tvs_ctx *c, int path) {
-    if (!c || path < -1 || path > 1) return fail(-EINVAL, "bad path");
+    if (!c || path < -1 || path > 2) return fail(-EINVAL, "bad path");
     if (path == 0 && c->plan.any_scale && !c->fused) return fail(-ENOSYS, "this shape is not supported by the fused kernel");
+    if (path == 2 && c->plan.any_scale && !c->streaming) return fail(-ENOSYS, "this shape is not supported by the streaming kernel");
     c->forced_path = path;
     return 0;
 }
