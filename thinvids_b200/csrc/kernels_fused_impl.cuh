@@ -74,6 +74,7 @@ struct FusedOpParams {
     size_t src_extent;
     int m_rows;            // rows of the shared-memory tiles
     float v_thr;           // |residual| at or above this needs the exact path
+    float v_init;          // start value of the vertical accumulators (see vertical_float_rule)
     int src_mode;          // kSrcU8 / kSrcU8Pair / kSrcU16 / kSrcU16Pair: sample width and spacing in the source plane
     float src_scale;       // 16-bit sources: 1, or 2^-6 for P010 (its 10 bits sit at the top of the word)
     float h_addend;        // subnormal offset of the H result: 16384 * 2^-149 when samples were centred on 512, else 0
@@ -217,7 +218,8 @@ __device__ __forceinline__ void load_row_coefs(f32x2 (&gg)[VT], const f32x2 *cv)
 template <int VT, int MODE, int OUT, bool DUAL>
 __device__ __forceinline__ void vertical_strip(const float *M, const f32x2 *cv, const int *vp, const int *exact, int r0,
                                                int ya, int yb, uint8_t *drow, ptrdiff_t dst_pitch, int dst_xstep, int dw,
-                                               int xa, bool right, float v_thr, int lane, int dst_shift, int dither_xoff) {
+                                               int xa, bool right, float v_thr, int lane, int dst_shift, int dither_xoff,
+                                               float v_init) {
     const int xb = xa + kHalfW;
     const float *m_col = M + 4 * lane;
     Quad wa[VT], wb[VT];
@@ -237,14 +239,14 @@ __device__ __forceinline__ void vertical_strip(const float *M, const f32x2 *cv, 
         if (next_row < first + VT) load_ring_rows<VT, DUAL>(wa, wb, slot, next_row, first + VT, mp);
         const float *m_first = m_col + (first - r0) * kTileW;
         RowExtras ex;
-        ex.init01 = ex.init23 = 0ull;
+        ex.init01 = ex.init23 = pack2(v_init, v_init);
         ex.dither = make_int4(0, 0, 0, 0);
         if (OUT == kOutU8Dither) {
             const int *drow_tab = kDither128i[y & 7];
             ex.dither = make_int4(drow_tab[dcol], drow_tab[(dcol + 1) & 7], drow_tab[(dcol + 2) & 7], drow_tab[(dcol + 3) & 7]);
             // (d - 64) * 4096 * 2^-42: the rounding quotient below already adds 64 << 12
-            ex.init01 = pack2(static_cast<float>(ex.dither.x - 64) * 0x1p-30f, static_cast<float>(ex.dither.y - 64) * 0x1p-30f);
-            ex.init23 = pack2(static_cast<float>(ex.dither.z - 64) * 0x1p-30f, static_cast<float>(ex.dither.w - 64) * 0x1p-30f);
+            ex.init01 = pack2(fmaf(static_cast<float>(ex.dither.x - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(ex.dither.y - 64), 0x1p-30f, v_init));
+            ex.init23 = pack2(fmaf(static_cast<float>(ex.dither.z - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(ex.dither.w - 64), 0x1p-30f, v_init));
         }
         unsigned word_a[2], word_b[2] = {0, 0};
         if (MODE == kStoreBoth && DUAL) {
@@ -557,22 +559,22 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
             if constexpr (kDual) {
                 if (words && x0 + kTileW <= dw)
                     vertical_strip<VT, kStoreBoth, OUT, true>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, kSample, dw, xa, true,
-                                                              op.v_thr, lane, op.dst_shift, op.dither_xoff);
+                                                              op.v_thr, lane, op.dst_shift, op.dither_xoff, op.v_init);
                 else if (words && x0 + kHalfW == dw)
                     vertical_strip<VT, kStoreLeft, OUT, true>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, kSample, dw, xa, false,
-                                                              op.v_thr, lane, op.dst_shift, op.dither_xoff);
+                                                              op.v_thr, lane, op.dst_shift, op.dither_xoff, op.v_init);
                 else
                     vertical_strip<VT, kStoreGeneric, OUT, true>(M, cv, vp, exact, r0, ya, yb, drow, dst_pitch, dst_xstep, dw, xa,
-                                                                 x0 + kHalfW < dw, op.v_thr, lane, op.dst_shift, op.dither_xoff);
+                                                                 x0 + kHalfW < dw, op.v_thr, lane, op.dst_shift, op.dither_xoff, op.v_init);
             } else {
                 for (int h = 0; h < kHalves && x0 + h * kHalfW < dw; ++h) {
                     const int xh = xa + h * kHalfW;
                     if (words && x0 + (h + 1) * kHalfW <= dw)
                         vertical_strip<VT, kStoreLeft, OUT, false>(M + h * kHalfW, cv, vp, exact, r0, ya, yb, drow, dst_pitch, kSample, dw,
-                                                                   xh, false, op.v_thr, lane, op.dst_shift, op.dither_xoff);
+                                                                   xh, false, op.v_thr, lane, op.dst_shift, op.dither_xoff, op.v_init);
                     else
                         vertical_strip<VT, kStoreGeneric, OUT, false>(M + h * kHalfW, cv, vp, exact, r0, ya, yb, drow, dst_pitch, dst_xstep,
-                                                                      dw, xh, false, op.v_thr, lane, op.dst_shift, op.dither_xoff);
+                                                                      dw, xh, false, op.v_thr, lane, op.dst_shift, op.dither_xoff, op.v_init);
                 }
             }
         }
@@ -597,7 +599,7 @@ struct FusedOp {
     int instance = -1;
     int th = 0, tiles_x = 0, tiles_y = 0, n_groups = 0, s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0, m_rows = 0;
     size_t smem_bytes = 0;
-    float v_thr = 0;
+    float v_thr = 0, v_init = 0;
     // offsets (in bytes) into the device blob
     size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vring_off = 0, vring_i_off = 0;
     int vtaps = 0;
@@ -696,9 +698,8 @@ FusedPlan *TVS_FUSED_FN(fused_plan_create)(const Plan &plan, const AxisTable hos
         }
         if (inst < 0) { err = "no kernel instance for this filter size"; delete fp; return nullptr; }
         const int SPAN = kInstances[inst].span, VT = kInstances[inst].vt;
-        const double e = vertical_error_bound(v, VT);
-        const double half_step = out_mode == kOutU10 ? 65536.0 : 262144.0;   // half of 2^17 / 2^19
-        if (e > half_step / 8) { err = "vertical error bound too large"; delete fp; return nullptr; }
+        const VerticalFloatRule vrule = vertical_float_rule(v, VT, out_mode == kOutU10, out_mode == kOutU8Dither);
+        if (!vrule.ok) { err = "vertical error bound too large"; delete fp; return nullptr; }
 
         FusedOp fo;
         fo.op_index = static_cast<int>(oi);
@@ -706,7 +707,8 @@ FusedPlan *TVS_FUSED_FN(fused_plan_create)(const Plan &plan, const AxisTable hos
         fo.n_groups = n_groups;
         fo.vtaps = v.taps;
         fo.tiles_x = (op.dw + kTileW - 1) / kTileW;
-        fo.v_thr = static_cast<float>(std::ldexp(half_step - e - 1.0, -42));
+        fo.v_thr = vrule.thr;
+        fo.v_init = vrule.init;
         fo.src_mode = src_mode;
         fo.out_mode = out_mode;
         fo.src_scale = op.src_shift ? std::ldexp(1.0f, -op.src_shift) : 1.0f;
@@ -868,7 +870,7 @@ int TVS_FUSED_FN(fused_launch)(const FusedPlan *p, const Plan &plan, const Sampl
             q.s_pitch = fo.s_pitch; q.s_chunks = fo.s_chunks; q.s_chunks_log2 = fo.s_chunks_log2; q.m_rows = fo.m_rows;
             q.src_lo = s.base - op.src_offset;
             q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
-            q.v_thr = fo.v_thr;
+            q.v_thr = fo.v_thr; q.v_init = fo.v_init;
             q.src_mode = fo.src_mode; q.src_scale = fo.src_scale; q.h_addend = fo.h_addend;
             q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
             std::copy(fo.tile_c0.begin(), fo.tile_c0.end(), q.tile_c0);

@@ -48,7 +48,7 @@ struct StreamOpParams {
     int rm_mask;           // rows of the intermediate ring - 1 (power of two)
     int s_pitch, s_chunks, s_chunks_log2;
     const uint8_t *src_lo; size_t src_extent;
-    float v_thr;
+    float v_thr, v_init;
     int src_mode; float src_scale, h_addend;
     int dst_shift, dither_xoff;
     short strip_c0[kMaxStrips], strip_nc[kMaxStrips];
@@ -221,7 +221,7 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
     constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
     const bool fast_store = dst_xstep == kSample && (dst_pitch & kAlign) == 0 && x0 + kStripW <= dw &&
                             ((reinterpret_cast<uintptr_t>(dst_base) + static_cast<uintptr_t>(x0) * kSample) & kAlign) == 0;
-    const float v_thr = op.v_thr;
+    const float v_thr = op.v_thr, v_init = op.v_init;
     const int dcol = (xq + op.dither_xoff) & 7;
     const float *m_col = M + 4 * lane;
 
@@ -261,13 +261,13 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
         for (int y = y_next + warp; y < y_end; y += kSWarps) {
             const int first = __ldg(op.vpos + y);
             const f32x2 *gp = reinterpret_cast<const f32x2 *>(op.vpair) + static_cast<size_t>(y) * VT;
-            f32x2 a01 = 0ull, a23 = 0ull;
+            f32x2 a01 = pack2(v_init, v_init), a23 = a01;
             int4 dither = make_int4(0, 0, 0, 0);
             if (OUT == kOutU8Dither) {
                 const int *tab = kDither128i[y & 7];
                 dither = make_int4(tab[dcol], tab[(dcol + 1) & 7], tab[(dcol + 2) & 7], tab[(dcol + 3) & 7]);
-                a01 = pack2(static_cast<float>(dither.x - 64) * 0x1p-30f, static_cast<float>(dither.y - 64) * 0x1p-30f);
-                a23 = pack2(static_cast<float>(dither.z - 64) * 0x1p-30f, static_cast<float>(dither.w - 64) * 0x1p-30f);
+                a01 = pack2(fmaf(static_cast<float>(dither.x - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(dither.y - 64), 0x1p-30f, v_init));
+                a23 = pack2(fmaf(static_cast<float>(dither.z - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(dither.w - 64), 0x1p-30f, v_init));
             }
 #pragma unroll
             for (int j = 0; j < VT; ++j) {
@@ -316,7 +316,7 @@ struct StreamOp {
     int op_index = 0, instance = -1, out_mode = 0, src_mode = 0;
     int strips = 0, vtaps = 0, kb = 0, n_blocks = 0, rm_rows = 0;
     int s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0;
-    float v_thr = 0, src_scale = 1.f, h_addend = 0.f;
+    float v_thr = 0, v_init = 0, src_scale = 1.f, h_addend = 0.f;
     size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vpair_off = 0, vint_off = 0, yend_off = 0;
     std::vector<short> strip_c0, strip_nc;
     size_t smem_bytes = 0;
@@ -374,18 +374,11 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         so.strips = (op.dw + kStripW - 1) / kStripW;
         if (so.strips > kMaxStrips) return bail("plane too wide for the strip table");
 
-        // float vertical sum: rounding-error bound and the residual threshold
-        long long vworst = 0;
-        for (int y = 0; y < v.length; ++y) {
-            long long s = 0;
-            for (int j = 0; j < v.taps; ++j) s += std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
-            vworst = std::max(vworst, s);
-        }
-        const double bound = 32767.0 * static_cast<double>(vworst) + 1.0;
-        const double e = 0.5 * std::ldexp(1.0, static_cast<int>(std::floor(std::log2(bound))) - 23) * VT;
-        const double half_step = so.out_mode == kOutU10 ? 65536.0 : 262144.0;
-        if (e > half_step / 8) return bail("vertical error bound too large");
-        so.v_thr = static_cast<float>(std::ldexp(half_step - e - 1.0, -42));
+        // float vertical sum: residual threshold / accumulator start (tvs_internal.h)
+        const VerticalFloatRule vrule = vertical_float_rule(v, VT, so.out_mode == kOutU10, so.out_mode == kOutU8Dither);
+        if (!vrule.ok) return bail("vertical error bound too large");
+        so.v_thr = vrule.thr;
+        so.v_init = vrule.init;
         so.src_scale = op.src_shift ? std::ldexp(1.0f, -op.src_shift) : 1.0f;
         so.h_addend = wide_src ? std::ldexp(16384.0f, -149) : 0.0f;
 
@@ -498,7 +491,7 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             q.s_pitch = so.s_pitch; q.s_chunks = so.s_chunks; q.s_chunks_log2 = so.s_chunks_log2;
             q.src_lo = s.base - op.src_offset;
             q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
-            q.v_thr = so.v_thr; q.src_mode = so.src_mode; q.src_scale = so.src_scale; q.h_addend = so.h_addend;
+            q.v_thr = so.v_thr; q.v_init = so.v_init; q.src_mode = so.src_mode; q.src_scale = so.src_scale; q.h_addend = so.h_addend;
             q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
             std::copy(so.strip_c0.begin(), so.strip_c0.end(), q.strip_c0);
             std::copy(so.strip_nc.begin(), so.strip_nc.end(), q.strip_nc);

@@ -3,8 +3,11 @@
 #pragma once
 #include <cuda_runtime.h>
 
+#include <cmath>
 #include <cstddef>
 #include <cstdint>
+#include <algorithm>
+#include <cstdlib>
 #include <string>
 #include <vector>
 
@@ -64,6 +67,41 @@ struct Plan {
     size_t mid_elems_per_frame = 0;        // int16 elements of two-pass scratch per frame
     bool any_scale = false;
 };
+
+// ---- the float vertical sum (shared by the tile and the streaming kernels) ---------------------------------
+// Both kernels accumulate acc * 2^-42 in FP32 and take q = RN(acc / 2^shift).  Two regimes:
+//  * general tables: every FMA may round; the accumulated error is at most `e` units of acc, so a sample whose exact
+//    residual is within e of a rounding boundary (|r| >= thr) is recomputed in int32;
+//  * tables whose coefficients are all multiples of 2^k with the largest partial sum below 2^(23+k) (area 2:1, any
+//    1-tap axis, ...): the float sum is exact, but exact ties (acc = odd * 2^(shift-1)) are then COMMON (1 sample in
+//    256 for a 2:1 box filter) and RN-to-even is not libswscale's round-half-up.  Starting the accumulator at half a
+//    unit, 2^(k-1), makes ties impossible and turns RN into round-half-up; no residual check is needed (thr = huge).
+struct VerticalFloatRule {
+    bool ok;      // false: error bound too large for this output rule, use the two-pass kernels
+    float thr;    // residual threshold, scaled by 2^-42
+    float init;   // accumulator start value, scaled by 2^-42
+};
+inline VerticalFloatRule vertical_float_rule(const AxisTable &v, int vt_inst, bool out10, bool dither) {
+    long long worst = 0;
+    int k = 31;
+    for (int y = 0; y < v.length; ++y) {
+        long long s = 0;
+        for (int j = 0; j < v.taps; ++j) {
+            const int c = std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+            s += c;
+            if (c) k = std::min(k, __builtin_ctz(static_cast<unsigned>(c)));
+        }
+        worst = std::max(worst, s);
+    }
+    const double bound = 32767.0 * static_cast<double>(worst) + 1.0;
+    const int bits = static_cast<int>(std::floor(std::log2(bound))) + 1;   // bits of the largest partial sum
+    const double half_step = out10 ? 65536.0 : 262144.0;                    // half of 2^17 / 2^19
+    if (dither) k = std::min(k, 13);                                        // dither offsets are multiples of 2^13
+    if (k >= 1 && k < 31 && bits - k + 1 <= 24) return {true, 3.0e38f, std::ldexp(1.0f, k - 1 - 42)};
+    const double e = 0.5 * std::ldexp(1.0, bits - 1 - 23) * vt_inst;        // half an ulp of the bound per FMA
+    if (e > half_step / 8) return {false, 0.f, 0.f};
+    return {true, static_cast<float>(std::ldexp(half_step - e - 1.0, -42)), 0.0f};
+}
 
 // ---- kernel launchers (kernels_generic.cu) -------------------------------------------------------
 // Each returns the number of kernels it launched, or -1 after a launch error (cudaGetLastError kept).
