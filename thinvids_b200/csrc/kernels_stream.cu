@@ -47,6 +47,7 @@ struct StreamOpParams {
     int kb, n_blocks;      // source rows per block
     int rm_mask;           // rows of the intermediate ring - 1 (power of two)
     int s_pitch, s_chunks, s_chunks_log2;
+    unsigned chunk_magic, word_magic;   // ceil(2^32 / s_chunks), ceil(2^32 / (4 * s_chunks)): exact division of small indices
     const uint8_t *src_lo; size_t src_extent;
     float v_thr, v_init;
     int src_mode; float src_scale, h_addend;
@@ -93,32 +94,30 @@ __device__ __noinline__ uint2 exact_fixup_ring(const float *m_col, int mask, int
 // kernel for the chunk / alignment rules; identical here).
 __device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const uint8_t *strip_base, const uint8_t *lo, const uint8_t *hi,
                                                int r_b, int rows, int last_byte, unsigned *raw, int tid) {
-    const int clog = min(op.s_chunks_log2, 7), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
+    const int s_chunks = op.s_chunks;
     const ptrdiff_t pitch = op.src_pitch;
     const uint8_t *base = strip_base + static_cast<ptrdiff_t>(r_b) * pitch;
     const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(base)) & 15u;
     const unsigned pmod = static_cast<unsigned>(pitch) & 15u;
-    const int rstep = kSThreads >> clog;
-    for (int ch = tid & cmask; ch < s_chunks; ch += 1 << clog) {
-        int row = tid >> clog;
-        uint4 *dst = reinterpret_cast<uint4 *>(raw) + row * s_chunks + ch;
-        const uint8_t *src = base + row * pitch + 16 * ch;
-        unsigned mis = (mis0 + row * pmod) & 15u;
-        const unsigned mstep = (rstep * pmod) & 15u;
-        for (; row < rows; row += rstep, dst += rstep * s_chunks, src += rstep * pitch, mis = (mis + mstep) & 15u) {
-            const int first = 16 * ch - static_cast<int>(mis);
-            const uint8_t *g = src - mis;
-            if (first > last_byte) {
-                *dst = make_uint4(0u, 0u, 0u, 0u);
-            } else if (g >= lo && g + 16 <= hi) {
-                cp_async16(dst, g);
-            } else {
+    const unsigned magic = op.chunk_magic;
+    // (row, chunk) pairs are spread over all threads: a row is rarely a power-of-two number of chunks
+    for (int idx = tid; idx < rows * s_chunks; idx += kSThreads) {
+        const int row = static_cast<int>(__umulhi(static_cast<unsigned>(idx), magic));
+        const int ch = idx - row * s_chunks;
+        const unsigned mis = (mis0 + row * pmod) & 15u;
+        uint4 *dst = reinterpret_cast<uint4 *>(raw) + idx;
+        const int first = 16 * ch - static_cast<int>(mis);
+        const uint8_t *g = base + row * pitch + first;
+        if (first > last_byte) {
+            *dst = make_uint4(0u, 0u, 0u, 0u);
+        } else if (g >= lo && g + 16 <= hi) {
+            cp_async16(dst, g);
+        } else {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
-                    if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
-                    else *d = 0u;
-                }
+            for (int k = 0; k < 4; ++k) {
+                unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+                if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
+                else *d = 0u;
             }
         }
     }
@@ -129,38 +128,26 @@ __device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const u
 __device__ __forceinline__ void convert_block(const StreamOpParams &op, const unsigned *raw, float *S, int rows, unsigned mis0, unsigned pmod,
                                               int tid) {
     const int words = op.s_chunks * 4, s_pitch = op.s_pitch;
-    const int wlog = min(op.s_chunks_log2 + 2, 7), wmask = (1 << wlog) - 1;
-    const int rstep = kSThreads >> wlog;
     const int src_mode = op.src_mode;
     const float sscale = op.src_scale;
-    for (int w = tid & wmask; w < words; w += 1 << wlog) {
-        int row = tid >> wlog;
-        const unsigned *rw = raw + row * words + w;
+    const unsigned magic = op.word_magic;
+    for (int idx = tid; idx < rows * words; idx += kSThreads) {
+        const int row = static_cast<int>(__umulhi(static_cast<unsigned>(idx), magic));
+        const int w = idx - row * words;
+        const unsigned v = raw[idx];
+        float *srow = S + row * s_pitch;
         if (src_mode == kSrcU8) {              // four samples per word
-            float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + w;
-            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 4)) {
-                const unsigned v = *rw;
-                *out = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u), byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
-            }
+            reinterpret_cast<float4 *>(srow)[w] =
+                make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u), byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
         } else if (src_mode == kSrcU8Pair) {   // interleaved 8-bit chroma: this plane is every other byte
-            float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
-            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 2)) {
-                const unsigned p = (mis0 + row * pmod) & 1u;
-                const unsigned v = *rw;
-                *out = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
-            }
+            const unsigned p = (mis0 + row * pmod) & 1u;
+            reinterpret_cast<float2 *>(srow)[w] = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
         } else if (src_mode == kSrcU16) {      // two 16-bit samples per word, centred on 512
-            float2 *out = reinterpret_cast<float2 *>(S + row * s_pitch) + w;
-            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * (s_pitch / 2)) {
-                const unsigned v = *rw;
-                *out = make_float2(fmaf(byte_to_float(v, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v, 0x7432u), sscale, -512.0f));
-            }
+            reinterpret_cast<float2 *>(srow)[w] =
+                make_float2(fmaf(byte_to_float(v, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v, 0x7432u), sscale, -512.0f));
         } else {                               // interleaved 16-bit chroma: one sample of this plane per word
-            float *out = S + row * s_pitch + w;
-            for (; row < rows; row += rstep, rw += rstep * words, out += rstep * s_pitch) {
-                const unsigned hi = (mis0 + row * pmod) & 2u;
-                *out = fmaf(byte_to_float(*rw, hi ? 0x7432u : 0x7410u), sscale, -512.0f);
-            }
+            const unsigned hi16 = (mis0 + row * pmod) & 2u;
+            srow[w] = fmaf(byte_to_float(v, hi16 ? 0x7432u : 0x7410u), sscale, -512.0f);
         }
     }
 }
@@ -393,7 +380,7 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
             so.strip_nc.push_back(static_cast<short>(h.pos[xb] + HT - h.pos[xa]));
             ncols_max = std::max(ncols_max, h.pos[xb] + HT - h.pos[xa]);
         }
-        so.s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
+        so.s_chunks = std::max(2, (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1);   // >= 2: the reciprocal fits 32 bits
         so.s_chunks_log2 = 0;
         while ((1 << so.s_chunks_log2) < so.s_chunks) ++so.s_chunks_log2;
         so.s_pitch = so.s_chunks * (16 / op.src_xstep);
@@ -489,6 +476,8 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             q.block_yend = reinterpret_cast<const int *>(p->blob + so.yend_off);
             q.kb = so.kb; q.n_blocks = so.n_blocks; q.rm_mask = so.rm_rows - 1;
             q.s_pitch = so.s_pitch; q.s_chunks = so.s_chunks; q.s_chunks_log2 = so.s_chunks_log2;
+            q.chunk_magic = static_cast<unsigned>((0x100000000ull + so.s_chunks - 1) / so.s_chunks);
+            q.word_magic = static_cast<unsigned>((0x100000000ull + 4 * so.s_chunks - 1) / (4 * so.s_chunks));
             q.src_lo = s.base - op.src_offset;
             q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
             q.v_thr = so.v_thr; q.v_init = so.v_init; q.src_mode = so.src_mode; q.src_scale = so.src_scale; q.h_addend = so.h_addend;
