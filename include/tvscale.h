@@ -148,7 +148,8 @@ TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size
  * Plan introspection for benchmarks and tests.
  *   TVS_INFO_KERNEL_LAUNCHES  kernels launched by this context so far (monotonic)
  *   TVS_INFO_PATH             0 = fused tile kernel, 1 = two-pass kernels through device scratch,
- *                             2 = same-size repack only, 3 = streaming (line-buffer) kernel for vertical down-scales
+ *                             2 = same-size repack only, 3 = streaming (line-buffer) kernel for vertical down-scales,
+ *                             4 = box-filter kernel (exact 2:1 area on 8-bit planes)
  *   TVS_INFO_SCRATCH_BYTES    device scratch currently owned by the context
  *   TVS_INFO_SRC_FRAME_BYTES / TVS_INFO_DST_FRAME_BYTES   tightly packed frame sizes
  */

@@ -119,6 +119,23 @@ def test_unscaled_all_format_pairs_against_oracle():
                     assert np.array_equal(a, b), (sf, df, w, h)
 
 
+def test_exact_two_to_one_area_box_kernel_against_oracle():
+    """Exact 2:1 area on 8-bit planes runs on the box-filter kernel ((p00+p01+p10+p11+2)>>2); odd alignments included."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    for fmt in (F.YUV420P, F.NV12):
+        for dw, dh in [(4, 4), (6, 10), (322, 182), (1000, 66), (962, 542)]:
+            sw, sh = 2 * dw, 2 * dh
+            for seed, frame in [(1, F.random_frame(fmt, sw, sh, 77)), (2, F.pattern_frame(fmt, sw, sh, "checker")),
+                                (3, F.pattern_frame(fmt, sw, sh, "white"))]:
+                want = port.PortScaler(sw, sh, fmt, dw, dh, fmt, F.SWS_AREA).scale(frame)
+                with Scaler(sw, sh, fmt, dw, dh, fmt, F.SWS_AREA) as s:
+                    assert s.path == ("box2" if sw % 4 == 0 and sh % 4 == 0 else s.path)
+                    got = s.scale(frame)
+                for a, b in zip(got, want):
+                    assert np.array_equal(a, b), (fmt, dw, dh, seed)
+
+
 def test_chroma_siting_against_oracle():
     from oracle import port
     from thinvids_b200.swscale import Scaler

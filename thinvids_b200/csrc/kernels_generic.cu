@@ -162,6 +162,59 @@ interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__restrict__ v, 
     }
 }
 
+// ---- exact 2:1 "area" down-scale of 8-bit planes (the 4K -> 1080p ladder rung) --------------------------------------
+// With flags=area and an exact 2:1 ratio every row of libswscale's tables is [8192, 8192] (horizontal, >> 7) and
+// [2048, 2048] (vertical, +2^18 >> 19) on sample pairs 2x, 2x+1 / rows 2y, 2y+1, so the whole chain collapses to
+//     out = (p00 + p01 + p10 + p11 + 2) >> 2
+// exactly: the 15-bit intermediate (p0 + p1) * 64 never reaches the 32767 clamp and the final value never leaves
+// 0..255.  PAIR = false: one component per byte (planar planes, luma).  PAIR = true: interleaved UV bytes, the two
+// components are filtered independently and stay interleaved.  Each thread produces 8 output bytes from 2 x 16 source
+// bytes with 16-bit SIMD-in-a-register adds; VEC = false is the scalar form for unaligned rows.
+template <bool PAIR, bool VEC>
+__global__ void __launch_bounds__(256)
+box2_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, uint8_t *__restrict__ dst, ptrdiff_t dpitch,
+            ptrdiff_t dframe, int out_bytes, int rows) {
+    const int per = VEC ? 8 : (PAIR ? 2 : 1);                 // output bytes per thread
+    const int slots = (out_bytes + per - 1) / per;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, i = idx - y * slots;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const uint8_t *s0 = src + f * sframe + static_cast<ptrdiff_t>(2 * y) * spitch, *s1 = s0 + spitch;
+    uint8_t *d = dst + f * dframe + y * dpitch;
+    if (VEC && 8 * i + 8 <= out_bytes) {
+        const uint4 a = __ldg(reinterpret_cast<const uint4 *>(s0) + i), b = __ldg(reinterpret_cast<const uint4 *>(s1) + i);
+        const unsigned wa[4] = {a.x, a.y, a.z, a.w}, wb[4] = {b.x, b.y, b.z, b.w};
+        unsigned o[4];   // per source word: two results in the low bytes of its 16-bit halves
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            // planar: [b0+b1, b2+b3]; interleaved: [U0, U1] and [V0, V1] in the halves of two masked words
+            const unsigned even = (wa[k] & 0x00ff00ffu) + (wb[k] & 0x00ff00ffu);             // bytes 0 and 2 of both rows
+            const unsigned odd = ((wa[k] >> 8) & 0x00ff00ffu) + ((wb[k] >> 8) & 0x00ff00ffu); // bytes 1 and 3
+            if (!PAIR) {
+                o[k] = ((even + odd + 0x00020002u) >> 2) & 0x00ff00ffu;                        // out0 | out1 << 16
+            } else {
+                const unsigned u = ((even & 0xffffu) + (even >> 16) + 2u) >> 2, v = ((odd & 0xffffu) + (odd >> 16) + 2u) >> 2;
+                o[k] = u | (v << 8);                                                            // U | V << 8
+            }
+        }
+        uint2 out;
+        if (!PAIR) {
+            out.x = __byte_perm(o[0], o[1], 0x6420);   // bytes 0,2 of o[0], then 0,2 of o[1]
+            out.y = __byte_perm(o[2], o[3], 0x6420);
+        } else {
+            out.x = o[0] | (o[1] << 16);
+            out.y = o[2] | (o[3] << 16);
+        }
+        reinterpret_cast<uint2 *>(d)[i] = out;
+    } else {
+        for (int k = per * i; k < min(per * i + per, out_bytes); ++k) {
+            const int sx = PAIR ? 4 * (k >> 1) + (k & 1) : 2 * k, step = PAIR ? 2 : 1;
+            d[k] = static_cast<uint8_t>((s0[sx] + s0[sx + step] + s1[sx] + s1[sx + step] + 2) >> 2);
+        }
+    }
+}
+
 inline dim3 plane_grid(int w, int h, int n_frames) { return dim3((w + 255) / 256, h, n_frames); }
 
 }  // namespace
@@ -234,6 +287,18 @@ int launch_interleave(const SampleView &u, const SampleView &v, const SampleView
     if (sample_bytes == 1) { if (vec) TVS_ILV(uint8_t, true); else TVS_ILV(uint8_t, false); }
     else { if (vec) TVS_ILV(uint16_t, true); else TVS_ILV(uint16_t, false); }
 #undef TVS_ILV
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_box2(const SampleView &src, const SampleView &dst, bool pair, int out_bytes, int rows, int n_frames, cudaStream_t stream) {
+    const bool vec = aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 16) && aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 8);
+    const int per = vec ? 8 : (pair ? 2 : 1);
+    const int slots = (out_bytes + per - 1) / per;
+    const dim3 grid((static_cast<unsigned>(slots) * rows + 255) / 256, 1, n_frames);
+#define TVS_BOX(P, V) box2_kernel<P, V><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, out_bytes, rows)
+    if (pair) { if (vec) TVS_BOX(true, true); else TVS_BOX(true, false); }
+    else { if (vec) TVS_BOX(false, true); else TVS_BOX(false, false); }
+#undef TVS_BOX
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

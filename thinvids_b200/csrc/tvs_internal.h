@@ -112,6 +112,8 @@ int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceT
 int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
 // memcpy-class special cases of the same-size converters
 int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream);
+// exact 2:1 area down-scale of an 8-bit plane (pair = interleaved UV bytes)
+int launch_box2(const SampleView &src, const SampleView &dst, bool pair, int out_bytes, int rows, int n_frames, cudaStream_t stream);
 int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,
                       cudaStream_t stream);
 

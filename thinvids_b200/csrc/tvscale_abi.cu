@@ -72,6 +72,7 @@ struct tvs_ctx {
     FusedPlan *fused = nullptr;
     bool fused_narrow = false;   // which build of the fused kernel owns `fused`: 128-column (true) or 256-column tiles
     StreamPlan *streaming = nullptr;   // vertical down-scales: the line-buffer kernel
+    bool box2 = false;                 // exact 2:1 area on 8-bit planes with matching layouts: the box-filter kernel
     int forced_path = -1;
     // two-pass scratch
     int16_t *mid = nullptr;
@@ -272,6 +273,18 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     }
     if (!plan.any_scale) return 0;
 
+    if (c->box2 && c->forced_path < 0) {
+        // one launch per stored plane: Y, then U and V (planar) or the interleaved UV plane
+        for (size_t i = 0; i < plan.ops.size(); ++i) {
+            const PlaneOp &op = plan.ops[i];
+            const bool pair = op.src_xstep == 2;
+            if (pair && op.src_offset != 0) continue;   // the V view of an interleaved plane: done with its U view
+            if (launch_box2(sv[i], dv[i], pair, pair ? 2 * op.dw : op.dw, op.dh, n_frames, stream) < 0)
+                return cuda_fail(cudaGetLastError(), "box-filter kernel launch");
+            ++c->launches;
+        }
+        return 0;
+    }
     if (c->forced_path == 2 && !c->streaming) return fail(-ENOSYS, "streaming path requested but this shape is not supported by it");
     if (use_stream_path(c)) {
         const int n = stream_launch(c->streaming, plan, sv.data(), dv.data(), n_frames, stream);
@@ -418,6 +431,19 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         tvs_destroy(c);
         return nullptr;
     }
+    // Exact 2:1 area: every table row is the pair [one/2, one/2] on samples 2i, 2i+1 (see box2_kernel).
+    {
+        auto is_box = [](const AxisTable &t, int one) {
+            if (t.taps != 2) return false;
+            for (int i = 0; i < t.length; ++i)
+                if (t.pos[i] != 2 * i || t.coef[2 * i] != one / 2 || t.coef[2 * i + 1] != one / 2) return false;
+            return true;
+        };
+        bool ok = c->plan.any_scale && sfi.bits == 8 && dfi.bits == 8 && src_w == 2 * dst_w && src_h == 2 * dst_h &&
+                  (src_w % 4) == 0 && (src_h % 4) == 0 && sfi.semi == dfi.semi;
+        for (int i = 0; ok && i < 4; ++i) ok = is_box(c->host_tables[i], i < 2 ? 1 << 14 : 1 << 12);
+        c->box2 = ok;
+    }
     if (c->plan.any_scale) {
         std::string why;
         // Down-scales stage a wide source footprint and do better with 128-column tiles; up-scales amortise the
@@ -534,7 +560,7 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const bool dst_packed = packed(reinterpret_cast<const void *const *>(dst), dst_pitch, dst_frame_stride, c->dfi, d_off, d_pitch, dframe);
 
     // The two-pass path owns ONE intermediate buffer, so its chunks must not overlap on the device.
-    const bool single_stream = c->plan.any_scale && !use_fused_path(c) && !use_stream_path(c);
+    const bool single_stream = c->plan.any_scale && !use_fused_path(c) && !use_stream_path(c) && !(c->box2 && c->forced_path < 0);
     int slot = 0;
     for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk), slot = single_stream ? 0 : slot ^ 1) {
         const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
@@ -588,6 +614,7 @@ long long tvs_info(const tvs_ctx *c, int what) {
     case TVS_INFO_KERNEL_LAUNCHES: return c->launches;
     case TVS_INFO_PATH:
         if (!c->plan.any_scale) return 2;
+        if (c->box2 && c->forced_path < 0) return 4;
         return use_stream_path(c) ? 3 : use_fused_path(c) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
         return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + 2 * (c->stage_src_bytes + c->stage_dst_bytes));
