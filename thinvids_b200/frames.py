@@ -154,6 +154,8 @@ CONFIGS = {
 EXTRA_CONFIGS = {
     "W1080": ScaleConfig("W1080", "yuv420p", 720, 480, "nv12", 1620, 1080, "bicubic", 300),
     "W720": ScaleConfig("W720", "yuv420p", 1920, 1080, "nv12", 1280, 720, "bicubic", 128),
+    "W720P": ScaleConfig("W720P", "yuv420p", 1920, 1080, "yuv420p", 1280, 720, "bicubic", 128),
+    "W4K": ScaleConfig("W4K", "yuv420p", 3840, 2160, "nv12", 1920, 1080, "bicubic", 64),
     "DVD480": ScaleConfig("DVD480", "yuv420p", 720, 480, "nv12", 720, 480, "bicubic", 1000),      # SCALE_FILTER_480 on a DVD source
     "HDR8": ScaleConfig("HDR8", "yuv420p10le", 1920, 1080, "nv12", 1920, 1080, "bicubic", 128),   # same-size 10 -> 8 bit
     "C3P": ScaleConfig("C3P", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "area", 64),
