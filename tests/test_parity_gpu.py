@@ -155,7 +155,12 @@ def test_pitched_and_strided_device_surfaces():
     from thinvids_b200.swscale import Scaler
     for sf, df, sw, sh, dw, dh, alg, spitch_extra, dpitch_extra in [
         (1, 1, 320, 180, 480, 270, F.SWS_LANCZOS, 192, 32), (0, 0, 322, 182, 161, 91, F.SWS_BICUBIC, 3, 5),
-        (3, 3, 128, 72, 256, 144, F.SWS_BICUBIC, 64, 2), (2, 0, 130, 74, 99, 55, F.SWS_AREA, 6, 1)]:
+        (3, 3, 128, 72, 256, 144, F.SWS_BICUBIC, 64, 2), (2, 0, 130, 74, 99, 55, F.SWS_AREA, 6, 1),
+        # down-scales of 8-bit planes: source rows 4-byte aligned to each other (the streaming kernel's raw-byte
+        # horizontal pass) and not (its float pass), planar and interleaved chroma
+        (0, 0, 648, 360, 220, 122, F.SWS_LANCZOS, 0, 0), (0, 1, 648, 360, 220, 122, F.SWS_LANCZOS, 3, 0),
+        (1, 1, 1288, 200, 860, 134, F.SWS_BICUBIC, 4, 4), (1, 0, 1288, 200, 860, 134, F.SWS_BICUBIC, 2, 1),
+        (1, 1, 2000, 64, 500, 16, F.SWS_BILINEAR, 8, 0)]:
         n = 3
         frames = [F.random_frame(sf, sw, sh, 50 + i) for i in range(n)]
         want = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(fr) for fr in frames]

@@ -17,6 +17,7 @@
 // Arithmetic, exactness argument and output rules are those of the tile kernel (scale_device.cuh).
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 
 #include "scale_device.cuh"
@@ -40,6 +41,8 @@ struct StreamOpParams {
     int strips, strip_begin;
     const float *hcoef;    // [dw][HT]             c * 2^-(23+hshift) in tap order (zero padded to HT)
     const int *hpos;       // [dw]                 first source column of each output column
+    const short *hcoef_i;  // [dw][h_taps]         the integer coefficients (raw-byte horizontal pass)
+    int h_taps;            // real horizontal taps (row length of hcoef_i)
     const int *vpos;       // [dh]
     const float *vpair;    // [dh][VT][2]          (g, g) * 2^107 in tap order
     const int *vint;       // [dh][VT]             the same coefficients as integers (exact path)
@@ -152,7 +155,22 @@ __device__ __forceinline__ void convert_block(const StreamOpParams &op, const un
     }
 }
 
-template <int HT, int VT, int OUT>
+__device__ __forceinline__ int dp2a_lo(unsigned pixels, int coef_pair, int acc) {
+    int d;   // acc + s16(coef_pair.lo) * u8(pixels.b0) + s16(coef_pair.hi) * u8(pixels.b1)
+    asm("dp2a.lo.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef_pair), "r"(pixels), "r"(acc));
+    return d;
+}
+__device__ __forceinline__ int dp2a_hi(unsigned pixels, int coef_pair, int acc) {
+    int d;   // the same on bytes 2 and 3
+    asm("dp2a.hi.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(coef_pair), "r"(pixels), "r"(acc));
+    return d;
+}
+
+// NW = 0: the horizontal pass runs on float samples (any source).  NW > 0: 8-bit sources whose rows are 4-byte
+// aligned relative to each other skip the float conversion altogether: the pass reads the raw staged words and does
+// two taps per IDP.2A, with each column's 16-bit coefficients pre-placed at the byte positions of its window inside NW
+// consecutive words (the placement depends only on the column and on the strip's alignment, not on the row).
+template <int HT, int VT, int OUT, int NW>
 __global__ void __launch_bounds__(kSThreads, 4)
 stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
@@ -185,16 +203,40 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
     // neighbouring output columns read windows that are a whole source step apart, so consecutive lanes touch
     // consecutive shared-memory words (no bank conflicts) and every multiply-add is a real tap.  The coefficients of
     // the four columns stay in registers for the whole strip.
-    float ck[4][HT];
-    int hstart[4];
-#pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int x = min(x0 + lane + 32 * k, dw - 1);
-        hstart[k] = __ldg(op.hpos + x) - c0;
-#pragma unroll
-        for (int j = 0; j < HT; ++j) ck[k][j] = __ldg(op.hcoef + static_cast<size_t>(x) * HT + j);
-    }
+    float ck[NW ? 1 : 4][NW ? 1 : HT];
+    int cp[NW ? 4 : 1][NW ? 2 * NW : 1];   // raw mode: (c[p], c[p+1]) pairs by byte position inside the NW words
+    int hstart[4];                       // float mode: first sample of the window; raw mode: its first word
     const int src_mode = op.src_mode;
+    if (NW == 0) {
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int x = min(x0 + lane + 32 * k, dw - 1);
+            hstart[k] = __ldg(op.hpos + x) - c0;
+#pragma unroll
+            for (int j = 0; j < HT; ++j) ck[k][j] = __ldg(op.hcoef + static_cast<size_t>(x) * HT + j);
+        }
+    } else {
+        // rows are a multiple of 4 bytes apart, so the byte phase of a window is the same in every row
+        const int a = static_cast<int>(reinterpret_cast<uintptr_t>(strip_base) & 3u);
+        const int taps = op.h_taps;
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            const int x = min(x0 + lane + 32 * k, dw - 1);
+            const int byte0 = a + (__ldg(op.hpos + x) - c0) * xs;      // position of tap 0 relative to the aligned row start
+            hstart[k] = byte0 >> 2;
+            const int phase = byte0 & 3;
+            const short *ci = op.hcoef_i + static_cast<size_t>(x) * taps;
+#pragma unroll
+            for (int h = 0; h < 2 * NW; ++h) {
+                // byte positions 2h and 2h + 1 of the window's words hold taps (2h - phase) / xs and (2h + 1 - phase) / xs
+                int lo16 = 0, hi16 = 0;
+                const int p0 = 2 * h - phase, p1 = p0 + 1;
+                if (p0 >= 0 && (p0 % xs) == 0 && p0 / xs < taps) lo16 = __ldg(ci + p0 / xs);
+                if (p1 >= 0 && (p1 % xs) == 0 && p1 / xs < taps) hi16 = __ldg(ci + p1 / xs);
+                cp[k][h] = (lo16 & 0xffff) | (hi16 << 16);
+            }
+        }
+    }
     const float h_addend = op.h_addend, t_max = __int_as_float(32767);
 
     // rows the vertical pass may touch before they are produced (tap padding) must read as finite values
@@ -224,21 +266,46 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
         }
         __syncthreads();   // the block's raw rows are visible to everyone; S is free (previous horizontal pass is over)
         const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(strip_base + static_cast<ptrdiff_t>(r_b) * src_pitch)) & 15u;
-        convert_block(op, RAW + (b & 1) * raw_words, S, rows, mis0, pmod, tid);
-        __syncthreads();   // S holds the block
+        if (NW == 0) {
+            convert_block(op, RAW + (b & 1) * raw_words, S, rows, mis0, pmod, tid);
+            __syncthreads();   // S holds the block
+        }
 
         // ---- horizontal pass of the block's rows into the ring ----
-        for (int i = warp; i < rows; i += kSWarps) {
-            const unsigned mis = (mis0 + i * pmod) & 15u;
-            const float *srow = S + i * op.s_pitch + (src_mode == kSrcU8 ? mis : src_mode == kSrcU16Pair ? (mis >> 2) : (mis >> 1));
-            float *mrow = M + ((r_b + i) & mask) * kStripW + lane;
+        if (NW == 0) {
+            for (int i = warp; i < rows; i += kSWarps) {
+                const unsigned mis = (mis0 + i * pmod) & 15u;
+                const float *srow = S + i * op.s_pitch + (src_mode == kSrcU8 ? mis : src_mode == kSrcU16Pair ? (mis >> 2) : (mis >> 1));
+                float *mrow = M + ((r_b + i) & mask) * kStripW + lane;
 #pragma unroll
-            for (int k = 0; k < 4; ++k) {
-                const float *sp = srow + hstart[k];
-                float acc = 0.0f;
+                for (int k = 0; k < 4; ++k) {
+                    const float *sp = srow + hstart[k];
+                    float acc = 0.0f;
 #pragma unroll
-                for (int j = 0; j < HT; ++j) acc = fmaf(sp[j], ck[k][j], acc);
-                mrow[32 * k] = fminf(fma_rm(acc, 0x1p-126f, h_addend), t_max);   // floor(sum >> hshift), clamped above
+                    for (int j = 0; j < HT; ++j) acc = fmaf(sp[j], ck[k][j], acc);
+                    mrow[32 * k] = fminf(fma_rm(acc, 0x1p-126f, h_addend), t_max);   // floor(sum >> hshift), clamped above
+                }
+            }
+        } else {
+            const unsigned *rblock = RAW + (b & 1) * raw_words;
+            const int row_words = op.s_chunks * 4;
+            for (int i = warp; i < rows; i += kSWarps) {
+                const unsigned mis = (mis0 + i * pmod) & 15u;        // a multiple of 4 apart from row to row
+                const unsigned *rrow = rblock + i * row_words + (mis >> 2);
+                unsigned *mrow = reinterpret_cast<unsigned *>(M) + ((r_b + i) & mask) * kStripW + lane;
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const unsigned *wp = rrow + hstart[k];
+                    int acc = 0;
+#pragma unroll
+                    for (int w = 0; w < NW; ++w) {
+                        const unsigned v = wp[w];
+                        acc = dp2a_lo(v, cp[k][2 * w], acc);
+                        acc = dp2a_hi(v, cp[k][2 * w + 1], acc);
+                    }
+                    const int t = min(acc >> 7, 32767);
+                    mrow[32 * k] = static_cast<unsigned>(abs(t)) | (static_cast<unsigned>(t) & 0x80000000u);   // sign-magnitude = t * 2^-149
+                }
             }
         }
         __syncthreads();   // the ring holds every row up to r_b + rows
@@ -281,13 +348,22 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
 }
 
 using StreamFn = void (*)(const StreamLaunchParams);
-struct StreamInstance { int ht, vt; StreamFn fn[3]; };   // horizontal taps, vertical taps; one kernel per output rule
-#define TVS_SINST(H, V) {H, V, {stream_scale_kernel<H, V, kOutU8>, stream_scale_kernel<H, V, kOutU8Dither>, stream_scale_kernel<H, V, kOutU10>}}
+// horizontal taps, vertical taps, raw-byte words (0 = float horizontal pass); one kernel per output rule (raw: 8-bit out only)
+struct StreamInstance { int ht, vt, nw; StreamFn fn[3]; };
+#define TVS_SINST(H, V) {H, V, 0, {stream_scale_kernel<H, V, kOutU8, 0>, stream_scale_kernel<H, V, kOutU8Dither, 0>, stream_scale_kernel<H, V, kOutU10, 0>}}
+#define TVS_SRAW(H, V, W) {H, V, W, {stream_scale_kernel<H, V, kOutU8, W>, nullptr, nullptr}}
 const StreamInstance kStreamInstances[] = {
     TVS_SINST(2, 2), TVS_SINST(4, 2), TVS_SINST(4, 3),  TVS_SINST(4, 4),  TVS_SINST(6, 4),  TVS_SINST(6, 6),   TVS_SINST(8, 6),
     TVS_SINST(8, 8), TVS_SINST(9, 9), TVS_SINST(12, 9), TVS_SINST(12, 12), TVS_SINST(16, 12),
+    // raw-byte horizontal pass: NW words cover phase (<= 3) + the window's bytes
+    TVS_SRAW(2, 2, 2), TVS_SRAW(4, 4, 2), TVS_SRAW(4, 4, 3), TVS_SRAW(6, 6, 3), TVS_SRAW(6, 6, 4), TVS_SRAW(9, 9, 3), TVS_SRAW(9, 9, 5),
+    TVS_SRAW(12, 12, 4), TVS_SRAW(12, 12, 7),
 };
 #undef TVS_SINST
+#undef TVS_SRAW
+
+// test / profiling aid: TVS_STREAM_FLOAT=1 keeps the float horizontal pass even where the raw-byte one applies
+const bool g_stream_force_float = [] { const char *e = getenv("TVS_STREAM_FLOAT"); return e && e[0] == '1'; }();
 
 template <typename T>
 size_t append_blob(std::vector<uint8_t> &blob, const std::vector<T> &v) {
@@ -300,11 +376,11 @@ size_t append_blob(std::vector<uint8_t> &blob, const std::vector<T> &v) {
 }  // namespace
 
 struct StreamOp {
-    int op_index = 0, instance = -1, out_mode = 0, src_mode = 0;
+    int op_index = 0, instance = -1, raw_instance = -1, out_mode = 0, src_mode = 0, h_taps = 0;
     int strips = 0, vtaps = 0, kb = 0, n_blocks = 0, rm_rows = 0;
     int s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0;
     float v_thr = 0, v_init = 0, src_scale = 1.f, h_addend = 0.f;
-    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vpair_off = 0, vint_off = 0, yend_off = 0;
+    size_t hdense_off = 0, hint_off = 0, hbase_off = 0, vpos_off = 0, vpair_off = 0, vint_off = 0, yend_off = 0;
     std::vector<short> strip_c0, strip_nc;
     size_t smem_bytes = 0;
 };
@@ -351,10 +427,32 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         int inst = -1;
         const int n_inst = static_cast<int>(sizeof(kStreamInstances) / sizeof(kStreamInstances[0]));
         for (int i = 0; i < n_inst; ++i) {
-            if (kStreamInstances[i].ht < h.taps || kStreamInstances[i].vt < v.taps) continue;
+            if (kStreamInstances[i].nw != 0 || kStreamInstances[i].ht < h.taps || kStreamInstances[i].vt < v.taps) continue;
             if (inst < 0 || kStreamInstances[i].ht + kStreamInstances[i].vt < kStreamInstances[inst].ht + kStreamInstances[inst].vt) inst = i;
         }
         if (inst < 0) return bail("no streaming kernel instance for this filter size");
+        // raw-byte horizontal pass (8-bit in, plain 8-bit out): the words a window can touch at the worst byte phase
+        so.h_taps = h.taps;
+        bool fits16 = true;
+        for (int c : h.coef) fits16 = fits16 && c >= -32768 && c <= 32767;
+        if (!wide_src && so.out_mode == kOutU8 && fits16) {
+            const int need_words = (3 + (h.taps - 1) * op.src_xstep + 1 + 3) / 4;
+            for (int i = 0; i < n_inst; ++i) {
+                const StreamInstance &k = kStreamInstances[i];
+                if (k.nw < need_words || k.vt < v.taps || k.ht < h.taps) continue;
+                if (so.raw_instance < 0 || k.vt + k.nw < kStreamInstances[so.raw_instance].vt + kStreamInstances[so.raw_instance].nw) so.raw_instance = i;
+            }
+            // both variants share one vertical layout
+            if (so.raw_instance >= 0 && kStreamInstances[so.raw_instance].vt != kStreamInstances[inst].vt) {
+                int both = -1;
+                for (int i = 0; i < n_inst; ++i) {
+                    const StreamInstance &k = kStreamInstances[i];
+                    if (k.nw != 0 || k.ht < h.taps || k.vt != kStreamInstances[so.raw_instance].vt) continue;
+                    if (both < 0 || k.ht < kStreamInstances[both].ht) both = i;
+                }
+                if (both >= 0) inst = both; else so.raw_instance = -1;
+            }
+        }
         const int HT = kStreamInstances[inst].ht, VT = kStreamInstances[inst].vt;
         so.instance = inst;
         so.vtaps = v.taps;
@@ -381,6 +479,7 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
             ncols_max = std::max(ncols_max, h.pos[xb] + HT - h.pos[xa]);
         }
         so.s_chunks = std::max(2, (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1);   // >= 2: the reciprocal fits 32 bits
+        if (so.raw_instance >= 0) so.s_chunks += 2;   // the raw pass reads whole words, up to NW of them past a window's start
         so.s_chunks_log2 = 0;
         while ((1 << so.s_chunks_log2) < so.s_chunks) ++so.s_chunks_log2;
         so.s_pitch = so.s_chunks * (16 / op.src_xstep);
@@ -423,6 +522,7 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         }
         if (so.smem_bytes > 200 * 1024) return bail("strip does not fit in shared memory");
         so.hdense_off = append_blob(blob, hcoef);
+        if (so.raw_instance >= 0) so.hint_off = append_blob(blob, std::vector<short>(h.coef.begin(), h.coef.end()));
         so.hbase_off = append_blob(blob, h.pos);
         so.vpos_off = append_blob(blob, v.pos);
         so.vpair_off = append_blob(blob, vpair);
@@ -437,9 +537,13 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         return bail("device allocation for the streaming tables failed");
     }
     sp->blob_bytes = blob.size();
-    for (const StreamOp &so : sp->ops)
+    for (const StreamOp &so : sp->ops) {
         cudaFuncSetAttribute(reinterpret_cast<const void *>(kStreamInstances[so.instance].fn[so.out_mode]),
                              cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+        if (so.raw_instance >= 0)
+            cudaFuncSetAttribute(reinterpret_cast<const void *>(kStreamInstances[so.raw_instance].fn[so.out_mode]),
+                                 cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    }
     return sp;
 }
 
@@ -453,13 +557,21 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
                   cudaStream_t stream) {
     int launched = 0;
     std::vector<bool> done(p->ops.size(), false);
+    // the raw-byte variant needs source rows a multiple of 4 bytes apart (a window's byte phase is then row-independent)
+    std::vector<int> chosen(p->ops.size());
+    for (size_t i = 0; i < p->ops.size(); ++i) {
+        const StreamOp &so = p->ops[i];
+        const bool raw_ok = so.raw_instance >= 0 && (src_views[so.op_index].pitch & 3) == 0 && !g_stream_force_float;
+        chosen[i] = raw_ok ? so.raw_instance : so.instance;
+    }
     for (size_t i = 0; i < p->ops.size(); ++i) {
         if (done[i]) continue;
+        const bool raw = kStreamInstances[chosen[i]].nw != 0;
         StreamLaunchParams lp{};
         int strips = 0, m_floats = 0, s_floats = 0, raw_words = 0;
         for (size_t j = i; j < p->ops.size() && lp.n_ops < kMaxStreamOps; ++j) {
             const StreamOp &so = p->ops[j];
-            if (done[j] || so.instance != p->ops[i].instance || so.out_mode != p->ops[i].out_mode) continue;
+            if (done[j] || chosen[j] != chosen[i] || so.out_mode != p->ops[i].out_mode) continue;
             done[j] = true;
             const PlaneOp &op = plan.ops[so.op_index];
             const SampleView &s = src_views[so.op_index], &d = dst_views[so.op_index];
@@ -470,6 +582,8 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             q.strips = so.strips; q.strip_begin = strips;
             q.hcoef = reinterpret_cast<const float *>(p->blob + so.hdense_off);
             q.hpos = reinterpret_cast<const int *>(p->blob + so.hbase_off);
+            q.hcoef_i = reinterpret_cast<const short *>(p->blob + so.hint_off);
+            q.h_taps = so.h_taps;
             q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
             q.vpair = reinterpret_cast<const float *>(p->blob + so.vpair_off);
             q.vint = reinterpret_cast<const int *>(p->blob + so.vint_off);
@@ -486,14 +600,14 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             std::copy(so.strip_nc.begin(), so.strip_nc.end(), q.strip_nc);
             strips += so.strips;
             m_floats = std::max(m_floats, so.rm_rows * kStripW);
-            s_floats = std::max(s_floats, so.kb * so.s_pitch);
+            if (!raw) s_floats = std::max(s_floats, so.kb * so.s_pitch);
             raw_words = std::max(raw_words, so.kb * so.s_chunks * 4);
         }
         lp.m_floats = m_floats; lp.s_floats = s_floats; lp.raw_words = raw_words;
         const size_t smem = static_cast<size_t>(m_floats + s_floats + 2 * raw_words) * 4;
         if (smem > 200 * 1024) return -2;
         const dim3 grid(strips, n_frames);
-        kStreamInstances[p->ops[i].instance].fn[p->ops[i].out_mode]<<<grid, kSThreads, smem, stream>>>(lp);
+        kStreamInstances[chosen[i]].fn[p->ops[i].out_mode]<<<grid, kSThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
         ++launched;
     }

@@ -16,6 +16,11 @@ for sf in range(4):
         cases.append((sf, 211, 119, df, 67, 41, F.SWS_BICUBIC))
 cases += [(0, 720, 480, 0, 1920, 1080, F.SWS_LANCZOS), (1, 640, 360, 1, 320, 180, F.SWS_AREA), (0, 300, 200, 1, 300, 200, F.SWS_BICUBIC),
           (3, 257, 131, 1, 257, 131, F.SWS_BICUBIC), (0, 1810, 64, 0, 905, 32, F.SWS_BICUBIC)]
+# widths whose planes keep 4-byte row alignment: the raw-byte horizontal pass of the streaming kernel
+for sf in (0, 1):
+    for df in (0, 1):
+        cases += [(sf, 216, 120, df, 68, 40, F.SWS_LANCZOS), (sf, 1928, 136, df, 1284, 90, F.SWS_BICUBIC), (sf, 648, 360, df, 220, 122, F.SWS_AREA),
+                  (sf, 1000, 96, df, 334, 46, F.SWS_BILINEAR), (sf, 3840, 64, df, 1280, 22, F.SWS_LANCZOS)]
 bad = 0
 for sf, sw, sh, df, dw, dh, alg in cases:
     src = [F.random_frame(sf, sw, sh, 9), F.random_frame(sf, sw, sh, 10)]
