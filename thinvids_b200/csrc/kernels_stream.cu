@@ -43,6 +43,7 @@ struct StreamOpParams {
     const int *hpos;       // [dw]                 first source column of each output column
     const short *hcoef_i;  // [dw][h_taps]         the integer coefficients (raw-byte horizontal pass)
     int h_taps;            // real horizontal taps (row length of hcoef_i)
+    int pf_step_rows, pf_step_chunks;   // kSThreads split into whole staged rows + chunks (prefetch loop stride)
     const int *vpos;       // [dh]
     const float *vpair;    // [dh][VT][2]          (g, g) * 2^107 in tap order
     const int *vint;       // [dh][VT]             the same coefficients as integers (exact path)
@@ -102,18 +103,23 @@ __device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const u
     const uint8_t *base = strip_base + static_cast<ptrdiff_t>(r_b) * pitch;
     const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(base)) & 15u;
     const unsigned pmod = static_cast<unsigned>(pitch) & 15u;
-    const unsigned magic = op.chunk_magic;
-    // (row, chunk) pairs are spread over all threads: a row is rarely a power-of-two number of chunks
-    for (int idx = tid; idx < rows * s_chunks; idx += kSThreads) {
-        const int row = static_cast<int>(__umulhi(static_cast<unsigned>(idx), magic));
-        const int ch = idx - row * s_chunks;
+    // (row, chunk) pairs are spread over all threads (a row is rarely a power-of-two number of chunks); the pair of
+    // the next index is derived from the previous one, no division in the loop
+    const int total = rows * s_chunks;
+    const int step_rows = op.pf_step_rows, step_chunks = op.pf_step_chunks;   // kSThreads = step_rows * s_chunks + step_chunks
+    int row = static_cast<int>(__umulhi(static_cast<unsigned>(tid), op.chunk_magic));
+    int ch = tid - row * s_chunks;
+    const int pitch32 = static_cast<int>(pitch);   // a block spans far less than 2 GB
+    // every chunk of an interior block lies inside the plane's allocation: no per-chunk range checks
+    const bool interior = base - 16 >= lo && base + static_cast<ptrdiff_t>(rows - 1) * pitch + 16 * s_chunks <= hi;
+    for (int idx = tid; idx < total; idx += kSThreads) {
         const unsigned mis = (mis0 + row * pmod) & 15u;
         uint4 *dst = reinterpret_cast<uint4 *>(raw) + idx;
         const int first = 16 * ch - static_cast<int>(mis);
-        const uint8_t *g = base + row * pitch + first;
+        const uint8_t *g = base + (row * pitch32 + first);
         if (first > last_byte) {
             *dst = make_uint4(0u, 0u, 0u, 0u);
-        } else if (g >= lo && g + 16 <= hi) {
+        } else if (interior || (g >= lo && g + 16 <= hi)) {
             cp_async16(dst, g);
         } else {
 #pragma unroll
@@ -123,6 +129,9 @@ __device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const u
                 else *d = 0u;
             }
         }
+        row += step_rows;
+        ch += step_chunks;
+        if (ch >= s_chunks) { ch -= s_chunks; ++row; }
     }
 }
 
@@ -223,7 +232,7 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
         for (int k = 0; k < 4; ++k) {
             const int x = min(x0 + lane + 32 * k, dw - 1);
             const int byte0 = a + (__ldg(op.hpos + x) - c0) * xs;      // position of tap 0 relative to the aligned row start
-            hstart[k] = byte0 >> 2;
+            hstart[k] = byte0 & ~3;   // byte offset of the window's first word
             const int phase = byte0 & 3;
             const short *ci = op.hcoef_i + static_cast<size_t>(x) * taps;
 #pragma unroll
@@ -231,8 +240,9 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
                 // byte positions 2h and 2h + 1 of the window's words hold taps (2h - phase) / xs and (2h + 1 - phase) / xs
                 int lo16 = 0, hi16 = 0;
                 const int p0 = 2 * h - phase, p1 = p0 + 1;
-                if (p0 >= 0 && (p0 % xs) == 0 && p0 / xs < taps) lo16 = __ldg(ci + p0 / xs);
-                if (p1 >= 0 && (p1 % xs) == 0 && p1 / xs < taps) hi16 = __ldg(ci + p1 / xs);
+                const int xsh = xs - 1;   // the byte step of a sample is 1 or 2
+                if (p0 >= 0 && (p0 & xsh) == 0 && (p0 >> xsh) < taps) lo16 = __ldg(ci + (p0 >> xsh));
+                if (p1 >= 0 && (p1 & xsh) == 0 && (p1 >> xsh) < taps) hi16 = __ldg(ci + (p1 >> xsh));
                 cp[k][h] = (lo16 & 0xffff) | (hi16 << 16);
             }
         }
@@ -259,6 +269,7 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
     int y_next = 0;
     for (int b = 0; b < op.n_blocks; ++b) {
         const int r_b = b * kb, rows = min(kb, sh - r_b);
+        const int y_end = __ldg(op.block_yend + b);   // needed after the horizontal pass; asked for now
         cp_async_wait_all();
         if (b + 1 < op.n_blocks) {
             prefetch_block(op, strip_base, lo, hi, r_b + kb, min(kb, sh - r_b - kb), last_byte, RAW + ((b + 1) & 1) * raw_words, tid);
@@ -287,23 +298,29 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
                 }
             }
         } else {
-            const unsigned *rblock = RAW + (b & 1) * raw_words;
-            const int row_words = op.s_chunks * 4;
+            const char *rblock = reinterpret_cast<const char *>(RAW + (b & 1) * raw_words);
+            const int row_bytes = op.s_chunks * 16;
             for (int i = warp; i < rows; i += kSWarps) {
                 const unsigned mis = (mis0 + i * pmod) & 15u;        // a multiple of 4 apart from row to row
-                const unsigned *rrow = rblock + i * row_words + (mis >> 2);
+                const char *rrow = rblock + i * row_bytes + (mis & ~3u);
                 unsigned *mrow = reinterpret_cast<unsigned *>(M) + ((r_b + i) & mask) * kStripW + lane;
+                unsigned v[4][NW ? NW : 1];
+#pragma unroll
+                for (int k = 0; k < 4; ++k)
+#pragma unroll
+                    for (int w = 0; w < NW; ++w) v[k][w] = *reinterpret_cast<const unsigned *>(rrow + hstart[k] + 4 * w);
+                // the four columns' dot products advance together: four independent dependency chains
+                int acc[4] = {0, 0, 0, 0};
+#pragma unroll
+                for (int w = 0; w < NW; ++w) {
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) acc[k] = dp2a_lo(v[k][w], cp[k][2 * w], acc[k]);
+#pragma unroll
+                    for (int k = 0; k < 4; ++k) acc[k] = dp2a_hi(v[k][w], cp[k][2 * w + 1], acc[k]);
+                }
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
-                    const unsigned *wp = rrow + hstart[k];
-                    int acc = 0;
-#pragma unroll
-                    for (int w = 0; w < NW; ++w) {
-                        const unsigned v = wp[w];
-                        acc = dp2a_lo(v, cp[k][2 * w], acc);
-                        acc = dp2a_hi(v, cp[k][2 * w + 1], acc);
-                    }
-                    const int t = min(acc >> 7, 32767);
+                    const int t = min(acc[k] >> 7, 32767);
                     mrow[32 * k] = static_cast<unsigned>(abs(t)) | (static_cast<unsigned>(t) & 0x80000000u);   // sign-magnitude = t * 2^-149
                 }
             }
@@ -311,7 +328,6 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
         __syncthreads();   // the ring holds every row up to r_b + rows
 
         // ---- vertical pass of the output rows whose windows are now complete ----
-        const int y_end = __ldg(op.block_yend + b);
         for (int y = y_next + warp; y < y_end; y += kSWarps) {
             const int first = __ldg(op.vpos + y);
             const f32x2 *gp = reinterpret_cast<const f32x2 *>(op.vpair) + static_cast<size_t>(y) * VT;
@@ -323,12 +339,25 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
                 a01 = pack2(fmaf(static_cast<float>(dither.x - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(dither.y - 64), 0x1p-30f, v_init));
                 a23 = pack2(fmaf(static_cast<float>(dither.z - 64), 0x1p-30f, v_init), fmaf(static_cast<float>(dither.w - 64), 0x1p-30f, v_init));
             }
+            // even and odd taps accumulate separately (two dependency chains per pair instead of one) when there are
+            // enough taps for that to matter; the extra addition is counted in the error bound (stream_plan_create)
+            f32x2 b01 = 0ull, b23 = 0ull;
 #pragma unroll
             for (int j = 0; j < VT; ++j) {
                 const Quad q = load_quad(m_col + ((first + j) & mask) * kStripW);
                 const f32x2 gg = __ldg(gp + j);
-                a01 = fma2(q.lo, gg, a01);
-                a23 = fma2(q.hi, gg, a23);
+                if (VT >= 4 && (j & 1)) {
+                    b01 = fma2(q.lo, gg, b01);
+                    b23 = fma2(q.hi, gg, b23);
+                } else {
+                    a01 = fma2(q.lo, gg, a01);
+                    a23 = fma2(q.hi, gg, a23);
+                }
+            }
+            if (VT >= 4) {
+                const f32x2 one = pack2(1.0f, 1.0f);
+                a01 = fma2(b01, one, a01);
+                a23 = fma2(b23, one, a23);
             }
             unsigned word[2];
             float r[4];
@@ -460,7 +489,7 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         if (so.strips > kMaxStrips) return bail("plane too wide for the strip table");
 
         // float vertical sum: residual threshold / accumulator start (tvs_internal.h)
-        const VerticalFloatRule vrule = vertical_float_rule(v, VT, so.out_mode == kOutU10, so.out_mode == kOutU8Dither);
+        const VerticalFloatRule vrule = vertical_float_rule(v, VT + 1, so.out_mode == kOutU10, so.out_mode == kOutU8Dither);
         if (!vrule.ok) return bail("vertical error bound too large");
         so.v_thr = vrule.thr;
         so.v_init = vrule.init;
@@ -584,6 +613,7 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             q.hpos = reinterpret_cast<const int *>(p->blob + so.hbase_off);
             q.hcoef_i = reinterpret_cast<const short *>(p->blob + so.hint_off);
             q.h_taps = so.h_taps;
+            q.pf_step_rows = kSThreads / so.s_chunks; q.pf_step_chunks = kSThreads % so.s_chunks;
             q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
             q.vpair = reinterpret_cast<const float *>(p->blob + so.vpair_off);
             q.vint = reinterpret_cast<const int *>(p->blob + so.vint_off);
