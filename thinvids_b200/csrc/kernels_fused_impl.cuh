@@ -179,13 +179,15 @@ __device__ __forceinline__ void vertical_row(const Quad (&wa)[VT], const Quad (&
         }
     }
     float ra[4], rb[4];
-    float worst = finish_quad<OUT>(a01, a23, dst_shift, word_a, ra);
-    if (RIGHT) worst = fmaxf(worst, finish_quad<OUT>(b01, b23, dst_shift, word_b, rb));
-    if (worst >= v_thr) {
-        const uint2 fa = exact_fixup<VT, OUT>(m_first, first, exact_coef, v_thr, ra[0], ra[1], ra[2], ra[3], ex.dither, dst_shift,
-                                              make_uint2(word_a[0], word_a[1]));
-        word_a[0] = fa.x; word_a[1] = fa.y;
-        if (RIGHT) {
+    const float worst_a = finish_quad<OUT>(a01, a23, dst_shift, word_a, ra);
+    const float worst_b = RIGHT ? finish_quad<OUT>(b01, b23, dst_shift, word_b, rb) : 0.0f;
+    if (fmaxf(worst_a, worst_b) >= v_thr) {   // one branch on the common path; each half is redone only if it asked
+        if (worst_a >= v_thr) {
+            const uint2 fa = exact_fixup<VT, OUT>(m_first, first, exact_coef, v_thr, ra[0], ra[1], ra[2], ra[3], ex.dither, dst_shift,
+                                                  make_uint2(word_a[0], word_a[1]));
+            word_a[0] = fa.x; word_a[1] = fa.y;
+        }
+        if (RIGHT && worst_b >= v_thr) {
             const uint2 fb = exact_fixup<VT, OUT>(m_first + kHalfW, first, exact_coef, v_thr, rb[0], rb[1], rb[2], rb[3], ex.dither,
                                                   dst_shift, make_uint2(word_b[0], word_b[1]));
             word_b[0] = fb.x; word_b[1] = fb.y;
@@ -299,6 +301,19 @@ __device__ __forceinline__ TileCoord decode_tile(const FusedLaunchParams &P, int
     const int tiles_y = P.op[c.oi].tiles_y;     // tiles of one column are consecutive: they share coefficients and halo rows
     c.tx = rem / tiles_y;
     c.ty = rem - c.tx * tiles_y;
+    return c;
+}
+
+// The tile after `c` in the launch's tile order (rows of a tile column, columns of a plane, planes of a frame,
+// frames): no divisions, unlike decode_tile.
+__device__ __forceinline__ TileCoord next_tile(const FusedLaunchParams &P, TileCoord c) {
+    if (++c.ty < P.op[c.oi].tiles_y) return c;
+    c.ty = 0;
+    if (++c.tx < P.op[c.oi].tiles_x) return c;
+    c.tx = 0;
+    if (++c.oi < P.n_ops) return c;
+    c.oi = 0;
+    ++c.f;
     return c;
 }
 
@@ -419,7 +434,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
         TileCoord nxt = cur;
         const bool more = tile + 1 < t_end;
         if (more) {
-            nxt = decode_tile(P, tile + 1);
+            nxt = next_tile(P, cur);
             prefetch_tile_source(P, nxt, RAW + (buf ^ 1) * P.raw_words, tid);
             cp_async_commit();
         }
