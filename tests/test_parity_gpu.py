@@ -160,7 +160,12 @@ def test_pitched_and_strided_device_surfaces():
         # horizontal pass) and not (its float pass), planar and interleaved chroma
         (0, 0, 648, 360, 220, 122, F.SWS_LANCZOS, 0, 0), (0, 1, 648, 360, 220, 122, F.SWS_LANCZOS, 3, 0),
         (1, 1, 1288, 200, 860, 134, F.SWS_BICUBIC, 4, 4), (1, 0, 1288, 200, 860, 134, F.SWS_BICUBIC, 2, 1),
-        (1, 1, 2000, 64, 500, 16, F.SWS_BILINEAR, 8, 0)]:
+        (1, 1, 2000, 64, 500, 16, F.SWS_BILINEAR, 8, 0),
+        # same-size 10 -> 8 bit: the vector dither kernels (aligned pitches, ragged widths, P010's raw tail) and the
+        # per-sample fallback (unaligned pitches)
+        (2, 1, 1920, 18, 1920, 18, F.SWS_BICUBIC, 0, 0), (2, 1, 20, 6, 20, 6, F.SWS_BICUBIC, 4, 12), (2, 1, 20, 6, 20, 6, F.SWS_BICUBIC, 6, 12),
+        (3, 1, 20, 6, 20, 6, F.SWS_BICUBIC, 4, 12), (3, 1, 200, 10, 200, 10, F.SWS_BICUBIC, 0, 0), (2, 0, 64, 10, 64, 10, F.SWS_BICUBIC, 8, 8),
+        (3, 0, 36, 4, 36, 4, F.SWS_BICUBIC, 3, 1)]:
         n = 3
         frames = [F.random_frame(sf, sw, sh, 50 + i) for i in range(n)]
         want = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(fr) for fr in frames]

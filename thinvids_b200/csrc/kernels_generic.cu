@@ -83,7 +83,7 @@ template <typename SrcT, typename DstT>
 __global__ void __launch_bounds__(256)
 repack_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, int sxstep, int src_shift,
               uint8_t *__restrict__ dst, ptrdiff_t dpitch, ptrdiff_t dframe, int dxstep, int dst_shift,
-              int w, int kind, int raw_tail_from) {
+              int w, int kind, int raw_tail_from, int dither_xoff) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int y = blockIdx.y;
     const int f = blockIdx.z;
@@ -94,10 +94,136 @@ repack_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sfram
         const unsigned d = (y & 1) ? ((x & 1) ? 0u : 3u) : ((x & 1) ? 2u : 1u);
         const unsigned t = (v + d) >> 2;
         v = (t - (t >> 8)) & 0xffu;
+    } else if (kind == kOpDither128) {
+        const unsigned t = min((v >> src_shift) << 5, 32767u);
+        v = min((t + kDither128[y & 7][(x + dither_xoff) & 7]) >> 7, 255u);
     } else {
         v = (v >> src_shift) << dst_shift;
     }
     *reinterpret_cast<DstT *>(dst + f * dframe + y * dpitch + static_cast<ptrdiff_t>(x) * dxstep) = static_cast<DstT>(v);
+}
+
+// ---- vector forms of kOpDither2 (same-size 10 -> 8 bit, e.g. a yuv420p10le / p010le source going to nv12 for the
+// hardware encoder) -------------------------------------------------------------------------------------------------
+// One sample, exactly as repack_kernel does it.
+__device__ __forceinline__ unsigned dither2_sample(unsigned v, int x, int y) {
+    const unsigned d = (y & 1) ? ((x & 1) ? 0u : 3u) : ((x & 1) ? 2u : 1u);
+    const unsigned t = (v + d) >> 2;
+    return (t - (t >> 8)) & 0xffu;
+}
+// Two 16-bit samples per word (even column in the low half).  Exact for any 16-bit input: (v + d) >> 2 is taken as
+// (v >> 2) + (((v & 3) + d) >> 2), which cannot carry from one half into the other.
+__device__ __forceinline__ unsigned dither2_pair(unsigned word, int shift, unsigned d2) {
+    const unsigned v2 = (word >> shift) & (0xffffu >> shift) * 0x00010001u;
+    const unsigned carry = (((v2 & 0x00030003u) + d2) >> 2) & 0x00010001u;
+    const unsigned t2 = ((v2 >> 2) & 0x3fff3fffu) + carry;
+    return (t2 - ((t2 >> 8) & 0x00ff00ffu)) & 0x00ff00ffu;   // one result byte in each half
+}
+// Eight consecutive samples (16 bytes, the first on an even column) -> eight bytes.
+__device__ __forceinline__ uint2 dither2_oct(uint4 in, int shift, unsigned d2) {
+    const unsigned a = dither2_pair(in.x, shift, d2), b = dither2_pair(in.y, shift, d2);
+    const unsigned c = dither2_pair(in.z, shift, d2), d = dither2_pair(in.w, shift, d2);
+    return make_uint2(__byte_perm(a, b, 0x6420), __byte_perm(c, d, 0x6420));
+}
+
+// A plane of back-to-back 16-bit samples -> a plane of back-to-back bytes, 8 samples per thread.  `raw_tail_from`
+// (a multiple of 8, or -1) keeps libswscale's P010 tail quirk: columns from there on skip the shift.
+__global__ void __launch_bounds__(256)
+dither2_rows_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, uint8_t *__restrict__ dst, ptrdiff_t dpitch,
+                    ptrdiff_t dframe, int w, int rows, int src_shift, int raw_tail_from) {
+    const int slots = (w + 7) >> 3;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, x = (idx - y * slots) * 8;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const uint8_t *s = src + f * sframe + y * spitch + 2 * static_cast<ptrdiff_t>(x);
+    uint8_t *d = dst + f * dframe + y * dpitch + x;
+    const int shift = (raw_tail_from >= 0 && x >= raw_tail_from) ? 0 : src_shift;
+    if (x + 8 <= w) {
+        const unsigned d2 = (y & 1) ? 0x00000003u : 0x00020001u;
+        *reinterpret_cast<uint2 *>(d) = dither2_oct(__ldg(reinterpret_cast<const uint4 *>(s)), shift, d2);
+    } else {
+        for (int k = 0; x + k < w; ++k) d[k] = static_cast<uint8_t>(dither2_sample(reinterpret_cast<const uint16_t *>(s)[k] >> shift, x + k, y));
+    }
+}
+
+// Two planar 16-bit chroma planes -> one interleaved byte plane, 8 sample pairs per thread.
+__global__ void __launch_bounds__(256)
+dither2_interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__restrict__ v, ptrdiff_t spitch_u, ptrdiff_t spitch_v,
+                          ptrdiff_t sframe_u, ptrdiff_t sframe_v, uint8_t *__restrict__ dst, ptrdiff_t dpitch, ptrdiff_t dframe, int w,
+                          int rows, int src_shift) {
+    const int slots = (w + 7) >> 3;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, x = (idx - y * slots) * 8;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const uint8_t *us = u + f * sframe_u + y * spitch_u + 2 * static_cast<ptrdiff_t>(x);
+    const uint8_t *vs = v + f * sframe_v + y * spitch_v + 2 * static_cast<ptrdiff_t>(x);
+    uint8_t *d = dst + f * dframe + y * dpitch + 2 * x;
+    if (x + 8 <= w) {
+        const unsigned d2 = (y & 1) ? 0x00000003u : 0x00020001u;
+        const uint2 a = dither2_oct(__ldg(reinterpret_cast<const uint4 *>(us)), src_shift, d2);
+        const uint2 b = dither2_oct(__ldg(reinterpret_cast<const uint4 *>(vs)), src_shift, d2);
+        uint4 o;
+        o.x = __byte_perm(a.x, b.x, 0x5140); o.y = __byte_perm(a.x, b.x, 0x7362);
+        o.z = __byte_perm(a.y, b.y, 0x5140); o.w = __byte_perm(a.y, b.y, 0x7362);
+        *reinterpret_cast<uint4 *>(d) = o;
+    } else {
+        for (int k = 0; x + k < w; ++k) {
+            d[2 * k] = static_cast<uint8_t>(dither2_sample(reinterpret_cast<const uint16_t *>(us)[k] >> src_shift, x + k, y));
+            d[2 * k + 1] = static_cast<uint8_t>(dither2_sample(reinterpret_cast<const uint16_t *>(vs)[k] >> src_shift, x + k, y));
+        }
+    }
+}
+
+// kOpDither128 for the chroma of a planar 10-bit source going to NV12: 8 U + 8 V samples -> 16 interleaved bytes.
+// Rows of the 8x8 dither matrix packed one byte per column.
+__device__ const unsigned kDither128Packed[8][2] = {
+    {0x5c3c4424u, 0x5a3a4222u}, {0x1c7c0464u, 0x1a7a0262u}, {0x4c2c5434u, 0x4a2a5232u}, {0x0c6c1474u, 0x0a6a1272u},
+    {0x58384020u, 0x5e3e4626u}, {0x18780060u, 0x1e7e0666u}, {0x48285030u, 0x4e2e5636u}, {0x08681070u, 0x0e6e1676u},
+};
+__device__ __forceinline__ unsigned dither128_sample(unsigned v, unsigned d) {
+    return min((min(v << 5, 32767u) + d) >> 7, 255u);
+}
+// eight 16-bit samples starting on a column that is a multiple of 8; `rot` = dither_xoff (0 or 3)
+__device__ __forceinline__ uint2 dither128_oct(uint4 in, int shift, unsigned d_lo, unsigned d_hi, int rot) {
+    const unsigned w[4] = {in.x, in.y, in.z, in.w};
+    const unsigned long long d = (static_cast<unsigned long long>(d_hi) << 32) | d_lo;
+    const unsigned long long dr = rot ? ((d >> (8 * rot)) | (d << (64 - 8 * rot))) : d;   // column k uses entry (k + rot) & 7
+    unsigned out[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) {
+        const unsigned v = ((w[k >> 1] >> (16 * (k & 1))) & 0xffffu) >> shift;
+        out[k] = dither128_sample(v, static_cast<unsigned>(dr >> (8 * k)) & 0xffu);
+    }
+    return make_uint2(out[0] | (out[1] << 8) | (out[2] << 16) | (out[3] << 24), out[4] | (out[5] << 8) | (out[6] << 16) | (out[7] << 24));
+}
+__global__ void __launch_bounds__(256)
+dither128_interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__restrict__ v, ptrdiff_t spitch_u, ptrdiff_t spitch_v,
+                            ptrdiff_t sframe_u, ptrdiff_t sframe_v, uint8_t *__restrict__ dst, ptrdiff_t dpitch, ptrdiff_t dframe, int w,
+                            int rows, int src_shift, int xoff_u, int xoff_v) {
+    const int slots = (w + 7) >> 3;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / slots, x = (idx - y * slots) * 8;
+    if (y >= rows) return;
+    const int f = blockIdx.z;
+    const uint8_t *us = u + f * sframe_u + y * spitch_u + 2 * static_cast<ptrdiff_t>(x);
+    const uint8_t *vs = v + f * sframe_v + y * spitch_v + 2 * static_cast<ptrdiff_t>(x);
+    uint8_t *d = dst + f * dframe + y * dpitch + 2 * x;
+    if (x + 8 <= w) {
+        const unsigned d_lo = kDither128Packed[y & 7][0], d_hi = kDither128Packed[y & 7][1];
+        const uint2 a = dither128_oct(__ldg(reinterpret_cast<const uint4 *>(us)), src_shift, d_lo, d_hi, xoff_u);
+        const uint2 b = dither128_oct(__ldg(reinterpret_cast<const uint4 *>(vs)), src_shift, d_lo, d_hi, xoff_v);
+        uint4 o;
+        o.x = __byte_perm(a.x, b.x, 0x5140); o.y = __byte_perm(a.x, b.x, 0x7362);
+        o.z = __byte_perm(a.y, b.y, 0x5140); o.w = __byte_perm(a.y, b.y, 0x7362);
+        *reinterpret_cast<uint4 *>(d) = o;
+    } else {
+        for (int k = 0; x + k < w; ++k) {
+            d[2 * k] = static_cast<uint8_t>(dither128_sample(reinterpret_cast<const uint16_t *>(us)[k] >> src_shift, kDither128[y & 7][(x + k + xoff_u) & 7]));
+            d[2 * k + 1] = static_cast<uint8_t>(dither128_sample(reinterpret_cast<const uint16_t *>(vs)[k] >> src_shift, kDither128[y & 7][(x + k + xoff_v) & 7]));
+        }
+    }
 }
 
 // ---- memcpy-class fast paths of the same-size converters (the DVD production shape: yuv420p -> nv12 at equal size,
@@ -249,7 +375,7 @@ int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &ds
     const dim3 grid = plane_grid(op.dw, op.dh, n_frames);
 #define TVS_REPACK(S, D)                                                                                          \
     repack_kernel<S, D><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep, op.src_shift, \
-        dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.dw, op.kind, op.raw_tail_from)
+        dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.dw, op.kind, op.raw_tail_from, op.dither_xoff)
     if (op.src_bits == 8 && op.dst_bits == 8) TVS_REPACK(uint8_t, uint8_t);
     else if (op.src_bits == 8) TVS_REPACK(uint8_t, uint16_t);
     else if (op.dst_bits == 8) TVS_REPACK(uint16_t, uint8_t);
@@ -287,6 +413,41 @@ int launch_interleave(const SampleView &u, const SampleView &v, const SampleView
     if (sample_bytes == 1) { if (vec) TVS_ILV(uint8_t, true); else TVS_ILV(uint8_t, false); }
     else { if (vec) TVS_ILV(uint16_t, true); else TVS_ILV(uint16_t, false); }
 #undef TVS_ILV
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_dither2_rows(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream) {
+    if (!aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 16) || !aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 8) ||
+        (op.raw_tail_from >= 0 && (op.raw_tail_from & 7)))
+        return 0;   // not this kernel's case: the caller falls back to the per-sample kernel
+    const int slots = (op.dw + 7) / 8;
+    const dim3 grid((static_cast<unsigned>(slots) * op.dh + 255) / 256, 1, n_frames);
+    dither2_rows_kernel<<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, op.dw, op.dh,
+                                                  op.src_shift, op.raw_tail_from);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_dither2_interleave(const PlaneOp &op, const SampleView &u, const SampleView &v, const SampleView &dst, int n_frames,
+                              cudaStream_t stream) {
+    if (!aligned_for(u.base, u.pitch, u.frame_stride, n_frames, 16) || !aligned_for(v.base, v.pitch, v.frame_stride, n_frames, 16) ||
+        !aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16))
+        return 0;
+    const int slots = (op.dw + 7) / 8;
+    const dim3 grid((static_cast<unsigned>(slots) * op.dh + 255) / 256, 1, n_frames);
+    dither2_interleave_kernel<<<grid, 256, 0, stream>>>(u.base, v.base, u.pitch, v.pitch, u.frame_stride, v.frame_stride, dst.base, dst.pitch,
+                                                        dst.frame_stride, op.dw, op.dh, op.src_shift);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const SampleView &v, const SampleView &dst, int n_frames,
+                                cudaStream_t stream) {
+    if (!aligned_for(u.base, u.pitch, u.frame_stride, n_frames, 16) || !aligned_for(v.base, v.pitch, v.frame_stride, n_frames, 16) ||
+        !aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16))
+        return 0;
+    const int slots = (op.dw + 7) / 8;
+    const dim3 grid((static_cast<unsigned>(slots) * op.dh + 255) / 256, 1, n_frames);
+    dither128_interleave_kernel<<<grid, 256, 0, stream>>>(u.base, v.base, u.pitch, v.pitch, u.frame_stride, v.frame_stride, dst.base,
+                                                          dst.pitch, dst.frame_stride, op.dw, op.dh, op.src_shift, 0, 3);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

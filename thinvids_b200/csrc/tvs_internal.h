@@ -42,7 +42,10 @@ enum OutputRule : int {
 enum PlaneOpKind : int {
     kOpScale = 0,   // horizontal + vertical filter (also used with 1-tap tables for depth changes)
     kOpCopy = 1,    // same-size, same-depth sample copy (re-interleave / de-interleave)
-    kOpDither2 = 2  // same-size 10 -> 8 bit copy with libswscale's 2-bit ordered dither
+    kOpDither2 = 2, // same-size 10 -> 8 bit copy with libswscale's 2-bit ordered dither
+    // same-size 10 -> 8 bit through the scaler proper when both of its filters are the 1-tap identity: per sample
+    // t = min(32 v, 32767), out = min((t + D128[y & 7][(x + dither_xoff) & 7]) >> 7, 255)  (SURVEY.md A.3 with one tap)
+    kOpDither128 = 3
 };
 
 // One unit of work of a frame: produce one logical (or, for the P010->NV12 copy, stored) plane.
@@ -112,6 +115,14 @@ int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceT
 int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
 // memcpy-class special cases of the same-size converters
 int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream);
+// vector forms of kOpDither2 (contiguous 16-bit plane -> byte plane; planar U + V -> interleaved bytes); they return 0
+// without launching when the surfaces are not aligned for them
+int launch_dither2_rows(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
+int launch_dither2_interleave(const PlaneOp &op, const SampleView &u, const SampleView &v, const SampleView &dst, int n_frames,
+                              cudaStream_t stream);
+// kOpDither128 for planar U + V -> interleaved bytes (returns 0 when the surfaces are not aligned for it)
+int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const SampleView &v, const SampleView &dst, int n_frames,
+                                cudaStream_t stream);
 // exact 2:1 area down-scale of an 8-bit plane (pair = interleaved UV bytes)
 int launch_box2(const SampleView &src, const SampleView &dst, bool pair, int out_bytes, int rows, int n_frames, cudaStream_t stream);
 int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,

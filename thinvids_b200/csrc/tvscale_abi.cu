@@ -112,6 +112,14 @@ void logical_plane(const FormatInfo &fi, int pl, int &stored, int &offset, int &
     }
 }
 
+// every output sample is one input sample times `one` (what initFilter yields for equal sizes and equal siting)
+bool identity_table(const AxisTable &t, int one) {
+    if (t.taps != 1) return false;
+    for (int i = 0; i < t.length; ++i)
+        if (t.pos[i] != i || t.coef[i] != one) return false;
+    return true;
+}
+
 void build_plan(tvs_ctx *c) {
     Plan &p = c->plan;
     p.ops.clear();
@@ -158,6 +166,9 @@ void build_plan(tvs_ctx *c) {
                 if (s.bits == d.bits) kind = kOpCopy;
                 else if (s.bits == 10 && !s.semi && !d.semi) kind = kOpDither2;        // yuv420p10le -> yuv420p
                 else if (s.bits == 10 && !s.semi && d.semi && pl == 0) kind = kOpDither2;  // -> nv12 luma
+                else if (s.bits == 10 && !s.semi && d.semi && d.bits == 8 && identity_table(c->host_tables[1], 1 << 14) &&
+                         identity_table(c->host_tables[3], 1 << 12))
+                    kind = kOpDither128;                                                   // -> nv12 chroma: a 1-tap scaler pass
             }
             p.ops.push_back(logical_op(pl, kind));
         }
@@ -266,7 +277,22 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
             rc = launch_copy_rows(sv[i], dv[i], 2 * op.dw * bytes, op.dh, n_frames, stream);              // UV -> UV as one byte plane
             ++i;
         } else {
-            rc = launch_repack(op, sv[i], dv[i], n_frames, stream);
+            rc = 0;
+            if (op.kind == kOpDither2 && op.src_xstep == 2 && op.dst_xstep == 1) {
+                rc = launch_dither2_rows(op, sv[i], dv[i], n_frames, stream);                             // plane -> plane, 10 -> 8 bit
+            } else if (op.kind == kOpDither2 && op.src_xstep == 2 && op.dst_xstep == 2 && op.dst_offset == 0 && op.raw_tail_from < 0 &&
+                       i + 1 < plan.ops.size() && plan.ops[i + 1].kind == kOpDither2 && plan.ops[i + 1].dst_plane == op.dst_plane &&
+                       plan.ops[i + 1].src_xstep == 2 && plan.ops[i + 1].dst_offset == 1 && plan.ops[i + 1].src_shift == op.src_shift) {
+                rc = launch_dither2_interleave(op, sv[i], sv[i + 1], dv[i], n_frames, stream);            // U, V -> UV, 10 -> 8 bit
+                if (rc > 0) ++i;
+            }
+            if (op.kind == kOpDither128 && op.src_xstep == 2 && op.dst_xstep == 2 && op.dst_offset == 0 && op.dither_xoff == 0 &&
+                i + 1 < plan.ops.size() && plan.ops[i + 1].kind == kOpDither128 && plan.ops[i + 1].dst_plane == op.dst_plane &&
+                plan.ops[i + 1].dst_offset == 1 && plan.ops[i + 1].dither_xoff == 3) {
+                rc = launch_dither128_interleave(op, sv[i], sv[i + 1], dv[i], n_frames, stream);          // U, V -> UV through the 1-tap scaler rule
+                if (rc > 0) ++i;
+            }
+            if (rc == 0) rc = launch_repack(op, sv[i], dv[i], n_frames, stream);
         }
         if (rc < 0) return cuda_fail(cudaGetLastError(), "repack kernel launch");
         ++c->launches;
