@@ -135,13 +135,47 @@ __device__ __forceinline__ void prefetch_block(const StreamOpParams &op, const u
     }
 }
 
-// Raw words -> float samples of S.  Consecutive threads take consecutive 4-byte words, so the 16-byte stores of a
-// warp land on consecutive banks (the caller has made the copied chunks visible with a barrier).
+// One 16-bit sample (byte pair `selector` of `word`) -> (v * scale - 512) as a float, in two instructions: PRMT puts
+// the sample under the exponent of 2^23 and one FMA removes 2^23 * scale + 512 (`bias`); every step is exact.
+__device__ __forceinline__ float wide_to_float(unsigned word, unsigned selector, float scale, float bias) {
+    return fmaf(__uint_as_float(__byte_perm(word, 0x4B000000u, selector)), scale, bias);
+}
+
+// Raw staged bytes -> float samples of S (the caller has made the copied chunks visible with a barrier).
+// 8-bit sources: consecutive threads take consecutive 4-byte words, so a warp's 16-byte stores land on consecutive
+// banks.  16-bit sources: a thread takes a whole 16-byte chunk (8 samples, or 4 of an interleaved pair plane) and
+// steps its (row, chunk) position without divisions.
 __device__ __forceinline__ void convert_block(const StreamOpParams &op, const unsigned *raw, float *S, int rows, unsigned mis0, unsigned pmod,
                                               int tid) {
-    const int words = op.s_chunks * 4, s_pitch = op.s_pitch;
+    const int s_pitch = op.s_pitch;
     const int src_mode = op.src_mode;
-    const float sscale = op.src_scale;
+    if (src_mode >= kSrcU16) {
+        const int s_chunks = op.s_chunks;
+        const float sscale = op.src_scale, bias = -(8388608.0f * sscale + 512.0f);
+        const int total = rows * s_chunks;
+        const int step_rows = op.pf_step_rows, step_chunks = op.pf_step_chunks;
+        int row = static_cast<int>(__umulhi(static_cast<unsigned>(tid), op.chunk_magic));
+        int ch = tid - row * s_chunks;
+        for (int idx = tid; idx < total; idx += kSThreads) {
+            const uint4 v = reinterpret_cast<const uint4 *>(raw)[idx];
+            float *srow = S + row * s_pitch;
+            if (src_mode == kSrcU16) {      // eight samples per chunk
+                reinterpret_cast<float4 *>(srow)[2 * ch] = make_float4(wide_to_float(v.x, 0x7410u, sscale, bias), wide_to_float(v.x, 0x7432u, sscale, bias),
+                                                                      wide_to_float(v.y, 0x7410u, sscale, bias), wide_to_float(v.y, 0x7432u, sscale, bias));
+                reinterpret_cast<float4 *>(srow)[2 * ch + 1] = make_float4(wide_to_float(v.z, 0x7410u, sscale, bias), wide_to_float(v.z, 0x7432u, sscale, bias),
+                                                                          wide_to_float(v.w, 0x7410u, sscale, bias), wide_to_float(v.w, 0x7432u, sscale, bias));
+            } else {                        // interleaved 16-bit chroma: one sample of this plane per word
+                const unsigned sel = ((mis0 + row * pmod) & 2u) ? 0x7432u : 0x7410u;
+                reinterpret_cast<float4 *>(srow)[ch] = make_float4(wide_to_float(v.x, sel, sscale, bias), wide_to_float(v.y, sel, sscale, bias),
+                                                                  wide_to_float(v.z, sel, sscale, bias), wide_to_float(v.w, sel, sscale, bias));
+            }
+            row += step_rows;
+            ch += step_chunks;
+            if (ch >= s_chunks) { ch -= s_chunks; ++row; }
+        }
+        return;
+    }
+    const int words = op.s_chunks * 4;
     const unsigned magic = op.word_magic;
     for (int idx = tid; idx < rows * words; idx += kSThreads) {
         const int row = static_cast<int>(__umulhi(static_cast<unsigned>(idx), magic));
@@ -151,15 +185,9 @@ __device__ __forceinline__ void convert_block(const StreamOpParams &op, const un
         if (src_mode == kSrcU8) {              // four samples per word
             reinterpret_cast<float4 *>(srow)[w] =
                 make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u), byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
-        } else if (src_mode == kSrcU8Pair) {   // interleaved 8-bit chroma: this plane is every other byte
+        } else {                               // interleaved 8-bit chroma: this plane is every other byte
             const unsigned p = (mis0 + row * pmod) & 1u;
             reinterpret_cast<float2 *>(srow)[w] = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
-        } else if (src_mode == kSrcU16) {      // two 16-bit samples per word, centred on 512
-            reinterpret_cast<float2 *>(srow)[w] =
-                make_float2(fmaf(byte_to_float(v, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v, 0x7432u), sscale, -512.0f));
-        } else {                               // interleaved 16-bit chroma: one sample of this plane per word
-            const unsigned hi16 = (mis0 + row * pmod) & 2u;
-            srow[w] = fmaf(byte_to_float(v, hi16 ? 0x7432u : 0x7410u), sscale, -512.0f);
         }
     }
 }
@@ -291,9 +319,15 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
 #pragma unroll
                 for (int k = 0; k < 4; ++k) {
                     const float *sp = srow + hstart[k];
-                    float acc = 0.0f;
+                    // taps in pairs: one FFMA2 does two of them (the sums are exact integers * 2^-(23+hshift), so
+                    // the order of the additions does not matter)
+                    f32x2 acc2 = 0ull;
 #pragma unroll
-                    for (int j = 0; j < HT; ++j) acc = fmaf(sp[j], ck[k][j], acc);
+                    for (int j = 0; j + 1 < HT; j += 2) acc2 = fma2(pack2(sp[j], sp[j + 1]), pack2(ck[k][j], ck[k][j + 1]), acc2);
+                    float even, odd;
+                    unpack2(acc2, even, odd);
+                    float acc = even + odd;
+                    if (HT & 1) acc = fmaf(sp[HT - 1], ck[k][HT - 1], acc);
                     mrow[32 * k] = fminf(fma_rm(acc, 0x1p-126f, h_addend), t_max);   // floor(sum >> hshift), clamped above
                 }
             }
@@ -342,16 +376,35 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
             // even and odd taps accumulate separately (two dependency chains per pair instead of one) when there are
             // enough taps for that to matter; the extra addition is counted in the error bound (stream_plan_create)
             f32x2 b01 = 0ull, b23 = 0ull;
+            // this row's (g, g) pairs: two per 128-bit load when the row starts on a 16-byte boundary
+            f32x2 gg[VT];
+            if constexpr (VT % 2 == 0) {
 #pragma unroll
-            for (int j = 0; j < VT; ++j) {
-                const Quad q = load_quad(m_col + ((first + j) & mask) * kStripW);
-                const f32x2 gg = __ldg(gp + j);
-                if (VT >= 4 && (j & 1)) {
-                    b01 = fma2(q.lo, gg, b01);
-                    b23 = fma2(q.hi, gg, b23);
-                } else {
-                    a01 = fma2(q.lo, gg, a01);
-                    a23 = fma2(q.hi, gg, a23);
+                for (int j = 0; j < VT; j += 2) {
+                    const ulonglong2 c2 = __ldg(reinterpret_cast<const ulonglong2 *>(gp + j));
+                    gg[j] = c2.x; gg[j + 1] = c2.y;
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < VT; ++j) gg[j] = __ldg(gp + j);
+            }
+            // The window's rows sit at consecutive ring slots unless it wraps: then every address is one base register
+            // plus a constant.
+            const int slot0 = first & mask;
+            if (slot0 + VT <= mask + 1) {
+                const float *w0 = m_col + slot0 * kStripW;
+#pragma unroll
+                for (int j = 0; j < VT; ++j) {
+                    const Quad q = load_quad(w0 + j * kStripW);
+                    if (VT >= 4 && (j & 1)) { b01 = fma2(q.lo, gg[j], b01); b23 = fma2(q.hi, gg[j], b23); }
+                    else { a01 = fma2(q.lo, gg[j], a01); a23 = fma2(q.hi, gg[j], a23); }
+                }
+            } else {
+#pragma unroll
+                for (int j = 0; j < VT; ++j) {
+                    const Quad q = load_quad(m_col + ((first + j) & mask) * kStripW);
+                    if (VT >= 4 && (j & 1)) { b01 = fma2(q.lo, gg[j], b01); b23 = fma2(q.hi, gg[j], b23); }
+                    else { a01 = fma2(q.lo, gg[j], a01); a23 = fma2(q.hi, gg[j], a23); }
                 }
             }
             if (VT >= 4) {
