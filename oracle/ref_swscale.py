@@ -16,7 +16,7 @@ import numpy as np
 
 from . import build as _build
 
-_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le"}
+_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24"}
 _libs = None
 
 
@@ -111,7 +111,19 @@ class RefScaler:
         return self._sws.sws_scale(self._ctx, sp, ss, 0, self.src[1], dp, ds)
 
     def scale(self, src_planes):
-        from thinvids_b200.frames import alloc_frame
+        from thinvids_b200.frames import alloc_frame, plane_shapes, sample_dtype
+        if self.src[2] == 4:
+            # rgb24: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
+            # give it padded buffers and crop
+            h, row = src_planes[0].shape
+            pad = np.zeros((h + 2, row + 64), dtype=np.uint8)
+            pad[:h, :row] = src_planes[0]
+            shapes = plane_shapes(self.dst[2], self.dst[0], self.dst[1])
+            big = [np.zeros((r + 2, c + 64), dtype=sample_dtype(self.dst[2])) for r, c in shapes]
+            rows = self.scale_into([pad[:h]], [b[:r] for b, (r, c) in zip(big, shapes)])
+            if rows != self.dst[1]:
+                raise RuntimeError(f"sws_scale returned {rows}")
+            return [np.ascontiguousarray(b[:r, :c]) for b, (r, c) in zip(big, shapes)]
         dst = alloc_frame(self.dst[2], self.dst[0], self.dst[1])
         rows = self.scale_into(src_planes, dst)
         if rows != self.dst[1]:

@@ -26,7 +26,7 @@
 #include <stdlib.h>
 #include <string.h>
 
-enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3 };
+enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */ };
 enum { ALG_BILINEAR = 2, ALG_BICUBIC = 4, ALG_AREA = 0x20, ALG_LANCZOS = 0x200 };
 
 typedef struct {
@@ -39,12 +39,14 @@ typedef struct {
 typedef struct {
     int sw, sh, dw, dh, sfmt, dfmt, alg;
     int csw, csh, cdw, cdh;
+    int rgb_half;       /* FMT_RGB24 source: chroma is made at half width */
+    uint16_t *rgb[3];   /* FMT_RGB24 source: the input stage's Y, U, V lines for the frame being scaled */
     o_filter hl, hc, vl, vc;
 } o_ctx;
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
 static int64_t iabs64(int64_t v) { return v < 0 ? -v : v; }
-static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12) ? 8 : 10; }
+static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24) ? 8 : 10; }
 static int fmt_semi(int f) { return f == FMT_NV12 || f == FMT_P010; }
 
 /* SURVEY.md A.2 — coefficient table for one axis. */
@@ -225,6 +227,20 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
     o_ctx *c = (o_ctx *)calloc(1, sizeof(*c));
     c->sw = sw; c->sh = sh; c->dw = dw; c->dh = dh; c->sfmt = sfmt; c->dfmt = dfmt; c->alg = alg;
     c->csw = (sw + 1) >> 1; c->csh = (sh + 1) >> 1; c->cdw = (dw + 1) >> 1; c->cdh = (dh + 1) >> 1;
+    if (sfmt == FMT_RGB24) {
+        /* RGB has no chroma planes of its own: the input stage makes them, at full height and -- unless the
+         * destination chroma is wider than half the source -- at half width (rgb24ToUV_half_c, the sum of two
+         * pixels); both cases sit at libswscale's default (centred) positions. */
+        c->rgb_half = (dw >> 1) <= (sw >> 1);
+        c->csw = c->rgb_half ? (sw + 1) >> 1 : sw;
+        c->csh = sh;
+        make_filter(&c->hl, step16(sw, dw), sw, dw, 1 << 14, alg, local_pos(-513, 0), local_pos(-513, 0));
+        make_filter(&c->hc, step16(c->csw, c->cdw), c->csw, c->cdw, 1 << 14, alg,
+                    local_pos(chr_pos[0], c->rgb_half ? 1 : 0), local_pos(chr_pos[2], 1));
+        make_filter(&c->vl, step16(sh, dh), sh, dh, 1 << 12, alg, local_pos(-513, 0), local_pos(-513, 0));
+        make_filter(&c->vc, step16(c->csh, c->cdh), c->csh, c->cdh, 1 << 12, alg, local_pos(chr_pos[1], 0), local_pos(chr_pos[3], 1));
+        return c;
+    }
     make_filter(&c->hl, step16(sw, dw), sw, dw, 1 << 14, alg, local_pos(-513, 0), local_pos(-513, 0));
     make_filter(&c->hc, step16(c->csw, c->cdw), c->csw, c->cdw, 1 << 14, alg,
                 local_pos(chr_pos[0], 1), local_pos(chr_pos[2], 1));
@@ -263,6 +279,7 @@ static const uint8_t D128[8][8] = {
 static inline int src_sample(const o_ctx *c, const uint8_t *const src[], const int stride[], int pl, int r, int x)
 {
     switch (c->sfmt) {
+    case FMT_RGB24: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
     case FMT_YUV420P: return src[pl][(size_t)r * stride[pl] + x];
     case FMT_NV12:
         return pl == 0 ? src[0][(size_t)r * stride[0] + x] : src[1][(size_t)r * stride[1] + 2 * x + (pl - 1)];
@@ -303,7 +320,8 @@ static int scale_plane(const o_ctx *c, const uint8_t *const src[], const int sst
     const int sw = pl ? c->csw : c->sw, sh = pl ? c->csh : c->sh;
     const int dw = pl ? c->cdw : c->dw, dh = pl ? c->cdh : c->dh;
     const int sbits = fmt_bits(c->sfmt), dbits = fmt_bits(c->dfmt);
-    const int hshift = sbits == 8 ? 7 : sbits - 1;
+    /* RGB input reaches the scaler as 14/15-bit lines (srcBpc = 16) and hScale16To15 then shifts by 13 */
+    const int hshift = c->sfmt == FMT_RGB24 ? 13 : sbits == 8 ? 7 : sbits - 1;
     int16_t *mid = (int16_t *)malloc((size_t)sh * dw * sizeof(int16_t));
     if (!mid) return -1;
 
@@ -408,9 +426,50 @@ static int unscaled_rule(const o_ctx *c, int pl)
     return 0;                                  /* p010le -> yuv420p */
 }
 
+/* libswscale's input stage for packed RGB (input.c: rgb24ToY_c, rgb24ToUV_c, rgb24ToUV_half_c) with the default
+ * ITU-R BT.601 limited-range table; RGB2YUV_SHIFT = 15.  Restated and checked against the genuine library on 300
+ * random even-width cases (tests/golden/make_golden.py --rgb). */
+enum { RY = 8414, GY = 16519, BY = 3208, RU = -4865, GU = -9528, BU = 14392, RV = 14392, GV = -12061, BV = -2332 };
+
+static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
+{
+    for (int pl = 0; pl < 3; pl++) {
+        c->rgb[pl] = (uint16_t *)malloc((size_t)c->sh * (pl ? c->csw : c->sw) * sizeof(uint16_t));
+        if (!c->rgb[pl]) return -1;
+    }
+    for (int r = 0; r < c->sh; r++) {
+        const uint8_t *row = rgb + (size_t)r * stride;
+        for (int x = 0; x < c->sw; x++) {
+            const int R = row[3 * x], G = row[3 * x + 1], B = row[3 * x + 2];
+            c->rgb[0][(size_t)r * c->sw + x] = (uint16_t)((RY * R + GY * G + BY * B + (32 << 14) + (1 << 8)) >> 9);
+            if (!c->rgb_half) {
+                c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (256 << 14) + (1 << 8)) >> 9);
+                c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)((RV * R + GV * G + BV * B + (256 << 14) + (1 << 8)) >> 9);
+            }
+        }
+        if (c->rgb_half)
+            for (int x = 0; x < c->csw; x++) {
+                const int R = row[6 * x] + row[6 * x + 3], G = row[6 * x + 1] + row[6 * x + 4], B = row[6 * x + 2] + row[6 * x + 5];
+                c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (256 << 15) + (1 << 9)) >> 10);
+                c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)((RV * R + GV * G + BV * B + (256 << 15) + (1 << 9)) >> 10);
+            }
+    }
+    return 0;
+}
+
 int tvo_scale(void *p, const uint8_t *const src[], const int sstride[], uint8_t *const dst[], const int dstride[])
 {
     o_ctx *c = (o_ctx *)p;
+    if (c->sfmt == FMT_RGB24) {
+        /* even widths only: with an odd width the library's half-width chroma reads one pixel past the row */
+        if ((c->sw & 1) || fmt_bits(c->dfmt) < 8 || c->dfmt == FMT_RGB24) return -1;
+        int rc = c->dh;
+        if (rgb_input_stage(c, src[0], sstride[0])) rc = -1;
+        for (int pl = 0; pl < 3 && rc >= 0; pl++)
+            if (scale_plane(c, src, sstride, dst, dstride, pl)) rc = -1;
+        for (int pl = 0; pl < 3; pl++) { free(c->rgb[pl]); c->rgb[pl] = NULL; }
+        return rc;
+    }
     const int same = c->sw == c->dw && c->sh == c->dh;
     /* planar -> p010le at equal size: libswscale's converter writes floor(w/2) chroma pairs, so
      * with an odd width the last pair of every chroma row is left untouched. */

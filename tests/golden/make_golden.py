@@ -88,6 +88,16 @@ EXTRA_CASES = [
     ("yuv420p", 720, 480, "yuv420p", 1620, 1080, "area", "seed:1234", None),
     ("nv12", 721, 479, "yuv420p", 333, 777, "lanczos", "seed:1234", None),
     ("yuv420p10le", 641, 361, "p010le", 1281, 723, "bicubic", "seed:1234", None),
+    # packed RGB sources: what tools/upscale_benchmark.py:159-182 feeds its lanczos stage
+    ("rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", "seed:1234", None),
+    ("rgb24", 720, 480, "nv12", 1620, 1080, "lanczos", "seed:1234", None),
+    ("rgb24", 1920, 1080, "yuv420p", 1280, 720, "lanczos", "seed:1234", None),    # half-width chroma input
+    ("rgb24", 1920, 1080, "nv12", 1280, 720, "bicubic", "seed:1234", None),
+    ("rgb24", 640, 360, "yuv420p10le", 1280, 720, "bicubic", "seed:1234", None),
+    ("rgb24", 720, 480, "yuv420p", 720, 480, "bicubic", "seed:1234", None),       # same size still runs the scaler
+    ("rgb24", 722, 479, "p010le", 333, 777, "area", "seed:1234", None),
+    ("rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", "pattern:checker", None),
+    ("rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", "pattern:white", None),
 ]
 
 # Small cases whose full output is stored (tests/golden/small_cases.npz).
@@ -106,6 +116,10 @@ SMALL_CASES = [
     ("yuv420p10le", 67, 35, "yuv420p", 67, 35, "bicubic"),
     ("yuv420p", 16, 16, "yuv420p", 8, 8, "bicubic"),
     ("yuv420p", 9, 7, "yuv420p", 31, 23, "lanczos"),
+    ("rgb24", 64, 48, "yuv420p", 160, 108, "lanczos"),
+    ("rgb24", 96, 64, "nv12", 48, 32, "bicubic"),
+    ("rgb24", 32, 18, "yuv420p", 32, 18, "bicubic"),
+    ("rgb24", 40, 30, "p010le", 50, 44, "bilinear"),
 ]
 
 

@@ -58,6 +58,16 @@ def test_scale_stage_from_reference_graphs():
     assert fg.ScaleStage.from_filtergraph("setpts=PTS-STARTPTS", 720, 480).is_identity
 
 
+def test_upscale_benchmark_filter_text_on_rgb_frames():
+    """tools/upscale_benchmark.py:163,182 -- PNG (rgb24) frames into `scale=-2:H:flags=lanczos,format=...`."""
+    st = fg.ScaleStage.from_filtergraph("scale=-2:1080:flags=lanczos,format=yuv420p", 720, 480, "rgb24")
+    assert (st.src_fmt, st.dst_w, st.dst_h, st.dst_fmt, st.flags) == ("rgb24", 1620, 1080, "yuv420p", F.SWS_LANCZOS)
+    st = fg.ScaleStage.from_filtergraph("scale=-2:720:flags=lanczos,format=nv12,hwupload", 1920, 1080, "rgb24")
+    assert (st.dst_w, st.dst_h, st.dst_fmt, st.hwupload) == (1280, 720, "nv12", True)
+    with pytest.raises(fg.FilterGraphError, match="explicit format"):
+        fg.ScaleStage.from_filtergraph("scale=-2:720", 1920, 1080, "rgb24")
+
+
 def test_scale_stage_rejects_what_it_cannot_do():
     with pytest.raises(fg.FilterGraphError, match="bwdif"):
         fg.ScaleStage.from_filtergraph(fg.SCALE_FILTER_480, 720, 480)

@@ -103,6 +103,24 @@ def test_port_equals_genuine_library_on_random_shapes():
 
 
 @needs_ref
+def test_port_equals_genuine_library_rgb24_sources():
+    """Packed RGB in (libswscale's input stage: rgb24ToY_c, rgb24ToUV_c / _half_c, then hScale16To15 with shift 13):
+    both chroma input widths, every destination format, same-size included.  Even widths only -- with an odd width the
+    library itself reads past the row."""
+    rnd = random.Random(23)
+    algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
+    for i in range(60):
+        sw, sh = 2 * rnd.randrange(1, 80), rnd.randrange(2, 100)
+        dw, dh = (sw, sh) if rnd.random() < 0.15 else (rnd.randrange(2, 240), rnd.randrange(2, 160))
+        alg, df = rnd.choice(algs), rnd.randrange(4)
+        src = F.random_frame(F.RGB24, sw, sh, 500 + i)
+        want = ref_swscale.RefScaler(sw, sh, F.RGB24, dw, dh, df, alg).scale(src)
+        got = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg).scale(src)
+        for x, y in zip(got, want):
+            assert np.array_equal(x, y), (sw, sh, dw, dh, df, hex(alg))
+
+
+@needs_ref
 def test_port_equals_genuine_library_unscaled_all_format_pairs():
     for sf in range(4):
         for df in range(4):

@@ -230,10 +230,44 @@ def test_full_size_batch_properties():
             assert all((p == v).all() for p in got), v
 
 
+def test_rgb24_sources_against_oracle():
+    """packed RGB frames in (input stage on the GPU, then the integer two-pass kernels), every
+    destination format, both chroma input widths, host planes and packed device batches."""
+    import torch
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    rnd = random.Random(77)
+    algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
+    for i in range(40):
+        sw, sh = 2 * rnd.randrange(1, 120), rnd.randrange(2, 140)
+        dw, dh = (sw, sh) if rnd.random() < 0.15 else (rnd.randrange(2, 400), rnd.randrange(2, 300))
+        alg, df = rnd.choice(algs), rnd.randrange(4)
+        frames = [F.random_frame(F.RGB24, sw, sh, 900 + 3 * i + k) for k in range(3)]
+        ref = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg)
+        want = [ref.scale(fr) for fr in frames]
+        with Scaler(sw, sh, F.RGB24, dw, dh, df, alg) as s:
+            assert s.path == "two-pass"
+            got = s.scale(frames[0])
+            d_src = torch.from_numpy(s.src_layout.pack(frames)).cuda()
+            d_dst = torch.zeros((3, s.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+            s.scale_packed_device(d_src, d_dst)
+            torch.cuda.synchronize()
+            got_batch = s.dst_layout.unpack(d_dst.cpu().numpy())
+        for a, b in zip(got, want[0]):
+            assert np.array_equal(a, b), (sw, sh, dw, dh, df, hex(alg))
+        for g, w in zip(got_batch, want):
+            for a, b in zip(g, w):
+                assert np.array_equal(a, b), (sw, sh, dw, dh, df, hex(alg), "batch")
+
+
 def test_error_paths():
     import ctypes
     from thinvids_b200 import lib as tv_lib
     from thinvids_b200.swscale import Scaler, PtrArr3, DiffArr3
+    with pytest.raises(tv_lib.TvscaleError, match="even width"):
+        Scaler(63, 64, F.RGB24, 32, 32, 0, F.SWS_BICUBIC)      # libswscale itself over-reads odd-width RGB rows
+    with pytest.raises(tv_lib.TvscaleError, match="source format only"):
+        Scaler(64, 64, 0, 32, 32, F.RGB24, F.SWS_BICUBIC)
     with pytest.raises(tv_lib.TvscaleError):
         Scaler(64, 64, 9, 32, 32, 0, F.SWS_BICUBIC)            # unknown format
     with pytest.raises(tv_lib.TvscaleError):

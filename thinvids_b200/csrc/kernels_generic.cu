@@ -226,6 +226,38 @@ dither128_interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__rest
     }
 }
 
+// ---- input stage for packed RGB sources (tools/upscale_benchmark.py feeds rgb24 frames) ----------
+// libswscale converts each RGB line to 16-bit Y / U / V lines before the scaler proper (input.c: rgb24ToY_c, rgb24ToUV_c,
+// rgb24ToUV_half_c; RGB2YUV_SHIFT = 15, default BT.601 limited-range table).  One thread per pixel pair.
+__global__ void __launch_bounds__(256)
+rgb_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *__restrict__ planes,
+                 size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half) {
+    constexpr int RY = 8414, GY = 16519, BY = 3208, RU = -4865, GU = -9528, BU = 14392, RV = 14392, GV = -12061, BV = -2332;
+    const int pairs = w >> 1;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / pairs, i = idx - y * pairs;
+    if (y >= h) return;
+    const int f = blockIdx.z;
+    const uint8_t *p = rgb + f * frame_stride + y * pitch + 6 * i;
+    const int r0 = p[0], g0 = p[1], b0 = p[2], r1 = p[3], g1 = p[4], b1 = p[5];
+    uint8_t *out = planes + f * planes_frame_stride;
+    uint16_t *yrow = reinterpret_cast<uint16_t *>(out) + static_cast<size_t>(y) * w + 2 * i;
+    yrow[0] = static_cast<uint16_t>((RY * r0 + GY * g0 + BY * b0 + (32 << 14) + (1 << 8)) >> 9);
+    yrow[1] = static_cast<uint16_t>((RY * r1 + GY * g1 + BY * b1 + (32 << 14) + (1 << 8)) >> 9);
+    uint16_t *u = reinterpret_cast<uint16_t *>(out + u_offset), *v = reinterpret_cast<uint16_t *>(out + u_offset + c_plane_bytes);
+    if (half) {
+        const int r = r0 + r1, g = g0 + g1, b = b0 + b1;
+        u[static_cast<size_t>(y) * pairs + i] = static_cast<uint16_t>((RU * r + GU * g + BU * b + (256 << 15) + (1 << 9)) >> 10);
+        v[static_cast<size_t>(y) * pairs + i] = static_cast<uint16_t>((RV * r + GV * g + BV * b + (256 << 15) + (1 << 9)) >> 10);
+    } else {
+        const size_t o = static_cast<size_t>(y) * w + 2 * i;
+        u[o] = static_cast<uint16_t>((RU * r0 + GU * g0 + BU * b0 + (256 << 14) + (1 << 8)) >> 9);
+        u[o + 1] = static_cast<uint16_t>((RU * r1 + GU * g1 + BU * b1 + (256 << 14) + (1 << 8)) >> 9);
+        v[o] = static_cast<uint16_t>((RV * r0 + GV * g0 + BV * b0 + (256 << 14) + (1 << 8)) >> 9);
+        v[o + 1] = static_cast<uint16_t>((RV * r1 + GV * g1 + BV * b1 + (256 << 14) + (1 << 8)) >> 9);
+    }
+}
+
 // ---- memcpy-class fast paths of the same-size converters (the DVD production shape: yuv420p -> nv12 at equal size,
 // worker/tasks.py:62-63) -------------------------------------------------------------------------------------------
 // Plain 2-D copy of `row_bytes` per row.  V = bytes per thread access (16, 4 or 1), chosen by the launcher from the
@@ -448,6 +480,15 @@ int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const Sa
     const dim3 grid((static_cast<unsigned>(slots) * op.dh + 255) / 256, 1, n_frames);
     dither128_interleave_kernel<<<grid, 256, 0, stream>>>(u.base, v.base, u.pitch, v.pitch, u.frame_stride, v.frame_stride, dst.base,
                                                           dst.pitch, dst.frame_stride, op.dw, op.dh, op.src_shift, 0, 3);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
+int launch_rgb_input(const uint8_t *rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *planes, size_t planes_frame_stride,
+                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, int n_frames, cudaStream_t stream) {
+    const unsigned total = static_cast<unsigned>(w / 2) * h;
+    const dim3 grid((total + 255) / 256, 1, n_frames);
+    rgb_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
+                                               half ? 1 : 0);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

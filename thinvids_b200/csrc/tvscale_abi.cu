@@ -42,19 +42,22 @@ struct FormatInfo {
     int shift;      // left shift of the significant bits inside the word (P010: 6)
     bool semi;      // chroma interleaved in one plane
     int planes;     // stored planes
+    bool rgb;       // one plane of packed R, G, B bytes (source only)
 };
 
 bool format_info(int fmt, FormatInfo &fi) {
     switch (fmt) {
-    case TVS_FMT_YUV420P: fi = {8, 1, 0, false, 3}; return true;
-    case TVS_FMT_NV12: fi = {8, 1, 0, true, 2}; return true;
-    case TVS_FMT_YUV420P10LE: fi = {10, 2, 0, false, 3}; return true;
-    case TVS_FMT_P010LE: fi = {10, 2, 6, true, 2}; return true;
+    case TVS_FMT_YUV420P: fi = {8, 1, 0, false, 3, false}; return true;
+    case TVS_FMT_NV12: fi = {8, 1, 0, true, 2, false}; return true;
+    case TVS_FMT_YUV420P10LE: fi = {10, 2, 0, false, 3, false}; return true;
+    case TVS_FMT_P010LE: fi = {10, 2, 6, true, 2, false}; return true;
+    case TVS_FMT_RGB24: fi = {8, 1, 0, false, 1, true}; return true;
     default: return false;
     }
 }
 
 size_t tight_frame_bytes(const FormatInfo &fi, int w, int h) {
+    if (fi.rgb) return static_cast<size_t>(3) * w * h;
     const size_t cw = (w + 1) / 2, ch = (h + 1) / 2;
     return (static_cast<size_t>(w) * h + 2 * cw * ch) * fi.bytes;
 }
@@ -77,6 +80,11 @@ struct tvs_ctx {
     // two-pass scratch
     int16_t *mid = nullptr;
     size_t mid_capacity_elems = 0;
+    // RGB sources: the input stage's 16-bit Y, U, V planes (libswscale's formatConvBuffer, for whole frames)
+    bool rgb_half = false;        // chroma made at half width (rgb24ToUV_half_c) or at full width
+    int rgb_cw = 0;               // its width
+    uint8_t *rgb_planes = nullptr;
+    size_t rgb_capacity = 0;
     // host-buffer path
     cudaStream_t copy_streams[2] = {nullptr, nullptr};
     uint8_t *stage_src[2] = {nullptr, nullptr};
@@ -145,7 +153,23 @@ void build_plan(tvs_ctx *c) {
         return op;
     };
 
-    if (same && s.bits == 10 && d.bits == 8 && s.semi && d.semi) {
+    if (s.rgb) {
+        // The scaler sees the input stage's planar 16-bit lines (virtual planes 0..2 in c->rgb_planes): luma sw x sh,
+        // chroma rgb_cw x sh (never subsampled vertically), 14/15-bit values, horizontal shift 13, no ordered dither.
+        for (int pl = 0; pl < 3; ++pl) {
+            PlaneOp op;
+            op.kind = kOpScale;
+            op.src_plane = pl; op.src_offset = 0; op.src_xstep = 2;
+            logical_plane(d, pl, op.dst_plane, op.dst_offset, op.dst_xstep);
+            op.src_bits = 16; op.dst_bits = d.bits; op.src_shift = 0; op.dst_shift = d.shift;
+            op.sw = pl ? c->rgb_cw : sw; op.sh = sh; op.dw = pl ? cdw : dw; op.dh = pl ? cdh : dh;
+            op.htable = pl ? 1 : 0; op.vtable = pl ? 3 : 2;
+            op.hshift = 13;
+            op.rule = d.bits > 8 ? kOut10 : kOut8;
+            op.dither_xoff = 0;
+            p.ops.push_back(op);
+        }
+    } else if (same && s.bits == 10 && d.bits == 8 && s.semi && d.semi) {
         // P010 -> NV12: each STORED plane is copied with the 2-bit dither, the UV plane as one plane of
         // 2*cw samples (SURVEY.md A.4 as extended in oracle/swscale_port.c).
         for (int st = 0; st < 2; ++st) {
@@ -214,7 +238,7 @@ int check_planes(const FormatInfo &fi, int w, int h, const void *const planes[3]
     const int cw = (w + 1) / 2;
     for (int i = 0; i < fi.planes; ++i) {
         if (!planes[i]) return fail(-EINVAL, "%s plane %d is NULL", side, i);
-        const ptrdiff_t row = static_cast<ptrdiff_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
+        const ptrdiff_t row = fi.rgb ? 3 * static_cast<ptrdiff_t>(w) : static_cast<ptrdiff_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
         if (pitch[i] < row) return fail(-EINVAL, "%s pitch[%d]=%td is smaller than a row (%td bytes)", side, i, pitch[i], row);
         if (fi.bytes == 2 && ((reinterpret_cast<uintptr_t>(planes[i]) | static_cast<uintptr_t>(pitch[i])) & 1))
             return fail(-EINVAL, "%s plane %d: 16-bit samples need 2-byte aligned pointer and pitch", side, i);
@@ -254,7 +278,7 @@ int ensure_mid(tvs_ctx *c, size_t elems) {
 }
 
 // Enqueue the whole batch on `stream`.  Pointers are device pointers.
-int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
+int enqueue_planar(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
                   void *const dst[3], const ptrdiff_t dp[3], const ptrdiff_t df[3], int n_frames, cudaStream_t stream) {
     std::vector<SampleView> sv, dv;
     bind_views(c, src, sp, sf, dst, dp, df, sv, dv);
@@ -378,6 +402,37 @@ int static_mid_for_device(int device, int16_t **out) {
     return 0;
 }
 
+// RGB sources first go through libswscale's input stage (rgb_input_kernel) into 16-bit planes owned by the context,
+// a bounded number of frames at a time, and then through the same launches as planar sources.
+int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
+                  void *const dst[3], const ptrdiff_t dp[3], const ptrdiff_t df[3], int n_frames, cudaStream_t stream) {
+    if (!c->sfi.rgb) return enqueue_planar(c, src, sp, sf, dst, dp, df, n_frames, stream);
+    const size_t y_bytes = static_cast<size_t>(c->src_w) * c->src_h * 2, c_bytes = static_cast<size_t>(c->rgb_cw) * c->src_h * 2;
+    const size_t per_frame = y_bytes + 2 * c_bytes;
+    size_t chunk = std::max<size_t>(1, (static_cast<size_t>(128) << 20) / per_frame);
+    chunk = std::min<size_t>(chunk, static_cast<size_t>(n_frames));
+    if (c->rgb_capacity < chunk * per_frame) {
+        if (c->rgb_planes) TVS_CUDA(cudaFree(c->rgb_planes), "cudaFree(rgb planes)");
+        c->rgb_planes = nullptr; c->rgb_capacity = 0;
+        TVS_CUDA(cudaMalloc(&c->rgb_planes, chunk * per_frame), "cudaMalloc(rgb planes)");
+        c->rgb_capacity = chunk * per_frame;
+    }
+    const void *vsrc[3] = {c->rgb_planes, c->rgb_planes + y_bytes, c->rgb_planes + y_bytes + c_bytes};
+    const ptrdiff_t vpitch[3] = {2 * static_cast<ptrdiff_t>(c->src_w), 2 * static_cast<ptrdiff_t>(c->rgb_cw), 2 * static_cast<ptrdiff_t>(c->rgb_cw)};
+    const ptrdiff_t vfs[3] = {static_cast<ptrdiff_t>(per_frame), static_cast<ptrdiff_t>(per_frame), static_cast<ptrdiff_t>(per_frame)};
+    for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk)) {
+        const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
+        if (launch_rgb_input(static_cast<const uint8_t *>(src[0]) + static_cast<ptrdiff_t>(f0) * sf[0], sp[0], sf[0], c->rgb_planes, per_frame,
+                             y_bytes, c_bytes, c->src_w, c->src_h, c->rgb_half, nf, stream) < 0)
+            return cuda_fail(cudaGetLastError(), "rgb input kernel launch");
+        ++c->launches;
+        void *vdst[3] = {nullptr, nullptr, nullptr};
+        for (int i = 0; i < c->dfi.planes; ++i) vdst[i] = static_cast<uint8_t *>(dst[i]) + static_cast<ptrdiff_t>(f0) * df[i];
+        if (int rc = enqueue_planar(c, vsrc, vpitch, vfs, vdst, dp, df, nf, stream)) return rc;
+    }
+    return 0;
+}
+
 }  // namespace
 
 extern "C" {
@@ -410,6 +465,15 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         fail(-EINVAL, "bad size %dx%d -> %dx%d", src_w, src_h, dst_w, dst_h);
         return nullptr;
     }
+    if (dfi.rgb) {
+        fail(-ENOSYS, "rgb24 is supported as a source format only");
+        return nullptr;
+    }
+    if (sfi.rgb && (src_w & 1)) {
+        // libswscale's half-width chroma input (rgb24ToUV_half_c) reads a pixel past the row when the width is odd
+        fail(-EINVAL, "rgb24 sources need an even width (got %d)", src_w);
+        return nullptr;
+    }
     const int alg_bits = flags & (TVS_BILINEAR | TVS_BICUBIC | TVS_AREA | TVS_LANCZOS);
     int alg = alg_bits ? alg_bits : TVS_BICUBIC;  // ffmpeg's default when flags= is absent
     if (alg & (alg - 1)) {
@@ -439,13 +503,24 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     c->sfi = sfi; c->dfi = dfi;
     static const int centred[4] = {TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT};
     if (!chr_pos) chr_pos = centred;
-    const int csw = (src_w + 1) / 2, csh = (src_h + 1) / 2, cdw = (dst_w + 1) / 2, cdh = (dst_h + 1) / 2;
+    int csw = (src_w + 1) / 2, csh = (src_h + 1) / 2;
+    const int cdw = (dst_w + 1) / 2, cdh = (dst_h + 1) / 2;
+    int src_hsub = 1, src_vsub = 1;   // log2 chroma subsampling of the source as the scaler sees it
+    if (sfi.rgb) {
+        // libswscale drops every other pixel for chroma "unless the destination chroma is wider than half the source"
+        // (sws_init_context: (dstW >> chrDstHSubSample) <= (srcW >> 1)); RGB chroma is never subsampled vertically.
+        c->rgb_half = (dst_w >> 1) <= (src_w >> 1);
+        c->rgb_cw = csw = c->rgb_half ? src_w / 2 : src_w;
+        csh = src_h;
+        src_hsub = c->rgb_half ? 1 : 0;
+        src_vsub = 0;
+    }
     const Algorithm a = static_cast<Algorithm>(alg);
     const int luma = axis_position(TVS_CHR_POS_DEFAULT, 0);
     const bool ok = build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma) &&
-                    build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], 1), axis_position(chr_pos[2], 1)) &&
+                    build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], src_hsub), axis_position(chr_pos[2], 1)) &&
                     build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma) &&
-                    build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], 1), axis_position(chr_pos[3], 1));
+                    build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], src_vsub), axis_position(chr_pos[3], 1));
     if (!ok) {
         fail(-ENOSYS, "%dx%d -> %dx%d needs a filter wider than 256 taps (libswscale would cascade); not supported",
              src_w, src_h, dst_w, dst_h);
@@ -470,7 +545,7 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         for (int i = 0; ok && i < 4; ++i) ok = is_box(c->host_tables[i], i < 2 ? 1 << 14 : 1 << 12);
         c->box2 = ok;
     }
-    if (c->plan.any_scale) {
+    if (c->plan.any_scale && !sfi.rgb) {   // RGB sources run on the integer two-pass kernels (15-bit samples: see 4.4 in DESIGN.md)
         std::string why;
         // Down-scales stage a wide source footprint and do better with 128-column tiles; up-scales amortise the
         // vertical pass over 256 columns.  If the preferred build cannot take the shape, try the other one;
@@ -493,6 +568,7 @@ void tvs_destroy(tvs_ctx *c) {
     if (c->streaming) stream_plan_destroy(c->streaming);
     if (c->dev_table_blob) cudaFree(c->dev_table_blob);
     if (c->mid) cudaFree(c->mid);
+    if (c->rgb_planes) cudaFree(c->rgb_planes);
     for (int i = 0; i < 2; ++i) {
         if (c->stage_src[i]) cudaFree(c->stage_src[i]);
         if (c->stage_dst[i]) cudaFree(c->stage_dst[i]);
@@ -530,6 +606,7 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const int cw_s = (c->src_w + 1) / 2, ch_s = (c->src_h + 1) / 2, cw_d = (c->dst_w + 1) / 2, ch_d = (c->dst_h + 1) / 2;
     auto plane_rows = [](int i, int h, int ch) { return i == 0 ? h : ch; };
     auto plane_row_bytes = [](const FormatInfo &fi, int i, int w, int cw) {
+        if (fi.rgb) return static_cast<size_t>(3) * w;
         return static_cast<size_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
     };
     const size_t sframe = tight_frame_bytes(c->sfi, c->src_w, c->src_h);
@@ -663,6 +740,7 @@ int tvs_scale_batch_static(tvs_ctx *c, const void *const src[3], const ptrdiff_t
                            int n_frames, void *stream) {
     if (!c) return fail(-EINVAL, "NULL context");
     if (n_frames < 0 || n_frames > 65535) return fail(-EINVAL, "n_frames must be 0..65535");
+    if (c->sfi.rgb) return fail(-ENOSYS, "rgb24 sources need the context's input-stage buffer; use tvs_scale_batch");
     if (int rc = check_planes(c->sfi, c->src_w, c->src_h, src, src_pitch, "src")) return rc;
     if (int rc = check_planes(c->dfi, c->dst_w, c->dst_h, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
     const Plan &plan = c->plan;

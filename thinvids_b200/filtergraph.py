@@ -199,8 +199,9 @@ class ScaleStage:
                         flags |= F.SWS_BICUBIC
             elif f.name == "format":
                 fmt = f.kwargs.get("pix_fmts", f.args[0] if f.args else "")
-                if fmt not in F.FMT_BY_NAME:
-                    raise FilterGraphError(f"format={fmt!r}: only {sorted(F.FMT_BY_NAME)} are supported")
+                if fmt not in F.FMT_BY_NAME or F.FMT_BY_NAME[fmt] in F.SOURCE_ONLY_FORMATS:
+                    ok = sorted(n for n, c in F.FMT_BY_NAME.items() if c not in F.SOURCE_ONLY_FORMATS)
+                    raise FilterGraphError(f"format={fmt!r}: only {ok} are supported")
                 dst_fmt = fmt
             elif f.name == "bwdif":
                 deint = True
@@ -213,6 +214,9 @@ class ScaleStage:
                                    "de-interlace upstream and pass deinterlaced_upstream=True")
         if src_fmt not in F.FMT_BY_NAME:
             raise FilterGraphError(f"source format {src_fmt!r} is not supported")
+        if F.FMT_BY_NAME[dst_fmt] in F.SOURCE_ONLY_FORMATS:
+            # tools/upscale_benchmark.py:163,182 always names the output format after its rgb24 input
+            raise FilterGraphError(f"a {src_fmt} source needs an explicit format= (yuv420p, nv12, ...) after scale")
         return cls(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, deint, hwup)
 
     @property

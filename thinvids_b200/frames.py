@@ -1,4 +1,5 @@
-"""Synthetic 4:2:0 frames and plane geometry for the scale / pixel-format stage.
+"""Synthetic frames and plane geometry for the scale / pixel-format stage (4:2:0 formats, plus packed rgb24 as a
+source: what tools/upscale_benchmark.py:159-182 feeds its lanczos stage).
 
 The reference never owns pixels itself (it hands files to ffmpeg, worker/tasks.py:1558-1586),
 so the frame containers here follow ffmpeg's pixel formats: a frame is a list of numpy planes,
@@ -16,8 +17,9 @@ from dataclasses import dataclass
 import numpy as np
 
 # Pixel-format codes of the C ABI (include/tvscale.h).
-YUV420P, NV12, YUV420P10LE, P010LE = 0, 1, 2, 3
-FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE}
+YUV420P, NV12, YUV420P10LE, P010LE, RGB24 = 0, 1, 2, 3, 4
+FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE, "rgb24": RGB24}
+SOURCE_ONLY_FORMATS = {RGB24}
 NAME_BY_FMT = {v: k for k, v in FMT_BY_NAME.items()}
 
 # Scaler algorithm flags, numerically equal to libswscale's SWS_* values.
@@ -35,7 +37,7 @@ def is_semiplanar(fmt) -> bool:
 
 
 def bit_depth(fmt) -> int:
-    return 8 if fmt_code(fmt) in (YUV420P, NV12) else 10
+    return 8 if fmt_code(fmt) in (YUV420P, NV12, RGB24) else 10
 
 
 def sample_dtype(fmt):
@@ -45,6 +47,8 @@ def sample_dtype(fmt):
 def plane_shapes(fmt, w: int, h: int):
     """(rows, cols-in-samples) of every stored plane of a tightly packed frame."""
     cw, ch = (w + 1) // 2, (h + 1) // 2
+    if fmt_code(fmt) == RGB24:
+        return [(h, 3 * w)]          # one plane of R, G, B bytes
     if is_semiplanar(fmt):
         return [(h, w), (ch, 2 * cw)]
     return [(h, w), (ch, cw), (ch, cw)]
@@ -159,6 +163,7 @@ EXTRA_CONFIGS = {
     "DVD480": ScaleConfig("DVD480", "yuv420p", 720, 480, "nv12", 720, 480, "bicubic", 1000),      # SCALE_FILTER_480 on a DVD source
     "HDR8": ScaleConfig("HDR8", "yuv420p10le", 1920, 1080, "nv12", 1920, 1080, "bicubic", 128),   # same-size 10 -> 8 bit
     "C3P": ScaleConfig("C3P", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "area", 64),
+    "RGB1": ScaleConfig("RGB1", "rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", 120),   # upscale_benchmark.py's real input
     "C4P8": ScaleConfig("C4P8", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "lanczos", 64),
 }
 CONFIGS.update(EXTRA_CONFIGS)
