@@ -19,6 +19,7 @@
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
+#include <type_traits>
 
 #include "scale_device.cuh"
 #include "tvs_internal.h"
@@ -51,6 +52,8 @@ struct StreamOpParams {
     int kb, n_blocks;      // source rows per block
     int rm_mask;           // rows of the intermediate ring - 1 (power of two)
     int s_pitch, s_chunks, s_chunks_log2;
+    int s_split;           // 16-bit planar sources at 2:1: a staged row keeps its even samples first and its odd samples from
+                           // this float offset on, so that lanes two samples apart read neighbouring words (0 = natural order)
     unsigned chunk_magic, word_magic;   // ceil(2^32 / s_chunks), ceil(2^32 / (4 * s_chunks)): exact division of small indices
     const uint8_t *src_lo; size_t src_extent;
     float v_thr, v_init;
@@ -159,7 +162,12 @@ __device__ __forceinline__ void convert_block(const StreamOpParams &op, const un
         for (int idx = tid; idx < total; idx += kSThreads) {
             const uint4 v = reinterpret_cast<const uint4 *>(raw)[idx];
             float *srow = S + row * s_pitch;
-            if (src_mode == kSrcU16) {      // eight samples per chunk
+            if (src_mode == kSrcU16 && op.s_split) {   // eight samples per chunk, even and odd positions apart
+                reinterpret_cast<float4 *>(srow)[ch] = make_float4(wide_to_float(v.x, 0x7410u, sscale, bias), wide_to_float(v.y, 0x7410u, sscale, bias),
+                                                                  wide_to_float(v.z, 0x7410u, sscale, bias), wide_to_float(v.w, 0x7410u, sscale, bias));
+                reinterpret_cast<float4 *>(srow + op.s_split)[ch] = make_float4(wide_to_float(v.x, 0x7432u, sscale, bias), wide_to_float(v.y, 0x7432u, sscale, bias),
+                                                                               wide_to_float(v.z, 0x7432u, sscale, bias), wide_to_float(v.w, 0x7432u, sscale, bias));
+            } else if (src_mode == kSrcU16) {          // eight samples per chunk
                 reinterpret_cast<float4 *>(srow)[2 * ch] = make_float4(wide_to_float(v.x, 0x7410u, sscale, bias), wide_to_float(v.x, 0x7432u, sscale, bias),
                                                                       wide_to_float(v.y, 0x7410u, sscale, bias), wide_to_float(v.y, 0x7432u, sscale, bias));
                 reinterpret_cast<float4 *>(srow)[2 * ch + 1] = make_float4(wide_to_float(v.z, 0x7410u, sscale, bias), wide_to_float(v.z, 0x7432u, sscale, bias),
@@ -312,22 +320,37 @@ stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
 
         // ---- horizontal pass of the block's rows into the ring ----
         if (NW == 0) {
+            const int split = op.s_split;
             for (int i = warp; i < rows; i += kSWarps) {
                 const unsigned mis = (mis0 + i * pmod) & 15u;
-                const float *srow = S + i * op.s_pitch + (src_mode == kSrcU8 ? mis : src_mode == kSrcU16Pair ? (mis >> 2) : (mis >> 1));
+                const int mis_samples = src_mode == kSrcU8 ? mis : src_mode == kSrcU16Pair ? (mis >> 2) : (mis >> 1);
+                const float *srow = S + i * op.s_pitch;
                 float *mrow = M + ((r_b + i) & mask) * kStripW + lane;
-#pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    const float *sp = srow + hstart[k];
-                    // taps in pairs: one FFMA2 does two of them (the sums are exact integers * 2^-(23+hshift), so
-                    // the order of the additions does not matter)
+                // taps in pairs: one FFMA2 does two of them (the sums are exact integers * 2^-(23+hshift), so the order of
+                // the additions does not matter).  `pe` / `po` address the even / odd taps, STEP floats apart.
+                auto column = [&](const float *pe, const float *po, auto step_tag, int k) {
+                    constexpr int STEP = decltype(step_tag)::value;
                     f32x2 acc2 = 0ull;
 #pragma unroll
-                    for (int j = 0; j + 1 < HT; j += 2) acc2 = fma2(pack2(sp[j], sp[j + 1]), pack2(ck[k][j], ck[k][j + 1]), acc2);
+                    for (int j = 0; j + 1 < HT; j += 2) acc2 = fma2(pack2(pe[(j >> 1) * STEP], po[(j >> 1) * STEP]), pack2(ck[k][j], ck[k][j + 1]), acc2);
                     float even, odd;
                     unpack2(acc2, even, odd);
                     float acc = even + odd;
-                    if (HT & 1) acc = fmaf(sp[HT - 1], ck[k][HT - 1], acc);
+                    if (HT & 1) acc = fmaf(pe[(HT >> 1) * STEP], ck[k][HT - 1], acc);
+                    return acc;
+                };
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    const int h0 = hstart[k] + mis_samples;
+                    float acc;
+                    if (split) {
+                        // split rows: the window's even-position samples in one half of the row, the odd ones in the other
+                        const int par = h0 & 1;
+                        acc = column(srow + (par ? split : 0) + (h0 >> 1), srow + (par ? 0 : split) + (h0 >> 1) + par,
+                                     std::integral_constant<int, 1>{}, k);
+                    } else {
+                        acc = column(srow + h0, srow + h0 + 1, std::integral_constant<int, 2>{}, k);
+                    }
                     mrow[32 * k] = fminf(fma_rm(acc, 0x1p-126f, h_addend), t_max);   // floor(sum >> hshift), clamped above
                 }
             }
@@ -460,7 +483,7 @@ size_t append_blob(std::vector<uint8_t> &blob, const std::vector<T> &v) {
 struct StreamOp {
     int op_index = 0, instance = -1, raw_instance = -1, out_mode = 0, src_mode = 0, h_taps = 0;
     int strips = 0, vtaps = 0, kb = 0, n_blocks = 0, rm_rows = 0;
-    int s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0;
+    int s_pitch = 0, s_chunks = 0, s_chunks_log2 = 0, s_split = 0;
     float v_thr = 0, v_init = 0, src_scale = 1.f, h_addend = 0.f;
     size_t hdense_off = 0, hint_off = 0, hbase_off = 0, vpos_off = 0, vpair_off = 0, vint_off = 0, yend_off = 0;
     std::vector<short> strip_c0, strip_nc;
@@ -566,6 +589,13 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         while ((1 << so.s_chunks_log2) < so.s_chunks) ++so.s_chunks_log2;
         so.s_pitch = so.s_chunks * (16 / op.src_xstep);
         if ((so.s_pitch & 31) == 0) so.s_pitch += 4;
+        if (so.src_mode == kSrcU16) {
+            // windows exactly two samples apart (2:1): keep even and odd samples of a staged row apart, so that lanes read
+            // consecutive words instead of every other one (2-way bank conflicts otherwise)
+            int twos = 0;
+            for (int x = 1; x < op.dw; ++x) twos += h.pos[x] - h.pos[x - 1] == 2;
+            if (op.dw > 8 && twos >= (op.dw - 1) * 9 / 10) so.s_split = so.s_chunks * 4;
+        }
 
         // vertical tables in tap order, (g, g) pairs and integers
         std::vector<float> vpair(static_cast<size_t>(op.dh) * VT * 2, 0.0f);
@@ -672,7 +702,7 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
             q.vint = reinterpret_cast<const int *>(p->blob + so.vint_off);
             q.block_yend = reinterpret_cast<const int *>(p->blob + so.yend_off);
             q.kb = so.kb; q.n_blocks = so.n_blocks; q.rm_mask = so.rm_rows - 1;
-            q.s_pitch = so.s_pitch; q.s_chunks = so.s_chunks; q.s_chunks_log2 = so.s_chunks_log2;
+            q.s_pitch = so.s_pitch; q.s_chunks = so.s_chunks; q.s_chunks_log2 = so.s_chunks_log2; q.s_split = so.s_split;
             q.chunk_magic = static_cast<unsigned>((0x100000000ull + so.s_chunks - 1) / so.s_chunks);
             q.word_magic = static_cast<unsigned>((0x100000000ull + 4 * so.s_chunks - 1) / (4 * so.s_chunks));
             q.src_lo = s.base - op.src_offset;
