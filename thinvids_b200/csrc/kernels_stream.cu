@@ -565,7 +565,7 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         if (so.strips > kMaxStrips) return bail("plane too wide for the strip table");
 
         // float vertical sum: residual threshold / accumulator start (tvs_internal.h)
-        const VerticalFloatRule vrule = vertical_float_rule(v, VT + 1, so.out_mode == kOutU10, so.out_mode == kOutU8Dither);
+        const VerticalFloatRule vrule = vertical_float_rule_split(v, VT, so.out_mode == kOutU10, so.out_mode == kOutU8Dither);
         if (!vrule.ok) return bail("vertical error bound too large");
         so.v_thr = vrule.thr;
         so.v_init = vrule.init;

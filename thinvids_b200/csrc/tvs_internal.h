@@ -106,6 +106,35 @@ inline VerticalFloatRule vertical_float_rule(const AxisTable &v, int vt_inst, bo
     return {true, static_cast<float>(std::ldexp(half_step - e - 1.0, -42)), 0.0f};
 }
 
+// The same rule for the streaming kernel, whose vertical sum runs in tap order with even and odd taps in separate chains
+// (joined by one addition) when there are at least 4 tap slots.  Each FMA's rounding error is at most half an ulp of ITS OWN
+// partial sum, bounded by 32767 * (sum of |g| accumulated so far in that chain): following the actual order row by row gives
+// a bound about a third of "taps * half an ulp of the largest possible sum" for lanczos / bicubic tables, and the exact path
+// runs that much less often.  `init_abs` bounds the accumulator's start value (ordered dither), in units of the integer sum.
+inline VerticalFloatRule vertical_float_rule_split(const AxisTable &v, int vt_inst, bool out10, bool dither) {
+    const VerticalFloatRule coarse = vertical_float_rule(v, vt_inst + 1, out10, dither);
+    if (!coarse.ok || coarse.thr > 1.0e38f) return coarse;   // exact tables keep their own treatment
+    auto half_ulp = [](double bound) { return bound < 1.0 ? 0.0 : 0.5 * std::ldexp(1.0, static_cast<int>(std::floor(std::log2(bound))) + 1 - 24); };
+    const double init_abs = dither ? 64.0 * 4096.0 : 0.0;
+    const bool split = vt_inst >= 4;
+    double e_max = 0.0;
+    for (int y = 0; y < v.length; ++y) {
+        double run[2] = {init_abs, 0.0}, e = 0.0;
+        for (int j = 0; j < v.taps; ++j) {
+            const int c = std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+            if (!c) continue;   // a zero coefficient leaves the accumulator unchanged, exactly
+            double &r = run[split ? (j & 1) : 0];
+            r += 32767.0 * c;
+            e += half_ulp(r);
+        }
+        if (split) e += half_ulp(run[0] + run[1]);
+        e_max = std::max(e_max, e);
+    }
+    const double half_step = out10 ? 65536.0 : 262144.0;
+    if (e_max > half_step / 8) return {false, 0.f, 0.f};
+    return {true, static_cast<float>(std::ldexp(half_step - e_max - 1.0, -42)), coarse.init};
+}
+
 // ---- kernel launchers (kernels_generic.cu) -------------------------------------------------------
 // Each returns the number of kernels it launched, or -1 after a launch error (cudaGetLastError kept).
 int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceTable &h, int16_t *mid,
