@@ -34,14 +34,13 @@ hpass_generic_kernel(const uint8_t *__restrict__ src, ptrdiff_t pitch, ptrdiff_t
     const int r = blockIdx.y;
     const int f = blockIdx.z;
     if (x >= dw) return;
-    const uint8_t *row = src + f * frame_stride + r * pitch;
     const int16_t *c = coef + static_cast<size_t>(x) * taps;
     const int first = pos[x];
+    const uint8_t *p = src + f * frame_stride + r * pitch + static_cast<ptrdiff_t>(first) * xstep;
+    const int n = min(taps, sw - first);   // taps past the row's end carry zero weight
     int acc = 0;
-    for (int j = 0; j < taps; ++j) {
-        const int sx = first + j;
-        if (sx < sw) acc += (load_sample<SrcT>(row + static_cast<ptrdiff_t>(sx) * xstep) >> src_shift) * c[j];
-    }
+#pragma unroll 4
+    for (int j = 0; j < n; ++j, p += xstep) acc += (load_sample<SrcT>(p) >> src_shift) * c[j];
     acc >>= hshift;
     mid[f * mid_frame_stride + static_cast<size_t>(r) * dw + x] = static_cast<int16_t>(min(acc, 32767));
 }
@@ -73,6 +72,48 @@ vpass_generic_kernel(const int16_t *__restrict__ mid, size_t mid_frame_stride, i
         v = min(max((acc + (d << 12)) >> 19, 0), 255);
     }
     *reinterpret_cast<DstT *>(dst + f * frame_stride + y * pitch + static_cast<ptrdiff_t>(x) * xstep) = static_cast<DstT>(v);
+}
+
+// Four adjacent output samples per thread: one 64-bit load of the intermediate and one coefficient load per tap serve
+// four multiply-adds.  The launcher uses it when rows of the intermediate are 8-byte aligned and dw is a multiple of 4.
+template <typename DstT>
+__global__ void __launch_bounds__(256)
+vpass_quad_kernel(const int16_t *__restrict__ mid, size_t mid_frame_stride, int sh, int dw,
+                  const int16_t *__restrict__ coef, const int32_t *__restrict__ pos, int taps,
+                  uint8_t *__restrict__ dst, ptrdiff_t pitch, ptrdiff_t frame_stride, int xstep, int dst_shift,
+                  int rule, int dither_xoff) {
+    const int x = 4 * (blockIdx.x * blockDim.x + threadIdx.x);
+    const int y = blockIdx.y;
+    const int f = blockIdx.z;
+    if (x >= dw) return;
+    const int16_t *c = coef + static_cast<size_t>(y) * taps;
+    const int first = pos[y];
+    const int n = min(taps, sh - first);
+    const uint2 *m = reinterpret_cast<const uint2 *>(mid + f * mid_frame_stride + static_cast<size_t>(first) * dw + x);
+    const int row_step = dw >> 2;
+    int a0 = 0, a1 = 0, a2 = 0, a3 = 0;
+#pragma unroll 4
+    for (int j = 0; j < n; ++j, m += row_step) {
+        const uint2 v = __ldg(m);
+        const int cj = c[j];
+        a0 += static_cast<int>(static_cast<short>(v.x & 0xffffu)) * cj;
+        a1 += (static_cast<int>(v.x) >> 16) * cj;
+        a2 += static_cast<int>(static_cast<short>(v.y & 0xffffu)) * cj;
+        a3 += (static_cast<int>(v.y) >> 16) * cj;
+    }
+    const int acc[4] = {a0, a1, a2, a3};
+    uint8_t *out = dst + f * frame_stride + y * pitch + static_cast<ptrdiff_t>(x) * xstep;
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        int v;
+        if (rule == kOut10) {
+            v = min(max((acc[k] + (1 << 16)) >> 17, 0), 1023) << dst_shift;
+        } else {
+            const int d = rule == kOut8 ? 64 : kDither128[y & 7][(x + k + dither_xoff) & 7];
+            v = min(max((acc[k] + (d << 12)) >> 19, 0), 255);
+        }
+        *reinterpret_cast<DstT *>(out + static_cast<ptrdiff_t>(k) * xstep) = static_cast<DstT>(v);
+    }
 }
 
 // Same-size converters.  kOpCopy moves a sample unchanged (dropping / restoring P010's padding bits);
@@ -392,8 +433,19 @@ int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceT
 
 int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceTable &v, const int16_t *mid,
                          size_t mid_frame_stride, int n_frames, cudaStream_t stream) {
-    const dim3 grid = plane_grid(op.dw, op.dh, n_frames);
     const int16_t *m = mid + op.mid_offset;
+    if ((op.dw & 3) == 0 && (mid_frame_stride & 3) == 0 && (reinterpret_cast<uintptr_t>(m) & 7) == 0) {
+        const int threads = op.dw / 4 >= 256 ? 256 : 64;
+        const dim3 g((op.dw / 4 + threads - 1) / threads, op.dh, n_frames);
+        if (op.dst_bits == 8)
+            vpass_quad_kernel<uint8_t><<<g, threads, 0, stream>>>(m, mid_frame_stride, op.sh, op.dw, v.coef, v.pos, v.taps,
+                dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.rule, op.dither_xoff);
+        else
+            vpass_quad_kernel<uint16_t><<<g, threads, 0, stream>>>(m, mid_frame_stride, op.sh, op.dw, v.coef, v.pos, v.taps,
+                dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.rule, op.dither_xoff);
+        return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+    }
+    const dim3 grid = plane_grid(op.dw, op.dh, n_frames);
     if (op.dst_bits == 8)
         vpass_generic_kernel<uint8_t><<<grid, 256, 0, stream>>>(m, mid_frame_stride, op.sh, op.dw, v.coef, v.pos, v.taps,
             dst.base, dst.pitch, dst.frame_stride, dst.xstep, op.dst_shift, op.rule, op.dither_xoff);
