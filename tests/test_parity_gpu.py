@@ -119,6 +119,24 @@ def test_unscaled_all_format_pairs_against_oracle():
                     assert np.array_equal(a, b), (sf, df, w, h)
 
 
+def test_fused_narrow_tiles_with_footprints_wider_than_the_cta():
+    """A strong horizontal down-scale of interleaved 16-bit chroma stages more 16-byte chunks per row than the 128-thread
+    tile build has threads (found by tools/gpu_fuzz.py: the staging loops then stepped by zero rows)."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    for sf, sw, sh, df, dw, dh, alg in [(3, 1090, 64, 3, 223, 60, F.SWS_AREA), (3, 1090, 728, 3, 223, 612, F.SWS_AREA),
+                                        (1, 1600, 40, 0, 260, 48, F.SWS_BILINEAR)]:
+        src = F.random_frame(sf, sw, sh, 12)
+        want = port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(src)
+        for path in PATHS:
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                if not _use_path(s, path):
+                    continue
+                got = s.scale(src)
+            for a, b in zip(got, want):
+                assert np.array_equal(a, b), (sf, sw, sh, df, dw, dh, path)
+
+
 def test_exact_two_to_one_area_box_kernel_against_oracle():
     """Exact 2:1 area on 8-bit planes runs on the box-filter kernel ((p00+p01+p10+p11+2)>>2); odd alignments included."""
     from oracle import port

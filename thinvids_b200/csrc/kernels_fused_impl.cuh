@@ -49,6 +49,7 @@ constexpr int kHalfW = 128;               // columns per half tile: lane * 4 + k
 constexpr int kTileW = kHalves * kHalfW;
 constexpr int kThreads = 128 * kHalves;
 constexpr int kWarps = kThreads / 32;
+constexpr int kThreadsLog2 = kHalves == 2 ? 8 : 7;   // the staging loops give each row 2^k <= kThreads threads
 constexpr int kGroup = 4;                 // adjacent output columns per lane
 constexpr int kGroupsPerHalf = kHalfW / kGroup;
 constexpr int kMaxFusedOps = 3;
@@ -444,7 +445,7 @@ __device__ __forceinline__ void prefetch_tile_source(const FusedLaunchParams &P,
     const int sample_bytes = op.src_mode >= kSrcU16 ? 2 : 1;
     // offset of the last needed byte of a footprint row (samples past the plane's width carry zero weight)
     const int last_byte = (min(static_cast<int>(op.tile_nc[c.tx]), op.sw - c0) - 1) * xs + sample_bytes - 1;
-    const int clog = min(op.s_chunks_log2, 8), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
+    const int clog = min(op.s_chunks_log2, kThreadsLog2), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
     const uint8_t *src_base = tile_src_base(op, c);
     const uint8_t *lo = op.src_lo + c.f * op.src_fstride, *hi = lo + op.src_extent;
     const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(src_base)) & 15u;
@@ -559,7 +560,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
 
         // ---- raw words -> float samples ----
         if (!(P.debug_skip & 1)) {
-            const int clog = min(op.s_chunks_log2, 8), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
+            const int clog = min(op.s_chunks_log2, kThreadsLog2), cmask = (1 << clog) - 1, s_chunks = op.s_chunks;
             const int rstep = kThreads >> clog;
             const int src_mode = op.src_mode;
             const float sscale = op.src_scale;
