@@ -34,6 +34,61 @@ def make_input(fmt, w, h, kind, seed):
     return planes
 
 
+def surfaces_case(rnd, sf, sw, sh, df, dw, dh, alg, seed):
+    """The same shape through tvs_scale_batch on pitched device surfaces: random pitch padding, random base misalignment,
+    a few frames, guard bytes around everything.  Returns a list of problems."""
+    import torch
+    n = rnd.randrange(1, 4)
+    frames = [make_input(sf, sw, sh, rnd.randrange(3), seed + i) for i in range(n)]
+    ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg)
+    want = [ref.scale(fr) for fr in frames]
+
+    def surfaces(fmt, w, h, fill_from=None):
+        bufs, ptrs, pitches, fstrides, metas = [], [], [], [], []
+        bps = 1 if F.bit_depth(fmt) == 8 else 2
+        for k, (rows, cols) in enumerate(F.plane_shapes(fmt, w, h)):
+            row_bytes = cols * bps
+            pitch = row_bytes + rnd.choice([0, 0, 4, 16, 1, 3, 6, 64, 10]) * (bps if bps == 2 else 1)
+            if bps == 2:
+                pitch += pitch & 1
+            lead = rnd.choice([0, 0, 16, 4, 2, 1, 8, 6]) * (1 if bps == 1 else 2) // (1 if bps == 1 else 1)
+            if bps == 2:
+                lead += lead & 1
+            fstride = (rows + 1) * pitch
+            host = np.full(lead + n * fstride + 32, 0xEE, dtype=np.uint8)
+            if fill_from is not None:
+                for i in range(n):
+                    view = host[lead + i * fstride: lead + i * fstride + rows * pitch].reshape(rows, pitch)
+                    view[:, :row_bytes] = np.ascontiguousarray(fill_from[i][k]).view(np.uint8).reshape(rows, row_bytes)
+            t = torch.from_numpy(host).cuda()
+            bufs.append(t); ptrs.append(t.data_ptr() + lead); pitches.append(pitch); fstrides.append(fstride)
+            metas.append((lead, rows, row_bytes, pitch, fstride))
+        return bufs, ptrs, pitches, fstrides, metas
+
+    sb, sp, spi, sfs, _ = surfaces(sf, sw, sh, frames)
+    db, dp, dpi, dfs, dmeta = surfaces(df, dw, dh)
+    problems = []
+    with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+        s.scale_device_planes(sp, spi, sfs, dp, dpi, dfs, n, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        used = s.path
+    for k, (lead, rows, row_bytes, pitch, fstride) in enumerate(dmeta):
+        host = db[k].cpu().numpy()
+        if not (host[:lead] == 0xEE).all() or not (host[lead + n * fstride:] == 0xEE).all():
+            problems.append(("guard before/after", k, used))
+        for i in range(n):
+            frame = host[lead + i * fstride: lead + (i + 1) * fstride].reshape(rows + 1, pitch)
+            exp = np.ascontiguousarray(want[i][k]).view(np.uint8).reshape(rows, row_bytes)
+            got = frame[:rows, :row_bytes]
+            if k == 1 and df == F.P010LE and sf in (F.YUV420P, F.YUV420P10LE) and sw % 2 and (sw, sh) == (dw, dh):
+                got, exp = got[:, :-4], exp[:, :-4]
+            if not np.array_equal(got, exp):
+                problems.append(("pixels", k, i, used, int((got != exp).sum())))
+            if not (frame[:rows, row_bytes:] == 0xEE).all() or not (frame[rows] == 0xEE).all():
+                problems.append(("padding written", k, i, used))
+    return problems
+
+
 def main():
     budget = float(sys.argv[1]) if len(sys.argv) > 1 else 120.0
     rnd = random.Random(int(sys.argv[2]) if len(sys.argv) > 2 else 2026)
@@ -88,6 +143,13 @@ def main():
                 if not np.array_equal(a, b):
                     bad += 1
                     print("MISMATCH", (sf, sw, sh, df, dw, dh, hex(alg)), path, used, "plane", k, int((a != b).sum()))
+        if os.environ.get("FUZZ_SURFACES") and not (sf == 4 and False):
+            try:
+                for pr in surfaces_case(rnd, sf, sw, sh, df, dw, dh, alg, 7000 + n):
+                    bad += 1
+                    print("SURFACE MISMATCH", (sf, sw, sh, df, dw, dh, hex(alg)), pr, flush=True)
+            except tv_lib.TvscaleError as e:
+                print("surfaces refused", (sf, sw, sh, df, dw, dh, hex(alg)), str(e)[:80])
         n += 1
         if n % 50 == 0:
             print("progress", n, "cases", bad, "mismatches", round(time.time() - t0), "s", flush=True)
