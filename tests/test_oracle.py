@@ -113,9 +113,10 @@ def test_port_equals_genuine_library_rgb24_sources():
         sw, sh = 2 * rnd.randrange(1, 80), rnd.randrange(2, 100)
         dw, dh = (sw, sh) if rnd.random() < 0.15 else (rnd.randrange(2, 240), rnd.randrange(2, 160))
         alg, df = rnd.choice(algs), rnd.randrange(4)
+        cp = rnd.choice([None, None, (0, -513, 0, -513), (0, 128, 0, 128), (64, 192, 0, 64)])   # explicit chroma siting too
         src = F.random_frame(F.RGB24, sw, sh, 500 + i)
-        want = ref_swscale.RefScaler(sw, sh, F.RGB24, dw, dh, df, alg).scale(src)
-        got = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg).scale(src)
+        want = ref_swscale.RefScaler(sw, sh, F.RGB24, dw, dh, df, alg, chr_pos=cp).scale(src)
+        got = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg, chr_pos=cp).scale(src)
         for x, y in zip(got, want):
             assert np.array_equal(x, y), (sw, sh, dw, dh, df, hex(alg))
 

@@ -111,13 +111,15 @@ def main():
         else:
             dw, dh = (rnd.randrange(100, 2200), rnd.randrange(60, 1300)) if big else (rnd.randrange(2, 500), rnd.randrange(2, 400))
         alg = rnd.choice(algs)
+        chr_pos = rnd.choice([None, None, None, (0, -513, 0, -513), (0, 128, 0, 128), (0, 0, 0, 0), (128, 128, 128, 128), (64, 192, 0, 64)]) \
+            if os.environ.get("FUZZ_CHRPOS") else None
         kind = rnd.randrange(3)
         if n < int(os.environ.get("FUZZ_SKIP", "0")):   # fast-forward the case stream
             n += 1
             continue
         src = make_input(sf, sw, sh, kind, n)
         try:
-            ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg)
+            ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=chr_pos)
             want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
             ref.scale_into(src, want)
         except Exception as e:  # shapes the oracle refuses are refused by the product too
@@ -126,7 +128,7 @@ def main():
             if os.environ.get("FUZZ_VERBOSE"):
                 print("case", n, (sf, sw, sh, df, dw, dh, hex(alg)), path, flush=True)
             try:
-                with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                with Scaler(sw, sh, sf, dw, dh, df, alg, chr_pos=chr_pos) as s:
                     try:
                         s.set_path(path)
                     except tv_lib.TvscaleError:
@@ -142,7 +144,7 @@ def main():
                     a, b = a[:, :-2], b[:, :-2]   # the one pair libswscale's same-size planar -> P010 converter leaves unwritten
                 if not np.array_equal(a, b):
                     bad += 1
-                    print("MISMATCH", (sf, sw, sh, df, dw, dh, hex(alg)), path, used, "plane", k, int((a != b).sum()))
+                    print("MISMATCH", (sf, sw, sh, df, dw, dh, hex(alg)), chr_pos, path, used, "plane", k, int((a != b).sum()))
         if os.environ.get("FUZZ_SURFACES") and not (sf == 4 and False):
             try:
                 for pr in surfaces_case(rnd, sf, sw, sh, df, dw, dh, alg, 7000 + n):
