@@ -97,8 +97,10 @@ def main():
     while time.time() - t0 < budget:
         sf = rnd.choice([0, 0, 1, 2, 3, 4])
         df = rnd.randrange(4)
-        big = rnd.random() < 0.25
-        sw, sh = (rnd.randrange(200, 1930), rnd.randrange(100, 1090)) if big else (rnd.randrange(2, 400), rnd.randrange(2, 300))
+        huge = bool(os.environ.get("FUZZ_HUGE"))   # up to 4K frames, every case large
+        big = huge or rnd.random() < 0.25
+        sw, sh = (rnd.randrange(200, 3850 if huge else 1930), rnd.randrange(100, 2170 if huge else 1090)) if big \
+            else (rnd.randrange(2, 400), rnd.randrange(2, 300))
         if sf == 4:
             sw += sw & 1
         mode = rnd.random()
@@ -109,7 +111,8 @@ def main():
         elif mode < 0.45:
             dw, dh = sw * 2, sh * 2
         else:
-            dw, dh = (rnd.randrange(100, 2200), rnd.randrange(60, 1300)) if big else (rnd.randrange(2, 500), rnd.randrange(2, 400))
+            dw, dh = (rnd.randrange(100, 4200 if huge else 2200), rnd.randrange(60, 2400 if huge else 1300)) if big \
+                else (rnd.randrange(2, 500), rnd.randrange(2, 400))
         alg = rnd.choice(algs)
         chr_pos = rnd.choice([None, None, None, (0, -513, 0, -513), (0, 128, 0, 128), (0, 0, 0, 0), (128, 128, 128, 128), (64, 192, 0, 64)]) \
             if os.environ.get("FUZZ_CHRPOS") else None
