@@ -185,7 +185,8 @@ def test_pitched_and_strided_device_surfaces():
         (3, 1, 20, 6, 20, 6, F.SWS_BICUBIC, 4, 12), (3, 1, 200, 10, 200, 10, F.SWS_BICUBIC, 0, 0), (2, 0, 64, 10, 64, 10, F.SWS_BICUBIC, 8, 8),
         (3, 0, 36, 4, 36, 4, F.SWS_BICUBIC, 3, 1),
         # 16-bit planar sources at 2:1: the streaming kernel's split (even / odd) staged rows, with row starts of either parity
-        (2, 2, 512, 96, 256, 48, F.SWS_LANCZOS, 3, 0), (2, 0, 384, 64, 192, 32, F.SWS_BICUBIC, 0, 5), (2, 3, 258, 40, 129, 20, F.SWS_BILINEAR, 1, 0)]:
+        (2, 2, 512, 96, 256, 48, F.SWS_LANCZOS, 3, 0), (2, 0, 384, 64, 192, 32, F.SWS_BICUBIC, 0, 5), (2, 3, 258, 40, 129, 20, F.SWS_BILINEAR, 1, 0),
+        (3, 3, 512, 64, 256, 32, F.SWS_LANCZOS, 1, 0), (3, 1, 384, 48, 192, 24, F.SWS_BICUBIC, 0, 3)]:   # ... and interleaved 16-bit chroma
         n = 3
         frames = [F.random_frame(sf, sw, sh, 50 + i) for i in range(n)]
         want = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(fr) for fr in frames]

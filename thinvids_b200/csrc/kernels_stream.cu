@@ -52,7 +52,7 @@ struct StreamOpParams {
     int kb, n_blocks;      // source rows per block
     int rm_mask;           // rows of the intermediate ring - 1 (power of two)
     int s_pitch, s_chunks, s_chunks_log2;
-    int s_split;           // 16-bit planar sources at 2:1: a staged row keeps its even samples first and its odd samples from
+    int s_split;           // 16-bit sources at 2:1: a staged row keeps its even samples first and its odd samples from
                            // this float offset on, so that lanes two samples apart read neighbouring words (0 = natural order)
     unsigned chunk_magic, word_magic;   // ceil(2^32 / s_chunks), ceil(2^32 / (4 * s_chunks)): exact division of small indices
     const uint8_t *src_lo; size_t src_extent;
@@ -172,6 +172,10 @@ __device__ __forceinline__ void convert_block(const StreamOpParams &op, const un
                                                                       wide_to_float(v.y, 0x7410u, sscale, bias), wide_to_float(v.y, 0x7432u, sscale, bias));
                 reinterpret_cast<float4 *>(srow)[2 * ch + 1] = make_float4(wide_to_float(v.z, 0x7410u, sscale, bias), wide_to_float(v.z, 0x7432u, sscale, bias),
                                                                           wide_to_float(v.w, 0x7410u, sscale, bias), wide_to_float(v.w, 0x7432u, sscale, bias));
+            } else if (op.s_split) {        // interleaved 16-bit chroma, even and odd sample positions apart
+                const unsigned sel = ((mis0 + row * pmod) & 2u) ? 0x7432u : 0x7410u;
+                reinterpret_cast<float2 *>(srow)[ch] = make_float2(wide_to_float(v.x, sel, sscale, bias), wide_to_float(v.z, sel, sscale, bias));
+                reinterpret_cast<float2 *>(srow + op.s_split)[ch] = make_float2(wide_to_float(v.y, sel, sscale, bias), wide_to_float(v.w, sel, sscale, bias));
             } else {                        // interleaved 16-bit chroma: one sample of this plane per word
                 const unsigned sel = ((mis0 + row * pmod) & 2u) ? 0x7432u : 0x7410u;
                 reinterpret_cast<float4 *>(srow)[ch] = make_float4(wide_to_float(v.x, sel, sscale, bias), wide_to_float(v.y, sel, sscale, bias),
@@ -589,12 +593,12 @@ StreamPlan *stream_plan_create(const Plan &plan, const AxisTable host_tables[4],
         while ((1 << so.s_chunks_log2) < so.s_chunks) ++so.s_chunks_log2;
         so.s_pitch = so.s_chunks * (16 / op.src_xstep);
         if ((so.s_pitch & 31) == 0) so.s_pitch += 4;
-        if (so.src_mode == kSrcU16) {
+        if (so.src_mode == kSrcU16 || so.src_mode == kSrcU16Pair) {
             // windows exactly two samples apart (2:1): keep even and odd samples of a staged row apart, so that lanes read
             // consecutive words instead of every other one (2-way bank conflicts otherwise)
             int twos = 0;
             for (int x = 1; x < op.dw; ++x) twos += h.pos[x] - h.pos[x - 1] == 2;
-            if (op.dw > 8 && twos >= (op.dw - 1) * 9 / 10) so.s_split = so.s_chunks * 4;
+            if (op.dw > 8 && twos >= (op.dw - 1) * 9 / 10) so.s_split = so.s_chunks * (so.src_mode == kSrcU16 ? 4 : 2);
         }
 
         // vertical tables in tap order, (g, g) pairs and integers

@@ -163,6 +163,8 @@ EXTRA_CONFIGS = {
     "DVD480": ScaleConfig("DVD480", "yuv420p", 720, 480, "nv12", 720, 480, "bicubic", 1000),      # SCALE_FILTER_480 on a DVD source
     "HDR8": ScaleConfig("HDR8", "yuv420p10le", 1920, 1080, "nv12", 1920, 1080, "bicubic", 128),   # same-size 10 -> 8 bit
     "C3P": ScaleConfig("C3P", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "area", 64),
+    "C4S": ScaleConfig("C4S", "p010le", 3840, 2160, "p010le", 1920, 1080, "lanczos", 64),      # C4 on NVDEC-style P010 surfaces
+    "C4N": ScaleConfig("C4N", "p010le", 3840, 2160, "nv12", 1920, 1080, "bicubic", 64),        # 10-bit 4K source to the 8-bit 1080p target
     "RGB1": ScaleConfig("RGB1", "rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", 120),   # upscale_benchmark.py's real input
     "C4P8": ScaleConfig("C4P8", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "lanczos", 64),
 }
