@@ -18,6 +18,14 @@
  * errno-style code on failure; tvs_last_error() then holds a human-readable message for the calling
  * thread.  A context belongs to one device and, like a SwsContext, must not be used by two threads at
  * once.  Plain C types only: no CUDA or torch types appear in any signature (streams travel as void*).
+ * Every entry point that takes a context makes that context's device the calling thread's current CUDA
+ * device (cudaSetDevice) and leaves it current; a host thread that drives several GPUs must not assume
+ * its previous device is still selected after a call.
+ *
+ * One deliberate difference from libswscale's bytes: for a same-size planar -> p010le conversion of an
+ * ODD-width frame libswscale writes only floor(w/2) chroma pairs and leaves the last pair of every chroma
+ * row untouched; this library writes all ceil(w/2) pairs (the value the scaler proper produces), so that
+ * every destination byte is defined.  Everything else is byte-identical.
  */
 #ifndef TVSCALE_H
 #define TVSCALE_H
@@ -118,8 +126,11 @@ TVS_API int tvs_scale_host(tvs_ctx *ctx,
  *   - n_frames x (intermediate of one frame: 2 bytes x dst_w x src_h for luma plus the two chroma planes) must fit in
  *     TVS_STATIC_SCRATCH_BYTES, e.g. 12 frames of 720x480 -> 1920x1080 or 2 frames of 1920x1080 -> 3840x2160.
  *     Larger requests fail with -E2BIG and a message that states the per-call maximum; split the batch.
- *   - The first call on each device looks up the array's device address (cudaGetSymbolAddress, with that device
- *     current).  Make that first call before starting any stream capture.
+ *   - The array's device address is looked up once per device (cudaGetSymbolAddress, with that device current).
+ *     tvs_create() does this, so the array's TVS_STATIC_SCRATCH_BYTES are taken from the device when the first
+ *     context is created there - the one moment at which this library allocates - and not by a scale call.  Should
+ *     that lookup have failed at creation, the first call here repeats it; make that first call before starting
+ *     any stream capture.
  *   - There is ONE array per device, shared by every context and every call in the process, and it keeps whatever
  *     the last call left in it.  Nothing in it needs clearing (each call overwrites what it later reads), but two
  *     calls whose kernels can run at the same time on one GPU - different streams, or different threads - race on
@@ -131,6 +142,15 @@ TVS_API int tvs_scale_batch_static(tvs_ctx *ctx,
                     const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
                     void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
                     int n_frames, void *stream);
+
+/*
+ * No counterpart in libswscale (which works on pageable memory): page-locked host buffers for tvs_scale_host().
+ * Frames read into / written from such a buffer cross PCIe without the driver's intermediate staging copy and let the
+ * host entry point overlap its copies with its kernels.  thinvids_b200/worker.py reads the decoder's raw video into a
+ * small ring of these.  Needs a CUDA device (returns NULL and sets tvs_last_error() without one).
+ */
+TVS_API void *tvs_host_alloc(size_t bytes);
+TVS_API void tvs_host_free(void *p);
 
 /*
  * Host-only: one axis of libswscale's initFilter.  No device needed.
@@ -151,7 +171,11 @@ TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size
  *   TVS_INFO_KERNEL_LAUNCHES  kernels launched by this context so far (monotonic)
  *   TVS_INFO_PATH             0 = fused tile kernel, 1 = two-pass kernels through device scratch,
  *                             2 = same-size repack only, 3 = streaming (line-buffer) kernel for vertical down-scales,
- *                             4 = box-filter kernel (exact 2:1 area on 8-bit planes)
+ *                             4 = box-filter kernel (exact 2:1 area on 8-bit planes),
+ *                             5 = slab kernel (warp-specialised row streaming for vertical up-scales).
+ *                             Shapes that fall back to 1 (two-pass): rgb24 sources, filters wider than the fused /
+ *                             streaming instances cover (more than 24 horizontal or 12 vertical taps), tables that fail the
+ *                             FP32 exactness preconditions, and footprints that do not fit in shared memory.
  *   TVS_INFO_SCRATCH_BYTES    device scratch currently owned by the context
  *   TVS_INFO_SRC_FRAME_BYTES / TVS_INFO_DST_FRAME_BYTES   tightly packed frame sizes
  */

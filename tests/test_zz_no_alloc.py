@@ -68,3 +68,29 @@ def test_static_scratch_entry_rejects_oversized_batches():
         assert e.value.code == -7 and "at most 2 frame" in str(e.value)   # -E2BIG
         sc.scale_packed_device_static(d_src[:2], d_dst[:2])
         torch.cuda.synchronize()
+
+
+def test_static_scratch_entry_takes_no_device_memory():
+    """The fixed array is brought onto the device when the context is created, so a scale call through the
+    no-allocation entry point leaves the device's free memory exactly where it was (cudaMemGetInfo)."""
+    import torch
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler
+    lib = tv_lib.load()
+    sf, sw, sh, df, dw, dh, alg, n = CASES[0]
+    with Scaler(sw, sh, sf, dw, dh, df, alg) as sc:
+        frames = [F.random_frame(sf, sw, sh, 4100 + i) for i in range(n)]
+        d_src = torch.from_numpy(sc.src_layout.pack(frames)).cuda()
+        out = torch.zeros((n, sc.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+        st = ctypes.c_void_p(torch.cuda.current_stream().cuda_stream)
+        sp, ss, sfs = sc.src_layout.pointer_args(d_src.data_ptr())
+        dp, ds, dfs = sc.dst_layout.pointer_args(out.data_ptr())
+        # load the two-pass kernels' code first (lazy module loading), through the allocating entry point
+        assert lib.tvs_set_path(sc._ctx, 1) == 0
+        assert lib.tvs_scale_batch(sc._ctx, sp, ss, sfs, dp, ds, dfs, n, st) == sc.dst_h, tv_lib.last_error()
+        torch.cuda.synchronize()
+        free_before, _ = torch.cuda.mem_get_info()
+        assert lib.tvs_scale_batch_static(sc._ctx, sp, ss, sfs, dp, ds, dfs, n, st) == sc.dst_h, tv_lib.last_error()
+        torch.cuda.synchronize()
+        free_after, _ = torch.cuda.mem_get_info()
+        assert free_after == free_before, f"free device memory changed by {free_before - free_after} bytes across the call"

@@ -1025,7 +1025,9 @@ int TVS_FUSED_FN(fused_launch)(const FusedPlan *p, const Plan &plan, const Sampl
         lp.total_tiles = tiles * n_frames;
         lp.m_floats = lay.m_floats; lp.s_floats = lay.s_floats; lp.raw_words = lay.raw_words;
         lp.cv_pairs = lay.cv_pairs; lp.vp_ints = lay.vp_ints;
+#ifdef TVS_PROFILING   // phase-skipping switch for profiling builds only: a production library never reads it
         if (const char *dbg = getenv("TVS_DEBUG_SKIP")) lp.debug_skip = atoi(dbg);
+#endif
         const size_t smem = layout_bytes(lay, kInstances[p->ops[i].instance].span);
         // persistent CTAs: two per SM, each walking a contiguous share of the tiles
         const int grid = std::min(lp.total_tiles, kCtasPerSM * p->sm_count);

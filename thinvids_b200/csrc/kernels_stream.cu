@@ -472,7 +472,11 @@ const StreamInstance kStreamInstances[] = {
 #undef TVS_SRAW
 
 // test / profiling aid: TVS_STREAM_FLOAT=1 keeps the float horizontal pass even where the raw-byte one applies
+#ifdef TVS_PROFILING
 const bool g_stream_force_float = [] { const char *e = getenv("TVS_STREAM_FLOAT"); return e && e[0] == '1'; }();
+#else
+constexpr bool g_stream_force_float = false;   // production builds read no environment switches
+#endif
 
 template <typename T>
 size_t append_blob(std::vector<uint8_t> &blob, const std::vector<T> &v) {

@@ -86,9 +86,11 @@ struct tvs_ctx {
     uint8_t *rgb_planes = nullptr;
     size_t rgb_capacity = 0;
     // host-buffer path
-    cudaStream_t copy_streams[2] = {nullptr, nullptr};
-    uint8_t *stage_src[2] = {nullptr, nullptr};
-    uint8_t *stage_dst[2] = {nullptr, nullptr};
+    static constexpr int kSlots = 3;                            // staging buffers in flight (copy in / scale / copy out)
+    cudaStream_t copy_streams[3] = {nullptr, nullptr, nullptr};   // host-to-device, kernels, device-to-host
+    cudaEvent_t stage_events[kSlots][3] = {};                     // per slot: source landed, kernels done, result copied out
+    uint8_t *stage_src[kSlots] = {nullptr, nullptr, nullptr};
+    uint8_t *stage_dst[kSlots] = {nullptr, nullptr, nullptr};
     size_t stage_src_bytes = 0, stage_dst_bytes = 0;
     long long launches = 0;
 };
@@ -454,6 +456,21 @@ int tvs_filter_table(int src_len, int dst_len, int alg, int one, int src_pos, in
     return t.taps;
 }
 
+void *tvs_host_alloc(size_t bytes) {
+    void *p = nullptr;
+    const cudaError_t e = cudaHostAlloc(&p, bytes ? bytes : 1, cudaHostAllocPortable);
+    if (e != cudaSuccess) {
+        cuda_fail(e, "cudaHostAlloc");
+        cudaGetLastError();
+        return nullptr;
+    }
+    return p;
+}
+
+void tvs_host_free(void *p) {
+    if (p) cudaFreeHost(p);
+}
+
 tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt, int flags,
                     const int chr_pos[4]) {
     FormatInfo sfi, dfi;
@@ -494,6 +511,14 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     if ((e = cudaSetDevice(device)) != cudaSuccess) {
         cuda_fail(e, "cudaSetDevice");
         return nullptr;
+    }
+
+    {
+        // Resolve the fixed scratch array of tvs_scale_batch_static on this device now.  With lazy module loading this
+        // is what brings the array's module (and its TVS_STATIC_SCRATCH_BYTES) onto the device, so it happens here,
+        // where allocation is expected, and never inside a scale call.  A failure is not fatal for the other entry points.
+        int16_t *unused = nullptr;
+        if (static_mid_for_device(device, &unused) != 0) cudaGetLastError();
     }
 
     tvs_ctx *c = new tvs_ctx;
@@ -569,11 +594,14 @@ void tvs_destroy(tvs_ctx *c) {
     if (c->dev_table_blob) cudaFree(c->dev_table_blob);
     if (c->mid) cudaFree(c->mid);
     if (c->rgb_planes) cudaFree(c->rgb_planes);
-    for (int i = 0; i < 2; ++i) {
+    for (int i = 0; i < tvs_ctx::kSlots; ++i) {
         if (c->stage_src[i]) cudaFree(c->stage_src[i]);
         if (c->stage_dst[i]) cudaFree(c->stage_dst[i]);
-        if (c->copy_streams[i]) cudaStreamDestroy(c->copy_streams[i]);
+        for (int k = 0; k < 3; ++k)
+            if (c->stage_events[i][k]) cudaEventDestroy(c->stage_events[i][k]);
     }
+    for (int i = 0; i < 3; ++i)
+        if (c->copy_streams[i]) cudaStreamDestroy(c->copy_streams[i]);
     delete c;
 }
 
@@ -611,26 +639,33 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     };
     const size_t sframe = tight_frame_bytes(c->sfi, c->src_w, c->src_h);
     const size_t dframe = tight_frame_bytes(c->dfi, c->dst_w, c->dst_h);
-    // Keep each chunk around 48 MiB so copies of one chunk overlap kernels of the other.
+    // Three stages - host-to-device copy, kernels, device-to-host copy - each on its own stream, chunks of about
+    // 48 MiB walking through kSlots staging buffers: while chunk i is scaled, chunk i+1 is coming in and chunk i-1
+    // is going out, so both copy engines and the SMs are busy at once.
     size_t chunk = (static_cast<size_t>(48) << 20) / (sframe + dframe);
     if (chunk < 1) chunk = 1;
     if (chunk > static_cast<size_t>(n_frames)) chunk = n_frames;
+    if (chunk > 65535) chunk = 65535;   // the kernels index frames through a 16-bit grid dimension
     if (c->stage_src_bytes < chunk * sframe || c->stage_dst_bytes < chunk * dframe) {
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < tvs_ctx::kSlots; ++i) {
             if (c->stage_src[i]) cudaFree(c->stage_src[i]);
             if (c->stage_dst[i]) cudaFree(c->stage_dst[i]);
             c->stage_src[i] = c->stage_dst[i] = nullptr;
         }
         c->stage_src_bytes = c->stage_dst_bytes = 0;
-        for (int i = 0; i < 2; ++i) {
+        for (int i = 0; i < tvs_ctx::kSlots; ++i) {
             TVS_CUDA(cudaMalloc(&c->stage_src[i], chunk * sframe), "cudaMalloc(src staging)");
             TVS_CUDA(cudaMalloc(&c->stage_dst[i], chunk * dframe), "cudaMalloc(dst staging)");
         }
         c->stage_src_bytes = chunk * sframe;
         c->stage_dst_bytes = chunk * dframe;
     }
-    for (int i = 0; i < 2; ++i)
+    for (int i = 0; i < 3; ++i)
         if (!c->copy_streams[i]) TVS_CUDA(cudaStreamCreateWithFlags(&c->copy_streams[i], cudaStreamNonBlocking), "cudaStreamCreate");
+    for (int i = 0; i < tvs_ctx::kSlots; ++i)
+        for (int k = 0; k < 3; ++k)
+            if (!c->stage_events[i][k]) TVS_CUDA(cudaEventCreateWithFlags(&c->stage_events[i][k], cudaEventDisableTiming), "cudaEventCreate");
+    cudaStream_t st_in = c->copy_streams[0], st_exec = c->copy_streams[1], st_out = c->copy_streams[2];
 
     // Device-side plane table of a staged chunk.
     ptrdiff_t s_pitch[3] = {0, 0, 0}, s_fs[3], d_pitch[3] = {0, 0, 0}, d_fs[3];
@@ -662,41 +697,57 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const bool src_packed = packed(src, src_pitch, src_frame_stride, c->sfi, s_off, s_pitch, sframe);
     const bool dst_packed = packed(reinterpret_cast<const void *const *>(dst), dst_pitch, dst_frame_stride, c->dfi, d_off, d_pitch, dframe);
 
-    // The two-pass path owns ONE intermediate buffer, so its chunks must not overlap on the device.
-    const bool single_stream = c->plan.any_scale && !use_fused_path(c) && !use_stream_path(c) && !(c->box2 && c->forced_path < 0);
-    int slot = 0;
-    for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk), slot = single_stream ? 0 : slot ^ 1) {
-        const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
-        cudaStream_t st = c->copy_streams[slot];
-        // The slot's previous chunk (two iterations ago) is ordered before us by the stream itself.
+    // One chunk: its copies and kernels, ordered against its neighbours through the slot's three events
+    // (0: source landed, 1: kernels done, 2: result copied out).
+    auto enqueue_chunk = [&](int index, int f0, int nf) -> int {
+        const int slot = index % tvs_ctx::kSlots;
+        cudaEvent_t ev_in = c->stage_events[slot][0], ev_exec = c->stage_events[slot][1], ev_out = c->stage_events[slot][2];
+        const bool reused = index >= tvs_ctx::kSlots;
+        if (reused) TVS_CUDA(cudaStreamWaitEvent(st_in, ev_exec, 0), "stream wait");   // the slot's source buffer has been consumed
         if (src_packed) {
             TVS_CUDA(cudaMemcpyAsync(c->stage_src[slot], static_cast<const uint8_t *>(src[0]) + static_cast<size_t>(f0) * sframe,
-                                     static_cast<size_t>(nf) * sframe, cudaMemcpyHostToDevice, st), "H2D copy");
+                                     static_cast<size_t>(nf) * sframe, cudaMemcpyHostToDevice, st_in), "H2D copy");
         } else {
             for (int f = 0; f < nf; ++f)
                 for (int i = 0; i < c->sfi.planes; ++i)
                     TVS_CUDA(cudaMemcpy2DAsync(c->stage_src[slot] + f * sframe + s_off[i], s_pitch[i],
                                                static_cast<const uint8_t *>(src[i]) + static_cast<ptrdiff_t>(f0 + f) * src_frame_stride[i],
-                                               src_pitch[i], s_pitch[i], plane_rows(i, c->src_h, ch_s), cudaMemcpyHostToDevice, st),
+                                               src_pitch[i], s_pitch[i], plane_rows(i, c->src_h, ch_s), cudaMemcpyHostToDevice, st_in),
                              "H2D plane copy");
         }
+        TVS_CUDA(cudaEventRecord(ev_in, st_in), "event record");
+        TVS_CUDA(cudaStreamWaitEvent(st_exec, ev_in, 0), "stream wait");
+        if (reused) TVS_CUDA(cudaStreamWaitEvent(st_exec, ev_out, 0), "stream wait");  // the slot's result buffer has been drained
         const void *sp[3] = {c->stage_src[slot] + s_off[0], c->stage_src[slot] + s_off[1], c->stage_src[slot] + s_off[2]};
         void *dp[3] = {c->stage_dst[slot] + d_off[0], c->stage_dst[slot] + d_off[1], c->stage_dst[slot] + d_off[2]};
-        if (int rc = enqueue_batch(c, sp, s_pitch, s_fs, dp, d_pitch, d_fs, nf, st)) return rc;
+        if (int rc = enqueue_batch(c, sp, s_pitch, s_fs, dp, d_pitch, d_fs, nf, st_exec)) return rc;
+        TVS_CUDA(cudaEventRecord(ev_exec, st_exec), "event record");
+        TVS_CUDA(cudaStreamWaitEvent(st_out, ev_exec, 0), "stream wait");
         if (dst_packed) {
             TVS_CUDA(cudaMemcpyAsync(static_cast<uint8_t *>(dst[0]) + static_cast<size_t>(f0) * dframe, c->stage_dst[slot],
-                                     static_cast<size_t>(nf) * dframe, cudaMemcpyDeviceToHost, st), "D2H copy");
+                                     static_cast<size_t>(nf) * dframe, cudaMemcpyDeviceToHost, st_out), "D2H copy");
         } else {
             for (int f = 0; f < nf; ++f)
                 for (int i = 0; i < c->dfi.planes; ++i)
                     TVS_CUDA(cudaMemcpy2DAsync(static_cast<uint8_t *>(dst[i]) + static_cast<ptrdiff_t>(f0 + f) * dst_frame_stride[i], dst_pitch[i],
                                                c->stage_dst[slot] + f * dframe + d_off[i], d_pitch[i], d_pitch[i],
-                                               plane_rows(i, c->dst_h, ch_d), cudaMemcpyDeviceToHost, st),
+                                               plane_rows(i, c->dst_h, ch_d), cudaMemcpyDeviceToHost, st_out),
                              "D2H plane copy");
         }
+        TVS_CUDA(cudaEventRecord(ev_out, st_out), "event record");
+        return 0;
+    };
+    int rc = 0, index = 0;
+    for (int f0 = 0; f0 < n_frames && rc == 0; f0 += static_cast<int>(chunk), ++index)
+        rc = enqueue_chunk(index, f0, std::min<int>(static_cast<int>(chunk), n_frames - f0));
+    // Whatever happened, nothing may still be writing the caller's buffers when we return.
+    const std::string first_error = rc ? g_last_error : std::string();
+    for (int i = 0; i < 3; ++i) {
+        const cudaError_t e = cudaStreamSynchronize(c->copy_streams[i]);
+        if (e != cudaSuccess && rc == 0) rc = cuda_fail(e, "stream sync");
     }
-    TVS_CUDA(cudaStreamSynchronize(c->copy_streams[0]), "stream sync");
-    TVS_CUDA(cudaStreamSynchronize(c->copy_streams[1]), "stream sync");
+    if (!first_error.empty()) g_last_error = first_error;
+    if (rc) return rc;
     return c->dst_h;
 }
 
@@ -720,7 +771,7 @@ long long tvs_info(const tvs_ctx *c, int what) {
         if (c->box2 && c->forced_path < 0) return 4;
         return use_stream_path(c) ? 3 : use_fused_path(c) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
-        return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + 2 * (c->stage_src_bytes + c->stage_dst_bytes));
+        return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + tvs_ctx::kSlots * (c->stage_src_bytes + c->stage_dst_bytes));
     case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
     case TVS_INFO_DST_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->dfi, c->dst_w, c->dst_h));
     default: return fail(-EINVAL, "unknown info key %d", what);
