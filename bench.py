@@ -187,7 +187,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=("ours", "reference"))
     ap.add_argument("--frames", type=int, default=0, help="frames per segment (default: the config's batch)")
     ap.add_argument("--segments", type=int, default=0, help="segments per step (default: 1 per GPU; C5: 64 in total)")
-    ap.add_argument("--path", default="auto", choices=("auto", "fused", "two-pass", "stream"))
+    ap.add_argument("--path", default="auto", choices=("auto", "fused", "two-pass", "stream", "slab"))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     args = ap.parse_args()

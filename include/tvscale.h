@@ -183,7 +183,7 @@ enum { TVS_INFO_KERNEL_LAUNCHES = 0, TVS_INFO_PATH = 1, TVS_INFO_SCRATCH_BYTES =
        TVS_INFO_SRC_FRAME_BYTES = 3, TVS_INFO_DST_FRAME_BYTES = 4 };
 TVS_API long long tvs_info(const tvs_ctx *ctx, int what);
 
-/* Force a kernel path for testing: -1 = automatic, 0 = fused tiles, 1 = two-pass, 2 = streaming.
+/* Force a kernel path for testing: -1 = automatic, 0 = fused tiles, 1 = two-pass, 2 = streaming, 3 = slab.
  * Returns 0, -EINVAL, or -ENOSYS when the requested kernel does not handle this context's shape. */
 TVS_API int tvs_set_path(tvs_ctx *ctx, int path);
 

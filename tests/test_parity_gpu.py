@@ -15,7 +15,7 @@ pytestmark = pytest.mark.gpu
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
 HASHES = json.load(open(os.path.join(GOLD, "swscale_hashes.json")))["cases"]
 SMALL = json.load(open(os.path.join(GOLD, "small_cases.json")))
-PATHS = ("auto", "two-pass", "fused", "stream")
+PATHS = ("auto", "two-pass", "fused", "stream", "slab")
 
 
 def _scaler(c, **kw):
@@ -31,7 +31,7 @@ def _use_path(s, path):
     try:
         s.set_path(path)
     except tv_lib.TvscaleError:
-        if path in ("fused", "stream"):
+        if path in ("fused", "stream", "slab"):
             return False
         raise
     return True
@@ -74,9 +74,12 @@ def test_small_golden_outputs(path):
 
 
 def test_random_shapes_against_oracle():
-    """Seeded random sizes/formats/algorithms, oracle port as the checker (it finishes these in milliseconds)."""
-    from oracle import port
+    """Seeded random sizes/formats/algorithms.  The checker is the genuine libswscale when its binaries travelled with
+    the tree (oracle/_ref), else the oracle port that tests/test_oracle.py pins to it."""
+    from oracle import port, ref_swscale
+    from thinvids_b200 import lib as tv_lib
     from thinvids_b200.swscale import Scaler
+    make_checker = ref_swscale.RefScaler if ref_swscale.available() else port.PortScaler
     rnd = random.Random(2026)
     algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
     for i in range(120):
@@ -87,7 +90,12 @@ def test_random_shapes_against_oracle():
         alg = rnd.choice(algs)
         src = F.random_frame(sf, sw, sh, 1000 + i)
         want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
-        port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale_into(src, want)
+        make_checker(sw, sh, sf, dw, dh, df, alg).scale_into(src, want)
+        try:
+            Scaler(sw, sh, sf, dw, dh, df, alg).close()
+        except tv_lib.TvscaleError as e:
+            assert "cascades" in str(e), e     # 171 taps or more: refused, never scaled differently from the library
+            continue
         for path in PATHS:
             got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
             with Scaler(sw, sh, sf, dw, dh, df, alg) as s:

@@ -1,0 +1,771 @@
+// Slab kernel: warp-specialised row streaming for planes that are not shrunk vertically (the up-scales of
+// BASELINE.json: 480p -> 1080p, 1080p -> 4K, and the worker's 480p -> 1080p NV12 target).
+//
+// A CTA is two warps that own one *slab* - 128 output columns of one plane of one frame - and walk it from its first
+// output row to its last:
+//
+//   warp 0 (producer)  cp.async the slab's raw source rows four at a time, three blocks ahead  -> RAW ring
+//                      bytes -> exact floats (one 32-bit word per lane)                          -> S (warp private)
+//                      horizontal pass, 4 adjacent output columns per lane, coefficients in
+//                      registers for the whole slab                                              -> M ring (16 rows)
+//   warp 1 (consumer)  vertical pass: a register ring of VT intermediate rows x 4 columns slides down the slab; each
+//                      new source row completes the output rows whose window ends there          -> HBM
+//
+// The two warps meet only through the M ring: one mbarrier pair (full / empty) per ring row, one arrival each.  Nothing
+// else synchronises - no CTA-wide barrier after start-up, no tile halo (every source row is filtered exactly once per
+// slab), no per-tile ring warm-up - and because each role needs only its own working set (horizontal coefficients OR
+// the vertical ring) the kernel fits in 64-80 registers: 28-32 warps per SM instead of the tile kernel's 16.  With about
+// 11 KB of shared memory per CTA, 14-16 CTAs share an SM and cover each other's latencies.
+//
+// Instruction budget (profiles/r02_issue_mix_raw.txt): on sm_100a a packed FFMA2 holds the issue port for 2.19 cycles
+// and does not overlap integer work, while scalar FFMA issues in 1.02 and lets IADD / LOP3 slip in beside it, so both
+// passes use scalar FFMA.  Arithmetic, exactness argument and output rules are those of DESIGN.md section 4 (the H sum is an
+// exact integer, floor by one FMA.RM onto the subnormal grid; the V sum carries a bounded error and samples whose
+// residual is within that bound of a rounding boundary are recomputed in int32 from the M ring).
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+
+#include "scale_device.cuh"
+#include "tvs_internal.h"
+
+namespace tvs {
+namespace {
+
+constexpr int kSlabW = 128;        // output columns per slab: lane * 4 + k
+constexpr int kSlabThreads = 64;   // warp 0 produces intermediate rows, warp 1 consumes them
+constexpr int kRing = 16;          // rows of the shared-memory intermediate ring (power of two)
+constexpr int kBlockRows = 4;      // source rows staged and converted together
+constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the producer prefetches kRawBlocks - 1 blocks ahead
+constexpr int kMaxSlabOps = 3;
+#ifndef TVS_SLAB_MIN_CTAS
+#define TVS_SLAB_MIN_CTAS 12
+#endif
+constexpr int kSlabCtasPerSM = 16;
+
+struct SlabOpParams {
+    const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
+    uint8_t *dst; ptrdiff_t dst_pitch, dst_fstride; int dst_xstep;
+    int sw, sh, dw, dh;
+    int n_groups;          // groups of 4 output columns
+    int n_slabs;           // ceil(dw / 128)
+    int chunk_rows;        // output rows per work item
+    int n_chunks;          // ceil(dh / chunk_rows)
+    int item_begin;        // first item of this plane inside a frame's item list
+    const float *hdense;   // [n_groups][4][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
+    const int *hbase;      // [n_groups]           first source column of the group's span
+    const int *vpos;       // [dh + 1]             first source row of each output row (one padding entry)
+    const float *vring;    // [dh + 1][VT]         g * 2^107 indexed by ring slot = source_row % VT
+    const int *vring_i;    // [dh + 1][VT]         the same coefficients as integers (exact path)
+    const uint8_t *src_lo; // first byte of the stored source plane (frame 0) and its extent: bounds for 16-byte reads
+    size_t src_extent;
+    float v_thr, v_init;
+    float h_addend;        // subnormal offset of the H result: 16384 * 2^-149 when samples were centred on 512, else 0
+    int src_mode;          // kSrcU8 / kSrcU8Pair / kSrcU16 / kSrcU16Pair
+    int src_shift;         // P010: the 10 bits sit 6 places up in the word
+    int dst_shift, dither_xoff;
+};
+
+struct SlabLaunchParams {
+    SlabOpParams op[kMaxSlabOps];
+    int n_ops;
+    int items_per_frame, n_items;
+    int s_pitch;           // floats per converted source row (multiple of 4)
+    int raw_pitch;         // bytes per staged raw row (multiple of 16)
+};
+
+// ---- mbarrier helpers (one arrival per phase) -------------------------------------------------------------------
+__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
+}
+__device__ __forceinline__ void mbar_arrive(unsigned bar) {
+    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "SLAB_WAIT_%=:\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+        "@p bra SLAB_DONE_%=;\n"
+        "bra SLAB_WAIT_%=;\n"
+        "SLAB_DONE_%=:\n"
+        "}" ::"r"(bar), "r"(parity) : "memory");
+}
+template <int N>
+__device__ __forceinline__ void cp_async_wait_pending() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
+
+// One work item: output rows [ya, yb) of slab `slab` of plane `oi` of frame `f`; the producer filters source rows
+// [r_begin, r_end) for it (rows at or past the plane's height are zero rows the vertical window may touch).
+struct SlabItem { int oi, f, slab, ya, yb, r_begin, r_end; };
+
+__device__ __forceinline__ SlabItem decode_item(const SlabLaunchParams &P, int item, int vt) {
+    SlabItem it;
+    it.f = item / P.items_per_frame;
+    int rem = item - it.f * P.items_per_frame;
+    it.oi = 0;
+    if (P.n_ops > 1 && rem >= P.op[1].item_begin) it.oi = 1;
+    if (P.n_ops > 2 && rem >= P.op[2].item_begin) it.oi = 2;
+    const SlabOpParams &op = P.op[it.oi];
+    rem -= op.item_begin;
+    const int chunk = rem / op.n_slabs;            // slabs of one row chunk are consecutive items: neighbours in L2
+    it.slab = rem - chunk * op.n_slabs;
+    it.ya = chunk * op.chunk_rows;
+    it.yb = min(it.ya + op.chunk_rows, op.dh);
+    it.r_begin = __ldg(op.vpos + it.ya);
+    it.r_end = __ldg(op.vpos + it.yb - 1) + vt;
+    return it;
+}
+
+// ---- producer ------------------------------------------------------------------------------------------------------
+// Start the asynchronous copy of raw source rows [row0, row0 + kBlockRows) of the slab's footprint (rows counted from
+// the item's first source row).  Rows are read as aligned 16-byte chunks starting at the chunk that holds the row's
+// first sample, so byte i of a footprint row lands at position mis + i of the staged row, mis (0..15) being the
+// misalignment of the row's first byte; any pitch works.  A chunk that would reach outside the plane is fetched as
+// 4-byte words that each contain at least one needed byte; chunks and words past the end of the row are zeroed.
+__device__ __forceinline__ void slab_prefetch_block(const SlabOpParams &op, const uint8_t *foot, const uint8_t *lo, const uint8_t *hi,
+                                                    int row0, int rows_real, int last_byte, int s_chunks, unsigned char *raw_block,
+                                                    int raw_pitch, int lane) {
+    const ptrdiff_t pitch = op.src_pitch;
+    int clog = 0;
+    while ((1 << clog) < s_chunks) ++clog;
+    clog = min(clog, 5);
+    const int cmask = (1 << clog) - 1, rstep = 32 >> clog;
+    for (int ch = lane & cmask; ch < s_chunks; ch += 1 << clog) {
+        for (int rr = lane >> clog; rr < kBlockRows; rr += rstep) {
+            const int row = row0 + rr;
+            uint4 *dst = reinterpret_cast<uint4 *>(raw_block + rr * raw_pitch) + ch;
+            if (row >= rows_real) { *dst = make_uint4(0u, 0u, 0u, 0u); continue; }
+            const uint8_t *rowp = foot + static_cast<ptrdiff_t>(row) * pitch;
+            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rowp)) & 15u;
+            const int first = 16 * ch - static_cast<int>(mis);      // footprint-row offset of the chunk's first byte
+            const uint8_t *g = rowp + first;
+            if (first > last_byte) {
+                *dst = make_uint4(0u, 0u, 0u, 0u);
+            } else if (g >= lo && g + 16 <= hi) {
+                cp_async16(dst, g);
+            } else {
+#pragma unroll
+                for (int k = 0; k < 4; ++k) {
+                    unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+                    if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
+                    else *d = 0u;
+                }
+            }
+        }
+    }
+}
+
+// Raw words of one staged row -> exact float samples.  Sample j of the footprint sits at float index
+// (mis >> log2(bytes per sample step)) + j of the converted row, so the conversion itself is alignment-blind.
+__device__ __forceinline__ void slab_convert_row(const unsigned *raw_row, float *s_row, int words, int src_mode, int src_shift,
+                                                 unsigned mis, int lane) {
+    if (src_mode == kSrcU8) {                       // 4 samples per word
+        for (int w = lane; w < words; w += 32) {
+            const unsigned v = raw_row[w];
+            *reinterpret_cast<float4 *>(s_row + 4 * w) = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
+                                                                     byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+        }
+    } else if (src_mode == kSrcU8Pair) {            // interleaved 8-bit chroma: this plane is every other byte
+        const unsigned p = mis & 1u;
+        for (int w = lane; w < words; w += 32) {
+            const unsigned v = raw_row[w];
+            *reinterpret_cast<float2 *>(s_row + 2 * w) = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
+        }
+    } else if (src_mode == kSrcU16) {               // two 16-bit samples per word, centred on 512
+        const unsigned keep = 0xffffu >> src_shift;
+        for (int w = lane; w < words; w += 32) {
+            const unsigned v = (raw_row[w] >> src_shift) & (keep | (keep << 16));   // P010: integer shift first, as libswscale does
+            *reinterpret_cast<float2 *>(s_row + 2 * w) = make_float2(byte_to_float(v, 0x7410u) - 512.0f, byte_to_float(v, 0x7432u) - 512.0f);
+        }
+    } else {                                        // interleaved 16-bit chroma: one sample of this plane per word
+        const unsigned sel = (mis & 2u) ? 0x7432u : 0x7410u;
+        const unsigned keep = 0xffffu >> src_shift;
+        for (int w = lane; w < words; w += 32) {
+            const unsigned v = (raw_row[w] >> src_shift) & (keep | (keep << 16));
+            s_row[w] = byte_to_float(v, sel) - 512.0f;
+        }
+    }
+}
+
+template <int SPAN>
+__device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const SlabItem &it, float *M, float *S, unsigned char *RAW,
+                                             unsigned bar_full, unsigned bar_empty, unsigned k_base, int lane) {
+    const SlabOpParams &op = P.op[it.oi];
+    // this lane's 4 output columns: dense coefficients over their common source span, for the life of the slab
+    const int g_first = it.slab * (kSlabW / 4);
+    const int g = min(g_first + lane, op.n_groups - 1);
+    float cd[4][SPAN];
+    {
+        const float4 *src = reinterpret_cast<const float4 *>(op.hdense + static_cast<size_t>(g) * (4 * SPAN));
+        float *flat = &cd[0][0];
+#pragma unroll
+        for (int i = 0; i < SPAN; ++i) {
+            const float4 v = __ldg(src + i);
+            flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
+        }
+    }
+    const int c0 = __ldg(op.hbase + g_first);
+    const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
+    const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
+    const int hb = __ldg(op.hbase + g) - c0;
+    const int xs = op.src_xstep;
+    const int sample_bytes = op.src_mode >= kSrcU16 ? 2 : 1;
+    const int mshift = op.src_mode == kSrcU8 ? 0 : op.src_mode == kSrcU16Pair ? 2 : 1;
+    const int last_byte = (ncols - 1) * xs + sample_bytes - 1;
+    // every staged row carries the launch's chunk count (chunks past a row's last needed byte are zeroed), so the
+    // converted rows are defined up to the same length whatever the plane
+    const int s_chunks = P.raw_pitch >> 4;
+    const int words = 4 * s_chunks;
+    const uint8_t *lo = op.src_lo + it.f * op.src_fstride, *hi = lo + op.src_extent;
+    // first byte of the footprint of the item's first source row
+    const uint8_t *foot = op.src + it.f * op.src_fstride + static_cast<ptrdiff_t>(it.r_begin) * op.src_pitch + static_cast<ptrdiff_t>(c0) * xs;
+    const int rows_total = it.r_end - it.r_begin;                       // rows the consumer will read
+    const int rows_real = min(it.r_end, op.sh) - it.r_begin;            // of which these exist in the source
+    const int n_blocks = (rows_total + kBlockRows - 1) / kBlockRows;
+    const int s_pitch = P.s_pitch, raw_pitch = P.raw_pitch;
+    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(foot)) & 15u;
+    const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 15u;
+    const float h_addend = op.h_addend;
+    const float t_max = __int_as_float(32767);
+    const int src_mode = op.src_mode, src_shift = op.src_shift;
+    float *m_lane = M + 4 * lane;
+
+    // prologue: the first kRawBlocks - 1 blocks are on their way before anything is converted
+#pragma unroll
+    for (int b = 0; b < kRawBlocks - 1; ++b) {
+        if (b < n_blocks)
+            slab_prefetch_block(op, foot, lo, hi, b * kBlockRows, rows_real, last_byte, s_chunks,
+                                RAW + (b % kRawBlocks) * kBlockRows * raw_pitch, raw_pitch, lane);
+        cp_async_commit();
+    }
+    unsigned k = k_base;
+    for (int b = 0; b < n_blocks; ++b) {
+        cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
+        __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
+        const unsigned char *raw_block = RAW + (b % kRawBlocks) * kBlockRows * raw_pitch;
+        const int row0 = b * kBlockRows;
+#pragma unroll
+        for (int rr = 0; rr < kBlockRows; ++rr) {
+            if (row0 + rr < rows_real)
+                slab_convert_row(reinterpret_cast<const unsigned *>(raw_block + rr * raw_pitch), S + rr * s_pitch, words, src_mode,
+                                 src_shift, (mis0 + (row0 + rr) * pmod) & 15u, lane);
+        }
+        __syncwarp();                              // S is complete; the raw block is free again
+        if (b + kRawBlocks - 1 < n_blocks)
+            slab_prefetch_block(op, foot, lo, hi, (b + kRawBlocks - 1) * kBlockRows, rows_real, last_byte, s_chunks,
+                                RAW + ((b + kRawBlocks - 1) % kRawBlocks) * kBlockRows * raw_pitch, raw_pitch, lane);
+        cp_async_commit();
+
+        // horizontal pass of the block's rows; the next row's window is loaded before the current row is filtered
+        const int rows_here = min(kBlockRows, rows_total - row0);
+        float px[SPAN], pn[SPAN];
+        {
+            const float *sp = S + hb + (((mis0 + row0 * pmod) & 15u) >> mshift);
+#pragma unroll
+            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+        }
+#pragma unroll
+        for (int rr = 0; rr < kBlockRows; ++rr) {
+            if (rr < rows_here) {
+                if (rr + 1 < kBlockRows) {
+                    const float *sp = S + (rr + 1) * s_pitch + hb + (((mis0 + (row0 + rr + 1) * pmod) & 15u) >> mshift);
+#pragma unroll
+                    for (int i = 0; i < SPAN; ++i) pn[i] = sp[i];
+                }
+                float4 o;
+                if (row0 + rr < rows_real) {
+                    float acc[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) acc[c] = px[0] * cd[c][0];
+#pragma unroll
+                    for (int i = 1; i < SPAN; ++i) {
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) acc[c] = fmaf(px[i], cd[c][i], acc[c]);
+                    }
+                    // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
+                    o = make_float4(fminf(fma_rm(acc[0], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[1], 0x1p-126f, h_addend), t_max),
+                                    fminf(fma_rm(acc[2], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[3], 0x1p-126f, h_addend), t_max));
+                } else {
+                    o = make_float4(0.f, 0.f, 0.f, 0.f);   // a row below the plane: zero weight in every window that reaches it
+                }
+                const unsigned slot = k & (kRing - 1);
+                // the slot's previous row (kRing rows ago) must have been released by the consumer
+                if (k >= kRing) mbar_wait(bar_empty + 8 * slot, ((k / kRing) - 1) & 1);
+                *reinterpret_cast<float4 *>(m_lane + slot * kSlabW) = o;
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_full + 8 * slot);
+                ++k;
+#pragma unroll
+                for (int i = 0; i < SPAN; ++i) px[i] = pn[i];
+            }
+        }
+    }
+    cp_async_wait_pending<0>();
+}
+
+// ---- consumer ------------------------------------------------------------------------------------------------------
+// Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: rare
+// (about one warp-row in a hundred), so it re-reads its VT intermediate rows from the shared-memory ring, which the
+// consumer releases only once no pending output row starts at or above them.
+template <int VT, int OUT>
+__device__ __noinline__ uint2 slab_fixup(const float *m_lane, unsigned k_first, int first, const int *exact_coef, float v_thr,
+                                         float r0, float r1, float r2, float r3, int4 dither, int dst_shift, uint2 packed) {
+    unsigned word[2] = {packed.x, packed.y};
+    const float r[4] = {r0, r1, r2, r3};
+    const int d[4] = {dither.x, dither.y, dither.z, dither.w};
+    int slot = first % VT;
+    int a[4] = {0, 0, 0, 0};
+    for (int j = 0; j < VT; ++j) {
+        const float4 t = *reinterpret_cast<const float4 *>(m_lane + ((k_first + j) & (kRing - 1)) * kSlabW);
+        const int c = __ldg(exact_coef + slot);
+        a[0] += subnormal_to_int(t.x) * c; a[1] += subnormal_to_int(t.y) * c;
+        a[2] += subnormal_to_int(t.z) * c; a[3] += subnormal_to_int(t.w) * c;
+        slot = slot + 1 == VT ? 0 : slot + 1;
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        if (fabsf(r[k]) >= v_thr) {
+            const int bias = OUT == kOutU8 ? (64 << 12) : OUT == kOutU8Dither ? (d[k] << 12) : (1 << 16);
+            const unsigned v = static_cast<unsigned>(min(max((a[k] + bias) >> OutRule<OUT>::kShift, 0), OutRule<OUT>::kMax));
+            if (OUT == kOutU10) {
+                const int sh = 16 * (k & 1);
+                word[k >> 1] = (word[k >> 1] & ~(0xffffu << sh)) | ((v << dst_shift) << sh);
+            } else {
+                word[0] = (word[0] & ~(0xffu << (8 * k))) | (v << (8 * k));
+            }
+        }
+    }
+    return make_uint2(word[0], word[1]);
+}
+
+// Quotient, residual and packing of one quad of float sums (scalar form of finish_quad).
+template <int OUT>
+__device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift, unsigned (&word)[2], float (&r)[4]) {
+    constexpr float kQ = OutRule<OUT>::kShift == 19 ? 0x1p-126f : 0x1p-124f;
+    constexpr float kBack = OutRule<OUT>::kShift == 19 ? -0x1p126f : -0x1p124f;
+    float q[4];
+#pragma unroll
+    for (int c = 0; c < 4; ++c) q[c] = a[c] * kQ;                    // round(acc / 2^shift) as a subnormal bit pattern
+#pragma unroll
+    for (int c = 0; c < 4; ++c) r[c] = fmaf(q[c], kBack, a[c]);     // exact residual
+    if (OUT == kOutU10) {
+        const float top = __int_as_float(1023);
+        const unsigned b0 = __float_as_uint(fminf(fmaxf(q[0], 0.f), top)) << dst_shift;
+        const unsigned b1 = __float_as_uint(fminf(fmaxf(q[1], 0.f), top)) << dst_shift;
+        const unsigned b2 = __float_as_uint(fminf(fmaxf(q[2], 0.f), top)) << dst_shift;
+        const unsigned b3 = __float_as_uint(fminf(fmaxf(q[3], 0.f), top)) << dst_shift;
+        word[0] = __byte_perm(b0, b1, 0x5410);
+        word[1] = __byte_perm(b2, b3, 0x5410);
+    } else {
+        word[0] = pack_sat_u8(__float_as_int(q[3]), __float_as_int(q[2]), 0u);
+        word[0] = pack_sat_u8(__float_as_int(q[1]), __float_as_int(q[0]), word[0]);
+        word[1] = 0;
+    }
+    return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
+}
+
+// FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
+// vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
+template <int VT, int OUT, bool FAST>
+__device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const SlabItem &it, const float *M, unsigned bar_full,
+                                             unsigned bar_empty, unsigned k_base, int lane) {
+    const SlabOpParams &op = P.op[it.oi];
+    const float *m_lane = M + 4 * lane;
+    const int x = it.slab * kSlabW + 4 * lane;
+    const int dw = op.dw, dst_xstep = op.dst_xstep, dst_shift = op.dst_shift;
+    const ptrdiff_t dst_pitch = op.dst_pitch;
+    uint8_t *drow = op.dst + it.f * op.dst_fstride + static_cast<ptrdiff_t>(it.ya) * dst_pitch;
+    uint8_t *dlane = drow + static_cast<ptrdiff_t>(x) * (OUT == kOutU10 ? 2 : 1);
+    const float v_thr = op.v_thr, v_init = op.v_init;
+    const int dcol = (x + op.dither_xoff) & 7;
+    const float *cv = op.vring + static_cast<size_t>(it.ya) * VT;
+    const int *vp = op.vpos + it.ya;
+    const int *exact = op.vring_i + static_cast<size_t>(it.ya) * VT;
+    const int r_begin = it.r_begin;
+
+    float w[VT][4];
+#pragma unroll
+    for (int s = 0; s < VT; ++s) w[s][0] = w[s][1] = w[s][2] = w[s][3] = 0.f;
+    float g[VT];
+#pragma unroll
+    for (int s = 0; s < VT; ++s) g[s] = __ldg(cv + s);
+    int first = r_begin;            // first source row of the output row being waited for
+    int next_row = r_begin;         // next source row to pull from the ring
+    unsigned k = k_base;            // its ring position
+    int y = it.ya;
+    const int yb = it.yb;
+    int slot = r_begin % VT;
+
+    // every output row whose last source row is now in the register ring; true once the item is finished
+    auto emit_ready = [&]() -> bool {
+        while (first + VT <= next_row) {
+            float a[4];
+            int4 dither = make_int4(0, 0, 0, 0);
+            if (OUT == kOutU8Dither) {
+                const int *tab = kDither128i[y & 7];
+                dither = make_int4(tab[dcol], tab[(dcol + 1) & 7], tab[(dcol + 2) & 7], tab[(dcol + 3) & 7]);
+                // (d - 64) * 4096 * 2^-42: the rounding quotient already adds 64 << 12
+                a[0] = fmaf(static_cast<float>(dither.x - 64), 0x1p-30f, v_init); a[1] = fmaf(static_cast<float>(dither.y - 64), 0x1p-30f, v_init);
+                a[2] = fmaf(static_cast<float>(dither.z - 64), 0x1p-30f, v_init); a[3] = fmaf(static_cast<float>(dither.w - 64), 0x1p-30f, v_init);
+            } else {
+                a[0] = a[1] = a[2] = a[3] = v_init;
+            }
+#pragma unroll
+            for (int s = 0; s < VT; ++s) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) a[c] = fmaf(w[s][c], g[s], a[c]);
+            }
+            // the next row's coefficients and start row (both tables carry a padding row)
+            cv += VT; ++vp;
+#pragma unroll
+            for (int s = 0; s < VT; ++s) g[s] = __ldg(cv + s);
+            const int first_next = __ldg(vp);
+
+            unsigned word[2];
+            float r[4];
+            const float worst = slab_finish<OUT>(a, dst_shift, word, r);
+            if (worst >= v_thr) {
+                const uint2 fx = slab_fixup<VT, OUT>(m_lane, k_base + static_cast<unsigned>(first - r_begin), first, exact + (y - it.ya) * VT,
+                                                     v_thr, r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
+                word[0] = fx.x; word[1] = fx.y;
+            }
+            if (FAST) {
+                store_quad_fast<OUT>(dlane, 0, word);
+                dlane += dst_pitch;
+            } else {
+                store_quad_slow<OUT>(drow, x, dw, dst_xstep, word);
+                drow += dst_pitch;
+            }
+            ++y;
+            if (y >= yb) return true;
+            if (first_next != first) {
+                // no pending output row starts at `first` any more: hand its ring row back to the producer
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_empty + 8 * ((k_base + static_cast<unsigned>(first - r_begin)) & (kRing - 1)));
+                first = first_next;
+            }
+        }
+        return false;
+    };
+
+#define TVS_SLAB_STEP(s)                                                                            \
+    case s:                                                                                         \
+        if constexpr (s < VT) {                                                                     \
+            mbar_wait(bar_full + 8 * (k & (kRing - 1)), (k / kRing) & 1);                           \
+            const float4 v = *reinterpret_cast<const float4 *>(m_lane + (k & (kRing - 1)) * kSlabW); \
+            w[s][0] = v.x; w[s][1] = v.y; w[s][2] = v.z; w[s][3] = v.w;                             \
+            ++k; ++next_row;                                                                        \
+            if (emit_ready()) break;                                                                \
+        }
+    bool done = false;
+    while (!done) {
+        switch (slot) {
+            TVS_SLAB_STEP(0) TVS_SLAB_STEP(1) TVS_SLAB_STEP(2) TVS_SLAB_STEP(3)
+            TVS_SLAB_STEP(4) TVS_SLAB_STEP(5) TVS_SLAB_STEP(6) TVS_SLAB_STEP(7)
+            slot = 0;
+            continue;
+        }
+        done = true;
+    }
+#undef TVS_SLAB_STEP
+    // hand back the rows the last output rows were still holding
+    __syncwarp();
+    if (lane == 0) {
+        for (int r = first; r < it.r_end; ++r) mbar_arrive(bar_empty + 8 * ((k_base + static_cast<unsigned>(r - r_begin)) & (kRing - 1)));
+    }
+}
+
+template <int SPAN, int VT, int OUT>
+__global__ void __launch_bounds__(kSlabThreads, TVS_SLAB_MIN_CTAS)
+slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
+    extern __shared__ __align__(16) float smem[];
+    float *M = smem;                                                       // [kRing][128] intermediate t * 2^-149
+    float *S = M + kRing * kSlabW;                                         // [kBlockRows][s_pitch] source samples as floats
+    unsigned char *RAW = reinterpret_cast<unsigned char *>(S + kBlockRows * P.s_pitch);   // [kRawBlocks][kBlockRows][raw_pitch]
+    unsigned long long *BAR = reinterpret_cast<unsigned long long *>(RAW + kRawBlocks * kBlockRows * P.raw_pitch);   // full[kRing], empty[kRing]
+    const unsigned bar_full = static_cast<unsigned>(__cvta_generic_to_shared(BAR));
+    const unsigned bar_empty = bar_full + 8 * kRing;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    if (threadIdx.x == 0) {
+        for (int i = 0; i < 2 * kRing; ++i) mbar_init(bar_full + 8 * i, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    // converted rows are read a little past their last written sample (dense windows of the slab's last columns):
+    // those floats must be finite, and nothing writes them later
+    for (int i = threadIdx.x; i < kBlockRows * P.s_pitch; i += kSlabThreads) S[i] = 0.f;
+    __syncthreads();
+
+    unsigned k_base = 0;   // intermediate rows produced / consumed so far: the ring position both warps agree on
+    for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
+        const SlabItem it = decode_item(P, item, VT);
+        if (warp == 0) {
+            slab_produce<SPAN>(P, it, M, S, RAW, bar_full, bar_empty, k_base, lane);
+        } else {
+            const SlabOpParams &op = P.op[it.oi];
+            constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
+            const uintptr_t d0 = reinterpret_cast<uintptr_t>(op.dst + it.f * op.dst_fstride) + static_cast<uintptr_t>(it.slab * kSlabW) * kSample;
+            const bool fast = op.dst_xstep == kSample && (op.dst_pitch & kAlign) == 0 && (d0 & kAlign) == 0 && (it.slab + 1) * kSlabW <= op.dw;
+            if (fast) slab_consume<VT, OUT, true>(P, it, M, bar_full, bar_empty, k_base, lane);
+            else slab_consume<VT, OUT, false>(P, it, M, bar_full, bar_empty, k_base, lane);
+        }
+        k_base += static_cast<unsigned>(it.r_end - it.r_begin);
+    }
+}
+
+using SlabKernelFn = void (*)(const SlabLaunchParams);
+struct SlabInstance { int span, vt; SlabKernelFn fn[3]; };   // one kernel per output rule
+#define TVS_SLAB_INST(S, V) {S, V, {slab_scale_kernel<S, V, kOutU8>, slab_scale_kernel<S, V, kOutU8Dither>, slab_scale_kernel<S, V, kOutU10>}}
+const SlabInstance kSlabInstances[] = {
+    TVS_SLAB_INST(4, 2), TVS_SLAB_INST(6, 4), TVS_SLAB_INST(8, 4), TVS_SLAB_INST(8, 6), TVS_SLAB_INST(12, 6), TVS_SLAB_INST(12, 8),
+};
+#undef TVS_SLAB_INST
+
+template <typename T>
+size_t slab_append(std::vector<uint8_t> &blob, const std::vector<T> &v) {
+    const size_t off = (blob.size() + 255) & ~static_cast<size_t>(255);
+    blob.resize(off + v.size() * sizeof(T));
+    memcpy(blob.data() + off, v.data(), v.size() * sizeof(T));
+    return off;
+}
+
+}  // namespace
+
+struct SlabOp {
+    int op_index = 0, instance = -1, out_mode = 0, src_mode = 0;
+    int n_groups = 0, n_slabs = 0;
+    int s_pitch = 0, raw_pitch = 0;
+    float v_thr = 0, v_init = 0, h_addend = 0;
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vring_off = 0, vring_i_off = 0;
+};
+
+struct SlabPlan {
+    std::vector<SlabOp> ops;
+    uint8_t *blob = nullptr;
+    size_t blob_bytes = 0;
+    int device = 0, sm_count = 148;
+};
+
+// The float vertical sum of this kernel runs in ring-slot order, slot = source_row % VT, one scalar FMA per slot:
+// follow that order row by row (each FMA rounds by at most half an ulp of its own partial sum, bounded through
+// |t| <= 32767) instead of charging every tap half an ulp of the largest possible sum.
+static VerticalFloatRule slab_vertical_rule(const AxisTable &v, int vt_inst, bool out10, bool dither) {
+    const VerticalFloatRule coarse = vertical_float_rule(v, vt_inst, out10, dither);
+    if (!coarse.ok || coarse.thr > 1.0e38f) return coarse;   // exact tables keep their tie-free treatment
+    auto half_ulp = [](double bound) { return bound < 1.0 ? 0.0 : 0.5 * std::ldexp(1.0, static_cast<int>(std::floor(std::log2(bound))) + 1 - 24); };
+    const double init_abs = dither ? 64.0 * 4096.0 : 0.0;
+    double e_max = 0.0;
+    std::vector<int> by_slot(vt_inst);
+    for (int y = 0; y < v.length; ++y) {
+        std::fill(by_slot.begin(), by_slot.end(), 0);
+        for (int j = 0; j < v.taps; ++j) by_slot[(v.pos[y] + j) % vt_inst] = std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+        double run = init_abs, e = 0.0;
+        for (int s = 0; s < vt_inst; ++s) {
+            if (!by_slot[s]) continue;   // a zero coefficient leaves the accumulator unchanged, exactly
+            run += 32767.0 * by_slot[s];
+            e += half_ulp(run * (1.0 + 1e-6));
+        }
+        e_max = std::max(e_max, e);
+    }
+    const double half_step = out10 ? 65536.0 : 262144.0;
+    if (e_max > half_step / 8) return {false, 0.f, 0.f};
+    return {true, static_cast<float>(std::ldexp(half_step - e_max - 1.0, -42)), coarse.init};
+}
+
+SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err) {
+    std::vector<uint8_t> blob;
+    auto sp = new SlabPlan;
+    sp->device = device;
+    cudaDeviceGetAttribute(&sp->sm_count, cudaDevAttrMultiProcessorCount, device);
+    for (size_t oi = 0; oi < plan.ops.size(); ++oi) {
+        const PlaneOp &op = plan.ops[oi];
+        if (op.kind != kOpScale) continue;
+        const AxisTable &h = host_tables[op.htable], &v = host_tables[op.vtable];
+        const bool wide_src = op.src_bits > 8;
+        const int sample_bytes = wide_src ? 2 : 1;
+        if (op.src_xstep != sample_bytes && op.src_xstep != 2 * sample_bytes) { err = "unexpected sample spacing"; delete sp; return nullptr; }
+        if (op.src_bits > 10) { err = "samples wider than 10 bits"; delete sp; return nullptr; }
+        const int src_mode = wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
+        const int out_mode = op.rule == kOut10 ? kOutU10 : op.rule == kOut8Dither ? kOutU8Dither : kOutU8;
+        // the walk is driven by source rows: consecutive output rows must start at the same source row or the next one
+        for (int y = 1; y < op.dh; ++y)
+            if (v.pos[y] < v.pos[y - 1] || v.pos[y] > v.pos[y - 1] + 1) { err = "plane is shrunk vertically"; delete sp; return nullptr; }
+        // float exactness of the horizontal sum (see the tile kernel)
+        long long worst_abs = 0;
+        for (int x = 0; x < op.dw; ++x) {
+            long long s = 0, a = 0;
+            for (int j = 0; j < h.taps; ++j) { const int c = h.coef[static_cast<size_t>(x) * h.taps + j]; s += c; a += std::abs(c); }
+            if (s != (1 << 14)) { err = "horizontal row does not sum to one"; delete sp; return nullptr; }
+            worst_abs = std::max(worst_abs, a);
+        }
+        if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete sp; return nullptr; }
+        const int n_groups = (op.dw + 3) / 4;
+        int span = 0;
+        for (int g = 0; g < n_groups; ++g) {
+            const int xa = g * 4, xb = std::min(xa + 4, op.dw) - 1;
+            span = std::max(span, h.pos[xb] + h.taps - h.pos[xa]);
+        }
+        int inst = -1;
+        for (size_t i = 0; i < sizeof(kSlabInstances) / sizeof(kSlabInstances[0]); ++i) {
+            if (kSlabInstances[i].span < span || kSlabInstances[i].vt < v.taps) continue;
+            if (inst < 0 || kSlabInstances[i].span + kSlabInstances[i].vt < kSlabInstances[inst].span + kSlabInstances[inst].vt) inst = static_cast<int>(i);
+        }
+        if (inst < 0) { err = "no slab kernel instance for this filter size"; delete sp; return nullptr; }
+        const int SPAN = kSlabInstances[inst].span, VT = kSlabInstances[inst].vt;
+        const VerticalFloatRule vrule = slab_vertical_rule(v, VT, out_mode == kOutU10, out_mode == kOutU8Dither);
+        if (!vrule.ok) { err = "vertical error bound too large"; delete sp; return nullptr; }
+
+        SlabOp so;
+        so.op_index = static_cast<int>(oi);
+        so.instance = inst;
+        so.out_mode = out_mode;
+        so.src_mode = src_mode;
+        so.n_groups = n_groups;
+        so.n_slabs = (op.dw + kSlabW - 1) / kSlabW;
+        so.v_thr = vrule.thr;
+        so.v_init = vrule.init;
+        so.h_addend = wide_src ? std::ldexp(16384.0f, -149) : 0.0f;   // (512 << 14) >> 9, as a subnormal
+
+        std::vector<float> hdense(static_cast<size_t>(n_groups) * 4 * SPAN, 0.0f);
+        std::vector<int> hbase(n_groups);
+        for (int g = 0; g < n_groups; ++g) {
+            const int xa = g * 4;
+            hbase[g] = h.pos[xa];
+            for (int k = 0; k < 4 && xa + k < op.dw; ++k) {
+                const int x = xa + k;
+                for (int j = 0; j < h.taps; ++j) {
+                    const int c = h.coef[static_cast<size_t>(x) * h.taps + j];
+                    // scaled so that one FMA by 2^-126 lands floor(sum >> hshift) on the subnormal grid
+                    if (c) hdense[(static_cast<size_t>(g) * 4 + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -(23 + op.hshift));
+                }
+            }
+        }
+        // widest slab footprint -> staged row sizes (worst alignment)
+        int ncols_max = 0;
+        for (int s = 0; s < so.n_slabs; ++s) {
+            const int ga = s * (kSlabW / 4), gb = std::min(ga + kSlabW / 4 - 1, n_groups - 1);
+            ncols_max = std::max(ncols_max, std::min(hbase[gb] + SPAN, op.sw) - hbase[ga]);
+        }
+        const int s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
+        so.raw_pitch = 16 * s_chunks;
+        // a converted row holds (16 / spacing) samples per chunk, and a lane's window may start up to SPAN short of its end
+        so.s_pitch = ((s_chunks * (16 / op.src_xstep) + SPAN + 3) & ~3) + 4;
+
+        const int rows = op.dh + 1;   // one padding row: the consumer requests a row's tables one row ahead
+        std::vector<float> vring(static_cast<size_t>(rows) * VT, 0.0f);
+        std::vector<int> vring_i(static_cast<size_t>(rows) * VT, 0);
+        std::vector<int> vpos(rows, v.pos[op.dh - 1]);
+        for (int y = 0; y < op.dh; ++y) {
+            vpos[y] = v.pos[y];
+            for (int j = 0; j < v.taps; ++j) {
+                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
+                const int slot = (v.pos[y] + j) % VT;
+                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
+                vring_i[static_cast<size_t>(y) * VT + slot] = c;
+            }
+        }
+        so.hdense_off = slab_append(blob, hdense);
+        so.hbase_off = slab_append(blob, hbase);
+        so.vpos_off = slab_append(blob, vpos);
+        so.vring_off = slab_append(blob, vring);
+        so.vring_i_off = slab_append(blob, vring_i);
+        sp->ops.push_back(so);
+    }
+    if (sp->ops.empty()) { err = "nothing to scale"; delete sp; return nullptr; }
+    if (cudaMalloc(&sp->blob, blob.size()) != cudaSuccess ||
+        cudaMemcpy(sp->blob, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
+        err = "device allocation for the slab tables failed";
+        cudaGetLastError();
+        if (sp->blob) cudaFree(sp->blob);
+        delete sp;
+        return nullptr;
+    }
+    sp->blob_bytes = blob.size();
+    return sp;
+}
+
+void slab_plan_destroy(SlabPlan *p) {
+    if (!p) return;
+    if (p->blob) cudaFree(p->blob);
+    delete p;
+}
+
+int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
+                cudaStream_t stream) {
+    int launched = 0;
+    std::vector<bool> done(p->ops.size(), false);
+    for (size_t i = 0; i < p->ops.size(); ++i) {
+        if (done[i]) continue;
+        // one launch covers every plane that runs on the same kernel instance
+        SlabLaunchParams lp{};
+        std::vector<size_t> members;
+        for (size_t j = i; j < p->ops.size() && members.size() < kMaxSlabOps; ++j)
+            if (!done[j] && p->ops[j].instance == p->ops[i].instance && p->ops[j].out_mode == p->ops[i].out_mode) { done[j] = true; members.push_back(j); }
+        // Row chunks: every item should cost about the same (all slabs are 128 columns wide, so cost ~ output rows) and
+        // there should be several items per resident CTA; a chunk is never shorter than 64 rows (ring warm-up, tables).
+        int min_dh = 1 << 30;
+        for (size_t j : members) min_dh = std::min(min_dh, plan.ops[p->ops[j].op_index].dh);
+        int chunk_rows = std::max(64, std::min(min_dh, 1024));
+        const long long slots = static_cast<long long>(kSlabCtasPerSM) * p->sm_count;
+        for (;;) {
+            long long items = 0;
+            for (size_t j : members) {
+                const PlaneOp &op = plan.ops[p->ops[j].op_index];
+                items += static_cast<long long>(p->ops[j].n_slabs) * ((op.dh + chunk_rows - 1) / chunk_rows);
+            }
+            if (items * n_frames >= 4 * slots || chunk_rows <= 64) break;
+            chunk_rows = std::max(64, chunk_rows / 2);
+        }
+        int items = 0;
+        for (size_t j : members) {
+            const SlabOp &so = p->ops[j];
+            const PlaneOp &op = plan.ops[so.op_index];
+            const SampleView &s = src_views[so.op_index], &d = dst_views[so.op_index];
+            SlabOpParams &q = lp.op[lp.n_ops++];
+            q.src = s.base; q.src_pitch = s.pitch; q.src_fstride = s.frame_stride; q.src_xstep = s.xstep;
+            q.dst = d.base; q.dst_pitch = d.pitch; q.dst_fstride = d.frame_stride; q.dst_xstep = d.xstep;
+            q.sw = op.sw; q.sh = op.sh; q.dw = op.dw; q.dh = op.dh;
+            q.n_groups = so.n_groups; q.n_slabs = so.n_slabs;
+            const int n_chunks = (op.dh + chunk_rows - 1) / chunk_rows;
+            q.chunk_rows = (op.dh + n_chunks - 1) / n_chunks;     // equal chunks
+            q.n_chunks = (op.dh + q.chunk_rows - 1) / q.chunk_rows;
+            q.item_begin = items;
+            items += q.n_slabs * q.n_chunks;
+            q.hdense = reinterpret_cast<const float *>(p->blob + so.hdense_off);
+            q.hbase = reinterpret_cast<const int *>(p->blob + so.hbase_off);
+            q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
+            q.vring = reinterpret_cast<const float *>(p->blob + so.vring_off);
+            q.vring_i = reinterpret_cast<const int *>(p->blob + so.vring_i_off);
+            q.src_lo = s.base - op.src_offset;
+            q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
+            q.v_thr = so.v_thr; q.v_init = so.v_init; q.h_addend = so.h_addend;
+            q.src_mode = so.src_mode; q.src_shift = op.src_shift;
+            q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
+            lp.raw_pitch = std::max(lp.raw_pitch, so.raw_pitch);
+        }
+        // every plane of the launch stages (and converts) the launch's chunk count per row: a converted row must hold
+        // that many samples of the plane with the closest sample spacing, plus the overhang of a dense window
+        for (size_t j : members) {
+            const int span = kSlabInstances[p->ops[j].instance].span;
+            lp.s_pitch = std::max(lp.s_pitch, ((lp.raw_pitch / plan.ops[p->ops[j].op_index].src_xstep + span + 3) & ~3) + 4);
+        }
+        lp.items_per_frame = items;
+        const long long total = static_cast<long long>(items) * n_frames;
+        if (total > 0x7fffffffLL) return -1;
+        lp.n_items = static_cast<int>(total);
+        const size_t smem = static_cast<size_t>(kRing) * kSlabW * 4 + static_cast<size_t>(kBlockRows) * lp.s_pitch * 4 +
+                            static_cast<size_t>(kRawBlocks) * kBlockRows * lp.raw_pitch + 2 * kRing * 8;
+        const SlabKernelFn fn = kSlabInstances[p->ops[i].instance].fn[p->ops[i].out_mode];
+        if (smem > 48 * 1024) cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        const int grid = static_cast<int>(std::min<long long>(total, slots));
+        fn<<<grid, kSlabThreads, smem, stream>>>(lp);
+        if (cudaPeekAtLastError() != cudaSuccess) return -1;
+        ++launched;
+    }
+    return launched;
+}
+
+size_t slab_plan_device_bytes(const SlabPlan *p) { return p ? p->blob_bytes : 0; }
+
+}  // namespace tvs

@@ -183,4 +183,13 @@ void stream_plan_destroy(StreamPlan *p);
 int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
                   cudaStream_t stream);
 
+// ---- slab kernel (kernels_slab.cu): warp-specialised row streaming for planes that are not shrunk vertically ----
+struct SlabPlan;  // opaque, owned by the context
+SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);
+void slab_plan_destroy(SlabPlan *p);
+size_t slab_plan_device_bytes(const SlabPlan *p);
+// Returns kernels launched, or a negative value after a launch error.
+int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
+                cudaStream_t stream);
+
 }  // namespace tvs

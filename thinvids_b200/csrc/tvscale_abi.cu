@@ -75,6 +75,7 @@ struct tvs_ctx {
     FusedPlan *fused = nullptr;
     bool fused_narrow = false;   // which build of the fused kernel owns `fused`: 128-column (true) or 256-column tiles
     StreamPlan *streaming = nullptr;   // vertical down-scales: the line-buffer kernel
+    SlabPlan *slab = nullptr;          // planes that are not shrunk vertically: the warp-specialised slab kernel
     bool box2 = false;                 // exact 2:1 area on 8-bit planes with matching layouts: the box-filter kernel
     int forced_path = -1;
     // two-pass scratch
@@ -101,10 +102,14 @@ namespace {
 bool fused_prefers_two_pass(const tvs_ctx *c) {
     return c->fused_narrow ? fused_plan_prefers_two_pass_w128(c->fused) : fused_plan_prefers_two_pass_w256(c->fused);
 }
-// forced_path: -1 automatic, 0 fused tile kernel, 1 two-pass kernels, 2 streaming kernel
+// forced_path: -1 automatic, 0 fused tile kernel, 1 two-pass kernels, 2 streaming kernel, 3 slab kernel
 bool use_stream_path(const tvs_ctx *c) { return c->streaming && (c->forced_path == 2 || c->forced_path < 0); }
-bool use_fused_path(const tvs_ctx *c) {
+bool use_slab_path(const tvs_ctx *c) {
     if (use_stream_path(c)) return false;
+    return c->slab && c->forced_path == 3;   // not yet the automatic choice: see DESIGN.md
+}
+bool use_fused_path(const tvs_ctx *c) {
+    if (use_stream_path(c) || use_slab_path(c)) return false;
     return c->fused && (c->forced_path == 0 || (c->forced_path < 0 && !fused_prefers_two_pass(c)));
 }
 
@@ -344,6 +349,13 @@ int enqueue_planar(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], 
         c->launches += n;
         return 0;
     }
+    if (c->forced_path == 3 && !c->slab) return fail(-ENOSYS, "slab path requested but this shape is not supported by it");
+    if (use_slab_path(c)) {
+        const int n = slab_launch(c->slab, plan, sv.data(), dv.data(), n_frames, stream);
+        if (n < 0) return cuda_fail(cudaGetLastError(), "slab kernel launch");
+        c->launches += n;
+        return 0;
+    }
     const bool use_fused = use_fused_path(c);
     if (c->forced_path == 0 && !c->fused) return fail(-ENOSYS, "fused path requested but this shape is not supported by it");
     if (use_fused) {
@@ -552,6 +564,15 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         delete c;
         return nullptr;
     }
+    // With accurate_rnd libswscale switches to two cascaded contexts once a filter, padded to the x86 build's table
+    // alignment (4 taps horizontally, 2 vertically), reaches 256 * 16 / 24 = 171 taps (RETCODE_USE_CASCADE).
+    if (((c->host_tables[0].taps + 3) & ~3) >= 171 || ((c->host_tables[1].taps + 3) & ~3) >= 171 ||
+        ((c->host_tables[2].taps + 1) & ~1) >= 171 || ((c->host_tables[3].taps + 1) & ~1) >= 171) {
+        fail(-ENOSYS, "%dx%d -> %dx%d needs a filter of 171 taps or more, where libswscale cascades two contexts; not supported",
+             src_w, src_h, dst_w, dst_h);
+        delete c;
+        return nullptr;
+    }
     build_plan(c);
     if (upload_tables(c) != 0) {
         tvs_destroy(c);
@@ -576,6 +597,7 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         // vertical pass over 256 columns.  If the preferred build cannot take the shape, try the other one;
         // nullptr = the shape is handled by the two-pass kernels.
         if (src_h > dst_h) c->streaming = stream_plan_create(c->plan, c->host_tables, device, why);
+        c->slab = slab_plan_create(c->plan, c->host_tables, device, why);   // nullptr unless no plane is shrunk vertically
         c->fused_narrow = src_w > dst_w;
         for (int attempt = 0; attempt < 2 && !c->fused; ++attempt, c->fused_narrow = !c->fused_narrow) {
             c->fused = c->fused_narrow ? fused_plan_create_w128(c->plan, c->host_tables, device, why)
@@ -591,6 +613,7 @@ void tvs_destroy(tvs_ctx *c) {
     cudaSetDevice(c->device);
     if (c->fused) { if (c->fused_narrow) fused_plan_destroy_w128(c->fused); else fused_plan_destroy_w256(c->fused); }
     if (c->streaming) stream_plan_destroy(c->streaming);
+    if (c->slab) slab_plan_destroy(c->slab);
     if (c->dev_table_blob) cudaFree(c->dev_table_blob);
     if (c->mid) cudaFree(c->mid);
     if (c->rgb_planes) cudaFree(c->rgb_planes);
@@ -769,7 +792,7 @@ long long tvs_info(const tvs_ctx *c, int what) {
     case TVS_INFO_PATH:
         if (!c->plan.any_scale) return 2;
         if (c->box2 && c->forced_path < 0) return 4;
-        return use_stream_path(c) ? 3 : use_fused_path(c) ? 0 : 1;
+        return use_stream_path(c) ? 3 : use_slab_path(c) ? 5 : use_fused_path(c) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
         return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + tvs_ctx::kSlots * (c->stage_src_bytes + c->stage_dst_bytes));
     case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
@@ -779,7 +802,8 @@ long long tvs_info(const tvs_ctx *c, int what) {
 }
 
 int tvs_set_path(tvs_ctx *c, int path) {
-    if (!c || path < -1 || path > 2) return fail(-EINVAL, "bad path");
+    if (!c || path < -1 || path > 3) return fail(-EINVAL, "bad path");
+    if (path == 3 && c->plan.any_scale && !c->slab) return fail(-ENOSYS, "this shape is not supported by the slab kernel");
     if (path == 0 && c->plan.any_scale && !c->fused) return fail(-ENOSYS, "this shape is not supported by the fused kernel");
     if (path == 2 && c->plan.any_scale && !c->streaming) return fail(-ENOSYS, "this shape is not supported by the streaming kernel");
     c->forced_path = path;

@@ -127,7 +127,7 @@ def main():
             ref.scale_into(src, want)
         except Exception as e:  # shapes the oracle refuses are refused by the product too
             continue
-        for path in ("auto", "two-pass", "fused", "stream"):
+        for path in ("auto", "two-pass", "fused", "stream", "slab"):
             if os.environ.get("FUZZ_VERBOSE"):
                 print("case", n, (sf, sw, sh, df, dw, dh, hex(alg)), path, flush=True)
             try:
