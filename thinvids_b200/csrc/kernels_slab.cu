@@ -35,12 +35,12 @@ namespace {
 
 constexpr int kSlabW = 128;        // output columns per slab: lane * 4 + k
 constexpr int kSlabThreads = 64;   // warp 0 produces intermediate rows, warp 1 consumes them
-constexpr int kRing = 16;          // rows of the shared-memory intermediate ring (power of two)
 constexpr int kBlockRows = 4;      // source rows staged and converted together
+constexpr int kRing = 16;          // rows of the shared-memory intermediate ring (power of two)
 constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the producer prefetches kRawBlocks - 1 blocks ahead
 constexpr int kMaxSlabOps = 3;
 #ifndef TVS_SLAB_MIN_CTAS
-#define TVS_SLAB_MIN_CTAS 12
+#define TVS_SLAB_MIN_CTAS 14
 #endif
 constexpr int kSlabCtasPerSM = 16;
 
@@ -56,7 +56,8 @@ struct SlabOpParams {
     const float *hdense;   // [n_groups][4][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
     const int *hbase;      // [n_groups]           first source column of the group's span
     const int *vpos;       // [dh + 1]             first source row of each output row (one padding entry)
-    const float *vring;    // [dh + 1][VT]         g * 2^107 indexed by ring slot = source_row % VT
+    const float4 *vrec;    // [dh + 1][REC]        per output row: VT coefficients g * 2^107 indexed by ring slot =
+                           //                      source_row % VT, then the NEXT row's first source row (as int bits)
     const int *vring_i;    // [dh + 1][VT]         the same coefficients as integers (exact path)
     const uint8_t *src_lo; // first byte of the stored source plane (frame 0) and its extent: bounds for 16-byte reads
     size_t src_extent;
@@ -71,27 +72,32 @@ struct SlabLaunchParams {
     SlabOpParams op[kMaxSlabOps];
     int n_ops;
     int items_per_frame, n_items;
-    int s_pitch;           // floats per converted source row (multiple of 4)
-    int raw_pitch;         // bytes per staged raw row (multiple of 16)
+    int raw_pitch;         // bytes per staged raw row (multiple of 16); a converted row holds raw_pitch / sample spacing floats
+    unsigned chunk_magic;  // ceil(2^32 / (raw_pitch / 16)): exact division of small indices by the chunks per row
 };
 
-// ---- mbarrier helpers (one arrival per phase) -------------------------------------------------------------------
+// ---- hand-over between the two warps ------------------------------------------------------------------------------
+// One mbarrier pair (full / empty) per ring row, one arrival per phase.  In steady state the producer is the faster
+// warp and spends part of its time waiting for a free row; a waiting warp must not eat issue slots, so a failed
+// try_wait is followed by a nanosleep (a first version that simply spun spent 30 % of all issued instructions in its
+// wait loops; named barriers would park the warp for free, but an SM has 64 of them - four per CTA at 16 CTAs per SM -
+// which is too few for a ring: profiles/r02_slab_history.md).  The ring's slack (16 rows, of which the consumer holds
+// at most VT + 1) covers the wake-up latency.
 __device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
 }
 __device__ __forceinline__ void mbar_arrive(unsigned bar) {
     asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
 }
+__device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
+    unsigned ok;
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+    return ok != 0;
+}
+template <unsigned SLEEP_NS>
 __device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-    asm volatile(
-        "{\n"
-        ".reg .pred p;\n"
-        "SLAB_WAIT_%=:\n"
-        "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-        "@p bra SLAB_DONE_%=;\n"
-        "bra SLAB_WAIT_%=;\n"
-        "SLAB_DONE_%=:\n"
-        "}" ::"r"(bar), "r"(parity) : "memory");
+    while (!mbar_try(bar, parity)) __nanosleep(SLEEP_NS);
 }
 template <int N>
 __device__ __forceinline__ void cp_async_wait_pending() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
@@ -119,78 +125,101 @@ __device__ __forceinline__ SlabItem decode_item(const SlabLaunchParams &P, int i
 }
 
 // ---- producer ------------------------------------------------------------------------------------------------------
+// Everything the producer needs to stage one block of source rows, fixed for the life of an item.  Offsets are 32-bit
+// and relative to the first byte of the frame's stored plane (a plane the slab kernel accepts is smaller than 2 GiB).
+struct SlabStage {
+    const uint8_t *lo;        // the stored plane of this frame: nothing outside [lo, lo + extent) is read
+    int extent;
+    int foot;                 // offset of the first byte of the footprint of the item's first source row
+    int pitch;
+    int rows_real;            // source rows of the item that exist
+    int last_byte;            // offset of the last needed byte inside a footprint row
+    int s_chunks;             // 16-byte chunks per staged row
+    unsigned chunk_magic;
+};
+
 // Start the asynchronous copy of raw source rows [row0, row0 + kBlockRows) of the slab's footprint (rows counted from
-// the item's first source row).  Rows are read as aligned 16-byte chunks starting at the chunk that holds the row's
-// first sample, so byte i of a footprint row lands at position mis + i of the staged row, mis (0..15) being the
-// misalignment of the row's first byte; any pitch works.  A chunk that would reach outside the plane is fetched as
-// 4-byte words that each contain at least one needed byte; chunks and words past the end of the row are zeroed.
-__device__ __forceinline__ void slab_prefetch_block(const SlabOpParams &op, const uint8_t *foot, const uint8_t *lo, const uint8_t *hi,
-                                                    int row0, int rows_real, int last_byte, int s_chunks, unsigned char *raw_block,
-                                                    int raw_pitch, int lane) {
-    const ptrdiff_t pitch = op.src_pitch;
-    int clog = 0;
-    while ((1 << clog) < s_chunks) ++clog;
-    clog = min(clog, 5);
-    const int cmask = (1 << clog) - 1, rstep = 32 >> clog;
-    for (int ch = lane & cmask; ch < s_chunks; ch += 1 << clog) {
-        for (int rr = lane >> clog; rr < kBlockRows; rr += rstep) {
-            const int row = row0 + rr;
-            uint4 *dst = reinterpret_cast<uint4 *>(raw_block + rr * raw_pitch) + ch;
-            if (row >= rows_real) { *dst = make_uint4(0u, 0u, 0u, 0u); continue; }
-            const uint8_t *rowp = foot + static_cast<ptrdiff_t>(row) * pitch;
-            const unsigned mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(rowp)) & 15u;
-            const int first = 16 * ch - static_cast<int>(mis);      // footprint-row offset of the chunk's first byte
-            const uint8_t *g = rowp + first;
-            if (first > last_byte) {
-                *dst = make_uint4(0u, 0u, 0u, 0u);
-            } else if (g >= lo && g + 16 <= hi) {
-                cp_async16(dst, g);
-            } else {
+// the item's first source row) into `raw_block` ([kBlockRows][s_chunks] 16-byte chunks).  Rows are read as aligned
+// chunks starting at the chunk that holds the row's first sample, so byte i of a footprint row lands at position
+// mis + i of the staged row, mis (0..15) being the misalignment of the row's first byte; any pitch works.  A chunk that
+// would reach outside the plane is fetched as 4-byte words that each contain at least one needed byte; chunks and words
+// past the end of the row, and rows below the plane, are zeroed.
+__device__ __forceinline__ void slab_prefetch_block(const SlabStage &st, int row0, uint4 *raw_block, int lane) {
+    const int total = kBlockRows * st.s_chunks;
+    const unsigned lo_mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(st.lo)) & 15u;
+#pragma unroll 1
+    for (int idx = lane; idx < total; idx += 32) {
+        const int rr = static_cast<int>(__umulhi(static_cast<unsigned>(idx), st.chunk_magic));
+        const int ch = idx - rr * st.s_chunks;
+        uint4 *dst = raw_block + idx;
+        const int row = row0 + rr;
+        const int rowo = st.foot + row * st.pitch;                                      // offset of the row's first needed byte
+        const int first = 16 * ch - static_cast<int>((lo_mis + static_cast<unsigned>(rowo)) & 15u);   // chunk start, relative to it
+        const int go = rowo + first;                                                    // chunk start, relative to the plane
+        if (row >= st.rows_real || first > st.last_byte) {
+            *dst = make_uint4(0u, 0u, 0u, 0u);
+        } else if (go >= 0 && go + 16 <= st.extent) {
+            cp_async16(dst, st.lo + go);
+        } else {
 #pragma unroll
-                for (int k = 0; k < 4; ++k) {
-                    unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
-                    if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
-                    else *d = 0u;
+            for (int k = 0; k < 4; ++k) {
+                unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+                if (first + 4 * k <= st.last_byte && first + 4 * k + 3 >= 0) cp_async4(d, st.lo + go + 4 * k);
+                else *d = 0u;
+            }
+        }
+    }
+}
+
+// Raw words of one staged block -> exact float samples.  The converted block mirrors the raw block: raw word i becomes
+// floats [i * n, (i + 1) * n) with n = 4 / (bytes between samples), so sample j of a footprint row sits at float index
+// (mis >> log2(bytes between samples)) + j of its converted row whatever the alignment.
+__device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
+                                                   unsigned mis0, unsigned pmod, int row0, int lane) {
+    const int total = kBlockRows * words_per_row;
+    if (src_mode == kSrcU8) {                       // 4 samples per word
+#pragma unroll 1
+        for (int i = lane; i < total; i += 32) {
+            const unsigned v = raw[i];
+            reinterpret_cast<float4 *>(S)[i] = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
+                                                           byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+        }
+    } else if (src_mode == kSrcU16) {               // two 16-bit samples per word, centred on 512
+        const unsigned keep = 0xffffu >> src_shift;
+#pragma unroll 1
+        for (int i = lane; i < total; i += 32) {
+            const unsigned v = (raw[i] >> src_shift) & (keep | (keep << 16));   // P010: integer shift first, as libswscale does
+            reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7410u) - 512.0f, byte_to_float(v, 0x7432u) - 512.0f);
+        }
+    } else {
+        // interleaved chroma: which byte / half of a word belongs to this plane depends on the row's alignment
+#pragma unroll 1
+        for (int rr = 0; rr < kBlockRows; ++rr) {
+            const unsigned mis = (mis0 + static_cast<unsigned>(row0 + rr) * pmod) & 15u;
+            const unsigned *rw = raw + rr * words_per_row;
+            if (src_mode == kSrcU8Pair) {
+                const unsigned p = mis & 1u;
+                float2 *out = reinterpret_cast<float2 *>(S) + rr * words_per_row;
+                for (int w = lane; w < words_per_row; w += 32) {
+                    const unsigned v = rw[w];
+                    out[w] = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
+                }
+            } else {
+                const unsigned sel = (mis & 2u) ? 0x7432u : 0x7410u;
+                const unsigned keep = 0xffffu >> src_shift;
+                float *out = S + rr * words_per_row;
+                for (int w = lane; w < words_per_row; w += 32) {
+                    const unsigned v = (rw[w] >> src_shift) & (keep | (keep << 16));
+                    out[w] = byte_to_float(v, sel) - 512.0f;
                 }
             }
         }
     }
 }
 
-// Raw words of one staged row -> exact float samples.  Sample j of the footprint sits at float index
-// (mis >> log2(bytes per sample step)) + j of the converted row, so the conversion itself is alignment-blind.
-__device__ __forceinline__ void slab_convert_row(const unsigned *raw_row, float *s_row, int words, int src_mode, int src_shift,
-                                                 unsigned mis, int lane) {
-    if (src_mode == kSrcU8) {                       // 4 samples per word
-        for (int w = lane; w < words; w += 32) {
-            const unsigned v = raw_row[w];
-            *reinterpret_cast<float4 *>(s_row + 4 * w) = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
-                                                                     byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
-        }
-    } else if (src_mode == kSrcU8Pair) {            // interleaved 8-bit chroma: this plane is every other byte
-        const unsigned p = mis & 1u;
-        for (int w = lane; w < words; w += 32) {
-            const unsigned v = raw_row[w];
-            *reinterpret_cast<float2 *>(s_row + 2 * w) = make_float2(byte_to_float(v, 0x7540u | p), byte_to_float(v, 0x7542u | p));
-        }
-    } else if (src_mode == kSrcU16) {               // two 16-bit samples per word, centred on 512
-        const unsigned keep = 0xffffu >> src_shift;
-        for (int w = lane; w < words; w += 32) {
-            const unsigned v = (raw_row[w] >> src_shift) & (keep | (keep << 16));   // P010: integer shift first, as libswscale does
-            *reinterpret_cast<float2 *>(s_row + 2 * w) = make_float2(byte_to_float(v, 0x7410u) - 512.0f, byte_to_float(v, 0x7432u) - 512.0f);
-        }
-    } else {                                        // interleaved 16-bit chroma: one sample of this plane per word
-        const unsigned sel = (mis & 2u) ? 0x7432u : 0x7410u;
-        const unsigned keep = 0xffffu >> src_shift;
-        for (int w = lane; w < words; w += 32) {
-            const unsigned v = (raw_row[w] >> src_shift) & (keep | (keep << 16));
-            s_row[w] = byte_to_float(v, sel) - 512.0f;
-        }
-    }
-}
-
+// `k_base`: intermediate rows this CTA has been through before this item (both warps count alike): the ring position.
 template <int SPAN>
-__device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const SlabItem &it, float *M, float *S, unsigned char *RAW,
+__device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const SlabItem &it, float *M, float *S, uint4 *RAW,
                                              unsigned bar_full, unsigned bar_empty, unsigned k_base, int lane) {
     const SlabOpParams &op = P.op[it.oi];
     // this lane's 4 output columns: dense coefficients over their common source span, for the life of the slab
@@ -206,100 +235,91 @@ __device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const Sl
             flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
         }
     }
-    const int c0 = __ldg(op.hbase + g_first);
-    const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
-    const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
-    const int hb = __ldg(op.hbase + g) - c0;
     const int xs = op.src_xstep;
-    const int sample_bytes = op.src_mode >= kSrcU16 ? 2 : 1;
     const int mshift = op.src_mode == kSrcU8 ? 0 : op.src_mode == kSrcU16Pair ? 2 : 1;
-    const int last_byte = (ncols - 1) * xs + sample_bytes - 1;
-    // every staged row carries the launch's chunk count (chunks past a row's last needed byte are zeroed), so the
-    // converted rows are defined up to the same length whatever the plane
-    const int s_chunks = P.raw_pitch >> 4;
-    const int words = 4 * s_chunks;
-    const uint8_t *lo = op.src_lo + it.f * op.src_fstride, *hi = lo + op.src_extent;
-    // first byte of the footprint of the item's first source row
-    const uint8_t *foot = op.src + it.f * op.src_fstride + static_cast<ptrdiff_t>(it.r_begin) * op.src_pitch + static_cast<ptrdiff_t>(c0) * xs;
     const int rows_total = it.r_end - it.r_begin;                       // rows the consumer will read
-    const int rows_real = min(it.r_end, op.sh) - it.r_begin;            // of which these exist in the source
     const int n_blocks = (rows_total + kBlockRows - 1) / kBlockRows;
-    const int s_pitch = P.s_pitch, raw_pitch = P.raw_pitch;
-    const unsigned mis0 = static_cast<unsigned>(reinterpret_cast<uintptr_t>(foot)) & 15u;
-    const unsigned pmod = static_cast<unsigned>(op.src_pitch) & 15u;
+    const int s_pitch = P.raw_pitch >> mshift;                          // floats per converted row
+    const int words_per_row = P.raw_pitch >> 2;
+    const int src_mode = op.src_mode, src_shift = op.src_shift;
+    SlabStage st;
+    int hb;
+    {
+        const int c0 = __ldg(op.hbase + g_first);
+        const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
+        const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
+        hb = __ldg(op.hbase + g) - c0;
+        st.last_byte = (ncols - 1) * xs + (src_mode >= kSrcU16 ? 1 : 0);
+        st.lo = op.src_lo + it.f * op.src_fstride;
+        st.extent = static_cast<int>(op.src_extent);
+        st.pitch = static_cast<int>(op.src_pitch);
+        st.foot = static_cast<int>(op.src - op.src_lo) + it.r_begin * st.pitch + c0 * xs;
+        st.rows_real = min(it.r_end, op.sh) - it.r_begin;
+        st.s_chunks = P.raw_pitch >> 4;
+        st.chunk_magic = P.chunk_magic;
+    }
+    const int rows_real = st.rows_real;
+    const unsigned mis0 = (static_cast<unsigned>(reinterpret_cast<uintptr_t>(st.lo)) + static_cast<unsigned>(st.foot)) & 15u;
+    const unsigned pmod = static_cast<unsigned>(st.pitch) & 15u;
     const float h_addend = op.h_addend;
     const float t_max = __int_as_float(32767);
-    const int src_mode = op.src_mode, src_shift = op.src_shift;
+    const int block_chunks = kBlockRows * st.s_chunks;
+    const float *s_lane = S + hb;
     float *m_lane = M + 4 * lane;
 
     // prologue: the first kRawBlocks - 1 blocks are on their way before anything is converted
-#pragma unroll
+#pragma unroll 1
     for (int b = 0; b < kRawBlocks - 1; ++b) {
-        if (b < n_blocks)
-            slab_prefetch_block(op, foot, lo, hi, b * kBlockRows, rows_real, last_byte, s_chunks,
-                                RAW + (b % kRawBlocks) * kBlockRows * raw_pitch, raw_pitch, lane);
+        if (b < n_blocks) slab_prefetch_block(st, b * kBlockRows, RAW + b * block_chunks, lane);
         cp_async_commit();
     }
+    unsigned mis = mis0;
     unsigned k = k_base;
+    int row = 0;
+#pragma unroll 1
     for (int b = 0; b < n_blocks; ++b) {
         cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
         __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
-        const unsigned char *raw_block = RAW + (b % kRawBlocks) * kBlockRows * raw_pitch;
-        const int row0 = b * kBlockRows;
-#pragma unroll
-        for (int rr = 0; rr < kBlockRows; ++rr) {
-            if (row0 + rr < rows_real)
-                slab_convert_row(reinterpret_cast<const unsigned *>(raw_block + rr * raw_pitch), S + rr * s_pitch, words, src_mode,
-                                 src_shift, (mis0 + (row0 + rr) * pmod) & 15u, lane);
-        }
+        slab_convert_block(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
+                           src_shift, mis0, pmod, b * kBlockRows, lane);
         __syncwarp();                              // S is complete; the raw block is free again
         if (b + kRawBlocks - 1 < n_blocks)
-            slab_prefetch_block(op, foot, lo, hi, (b + kRawBlocks - 1) * kBlockRows, rows_real, last_byte, s_chunks,
-                                RAW + ((b + kRawBlocks - 1) % kRawBlocks) * kBlockRows * raw_pitch, raw_pitch, lane);
+            slab_prefetch_block(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
         cp_async_commit();
 
-        // horizontal pass of the block's rows; the next row's window is loaded before the current row is filtered
-        const int rows_here = min(kBlockRows, rows_total - row0);
-        float px[SPAN], pn[SPAN];
+        // The ring rows of this block must have been released by the consumer.  Releases come in order, so waiting
+        // for the block's last row covers them all: one wait per four rows.
+        const int rows_here = min(kBlockRows, rows_total - row);
         {
-            const float *sp = S + hb + (((mis0 + row0 * pmod) & 15u) >> mshift);
-#pragma unroll
-            for (int i = 0; i < SPAN; ++i) px[i] = sp[i];
+            const unsigned k_last = k + static_cast<unsigned>(rows_here) - 1;
+            mbar_wait<400>(bar_empty + 8 * (k_last & (kRing - 1)), (k_last / kRing) & 1);
         }
+        const float *sp = s_lane;
+#pragma unroll 1
+        for (int rr = 0; rr < rows_here; ++rr, ++row, ++k, sp += s_pitch) {
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);   // a row below the plane: zero weight in every window that reaches it
+            if (row < rows_real) {
+                const float *w = sp + (mis >> mshift);
+                float px[SPAN];
 #pragma unroll
-        for (int rr = 0; rr < kBlockRows; ++rr) {
-            if (rr < rows_here) {
-                if (rr + 1 < kBlockRows) {
-                    const float *sp = S + (rr + 1) * s_pitch + hb + (((mis0 + (row0 + rr + 1) * pmod) & 15u) >> mshift);
+                for (int i = 0; i < SPAN; ++i) px[i] = w[i];
+                float acc[4];
 #pragma unroll
-                    for (int i = 0; i < SPAN; ++i) pn[i] = sp[i];
+                for (int c = 0; c < 4; ++c) acc[c] = px[0] * cd[c][0];
+#pragma unroll
+                for (int i = 1; i < SPAN; ++i) {
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) acc[c] = fmaf(px[i], cd[c][i], acc[c]);
                 }
-                float4 o;
-                if (row0 + rr < rows_real) {
-                    float acc[4];
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) acc[c] = px[0] * cd[c][0];
-#pragma unroll
-                    for (int i = 1; i < SPAN; ++i) {
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) acc[c] = fmaf(px[i], cd[c][i], acc[c]);
-                    }
-                    // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
-                    o = make_float4(fminf(fma_rm(acc[0], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[1], 0x1p-126f, h_addend), t_max),
-                                    fminf(fma_rm(acc[2], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[3], 0x1p-126f, h_addend), t_max));
-                } else {
-                    o = make_float4(0.f, 0.f, 0.f, 0.f);   // a row below the plane: zero weight in every window that reaches it
-                }
-                const unsigned slot = k & (kRing - 1);
-                // the slot's previous row (kRing rows ago) must have been released by the consumer
-                if (k >= kRing) mbar_wait(bar_empty + 8 * slot, ((k / kRing) - 1) & 1);
-                *reinterpret_cast<float4 *>(m_lane + slot * kSlabW) = o;
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_full + 8 * slot);
-                ++k;
-#pragma unroll
-                for (int i = 0; i < SPAN; ++i) px[i] = pn[i];
+                // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
+                o = make_float4(fminf(fma_rm(acc[0], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[1], 0x1p-126f, h_addend), t_max),
+                                fminf(fma_rm(acc[2], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[3], 0x1p-126f, h_addend), t_max));
             }
+            mis = (mis + pmod) & 15u;
+            const unsigned slot = k & (kRing - 1);
+            *reinterpret_cast<float4 *>(m_lane + slot * kSlabW) = o;
+            __syncwarp();
+            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
         }
     }
     cp_async_wait_pending<0>();
@@ -308,9 +328,9 @@ __device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const Sl
 // ---- consumer ------------------------------------------------------------------------------------------------------
 // Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: rare
 // (about one warp-row in a hundred), so it re-reads its VT intermediate rows from the shared-memory ring, which the
-// consumer releases only once no pending output row starts at or above them.
+// consumer releases only once no pending output row starts in them.
 template <int VT, int OUT>
-__device__ __noinline__ uint2 slab_fixup(const float *m_lane, unsigned k_first, int first, const int *exact_coef, float v_thr,
+__device__ __noinline__ uint2 slab_fixup(const float *m_lane, unsigned ring_first, int first, const int *exact_coef, float v_thr,
                                          float r0, float r1, float r2, float r3, int4 dither, int dst_shift, uint2 packed) {
     unsigned word[2] = {packed.x, packed.y};
     const float r[4] = {r0, r1, r2, r3};
@@ -318,7 +338,7 @@ __device__ __noinline__ uint2 slab_fixup(const float *m_lane, unsigned k_first, 
     int slot = first % VT;
     int a[4] = {0, 0, 0, 0};
     for (int j = 0; j < VT; ++j) {
-        const float4 t = *reinterpret_cast<const float4 *>(m_lane + ((k_first + j) & (kRing - 1)) * kSlabW);
+        const float4 t = *reinterpret_cast<const float4 *>(m_lane + ((ring_first + j) & (kRing - 1)) * kSlabW);
         const int c = __ldg(exact_coef + slot);
         a[0] += subnormal_to_int(t.x) * c; a[1] += subnormal_to_int(t.y) * c;
         a[2] += subnormal_to_int(t.z) * c; a[3] += subnormal_to_int(t.w) * c;
@@ -366,37 +386,45 @@ __device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift,
     return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
 }
 
+// float4 records per output row of the vertical table: VT coefficients, then the next row's first source row
+template <int VT> struct SlabRec { static constexpr int kFloat4s = VT <= 6 ? 2 : 3; };
+
 // FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
 // vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
 template <int VT, int OUT, bool FAST>
 __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const SlabItem &it, const float *M, unsigned bar_full,
                                              unsigned bar_empty, unsigned k_base, int lane) {
+    constexpr int REC = SlabRec<VT>::kFloat4s;
     const SlabOpParams &op = P.op[it.oi];
     const float *m_lane = M + 4 * lane;
     const int x = it.slab * kSlabW + 4 * lane;
     const int dw = op.dw, dst_xstep = op.dst_xstep, dst_shift = op.dst_shift;
-    const ptrdiff_t dst_pitch = op.dst_pitch;
+    const int dst_pitch = static_cast<int>(op.dst_pitch);
     uint8_t *drow = op.dst + it.f * op.dst_fstride + static_cast<ptrdiff_t>(it.ya) * dst_pitch;
-    uint8_t *dlane = drow + static_cast<ptrdiff_t>(x) * (OUT == kOutU10 ? 2 : 1);
+    if (FAST) drow += static_cast<ptrdiff_t>(x) * (OUT == kOutU10 ? 2 : 1);    // this lane's first sample of the row
     const float v_thr = op.v_thr, v_init = op.v_init;
     const int dcol = (x + op.dither_xoff) & 7;
-    const float *cv = op.vring + static_cast<size_t>(it.ya) * VT;
-    const int *vp = op.vpos + it.ya;
-    const int *exact = op.vring_i + static_cast<size_t>(it.ya) * VT;
-    const int r_begin = it.r_begin;
+    const float4 *rec = op.vrec + static_cast<size_t>(it.ya) * REC;
+    const unsigned ring_base = k_base;   // ring position of the item's first source row
 
     float w[VT][4];
 #pragma unroll
     for (int s = 0; s < VT; ++s) w[s][0] = w[s][1] = w[s][2] = w[s][3] = 0.f;
-    float g[VT];
+    // this row's coefficients in ring-slot order; the record's last float is the next row's first source row
+    float g[4 * REC];
 #pragma unroll
-    for (int s = 0; s < VT; ++s) g[s] = __ldg(cv + s);
-    int first = r_begin;            // first source row of the output row being waited for
-    int next_row = r_begin;         // next source row to pull from the ring
-    unsigned k = k_base;            // its ring position
+    for (int i = 0; i < REC; ++i) {
+        const float4 v = __ldg(rec + i);
+        g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
+    }
+    // source rows are counted from the item's first one
+    const int rows_total = it.r_end - it.r_begin;
+    int first = 0;                  // first source row of the output row being waited for
+    int next_row = 0;               // next source row to pull from the ring
     int y = it.ya;
     const int yb = it.yb;
-    int slot = r_begin % VT;
+    int slot = it.r_begin % VT;
+    const int slot_bias = it.r_begin;
 
     // every output row whose last source row is now in the register ring; true once the item is finished
     auto emit_ready = [&]() -> bool {
@@ -417,33 +445,34 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
 #pragma unroll
                 for (int c = 0; c < 4; ++c) a[c] = fmaf(w[s][c], g[s], a[c]);
             }
-            // the next row's coefficients and start row (both tables carry a padding row)
-            cv += VT; ++vp;
+            const int first_next = __float_as_int(g[4 * REC - 1]) - slot_bias;
+            // the next row's record (the table carries a padding row); its latency hides under the rounding and the store
+            rec += REC;
 #pragma unroll
-            for (int s = 0; s < VT; ++s) g[s] = __ldg(cv + s);
-            const int first_next = __ldg(vp);
+            for (int i = 0; i < REC; ++i) {
+                const float4 v = __ldg(rec + i);
+                g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
+            }
 
             unsigned word[2];
             float r[4];
             const float worst = slab_finish<OUT>(a, dst_shift, word, r);
             if (worst >= v_thr) {
-                const uint2 fx = slab_fixup<VT, OUT>(m_lane, k_base + static_cast<unsigned>(first - r_begin), first, exact + (y - it.ya) * VT,
-                                                     v_thr, r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
+                const uint2 fx = slab_fixup<VT, OUT>(m_lane, ring_base + static_cast<unsigned>(first), first + slot_bias,
+                                                     op.vring_i + static_cast<size_t>(y) * VT, v_thr, r[0], r[1], r[2], r[3], dither,
+                                                     dst_shift, make_uint2(word[0], word[1]));
                 word[0] = fx.x; word[1] = fx.y;
             }
-            if (FAST) {
-                store_quad_fast<OUT>(dlane, 0, word);
-                dlane += dst_pitch;
-            } else {
-                store_quad_slow<OUT>(drow, x, dw, dst_xstep, word);
-                drow += dst_pitch;
-            }
+            if (FAST) store_quad_fast<OUT>(drow, 0, word);
+            else store_quad_slow<OUT>(drow, x, dw, dst_xstep, word);
+            drow += dst_pitch;
             ++y;
             if (y >= yb) return true;
             if (first_next != first) {
                 // no pending output row starts at `first` any more: hand its ring row back to the producer
+                // (`first` moves by one row at a time: the plane is not shrunk vertically)
                 __syncwarp();
-                if (lane == 0) mbar_arrive(bar_empty + 8 * ((k_base + static_cast<unsigned>(first - r_begin)) & (kRing - 1)));
+                if (lane == 0) mbar_arrive(bar_empty + 8 * ((ring_base + static_cast<unsigned>(first)) & (kRing - 1)));
                 first = first_next;
             }
         }
@@ -453,10 +482,11 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
 #define TVS_SLAB_STEP(s)                                                                            \
     case s:                                                                                         \
         if constexpr (s < VT) {                                                                     \
-            mbar_wait(bar_full + 8 * (k & (kRing - 1)), (k / kRing) & 1);                           \
-            const float4 v = *reinterpret_cast<const float4 *>(m_lane + (k & (kRing - 1)) * kSlabW); \
+            const unsigned kk = ring_base + static_cast<unsigned>(next_row);                        \
+            mbar_wait<100>(bar_full + 8 * (kk & (kRing - 1)), (kk / kRing) & 1);                    \
+            const float4 v = *reinterpret_cast<const float4 *>(m_lane + (kk & (kRing - 1)) * kSlabW); \
             w[s][0] = v.x; w[s][1] = v.y; w[s][2] = v.z; w[s][3] = v.w;                             \
-            ++k; ++next_row;                                                                        \
+            ++next_row;                                                                             \
             if (emit_ready()) break;                                                                \
         }
     bool done = false;
@@ -470,10 +500,10 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
         done = true;
     }
 #undef TVS_SLAB_STEP
-    // hand back the rows the last output rows were still holding
+    // hand back the rows the last output rows were still holding (every row of the item is released exactly once)
     __syncwarp();
     if (lane == 0) {
-        for (int r = first; r < it.r_end; ++r) mbar_arrive(bar_empty + 8 * ((k_base + static_cast<unsigned>(r - r_begin)) & (kRing - 1)));
+        for (int r = first; r < rows_total; ++r) mbar_arrive(bar_empty + 8 * ((ring_base + static_cast<unsigned>(r)) & (kRing - 1)));
     }
 }
 
@@ -482,22 +512,27 @@ __global__ void __launch_bounds__(kSlabThreads, TVS_SLAB_MIN_CTAS)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
     float *M = smem;                                                       // [kRing][128] intermediate t * 2^-149
-    float *S = M + kRing * kSlabW;                                         // [kBlockRows][s_pitch] source samples as floats
-    unsigned char *RAW = reinterpret_cast<unsigned char *>(S + kBlockRows * P.s_pitch);   // [kRawBlocks][kBlockRows][raw_pitch]
-    unsigned long long *BAR = reinterpret_cast<unsigned long long *>(RAW + kRawBlocks * kBlockRows * P.raw_pitch);   // full[kRing], empty[kRing]
+    float *S = M + kRing * kSlabW;                                         // [kBlockRows][raw_pitch] floats at most, + a zero tail
+    const int s_floats = kBlockRows * P.raw_pitch + 32;
+    uint4 *RAW = reinterpret_cast<uint4 *>(S + s_floats);                  // [kRawBlocks][kBlockRows][raw_pitch / 16] chunks
+    unsigned long long *BAR = reinterpret_cast<unsigned long long *>(RAW + kRawBlocks * kBlockRows * (P.raw_pitch >> 4));   // full[kRing], empty[kRing]
     const unsigned bar_full = static_cast<unsigned>(__cvta_generic_to_shared(BAR));
     const unsigned bar_empty = bar_full + 8 * kRing;
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     if (threadIdx.x == 0) {
         for (int i = 0; i < 2 * kRing; ++i) mbar_init(bar_full + 8 * i, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        // every ring row starts out free: complete phase 0 of the empty barriers, so that the producer's n-th use of a
+        // row always waits for phase n (the consumer's release of use n - 1)
+        for (int i = 0; i < kRing; ++i) mbar_arrive(bar_empty + 8 * i);
     }
-    // converted rows are read a little past their last written sample (dense windows of the slab's last columns):
-    // those floats must be finite, and nothing writes them later
-    for (int i = threadIdx.x; i < kBlockRows * P.s_pitch; i += kSlabThreads) S[i] = 0.f;
+    // converted rows are read a little past their last written sample (dense windows of the slab's last columns run
+    // into the next row, the last row's into the tail): those floats must be finite
+    for (int i = threadIdx.x; i < s_floats; i += kSlabThreads) S[i] = 0.f;
     __syncthreads();
 
     unsigned k_base = 0;   // intermediate rows produced / consumed so far: the ring position both warps agree on
+#pragma unroll 1
     for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
         const SlabItem it = decode_item(P, item, VT);
         if (warp == 0) {
@@ -537,7 +572,7 @@ struct SlabOp {
     int n_groups = 0, n_slabs = 0;
     int s_pitch = 0, raw_pitch = 0;
     float v_thr = 0, v_init = 0, h_addend = 0;
-    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vring_off = 0, vring_i_off = 0;
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vrec_off = 0, vring_i_off = 0;
 };
 
 struct SlabPlan {
@@ -586,6 +621,7 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         const int sample_bytes = wide_src ? 2 : 1;
         if (op.src_xstep != sample_bytes && op.src_xstep != 2 * sample_bytes) { err = "unexpected sample spacing"; delete sp; return nullptr; }
         if (op.src_bits > 10) { err = "samples wider than 10 bits"; delete sp; return nullptr; }
+        if (static_cast<long long>(op.sh) * op.sw * op.src_xstep >= (1LL << 30)) { err = "plane too large for 32-bit offsets"; delete sp; return nullptr; }
         const int src_mode = wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
         const int out_mode = op.rule == kOut10 ? kOutU10 : op.rule == kOut8Dither ? kOutU8Dither : kOutU8;
         // the walk is driven by source rows: consecutive output rows must start at the same source row or the next one
@@ -652,23 +688,28 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         // a converted row holds (16 / spacing) samples per chunk, and a lane's window may start up to SPAN short of its end
         so.s_pitch = ((s_chunks * (16 / op.src_xstep) + SPAN + 3) & ~3) + 4;
 
-        const int rows = op.dh + 1;   // one padding row: the consumer requests a row's tables one row ahead
-        std::vector<float> vring(static_cast<size_t>(rows) * VT, 0.0f);
+        const int rows = op.dh + 1;   // one padding row: the consumer requests a row's record one row ahead
+        const int rec = VT <= 6 ? 8 : 12;   // floats per record (SlabRec)
+        std::vector<float> vrec(static_cast<size_t>(rows) * rec, 0.0f);
         std::vector<int> vring_i(static_cast<size_t>(rows) * VT, 0);
         std::vector<int> vpos(rows, v.pos[op.dh - 1]);
-        for (int y = 0; y < op.dh; ++y) {
-            vpos[y] = v.pos[y];
-            for (int j = 0; j < v.taps; ++j) {
-                const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
-                const int slot = (v.pos[y] + j) % VT;
-                vring[static_cast<size_t>(y) * VT + slot] = std::ldexp(static_cast<float>(c), 107);
-                vring_i[static_cast<size_t>(y) * VT + slot] = c;
+        for (int y = 0; y < op.dh; ++y) vpos[y] = v.pos[y];
+        for (int y = 0; y < rows; ++y) {
+            if (y < op.dh) {
+                for (int j = 0; j < v.taps; ++j) {
+                    const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
+                    const int slot = (v.pos[y] + j) % VT;
+                    vrec[static_cast<size_t>(y) * rec + slot] = std::ldexp(static_cast<float>(c), 107);
+                    vring_i[static_cast<size_t>(y) * VT + slot] = c;
+                }
             }
+            const int next_first = vpos[std::min(y + 1, rows - 1)];
+            memcpy(&vrec[static_cast<size_t>(y) * rec + rec - 1], &next_first, sizeof(int));
         }
         so.hdense_off = slab_append(blob, hdense);
         so.hbase_off = slab_append(blob, hbase);
         so.vpos_off = slab_append(blob, vpos);
-        so.vring_off = slab_append(blob, vring);
+        so.vrec_off = slab_append(blob, vrec);
         so.vring_i_off = slab_append(blob, vring_i);
         sp->ops.push_back(so);
     }
@@ -735,29 +776,26 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
             q.hdense = reinterpret_cast<const float *>(p->blob + so.hdense_off);
             q.hbase = reinterpret_cast<const int *>(p->blob + so.hbase_off);
             q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
-            q.vring = reinterpret_cast<const float *>(p->blob + so.vring_off);
+            q.vrec = reinterpret_cast<const float4 *>(p->blob + so.vrec_off);
             q.vring_i = reinterpret_cast<const int *>(p->blob + so.vring_i_off);
             q.src_lo = s.base - op.src_offset;
             q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
             q.v_thr = so.v_thr; q.v_init = so.v_init; q.h_addend = so.h_addend;
             q.src_mode = so.src_mode; q.src_shift = op.src_shift;
             q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
-            lp.raw_pitch = std::max(lp.raw_pitch, so.raw_pitch);
+            lp.raw_pitch = std::max(lp.raw_pitch, so.raw_pitch);   // every plane of the launch stages the launch's chunk count per row
         }
-        // every plane of the launch stages (and converts) the launch's chunk count per row: a converted row must hold
-        // that many samples of the plane with the closest sample spacing, plus the overhang of a dense window
-        for (size_t j : members) {
-            const int span = kSlabInstances[p->ops[j].instance].span;
-            lp.s_pitch = std::max(lp.s_pitch, ((lp.raw_pitch / plan.ops[p->ops[j].op_index].src_xstep + span + 3) & ~3) + 4);
-        }
+        lp.chunk_magic = static_cast<unsigned>((0x100000000ULL + (lp.raw_pitch >> 4) - 1) / (lp.raw_pitch >> 4));
         lp.items_per_frame = items;
         const long long total = static_cast<long long>(items) * n_frames;
         if (total > 0x7fffffffLL) return -1;
         lp.n_items = static_cast<int>(total);
-        const size_t smem = static_cast<size_t>(kRing) * kSlabW * 4 + static_cast<size_t>(kBlockRows) * lp.s_pitch * 4 +
+        const size_t smem = static_cast<size_t>(kRing) * kSlabW * 4 + (static_cast<size_t>(kBlockRows) * lp.raw_pitch + 32) * 4 +
                             static_cast<size_t>(kRawBlocks) * kBlockRows * lp.raw_pitch + 2 * kRing * 8;
         const SlabKernelFn fn = kSlabInstances[p->ops[i].instance].fn[p->ops[i].out_mode];
         if (smem > 48 * 1024) cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        // 14-16 CTAs of ~12 KB each share an SM: ask for the large shared-memory carve-out (the default sized it for 5)
+        cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         const int grid = static_cast<int>(std::min<long long>(total, slots));
         fn<<<grid, kSlabThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
