@@ -1,27 +1,29 @@
-// Slab kernel: warp-specialised row streaming for planes that are not shrunk vertically (the up-scales of
+// Slab kernel: one autonomous warp per 128-column slab, for planes that are not shrunk vertically (the up-scales of
 // BASELINE.json: 480p -> 1080p, 1080p -> 4K, and the worker's 480p -> 1080p NV12 target).
 //
-// A CTA is two warps that own one *slab* - 128 output columns of one plane of one frame - and walk it from its first
-// output row to its last:
+// A CTA is ONE warp.  It owns a *slab* - 128 output columns of one plane of one frame, lane L the columns 4L .. 4L+3 - and
+// walks it from its first output row to its last, source row by source row:
 //
-//   warp 0 (producer)  cp.async the slab's raw source rows four at a time, three blocks ahead  -> RAW ring
-//                      bytes -> exact floats (one 32-bit word per lane)                          -> S (warp private)
-//                      horizontal pass, 4 adjacent output columns per lane, coefficients in
-//                      registers for the whole slab                                              -> M ring (16 rows)
-//   warp 1 (consumer)  vertical pass: a register ring of VT intermediate rows x 4 columns slides down the slab; each
-//                      new source row completes the output rows whose window ends there          -> HBM
+//   every 4 source rows   cp.async the slab's raw rows, three blocks ahead                     -> RAW (warp private)
+//                         bytes -> exact floats, one 32-bit word per lane                        -> S   (warp private)
+//   every source row      horizontal pass of the lane's 4 columns (dense coefficients in registers for the whole slab);
+//                         the 4 results go straight into the lane's vertical register window (the last VT rows)
+//   then                  every output row whose window ends at that source row: VT x 4 FMAs from the ring, rounding,
+//                         packing, one 4-byte store per lane (a full 128-byte line per warp)             -> HBM
 //
-// The two warps meet only through the M ring: one mbarrier pair (full / empty) per ring row, one arrival each.  Nothing
-// else synchronises - no CTA-wide barrier after start-up, no tile halo (every source row is filtered exactly once per
-// slab), no per-tile ring warm-up - and because each role needs only its own working set (horizontal coefficients OR
-// the vertical ring) the kernel fits in 64-80 registers: 28-32 warps per SM instead of the tile kernel's 16.  With about
-// 11 KB of shared memory per CTA, 14-16 CTAs share an SM and cover each other's latencies.
+// Because a lane filters horizontally exactly the columns it later filters vertically, the intermediate never leaves the
+// register file: no shared-memory intermediate, no barrier of any kind after the warp's own __syncwarp around the
+// conversion, no tile halo (every source row is filtered once per slab), no ring warm-up per tile.  Warps are
+// completely independent, so an SM simply runs as many as fit (about 20 at 96 registers) and they cover each other's
+// latencies.  Two earlier forms of this kernel split the passes between a producer and a consumer warp meeting in a
+// shared-memory ring; their hand-over (mbarrier try_wait loops, or named barriers of which an SM only has 64) cost
+// more than it saved - profiles/r02_slab_history.md keeps the measurements.
 //
 // Instruction budget (profiles/r02_issue_mix_raw.txt): on sm_100a a packed FFMA2 holds the issue port for 2.19 cycles
 // and does not overlap integer work, while scalar FFMA issues in 1.02 and lets IADD / LOP3 slip in beside it, so both
-// passes use scalar FFMA.  Arithmetic, exactness argument and output rules are those of DESIGN.md section 4 (the H sum is an
-// exact integer, floor by one FMA.RM onto the subnormal grid; the V sum carries a bounded error and samples whose
-// residual is within that bound of a rounding boundary are recomputed in int32 from the M ring).
+// passes use scalar FFMA.  Arithmetic, exactness argument and output rules are those of DESIGN.md section 4 (the H sum
+// is an exact integer, floored by one FMA.RM onto the subnormal grid; the V sum carries a bounded error and samples whose
+// residual is within that bound of a rounding boundary are recomputed in int32 from the register ring).
 #include <algorithm>
 #include <cmath>
 #include <cstdlib>
@@ -34,15 +36,13 @@ namespace tvs {
 namespace {
 
 constexpr int kSlabW = 128;        // output columns per slab: lane * 4 + k
-constexpr int kSlabThreads = 64;   // warp 0 produces intermediate rows, warp 1 consumes them
+constexpr int kSlabThreads = 32;   // one warp
 constexpr int kBlockRows = 4;      // source rows staged and converted together
-constexpr int kRing = 16;          // rows of the shared-memory intermediate ring (power of two)
-constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the producer prefetches kRawBlocks - 1 blocks ahead
+constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the warp prefetches kRawBlocks - 1 blocks ahead
 constexpr int kMaxSlabOps = 3;
 #ifndef TVS_SLAB_MIN_CTAS
-#define TVS_SLAB_MIN_CTAS 14
+#define TVS_SLAB_MIN_CTAS 21
 #endif
-constexpr int kSlabCtasPerSM = 16;
 
 struct SlabOpParams {
     const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
@@ -56,8 +56,9 @@ struct SlabOpParams {
     const float *hdense;   // [n_groups][4][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
     const int *hbase;      // [n_groups]           first source column of the group's span
     const int *vpos;       // [dh + 1]             first source row of each output row (one padding entry)
-    const float4 *vrec;    // [dh + 1][REC]        per output row: VT coefficients g * 2^107 indexed by ring slot =
-                           //                      source_row % VT, then the NEXT row's first source row (as int bits)
+    const int *yend;       // [sh + VT + 1]        yend[r] = number of output rows whose window ends at or before source row r
+                           //                      (with VT-row windows): after row r, rows y < yend[r] can be produced
+    const float4 *vrec;    // [dh + 1][REC]        per output row: VT coefficients g * 2^107 in tap order
     const int *vring_i;    // [dh + 1][VT]         the same coefficients as integers (exact path)
     const uint8_t *src_lo; // first byte of the stored source plane (frame 0) and its extent: bounds for 16-byte reads
     size_t src_extent;
@@ -76,34 +77,11 @@ struct SlabLaunchParams {
     unsigned chunk_magic;  // ceil(2^32 / (raw_pitch / 16)): exact division of small indices by the chunks per row
 };
 
-// ---- hand-over between the two warps ------------------------------------------------------------------------------
-// One mbarrier pair (full / empty) per ring row, one arrival per phase.  In steady state the producer is the faster
-// warp and spends part of its time waiting for a free row; a waiting warp must not eat issue slots, so a failed
-// try_wait is followed by a nanosleep (a first version that simply spun spent 30 % of all issued instructions in its
-// wait loops; named barriers would park the warp for free, but an SM has 64 of them - four per CTA at 16 CTAs per SM -
-// which is too few for a ring: profiles/r02_slab_history.md).  The ring's slack (16 rows, of which the consumer holds
-// at most VT + 1) covers the wake-up latency.
-__device__ __forceinline__ void mbar_init(unsigned bar, unsigned count) {
-    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count));
-}
-__device__ __forceinline__ void mbar_arrive(unsigned bar) {
-    asm volatile("{ .reg .b64 st; mbarrier.arrive.shared::cta.b64 st, [%0]; }" ::"r"(bar) : "memory");
-}
-__device__ __forceinline__ bool mbar_try(unsigned bar, unsigned parity) {
-    unsigned ok;
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
-                 : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
-    return ok != 0;
-}
-template <unsigned SLEEP_NS>
-__device__ __forceinline__ void mbar_wait(unsigned bar, unsigned parity) {
-    while (!mbar_try(bar, parity)) __nanosleep(SLEEP_NS);
-}
 template <int N>
 __device__ __forceinline__ void cp_async_wait_pending() { asm volatile("cp.async.wait_group %0;" ::"n"(N) : "memory"); }
 
-// One work item: output rows [ya, yb) of slab `slab` of plane `oi` of frame `f`; the producer filters source rows
-// [r_begin, r_end) for it (rows at or past the plane's height are zero rows the vertical window may touch).
+// One work item: output rows [ya, yb) of slab `slab` of plane `oi` of frame `f`; source rows [r_begin, r_end) feed it
+// (rows at or past the plane's height are zero rows the vertical window may touch).
 struct SlabItem { int oi, f, slab, ya, yb, r_begin, r_end; };
 
 __device__ __forceinline__ SlabItem decode_item(const SlabLaunchParams &P, int item, int vt) {
@@ -124,9 +102,8 @@ __device__ __forceinline__ SlabItem decode_item(const SlabLaunchParams &P, int i
     return it;
 }
 
-// ---- producer ------------------------------------------------------------------------------------------------------
-// Everything the producer needs to stage one block of source rows, fixed for the life of an item.  Offsets are 32-bit
-// and relative to the first byte of the frame's stored plane (a plane the slab kernel accepts is smaller than 2 GiB).
+// Everything needed to stage one block of source rows, fixed for the life of an item.  Offsets are 32-bit and relative
+// to the first byte of the frame's stored plane (a plane the slab kernel accepts is smaller than 1 GiB).
 struct SlabStage {
     const uint8_t *lo;        // the stored plane of this frame: nothing outside [lo, lo + extent) is read
     int extent;
@@ -217,132 +194,23 @@ __device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S
     }
 }
 
-// `k_base`: intermediate rows this CTA has been through before this item (both warps count alike): the ring position.
-template <int SPAN>
-__device__ __forceinline__ void slab_produce(const SlabLaunchParams &P, const SlabItem &it, float *M, float *S, uint4 *RAW,
-                                             unsigned bar_full, unsigned bar_empty, unsigned k_base, int lane) {
-    const SlabOpParams &op = P.op[it.oi];
-    // this lane's 4 output columns: dense coefficients over their common source span, for the life of the slab
-    const int g_first = it.slab * (kSlabW / 4);
-    const int g = min(g_first + lane, op.n_groups - 1);
-    float cd[4][SPAN];
-    {
-        const float4 *src = reinterpret_cast<const float4 *>(op.hdense + static_cast<size_t>(g) * (4 * SPAN));
-        float *flat = &cd[0][0];
-#pragma unroll
-        for (int i = 0; i < SPAN; ++i) {
-            const float4 v = __ldg(src + i);
-            flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
-        }
-    }
-    const int xs = op.src_xstep;
-    const int mshift = op.src_mode == kSrcU8 ? 0 : op.src_mode == kSrcU16Pair ? 2 : 1;
-    const int rows_total = it.r_end - it.r_begin;                       // rows the consumer will read
-    const int n_blocks = (rows_total + kBlockRows - 1) / kBlockRows;
-    const int s_pitch = P.raw_pitch >> mshift;                          // floats per converted row
-    const int words_per_row = P.raw_pitch >> 2;
-    const int src_mode = op.src_mode, src_shift = op.src_shift;
-    SlabStage st;
-    int hb;
-    {
-        const int c0 = __ldg(op.hbase + g_first);
-        const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
-        const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
-        hb = __ldg(op.hbase + g) - c0;
-        st.last_byte = (ncols - 1) * xs + (src_mode >= kSrcU16 ? 1 : 0);
-        st.lo = op.src_lo + it.f * op.src_fstride;
-        st.extent = static_cast<int>(op.src_extent);
-        st.pitch = static_cast<int>(op.src_pitch);
-        st.foot = static_cast<int>(op.src - op.src_lo) + it.r_begin * st.pitch + c0 * xs;
-        st.rows_real = min(it.r_end, op.sh) - it.r_begin;
-        st.s_chunks = P.raw_pitch >> 4;
-        st.chunk_magic = P.chunk_magic;
-    }
-    const int rows_real = st.rows_real;
-    const unsigned mis0 = (static_cast<unsigned>(reinterpret_cast<uintptr_t>(st.lo)) + static_cast<unsigned>(st.foot)) & 15u;
-    const unsigned pmod = static_cast<unsigned>(st.pitch) & 15u;
-    const float h_addend = op.h_addend;
-    const float t_max = __int_as_float(32767);
-    const int block_chunks = kBlockRows * st.s_chunks;
-    const float *s_lane = S + hb;
-    float *m_lane = M + 4 * lane;
+// The register ring, passed by value to the (rare, out-of-line) exact path.
+template <int VT> struct SlabRing { float w[VT][4]; };
 
-    // prologue: the first kRawBlocks - 1 blocks are on their way before anything is converted
-#pragma unroll 1
-    for (int b = 0; b < kRawBlocks - 1; ++b) {
-        if (b < n_blocks) slab_prefetch_block(st, b * kBlockRows, RAW + b * block_chunks, lane);
-        cp_async_commit();
-    }
-    unsigned mis = mis0;
-    unsigned k = k_base;
-    int row = 0;
-#pragma unroll 1
-    for (int b = 0; b < n_blocks; ++b) {
-        cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
-        __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
-        slab_convert_block(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
-                           src_shift, mis0, pmod, b * kBlockRows, lane);
-        __syncwarp();                              // S is complete; the raw block is free again
-        if (b + kRawBlocks - 1 < n_blocks)
-            slab_prefetch_block(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
-        cp_async_commit();
-
-        // The ring rows of this block must have been released by the consumer.  Releases come in order, so waiting
-        // for the block's last row covers them all: one wait per four rows.
-        const int rows_here = min(kBlockRows, rows_total - row);
-        {
-            const unsigned k_last = k + static_cast<unsigned>(rows_here) - 1;
-            mbar_wait<400>(bar_empty + 8 * (k_last & (kRing - 1)), (k_last / kRing) & 1);
-        }
-        const float *sp = s_lane;
-#pragma unroll 1
-        for (int rr = 0; rr < rows_here; ++rr, ++row, ++k, sp += s_pitch) {
-            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);   // a row below the plane: zero weight in every window that reaches it
-            if (row < rows_real) {
-                const float *w = sp + (mis >> mshift);
-                float px[SPAN];
-#pragma unroll
-                for (int i = 0; i < SPAN; ++i) px[i] = w[i];
-                float acc[4];
-#pragma unroll
-                for (int c = 0; c < 4; ++c) acc[c] = px[0] * cd[c][0];
-#pragma unroll
-                for (int i = 1; i < SPAN; ++i) {
-#pragma unroll
-                    for (int c = 0; c < 4; ++c) acc[c] = fmaf(px[i], cd[c][i], acc[c]);
-                }
-                // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
-                o = make_float4(fminf(fma_rm(acc[0], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[1], 0x1p-126f, h_addend), t_max),
-                                fminf(fma_rm(acc[2], 0x1p-126f, h_addend), t_max), fminf(fma_rm(acc[3], 0x1p-126f, h_addend), t_max));
-            }
-            mis = (mis + pmod) & 15u;
-            const unsigned slot = k & (kRing - 1);
-            *reinterpret_cast<float4 *>(m_lane + slot * kSlabW) = o;
-            __syncwarp();
-            if (lane == 0) mbar_arrive(bar_full + 8 * slot);
-        }
-    }
-    cp_async_wait_pending<0>();
-}
-
-// ---- consumer ------------------------------------------------------------------------------------------------------
-// Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: rare
-// (about one warp-row in a hundred), so it re-reads its VT intermediate rows from the shared-memory ring, which the
-// consumer releases only once no pending output row starts in them.
+// Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: the
+// intermediates are the bit patterns held in the ring, the coefficients the integer copy of the row's record.
 template <int VT, int OUT>
-__device__ __noinline__ uint2 slab_fixup(const float *m_lane, unsigned ring_first, int first, const int *exact_coef, float v_thr,
-                                         float r0, float r1, float r2, float r3, int4 dither, int dst_shift, uint2 packed) {
+__device__ __noinline__ uint2 slab_fixup(SlabRing<VT> ring, const int *exact_coef, float v_thr, float r0, float r1, float r2, float r3,
+                                         int4 dither, int dst_shift, uint2 packed) {
     unsigned word[2] = {packed.x, packed.y};
     const float r[4] = {r0, r1, r2, r3};
     const int d[4] = {dither.x, dither.y, dither.z, dither.w};
-    int slot = first % VT;
     int a[4] = {0, 0, 0, 0};
-    for (int j = 0; j < VT; ++j) {
-        const float4 t = *reinterpret_cast<const float4 *>(m_lane + ((ring_first + j) & (kRing - 1)) * kSlabW);
-        const int c = __ldg(exact_coef + slot);
-        a[0] += subnormal_to_int(t.x) * c; a[1] += subnormal_to_int(t.y) * c;
-        a[2] += subnormal_to_int(t.z) * c; a[3] += subnormal_to_int(t.w) * c;
-        slot = slot + 1 == VT ? 0 : slot + 1;
+#pragma unroll
+    for (int s = 0; s < VT; ++s) {
+        const int c = __ldg(exact_coef + s);
+#pragma unroll
+        for (int k = 0; k < 4; ++k) a[k] += subnormal_to_int(ring.w[s][k]) * c;
     }
 #pragma unroll
     for (int k = 0; k < 4; ++k) {
@@ -386,17 +254,61 @@ __device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift,
     return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
 }
 
-// float4 records per output row of the vertical table: VT coefficients, then the next row's first source row
-template <int VT> struct SlabRec { static constexpr int kFloat4s = VT <= 6 ? 2 : 3; };
+// float4s per output row of the vertical table: VT coefficients, zero padded
+template <int VT> struct SlabRec { static constexpr int kFloat4s = VT <= 4 ? 1 : 2; };
 
 // FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
 // vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
-template <int VT, int OUT, bool FAST>
-__device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const SlabItem &it, const float *M, unsigned bar_full,
-                                             unsigned bar_empty, unsigned k_base, int lane) {
+template <int SPAN, int VT, int OUT, bool FAST>
+__device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
     constexpr int REC = SlabRec<VT>::kFloat4s;
     const SlabOpParams &op = P.op[it.oi];
-    const float *m_lane = M + 4 * lane;
+
+    // ---- horizontal side: this lane's 4 output columns, dense coefficients over their common source span ----
+    const int g_first = it.slab * (kSlabW / 4);
+    const int grp = min(g_first + lane, op.n_groups - 1);
+    float cd[4][SPAN];
+    {
+        const float4 *src = reinterpret_cast<const float4 *>(op.hdense + static_cast<size_t>(grp) * (4 * SPAN));
+        float *flat = &cd[0][0];
+#pragma unroll
+        for (int i = 0; i < SPAN; ++i) {
+            const float4 v = __ldg(src + i);
+            flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
+        }
+    }
+    const int xs = op.src_xstep;
+    const int mshift = op.src_mode == kSrcU8 ? 0 : op.src_mode == kSrcU16Pair ? 2 : 1;
+    const int rows_total = it.r_end - it.r_begin;                       // source rows the vertical windows will touch
+    const int n_blocks = (rows_total + kBlockRows - 1) / kBlockRows;
+    const int s_pitch = P.raw_pitch >> mshift;                          // floats per converted row
+    const int words_per_row = P.raw_pitch >> 2;
+    const int src_mode = op.src_mode, src_shift = op.src_shift;
+    SlabStage st;
+    int hb;
+    {
+        const int c0 = __ldg(op.hbase + g_first);
+        const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
+        const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
+        hb = __ldg(op.hbase + grp) - c0;
+        st.last_byte = (ncols - 1) * xs + (src_mode >= kSrcU16 ? 1 : 0);
+        st.lo = op.src_lo + it.f * op.src_fstride;
+        st.extent = static_cast<int>(op.src_extent);
+        st.pitch = static_cast<int>(op.src_pitch);
+        st.foot = static_cast<int>(op.src - op.src_lo) + it.r_begin * st.pitch + c0 * xs;
+        st.rows_real = min(it.r_end, op.sh) - it.r_begin;
+        st.s_chunks = P.raw_pitch >> 4;
+        st.chunk_magic = P.chunk_magic;
+    }
+    const int rows_real = st.rows_real;
+    const unsigned mis0 = (static_cast<unsigned>(reinterpret_cast<uintptr_t>(st.lo)) + static_cast<unsigned>(st.foot)) & 15u;
+    const unsigned pmod = static_cast<unsigned>(st.pitch) & 15u;
+    const float h_addend = op.h_addend;
+    const float t_max = __int_as_float(32767);
+    const int block_chunks = kBlockRows * st.s_chunks;
+    const float *s_lane = S + hb;
+
+    // ---- vertical side ----
     const int x = it.slab * kSlabW + 4 * lane;
     const int dw = op.dw, dst_xstep = op.dst_xstep, dst_shift = op.dst_shift;
     const int dst_pitch = static_cast<int>(op.dst_pitch);
@@ -405,30 +317,58 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
     const float v_thr = op.v_thr, v_init = op.v_init;
     const int dcol = (x + op.dither_xoff) & 7;
     const float4 *rec = op.vrec + static_cast<size_t>(it.ya) * REC;
-    const unsigned ring_base = k_base;   // ring position of the item's first source row
-
-    float w[VT][4];
+    SlabRing<VT> ring;
 #pragma unroll
-    for (int s = 0; s < VT; ++s) w[s][0] = w[s][1] = w[s][2] = w[s][3] = 0.f;
-    // this row's coefficients in ring-slot order; the record's last float is the next row's first source row
+    for (int s = 0; s < VT; ++s) ring.w[s][0] = ring.w[s][1] = ring.w[s][2] = ring.w[s][3] = 0.f;
+    // the next output row's coefficients, in tap order
     float g[4 * REC];
 #pragma unroll
     for (int i = 0; i < REC; ++i) {
         const float4 v = __ldg(rec + i);
         g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
     }
-    // source rows are counted from the item's first one
-    const int rows_total = it.r_end - it.r_begin;
-    int first = 0;                  // first source row of the output row being waited for
-    int next_row = 0;               // next source row to pull from the ring
     int y = it.ya;
     const int yb = it.yb;
-    int slot = it.r_begin % VT;
-    const int slot_bias = it.r_begin;
+    const int *yend = op.yend + it.r_begin;      // indexed by source rows counted from the item's first one
+    int y_ready = min(__ldg(yend), yb);          // output rows complete once source row 0 is in (requested a row ahead)
 
-    // every output row whose last source row is now in the register ring; true once the item is finished
-    auto emit_ready = [&]() -> bool {
-        while (first + VT <= next_row) {
+    unsigned mis = mis0;
+    int row = 0;                    // next source row to filter
+
+    // One source row: the ring moves up by one row (ring.w[0] is the oldest row, ring.w[VT - 1] the newest: one code
+    // copy serves every row, at the price of 4 * (VT - 1) register moves), the horizontal pass fills the newest row,
+    // then every output row whose window ends here is produced.
+    auto row_body = [&](const float *sp) {
+#pragma unroll
+        for (int s = 0; s + 1 < VT; ++s) {
+#pragma unroll
+            for (int c = 0; c < 4; ++c) ring.w[s][c] = ring.w[s + 1][c];
+        }
+        float (&o)[4] = ring.w[VT - 1];
+        if (row < rows_real) {
+            const float *win = sp + (mis >> mshift);
+            float px[SPAN];
+#pragma unroll
+            for (int i = 0; i < SPAN; ++i) px[i] = win[i];
+            float t[4];
+#pragma unroll
+            for (int c = 0; c < 4; ++c) t[c] = px[0] * cd[c][0];
+#pragma unroll
+            for (int i = 1; i < SPAN; ++i) {
+#pragma unroll
+                for (int c = 0; c < 4; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
+            }
+            // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
+#pragma unroll
+            for (int c = 0; c < 4; ++c) o[c] = fminf(fma_rm(t[c], 0x1p-126f, h_addend), t_max);
+        } else {
+            o[0] = o[1] = o[2] = o[3] = 0.f;   // a row below the plane: zero weight in every window that reaches it
+        }
+        mis = (mis + pmod) & 15u;
+        ++row;
+        const int y_stop = y_ready;
+        y_ready = min(__ldg(yend + row), yb);    // for the next source row: the load has a whole row to land
+        while (y < y_stop) {
             float a[4];
             int4 dither = make_int4(0, 0, 0, 0);
             if (OUT == kOutU8Dither) {
@@ -443,23 +383,21 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
 #pragma unroll
             for (int s = 0; s < VT; ++s) {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) a[c] = fmaf(w[s][c], g[s], a[c]);
+                for (int c = 0; c < 4; ++c) a[c] = fmaf(ring.w[s][c], g[s], a[c]);
             }
-            const int first_next = __float_as_int(g[4 * REC - 1]) - slot_bias;
-            // the next row's record (the table carries a padding row); its latency hides under the rounding and the store
+            // the next output row's record (the table carries a padding row); the latency hides under the rounding,
+            // the store and, more often than not, the next source row's horizontal pass
             rec += REC;
 #pragma unroll
             for (int i = 0; i < REC; ++i) {
                 const float4 v = __ldg(rec + i);
                 g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
             }
-
             unsigned word[2];
             float r[4];
             const float worst = slab_finish<OUT>(a, dst_shift, word, r);
             if (worst >= v_thr) {
-                const uint2 fx = slab_fixup<VT, OUT>(m_lane, ring_base + static_cast<unsigned>(first), first + slot_bias,
-                                                     op.vring_i + static_cast<size_t>(y) * VT, v_thr, r[0], r[1], r[2], r[3], dither,
+                const uint2 fx = slab_fixup<VT, OUT>(ring, op.vring_i + static_cast<size_t>(y) * VT, v_thr, r[0], r[1], r[2], r[3], dither,
                                                      dst_shift, make_uint2(word[0], word[1]));
                 word[0] = fx.x; word[1] = fx.y;
             }
@@ -467,85 +405,59 @@ __device__ __forceinline__ void slab_consume(const SlabLaunchParams &P, const Sl
             else store_quad_slow<OUT>(drow, x, dw, dst_xstep, word);
             drow += dst_pitch;
             ++y;
-            if (y >= yb) return true;
-            if (first_next != first) {
-                // no pending output row starts at `first` any more: hand its ring row back to the producer
-                // (`first` moves by one row at a time: the plane is not shrunk vertically)
-                __syncwarp();
-                if (lane == 0) mbar_arrive(bar_empty + 8 * ((ring_base + static_cast<unsigned>(first)) & (kRing - 1)));
-                first = first_next;
-            }
         }
-        return false;
     };
 
-#define TVS_SLAB_STEP(s)                                                                            \
-    case s:                                                                                         \
-        if constexpr (s < VT) {                                                                     \
-            const unsigned kk = ring_base + static_cast<unsigned>(next_row);                        \
-            mbar_wait<100>(bar_full + 8 * (kk & (kRing - 1)), (kk / kRing) & 1);                    \
-            const float4 v = *reinterpret_cast<const float4 *>(m_lane + (kk & (kRing - 1)) * kSlabW); \
-            w[s][0] = v.x; w[s][1] = v.y; w[s][2] = v.z; w[s][3] = v.w;                             \
-            ++next_row;                                                                             \
-            if (emit_ready()) break;                                                                \
-        }
-    bool done = false;
-    while (!done) {
-        switch (slot) {
-            TVS_SLAB_STEP(0) TVS_SLAB_STEP(1) TVS_SLAB_STEP(2) TVS_SLAB_STEP(3)
-            TVS_SLAB_STEP(4) TVS_SLAB_STEP(5) TVS_SLAB_STEP(6) TVS_SLAB_STEP(7)
-            slot = 0;
-            continue;
-        }
-        done = true;
+    // prologue: the first kRawBlocks - 1 blocks are on their way before anything is converted
+#pragma unroll 1
+    for (int b = 0; b < kRawBlocks - 1; ++b) {
+        if (b < n_blocks) slab_prefetch_block(st, b * kBlockRows, RAW + b * block_chunks, lane);
+        cp_async_commit();
     }
-#undef TVS_SLAB_STEP
-    // hand back the rows the last output rows were still holding (every row of the item is released exactly once)
-    __syncwarp();
-    if (lane == 0) {
-        for (int r = first; r < rows_total; ++r) mbar_arrive(bar_empty + 8 * ((ring_base + static_cast<unsigned>(r)) & (kRing - 1)));
+#pragma unroll 1
+    for (int b = 0; b < n_blocks; ++b) {
+        cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
+        __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
+        slab_convert_block(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
+                           src_shift, mis0, pmod, b * kBlockRows, lane);
+        __syncwarp();                              // S is complete; the raw block is free again
+        if (b + kRawBlocks - 1 < n_blocks)
+            slab_prefetch_block(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
+        cp_async_commit();
+
+        const int rows_here = min(kBlockRows, rows_total - row);
+        const float *sp = s_lane;
+#pragma unroll 1
+        for (int rr = 0; rr < rows_here; ++rr, sp += s_pitch) {
+            row_body(sp);
+        }
     }
+    cp_async_wait_pending<0>();
 }
 
 template <int SPAN, int VT, int OUT>
 __global__ void __launch_bounds__(kSlabThreads, TVS_SLAB_MIN_CTAS)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
-    float *M = smem;                                                       // [kRing][128] intermediate t * 2^-149
-    float *S = M + kRing * kSlabW;                                         // [kBlockRows][raw_pitch] floats at most, + a zero tail
+    float *S = smem;                                                       // [kBlockRows][raw_pitch] floats at most, + a zero tail
     const int s_floats = kBlockRows * P.raw_pitch + 32;
     uint4 *RAW = reinterpret_cast<uint4 *>(S + s_floats);                  // [kRawBlocks][kBlockRows][raw_pitch / 16] chunks
-    unsigned long long *BAR = reinterpret_cast<unsigned long long *>(RAW + kRawBlocks * kBlockRows * (P.raw_pitch >> 4));   // full[kRing], empty[kRing]
-    const unsigned bar_full = static_cast<unsigned>(__cvta_generic_to_shared(BAR));
-    const unsigned bar_empty = bar_full + 8 * kRing;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    if (threadIdx.x == 0) {
-        for (int i = 0; i < 2 * kRing; ++i) mbar_init(bar_full + 8 * i, 1);
-        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        // every ring row starts out free: complete phase 0 of the empty barriers, so that the producer's n-th use of a
-        // row always waits for phase n (the consumer's release of use n - 1)
-        for (int i = 0; i < kRing; ++i) mbar_arrive(bar_empty + 8 * i);
-    }
+    const int lane = threadIdx.x;
     // converted rows are read a little past their last written sample (dense windows of the slab's last columns run
     // into the next row, the last row's into the tail): those floats must be finite
-    for (int i = threadIdx.x; i < s_floats; i += kSlabThreads) S[i] = 0.f;
-    __syncthreads();
+    for (int i = lane; i < s_floats; i += kSlabThreads) S[i] = 0.f;
+    __syncwarp();
 
-    unsigned k_base = 0;   // intermediate rows produced / consumed so far: the ring position both warps agree on
 #pragma unroll 1
     for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
         const SlabItem it = decode_item(P, item, VT);
-        if (warp == 0) {
-            slab_produce<SPAN>(P, it, M, S, RAW, bar_full, bar_empty, k_base, lane);
-        } else {
-            const SlabOpParams &op = P.op[it.oi];
-            constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
-            const uintptr_t d0 = reinterpret_cast<uintptr_t>(op.dst + it.f * op.dst_fstride) + static_cast<uintptr_t>(it.slab * kSlabW) * kSample;
-            const bool fast = op.dst_xstep == kSample && (op.dst_pitch & kAlign) == 0 && (d0 & kAlign) == 0 && (it.slab + 1) * kSlabW <= op.dw;
-            if (fast) slab_consume<VT, OUT, true>(P, it, M, bar_full, bar_empty, k_base, lane);
-            else slab_consume<VT, OUT, false>(P, it, M, bar_full, bar_empty, k_base, lane);
-        }
-        k_base += static_cast<unsigned>(it.r_end - it.r_begin);
+        const SlabOpParams &op = P.op[it.oi];
+        constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
+        const uintptr_t d0 = reinterpret_cast<uintptr_t>(op.dst + it.f * op.dst_fstride) + static_cast<uintptr_t>(it.slab * kSlabW) * kSample;
+        const bool fast = op.dst_xstep == kSample && (op.dst_pitch & kAlign) == 0 && (d0 & kAlign) == 0 && (it.slab + 1) * kSlabW <= op.dw;
+        if (fast) slab_run_item<SPAN, VT, OUT, true>(P, it, S, RAW, lane);
+        else slab_run_item<SPAN, VT, OUT, false>(P, it, S, RAW, lane);
+        __syncwarp();
     }
 }
 
@@ -572,7 +484,7 @@ struct SlabOp {
     int n_groups = 0, n_slabs = 0;
     int s_pitch = 0, raw_pitch = 0;
     float v_thr = 0, v_init = 0, h_addend = 0;
-    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, vrec_off = 0, vring_i_off = 0;
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, yend_off = 0, vrec_off = 0, vring_i_off = 0;
 };
 
 struct SlabPlan {
@@ -582,8 +494,7 @@ struct SlabPlan {
     int device = 0, sm_count = 148;
 };
 
-// The float vertical sum of this kernel runs in ring-slot order, slot = source_row % VT, one scalar FMA per slot:
-// follow that order row by row (each FMA rounds by at most half an ulp of its own partial sum, bounded through
+// The float vertical sum of this kernel runs in tap order, one scalar FMA per tap: follow that order row by row (each FMA rounds by at most half an ulp of its own partial sum, bounded through
 // |t| <= 32767) instead of charging every tap half an ulp of the largest possible sum.
 static VerticalFloatRule slab_vertical_rule(const AxisTable &v, int vt_inst, bool out10, bool dither) {
     const VerticalFloatRule coarse = vertical_float_rule(v, vt_inst, out10, dither);
@@ -594,7 +505,7 @@ static VerticalFloatRule slab_vertical_rule(const AxisTable &v, int vt_inst, boo
     std::vector<int> by_slot(vt_inst);
     for (int y = 0; y < v.length; ++y) {
         std::fill(by_slot.begin(), by_slot.end(), 0);
-        for (int j = 0; j < v.taps; ++j) by_slot[(v.pos[y] + j) % vt_inst] = std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
+        for (int j = 0; j < v.taps; ++j) by_slot[j] = std::abs(static_cast<int>(v.coef[static_cast<size_t>(y) * v.taps + j]));
         double run = init_abs, e = 0.0;
         for (int s = 0; s < vt_inst; ++s) {
             if (!by_slot[s]) continue;   // a zero coefficient leaves the accumulator unchanged, exactly
@@ -689,7 +600,7 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         so.s_pitch = ((s_chunks * (16 / op.src_xstep) + SPAN + 3) & ~3) + 4;
 
         const int rows = op.dh + 1;   // one padding row: the consumer requests a row's record one row ahead
-        const int rec = VT <= 6 ? 8 : 12;   // floats per record (SlabRec)
+        const int rec = VT <= 4 ? 4 : 8;   // floats per record (SlabRec)
         std::vector<float> vrec(static_cast<size_t>(rows) * rec, 0.0f);
         std::vector<int> vring_i(static_cast<size_t>(rows) * VT, 0);
         std::vector<int> vpos(rows, v.pos[op.dh - 1]);
@@ -698,17 +609,24 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             if (y < op.dh) {
                 for (int j = 0; j < v.taps; ++j) {
                     const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
-                    const int slot = (v.pos[y] + j) % VT;
-                    vrec[static_cast<size_t>(y) * rec + slot] = std::ldexp(static_cast<float>(c), 107);
-                    vring_i[static_cast<size_t>(y) * VT + slot] = c;
+                    vrec[static_cast<size_t>(y) * rec + j] = std::ldexp(static_cast<float>(c), 107);
+                    vring_i[static_cast<size_t>(y) * VT + j] = c;
                 }
             }
-            const int next_first = vpos[std::min(y + 1, rows - 1)];
-            memcpy(&vrec[static_cast<size_t>(y) * rec + rec - 1], &next_first, sizeof(int));
+        }
+        // yend[r]: output rows whose VT-row window [pos, pos + VT) ends at or before source row r
+        std::vector<int> yend(op.sh + VT + 1, op.dh);
+        {
+            int y = 0;
+            for (int r = 0; r < op.sh + VT + 1; ++r) {
+                while (y < op.dh && v.pos[y] + VT - 1 <= r) ++y;
+                yend[r] = y;
+            }
         }
         so.hdense_off = slab_append(blob, hdense);
         so.hbase_off = slab_append(blob, hbase);
         so.vpos_off = slab_append(blob, vpos);
+        so.yend_off = slab_append(blob, yend);
         so.vrec_off = slab_append(blob, vrec);
         so.vring_i_off = slab_append(blob, vring_i);
         sp->ops.push_back(so);
@@ -748,7 +666,24 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
         int min_dh = 1 << 30;
         for (size_t j : members) min_dh = std::min(min_dh, plan.ops[p->ops[j].op_index].dh);
         int chunk_rows = std::max(64, std::min(min_dh, 1024));
-        const long long slots = static_cast<long long>(kSlabCtasPerSM) * p->sm_count;
+        const SlabKernelFn fn = kSlabInstances[p->ops[i].instance].fn[p->ops[i].out_mode];
+        size_t smem = 0;
+        {
+            int raw_pitch = 0;
+            for (size_t j : members) raw_pitch = std::max(raw_pitch, p->ops[j].raw_pitch);
+            smem = (static_cast<size_t>(kBlockRows) * raw_pitch + 32) * 4 + static_cast<size_t>(kRawBlocks) * kBlockRows * raw_pitch;
+        }
+        if (smem > 48 * 1024) cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
+        // Some twenty one-warp CTAs share an SM.  Ask for a shared-memory carve-out that holds them (the default sizes it
+        // for far fewer) but no more: the rest of the 256 KB stays L1, which serves the vertical tables and the source rows.
+        {
+            const size_t want = 24 * (smem + 1024);
+            int pct = static_cast<int>((want * 100 + (228 << 10) - 1) / (228 << 10));
+            cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributePreferredSharedMemoryCarveout, std::min(100, std::max(pct, 15)));
+        }
+        int resident = 0;
+        if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&resident, fn, kSlabThreads, smem) != cudaSuccess || resident < 1) return -1;
+        const long long slots = static_cast<long long>(resident) * p->sm_count;
         for (;;) {
             long long items = 0;
             for (size_t j : members) {
@@ -776,6 +711,7 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
             q.hdense = reinterpret_cast<const float *>(p->blob + so.hdense_off);
             q.hbase = reinterpret_cast<const int *>(p->blob + so.hbase_off);
             q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
+            q.yend = reinterpret_cast<const int *>(p->blob + so.yend_off);
             q.vrec = reinterpret_cast<const float4 *>(p->blob + so.vrec_off);
             q.vring_i = reinterpret_cast<const int *>(p->blob + so.vring_i_off);
             q.src_lo = s.base - op.src_offset;
@@ -790,12 +726,6 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
         const long long total = static_cast<long long>(items) * n_frames;
         if (total > 0x7fffffffLL) return -1;
         lp.n_items = static_cast<int>(total);
-        const size_t smem = static_cast<size_t>(kRing) * kSlabW * 4 + (static_cast<size_t>(kBlockRows) * lp.raw_pitch + 32) * 4 +
-                            static_cast<size_t>(kRawBlocks) * kBlockRows * lp.raw_pitch + 2 * kRing * 8;
-        const SlabKernelFn fn = kSlabInstances[p->ops[i].instance].fn[p->ops[i].out_mode];
-        if (smem > 48 * 1024) cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributeMaxDynamicSharedMemorySize, static_cast<int>(smem));
-        // 14-16 CTAs of ~12 KB each share an SM: ask for the large shared-memory carve-out (the default sized it for 5)
-        cudaFuncSetAttribute(reinterpret_cast<const void *>(fn), cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared);
         const int grid = static_cast<int>(std::min<long long>(total, slots));
         fn<<<grid, kSlabThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
