@@ -159,3 +159,161 @@ def test_decode_scale_encode_smoke_with_opencv(tmp_path):
     ok, frame = cap.read()
     cap.release()
     assert ok and frame.shape == (720, 960, 3)
+
+
+# ---- the task with the reference's signature (worker/tasks.py:1354-1366): argv of both children, status dicts ----------
+class _FakeProc:
+    def __init__(self, argv, stdout=None, stdin=None, stderr=None, rc=0, on_wait=None):
+        self.argv, self.stdout, self.stdin, self.stderr, self.rc, self.on_wait = argv, stdout, stdin, stderr, rc, on_wait
+        self.terminated = False
+
+    def wait(self, timeout=None):
+        if self.on_wait:
+            self.on_wait()
+        return self.rc
+
+    def terminate(self):
+        self.terminated = True
+
+    def kill(self):
+        self.terminated = True
+
+
+def _task_env(tmp_path, job, data, w, h, rc_enc=0, halted=lambda job_id: False, make_output=True):
+    from thinvids_b200 import worker
+    procs, beats, fields = [], [], {}
+    sink = io.BytesIO()
+    sink.close = lambda: None   # keep the encoder's stdin readable after the task closes it
+
+    def popen(argv, **kw):
+        if argv[-1] == "pipe:1":
+            pr = _FakeProc(argv, stdout=io.BytesIO(data))
+        else:
+            def touch():
+                if make_output:
+                    open(argv[-1], "wb").write(b"mp4")
+            pr = _FakeProc(argv, stdin=sink, stderr=io.BytesIO(b"frame=1\nprogress=continue\nprogress=end\n"), rc=rc_enc, on_wait=touch)
+        procs.append(pr)
+        return pr
+
+    uploads = []
+    env = worker.EncodeEnv(job_fields=lambda job_id: job, probe=lambda path: (w, h, "yuv420p", 24.0),
+                           set_job_fields=lambda job_id, m: fields.update(m), is_halted=halted,
+                           heartbeat=lambda job_id, stage, force=False, note="": beats.append(stage),
+                           base_dir=lambda job_id: str(tmp_path / job_id), popen=popen, scaler_factory=_StandIn,
+                           fetch_part=lambda job_id, idx, host, path: open(path, "wb").write(b"ts"),
+                           upload_result=lambda job_id, idx, host, path: uploads.append((host, os.path.basename(path))))
+    worker.configure(env)
+    return env, procs, beats, fields, uploads, sink
+
+
+import os  # noqa: E402
+
+
+def test_encode_task_vaapi_branch_builds_the_references_commands(tmp_path):
+    from thinvids_b200 import worker
+    _, data = _raw(F.YUV420P, 720, 480, 3)
+    env, procs, beats, fields, uploads, sink = _task_env(tmp_path, {"target_height": "1080", "software_encode": "0"}, data, 720, 480)
+    res = worker.encode("job1", 7, "http://master:8000", stitch_host="http://stitch:8000")
+    assert res == {"status": "COMPLETED", "idx": 7}
+    base = str(tmp_path / "job1")
+    dec, enc = procs[0].argv, procs[1].argv
+    assert dec == ["ffmpeg", "-hide_banner", "-nostats", "-loglevel", "error", "-fflags", "+genpts", "-i", f"{base}/in_007.ts",
+                   "-map", "0:v:0", "-an", "-sn", "-dn", "-vf", "setpts=PTS-STARTPTS", "-f", "rawvideo", "-pix_fmt", "yuv420p", "pipe:1"]
+    assert enc == ["ffmpeg", "-hide_banner", "-nostats", "-loglevel", "error", "-y", "-progress", "pipe:2",
+                   "-vaapi_device", "/dev/dri/renderD128", "-f", "rawvideo", "-pix_fmt", "nv12", "-s", "1620x1080", "-r", "24.000000",
+                   "-i", "pipe:0", "-fflags", "+genpts", "-i", f"{base}/in_007.ts", "-map", "0:v:0", "-map", "1:a?", "-vf", "hwupload",
+                   "-c:v", "h264_vaapi", "-rc_mode", "CQP", "-qp", "27", "-c:a", "aac", "-ac", "2", "-b:a", "192k", f"{base}/out_007.mp4"]
+    assert len(sink.getvalue()) == 3 * 1620 * 1080 * 3 // 2
+    assert fields == {"target_height_effective": 1080, "deinterlace_effective": "0"}
+    assert uploads == [("http://stitch:8000", "out_007.mp4")]
+    assert beats[0] == "encode_prepare" and "encode_start" in beats and beats[-1] == "upload_start"
+
+
+def test_encode_task_software_dvd_branch_deinterlaces_in_the_decode_child(tmp_path):
+    from thinvids_b200 import worker
+    _, data = _raw(F.YUV420P, 720, 480, 2)
+    job = {"target_height": "1080", "software_encode": "1", "filename": "/watch/dvd/movie.mkv", "source_codec": "mpeg2video",
+           "source_resolution": "720x480"}
+    env, procs, *_ = _task_env(tmp_path, job, data, 720, 480)
+    res = worker.encode("job2", 0, "http://master:8000", v_sel=1, a_sel=2, source_path="/src/movie.mkv", source_start_s=12.5,
+                        source_duration_s=10.0)
+    assert res == {"status": "COMPLETED", "idx": 0}
+    dec, enc = procs[0].argv, procs[1].argv
+    vf = dec[dec.index("-vf") + 1]
+    assert vf == "setpts=PTS-STARTPTS,bwdif=mode=send_frame:parity=auto:deint=all"     # DVD sources keep their height and de-interlace
+    assert dec[5:11] == ["-ss", "12.500000", "-i", "/src/movie.mkv", "-t", "10.000000"] and dec[dec.index("-map") + 1] == "0:v:1"
+    assert enc[enc.index("-s") + 1] == "720x480" and enc[enc.index("-pix_fmt") + 1] == "yuv420p"
+    tail = enc[enc.index("pipe:0") + 1:]
+    assert tail[:6] == ["-ss", "12.500000", "-i", "/src/movie.mkv", "-t", "10.000000"]
+    assert tail[6:] == ["-map", "0:v:0", "-map", "1:a:2?", "-sn", "-dn", "-map_metadata", "-1", "-map_chapters", "-1",
+                        "-c:v", "libx264", "-preset", "veryfast", "-crf", "23", "-c:a", "aac", "-ac", "2", "-b:a", "192k",
+                        enc[-1]]
+
+
+def test_encode_task_status_dicts(tmp_path):
+    from thinvids_b200 import worker
+    _, data = _raw(F.YUV420P, 64, 48, 2)
+    job = {"target_height": "720", "software_encode": "1"}
+    env, procs, *_ = _task_env(tmp_path, job, data, 64, 48)
+    env.token_is_current = lambda job_id, tok: tok == "current"
+    assert worker.encode("j", 1, "m", run_token="old") == {"status": "STALE", "job_id": "j", "idx": 1}
+    env, procs, *_ = _task_env(tmp_path, job, data, 64, 48, halted=lambda job_id: True)
+    assert worker.encode("j", 1, "m") == {"status": "ABORTED"} and not procs
+    env, procs, *_ = _task_env(tmp_path, job, data, 64, 48, rc_enc=1)
+    res = worker.encode("j", 1, "m")
+    assert res["status"] == "FAILED" and res["stage"] == "encode" and "ffmpeg rc=1" in res["reason"] and "progress=end" in res["reason"]
+    env, procs, *_ = _task_env(tmp_path, job, data, 64, 48, make_output=False)
+    assert worker.encode("j", 2, "m")["status"] == "FAILED"
+    n = {"calls": 0}
+
+    def halted_late(job_id):
+        n["calls"] += 1
+        return n["calls"] > 5
+    env, procs, *_ = _task_env(tmp_path, job, data, 64, 48, halted=halted_late)
+    env.batch_frames = 1
+    assert worker.encode("j", 3, "m") == {"status": "ABORTED"} and procs[0].terminated and procs[1].terminated
+
+
+def test_decoder_surface_descriptor():
+    from thinvids_b200.worker import DecoderSurface
+    s = DecoderSurface(dev_ptr=0x1000, pitch=2048, width=1920, height=1080, aligned_height=1088, frame_stride=2048 * 1088 * 3 // 2)
+    ptrs, pitch, fstride = s.plane_args()
+    assert s.fmt == "nv12" and ptrs == [0x1000, 0x1000 + 2048 * 1088] and pitch == [2048, 2048] and fstride == [s.frame_stride] * 2
+    assert DecoderSurface(0, 4096, 1920, 1080, bit_depth=10).fmt == "p010le"
+    assert DecoderSurface(0, 1024, 720, 479).chroma_offset == 1024 * 480
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("depth,w,h,aligned_h,pitch,dw,dh", [(8, 720, 480, 480, 768, 1620, 1080), (10, 1920, 1080, 1088, 4096, 1280, 720),
+                                                               (8, 1280, 718, 720, 1280, 1920, 1078)])
+def test_decoder_surfaces_are_scaled_in_place(depth, w, h, aligned_h, pitch, dw, dh):
+    """A batch of NVDEC-layout surfaces (luma, then interleaved chroma `pitch x aligned_height` further down, P016 for
+    10-bit streams) goes through tvs_scale_batch without a copy or a repack and matches the oracle."""
+    import torch
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    from thinvids_b200.worker import DecoderSurface, scale_surfaces
+    fmt = "nv12" if depth == 8 else "p010le"
+    n = 3
+    frames = [F.random_frame(fmt, w, h, 900 + i) for i in range(n)]
+    surface_bytes = pitch * aligned_h * 3 // 2
+    host = np.full((n, surface_bytes), 0xEE, dtype=np.uint8)
+    bps = 1 if depth == 8 else 2
+    for i, (y, uv) in enumerate(frames):
+        img = host[i].reshape(aligned_h * 3 // 2, pitch)
+        img[:h, :w * bps] = y.view(np.uint8).reshape(h, w * bps)
+        img[aligned_h:aligned_h + (h + 1) // 2, :uv.shape[1] * bps] = uv.view(np.uint8).reshape(uv.shape[0], uv.shape[1] * bps)
+    d_src = torch.from_numpy(host).cuda()
+    surf = DecoderSurface(dev_ptr=d_src.data_ptr(), pitch=pitch, width=w, height=h, aligned_height=aligned_h, bit_depth=depth,
+                          frame_stride=surface_bytes)
+    with Scaler(w, h, fmt, dw, dh, "nv12", "bicubic") as sc:
+        out = torch.zeros((n, sc.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+        dp, ds, df = sc.dst_layout.pointer_args(out.data_ptr())
+        scale_surfaces(sc, surf, list(dp)[:2], list(ds)[:2], list(df)[:2], n, torch.cuda.current_stream().cuda_stream)
+        torch.cuda.synchronize()
+        got = sc.dst_layout.unpack(out.cpu().numpy())
+    o = port.PortScaler(w, h, F.fmt_code(fmt), dw, dh, F.NV12, F.SWS_BICUBIC)
+    for fr, g in zip(frames, got):
+        for a, b in zip(g, o.scale(fr)):
+            assert np.array_equal(a, b)

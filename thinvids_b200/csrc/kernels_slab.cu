@@ -56,10 +56,7 @@ struct SlabOpParams {
     const float *hdense;   // [n_groups][4][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
     const int *hbase;      // [n_groups]           first source column of the group's span
     const int *vpos;       // [dh + 1]             first source row of each output row (one padding entry)
-    const int *yend;       // [sh + VT + 1]        yend[r] = number of output rows whose window ends at or before source row r
-                           //                      (with VT-row windows): after row r, rows y < yend[r] can be produced
-    const float4 *vrec;    // [dh + 1][REC]        per output row: VT coefficients g * 2^107 in tap order
-    const int *vring_i;    // [dh + 1][VT]         the same coefficients as integers (exact path)
+    int vclass;            // which SlabVClass of the launch holds this plane's vertical tables
     const uint8_t *src_lo; // first byte of the stored source plane (frame 0) and its extent: bounds for 16-byte reads
     size_t src_extent;
     float v_thr, v_init;
@@ -69,8 +66,21 @@ struct SlabOpParams {
     int dst_shift, dither_xoff;
 };
 
+// Vertical tables of one plane geometry (luma, or the two chroma planes), held in the kernel parameters: the constant
+// bank serves them through the uniform datapath, so the coefficients of an output row cost no vector registers, no
+// global loads and no latency to speak of.  Up-scale tables repeat (480 -> 1080 has 9 distinct rows plus a few edge
+// rows), so the rows are stored once and indexed per output row.
+constexpr int kSlabMaxDistinct = 48;     // distinct coefficient rows per geometry
+constexpr int kSlabMaxRows = 4352;       // output rows (and source rows + taps) per plane
+struct SlabVClass {
+    float4 coef[kSlabMaxDistinct][2];    // VT coefficients g * 2^107 in tap order, zero padded to 8
+    unsigned short yend[kSlabMaxRows];   // yend[r] = output rows whose VT-row window ends at or before source row r
+    unsigned char idx[kSlabMaxRows];     // coefficient row of each output row
+};
+
 struct SlabLaunchParams {
     SlabOpParams op[kMaxSlabOps];
+    SlabVClass vc[2];
     int n_ops;
     int items_per_frame, n_items;
     int raw_pitch;         // bytes per staged raw row (multiple of 16); a converted row holds raw_pitch / sample spacing floats
@@ -200,15 +210,16 @@ template <int VT> struct SlabRing { float w[VT][4]; };
 // Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: the
 // intermediates are the bit patterns held in the ring, the coefficients the integer copy of the row's record.
 template <int VT, int OUT>
-__device__ __noinline__ uint2 slab_fixup(SlabRing<VT> ring, const int *exact_coef, float v_thr, float r0, float r1, float r2, float r3,
+__device__ __noinline__ uint2 slab_fixup(SlabRing<VT> ring, float4 g0, float4 g1, float v_thr, float r0, float r1, float r2, float r3,
                                          int4 dither, int dst_shift, uint2 packed) {
     unsigned word[2] = {packed.x, packed.y};
     const float r[4] = {r0, r1, r2, r3};
     const int d[4] = {dither.x, dither.y, dither.z, dither.w};
     int a[4] = {0, 0, 0, 0};
+    const float gf[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
 #pragma unroll
     for (int s = 0; s < VT; ++s) {
-        const int c = __ldg(exact_coef + s);
+        const int c = static_cast<int>(gf[s] * 0x1p-107f);   // the table holds c * 2^107, exactly
 #pragma unroll
         for (int k = 0; k < 4; ++k) a[k] += subnormal_to_int(ring.w[s][k]) * c;
     }
@@ -254,15 +265,12 @@ __device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift,
     return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
 }
 
-// float4s per output row of the vertical table: VT coefficients, zero padded
-template <int VT> struct SlabRec { static constexpr int kFloat4s = VT <= 4 ? 1 : 2; };
-
 // FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
 // vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
 template <int SPAN, int VT, int OUT, bool FAST>
 __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
-    constexpr int REC = SlabRec<VT>::kFloat4s;
     const SlabOpParams &op = P.op[it.oi];
+    const SlabVClass &vc = P.vc[op.vclass];
 
     // ---- horizontal side: this lane's 4 output columns, dense coefficients over their common source span ----
     const int g_first = it.slab * (kSlabW / 4);
@@ -316,21 +324,12 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     if (FAST) drow += static_cast<ptrdiff_t>(x) * (OUT == kOutU10 ? 2 : 1);    // this lane's first sample of the row
     const float v_thr = op.v_thr, v_init = op.v_init;
     const int dcol = (x + op.dither_xoff) & 7;
-    const float4 *rec = op.vrec + static_cast<size_t>(it.ya) * REC;
     SlabRing<VT> ring;
 #pragma unroll
     for (int s = 0; s < VT; ++s) ring.w[s][0] = ring.w[s][1] = ring.w[s][2] = ring.w[s][3] = 0.f;
-    // the next output row's coefficients, in tap order
-    float g[4 * REC];
-#pragma unroll
-    for (int i = 0; i < REC; ++i) {
-        const float4 v = __ldg(rec + i);
-        g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
-    }
     int y = it.ya;
     const int yb = it.yb;
-    const int *yend = op.yend + it.r_begin;      // indexed by source rows counted from the item's first one
-    int y_ready = min(__ldg(yend), yb);          // output rows complete once source row 0 is in (requested a row ahead)
+    const int r_begin = it.r_begin;
 
     unsigned mis = mis0;
     int row = 0;                    // next source row to filter
@@ -366,9 +365,11 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
         }
         mis = (mis + pmod) & 15u;
         ++row;
-        const int y_stop = y_ready;
-        y_ready = min(__ldg(yend + row), yb);    // for the next source row: the load has a whole row to land
+        const int y_stop = min(static_cast<int>(vc.yend[r_begin + row - 1]), yb);   // rows complete now that this source row is in
         while (y < y_stop) {
+            const int id = vc.idx[y];
+            const float4 g0 = vc.coef[id][0], g1 = vc.coef[id][1];
+            const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
             float a[4];
             int4 dither = make_int4(0, 0, 0, 0);
             if (OUT == kOutU8Dither) {
@@ -385,20 +386,11 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 #pragma unroll
                 for (int c = 0; c < 4; ++c) a[c] = fmaf(ring.w[s][c], g[s], a[c]);
             }
-            // the next output row's record (the table carries a padding row); the latency hides under the rounding,
-            // the store and, more often than not, the next source row's horizontal pass
-            rec += REC;
-#pragma unroll
-            for (int i = 0; i < REC; ++i) {
-                const float4 v = __ldg(rec + i);
-                g[4 * i] = v.x; g[4 * i + 1] = v.y; g[4 * i + 2] = v.z; g[4 * i + 3] = v.w;
-            }
             unsigned word[2];
             float r[4];
             const float worst = slab_finish<OUT>(a, dst_shift, word, r);
             if (worst >= v_thr) {
-                const uint2 fx = slab_fixup<VT, OUT>(ring, op.vring_i + static_cast<size_t>(y) * VT, v_thr, r[0], r[1], r[2], r[3], dither,
-                                                     dst_shift, make_uint2(word[0], word[1]));
+                const uint2 fx = slab_fixup<VT, OUT>(ring, g0, g1, v_thr, r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
                 word[0] = fx.x; word[1] = fx.y;
             }
             if (FAST) store_quad_fast<OUT>(drow, 0, word);
@@ -484,7 +476,11 @@ struct SlabOp {
     int n_groups = 0, n_slabs = 0;
     int s_pitch = 0, raw_pitch = 0;
     float v_thr = 0, v_init = 0, h_addend = 0;
-    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0, yend_off = 0, vrec_off = 0, vring_i_off = 0;
+    size_t hdense_off = 0, hbase_off = 0, vpos_off = 0;
+    int vtable = 0;                         // which vertical table of the context (2 luma, 3 chroma): planes that share it share a class
+    std::vector<float> vcoef;               // [n_distinct][8]  distinct coefficient rows, c * 2^107 in tap order
+    std::vector<unsigned char> vidx;        // [dh]             coefficient row of each output row
+    std::vector<unsigned short> vyend;      // [sh + VT + 1]    see SlabVClass
 };
 
 struct SlabPlan {
@@ -599,36 +595,37 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         // a converted row holds (16 / spacing) samples per chunk, and a lane's window may start up to SPAN short of its end
         so.s_pitch = ((s_chunks * (16 / op.src_xstep) + SPAN + 3) & ~3) + 4;
 
-        const int rows = op.dh + 1;   // one padding row: the consumer requests a row's record one row ahead
-        const int rec = VT <= 4 ? 4 : 8;   // floats per record (SlabRec)
-        std::vector<float> vrec(static_cast<size_t>(rows) * rec, 0.0f);
-        std::vector<int> vring_i(static_cast<size_t>(rows) * VT, 0);
-        std::vector<int> vpos(rows, v.pos[op.dh - 1]);
+        std::vector<int> vpos(op.dh + 1, v.pos[op.dh - 1]);
         for (int y = 0; y < op.dh; ++y) vpos[y] = v.pos[y];
-        for (int y = 0; y < rows; ++y) {
-            if (y < op.dh) {
-                for (int j = 0; j < v.taps; ++j) {
-                    const int c = v.coef[static_cast<size_t>(y) * v.taps + j];
-                    vrec[static_cast<size_t>(y) * rec + j] = std::ldexp(static_cast<float>(c), 107);
-                    vring_i[static_cast<size_t>(y) * VT + j] = c;
-                }
+        // vertical tables for the kernel parameters: distinct coefficient rows, a row index per output row, and per
+        // source row the number of output rows whose VT-row window [pos, pos + VT) ends at or before it
+        if (op.dh > kSlabMaxRows || op.sh + VT + 1 > kSlabMaxRows) { err = "plane taller than the slab kernel's tables"; delete sp; return nullptr; }
+        so.vtable = op.vtable;
+        so.vidx.resize(op.dh);
+        for (int y = 0; y < op.dh; ++y) {
+            float row[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            for (int j = 0; j < v.taps; ++j) row[j] = std::ldexp(static_cast<float>(v.coef[static_cast<size_t>(y) * v.taps + j]), 107);
+            int id = -1;
+            for (size_t k = 0; k + 8 <= so.vcoef.size() && id < 0; k += 8)
+                if (memcmp(&so.vcoef[k], row, sizeof row) == 0) id = static_cast<int>(k / 8);
+            if (id < 0) {
+                id = static_cast<int>(so.vcoef.size() / 8);
+                if (id >= kSlabMaxDistinct) { err = "too many distinct vertical coefficient rows (not a repeating ratio)"; delete sp; return nullptr; }
+                so.vcoef.insert(so.vcoef.end(), row, row + 8);
             }
+            so.vidx[y] = static_cast<unsigned char>(id);
         }
-        // yend[r]: output rows whose VT-row window [pos, pos + VT) ends at or before source row r
-        std::vector<int> yend(op.sh + VT + 1, op.dh);
+        so.vyend.assign(op.sh + VT + 1, static_cast<unsigned short>(op.dh));
         {
             int y = 0;
             for (int r = 0; r < op.sh + VT + 1; ++r) {
                 while (y < op.dh && v.pos[y] + VT - 1 <= r) ++y;
-                yend[r] = y;
+                so.vyend[r] = static_cast<unsigned short>(y);
             }
         }
         so.hdense_off = slab_append(blob, hdense);
         so.hbase_off = slab_append(blob, hbase);
         so.vpos_off = slab_append(blob, vpos);
-        so.yend_off = slab_append(blob, yend);
-        so.vrec_off = slab_append(blob, vrec);
-        so.vring_i_off = slab_append(blob, vring_i);
         sp->ops.push_back(so);
     }
     if (sp->ops.empty()) { err = "nothing to scale"; delete sp; return nullptr; }
@@ -694,6 +691,7 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
             chunk_rows = std::max(64, chunk_rows / 2);
         }
         int items = 0;
+        int n_classes = 0, class_vtable[2] = {-1, -1};
         for (size_t j : members) {
             const SlabOp &so = p->ops[j];
             const PlaneOp &op = plan.ops[so.op_index];
@@ -711,9 +709,19 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
             q.hdense = reinterpret_cast<const float *>(p->blob + so.hdense_off);
             q.hbase = reinterpret_cast<const int *>(p->blob + so.hbase_off);
             q.vpos = reinterpret_cast<const int *>(p->blob + so.vpos_off);
-            q.yend = reinterpret_cast<const int *>(p->blob + so.yend_off);
-            q.vrec = reinterpret_cast<const float4 *>(p->blob + so.vrec_off);
-            q.vring_i = reinterpret_cast<const int *>(p->blob + so.vring_i_off);
+            // planes with the same vertical table (the two chroma planes) share a class
+            int cls = -1;
+            for (int k = 0; k < n_classes; ++k) if (class_vtable[k] == so.vtable) cls = k;
+            if (cls < 0) {
+                if (n_classes == 2) return -1;
+                cls = n_classes++;
+                class_vtable[cls] = so.vtable;
+                SlabVClass &vc = lp.vc[cls];
+                memcpy(vc.coef, so.vcoef.data(), so.vcoef.size() * sizeof(float));
+                memcpy(vc.idx, so.vidx.data(), so.vidx.size());
+                memcpy(vc.yend, so.vyend.data(), so.vyend.size() * sizeof(unsigned short));
+            }
+            q.vclass = cls;
             q.src_lo = s.base - op.src_offset;
             q.src_extent = static_cast<size_t>(op.sh - 1) * static_cast<size_t>(s.pitch) + static_cast<size_t>(op.sw) * op.src_xstep;
             q.v_thr = so.v_thr; q.v_init = so.v_init; q.h_addend = so.h_addend;
