@@ -70,17 +70,18 @@ struct SlabOpParams {
 // bank serves them through the uniform datapath, so the coefficients of an output row cost no vector registers, no
 // global loads and no latency to speak of.  Up-scale tables repeat (480 -> 1080 has 9 distinct rows plus a few edge
 // rows), so the rows are stored once and indexed per output row.
-constexpr int kSlabMaxDistinct = 48;     // distinct coefficient rows per geometry
-constexpr int kSlabMaxRows = 4352;       // output rows (and source rows + taps) per plane
-struct SlabVClass {
-    float4 coef[kSlabMaxDistinct][2];    // VT coefficients g * 2^107 in tap order, zero padded to 8
-    unsigned short yend[kSlabMaxRows];   // yend[r] = output rows whose VT-row window ends at or before source row r
-    unsigned char idx[kSlabMaxRows];     // coefficient row of each output row
-};
+// All classes of a launch share one pool of 32-bit words inside the parameters (kernel parameters may be 32,764 bytes):
+//   coef  [n_distinct][VT] floats   g * 2^107 in tap order
+//   idx   [dh] uint16               coefficient row of each output row
+//   yend  [sh + VT + 1] uint16      yend[r] = output rows whose VT-row window ends at or before source row r
+// 480 -> 1080 lanczos needs 11 KB of it, 1080 -> 2160 10 KB; a shape whose tables do not fit runs on the tile kernel.
+constexpr int kSlabPoolWords = 7800;
+struct SlabVClass { int coef_off, idx_off, yend_off; };   // word offsets into the pool
 
 struct SlabLaunchParams {
     SlabOpParams op[kMaxSlabOps];
     SlabVClass vc[2];
+    unsigned pool[kSlabPoolWords];
     int n_ops;
     int items_per_frame, n_items;
     int raw_pitch;         // bytes per staged raw row (multiple of 16); a converted row holds raw_pitch / sample spacing floats
@@ -270,7 +271,9 @@ __device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift,
 template <int SPAN, int VT, int OUT, bool FAST>
 __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
     const SlabOpParams &op = P.op[it.oi];
-    const SlabVClass &vc = P.vc[op.vclass];
+    const float *v_coef = reinterpret_cast<const float *>(P.pool + P.vc[op.vclass].coef_off);
+    const unsigned short *v_idx = reinterpret_cast<const unsigned short *>(P.pool + P.vc[op.vclass].idx_off);
+    const unsigned short *v_yend = reinterpret_cast<const unsigned short *>(P.pool + P.vc[op.vclass].yend_off) + it.r_begin;
 
     // ---- horizontal side: this lane's 4 output columns, dense coefficients over their common source span ----
     const int g_first = it.slab * (kSlabW / 4);
@@ -329,7 +332,6 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     for (int s = 0; s < VT; ++s) ring.w[s][0] = ring.w[s][1] = ring.w[s][2] = ring.w[s][3] = 0.f;
     int y = it.ya;
     const int yb = it.yb;
-    const int r_begin = it.r_begin;
 
     unsigned mis = mis0;
     int row = 0;                    // next source row to filter
@@ -357,19 +359,22 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 #pragma unroll
                 for (int c = 0; c < 4; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
             }
-            // floor(sum >> hshift) lands on the subnormal grid, clamped above like libswscale's int16 store
+            // floor(sum >> hshift) lands on the subnormal grid (one multiplication rounded toward minus infinity; for
+            // samples centred on 512 the offset is an integer on that grid, so adding it afterwards is exact), clamped
+            // above like libswscale's int16 store
 #pragma unroll
-            for (int c = 0; c < 4; ++c) o[c] = fminf(fma_rm(t[c], 0x1p-126f, h_addend), t_max);
+            for (int c = 0; c < 4; ++c) o[c] = fminf(__fmul_rd(t[c], 0x1p-126f) + h_addend, t_max);
         } else {
             o[0] = o[1] = o[2] = o[3] = 0.f;   // a row below the plane: zero weight in every window that reaches it
         }
         mis = (mis + pmod) & 15u;
         ++row;
-        const int y_stop = min(static_cast<int>(vc.yend[r_begin + row - 1]), yb);   // rows complete now that this source row is in
+        const int y_stop = min(static_cast<int>(v_yend[row - 1]), yb);   // rows complete now that this source row is in
         while (y < y_stop) {
-            const int id = vc.idx[y];
-            const float4 g0 = vc.coef[id][0], g1 = vc.coef[id][1];
-            const float g[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+            const float *gp = v_coef + static_cast<int>(v_idx[y]) * VT;
+            float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll
+            for (int s = 0; s < VT; ++s) g[s] = gp[s];
             float a[4];
             int4 dither = make_int4(0, 0, 0, 0);
             if (OUT == kOutU8Dither) {
@@ -390,7 +395,8 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
             float r[4];
             const float worst = slab_finish<OUT>(a, dst_shift, word, r);
             if (worst >= v_thr) {
-                const uint2 fx = slab_fixup<VT, OUT>(ring, g0, g1, v_thr, r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
+                const uint2 fx = slab_fixup<VT, OUT>(ring, make_float4(g[0], g[1], g[2], g[3]), make_float4(g[4], g[5], g[6], g[7]), v_thr,
+                                                     r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
                 word[0] = fx.x; word[1] = fx.y;
             }
             if (FAST) store_quad_fast<OUT>(drow, 0, word);
@@ -427,8 +433,12 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     cp_async_wait_pending<0>();
 }
 
+// Resident warps per SM the register budget is set for: 21 (80 registers) for short filters, 18 (96 registers) once the
+// horizontal coefficients and the vertical window together need more (measured: profiles/r02_slab_history.md).
+template <int SPAN, int VT> struct SlabBudget { static constexpr int kMinCtas = (SPAN >= 8 && VT >= 6) ? 18 : TVS_SLAB_MIN_CTAS; };
+
 template <int SPAN, int VT, int OUT>
-__global__ void __launch_bounds__(kSlabThreads, TVS_SLAB_MIN_CTAS)
+__global__ void __launch_bounds__(kSlabThreads, SlabBudget<SPAN, VT>::kMinCtas)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
     float *S = smem;                                                       // [kBlockRows][raw_pitch] floats at most, + a zero tail
@@ -478,9 +488,10 @@ struct SlabOp {
     float v_thr = 0, v_init = 0, h_addend = 0;
     size_t hdense_off = 0, hbase_off = 0, vpos_off = 0;
     int vtable = 0;                         // which vertical table of the context (2 luma, 3 chroma): planes that share it share a class
-    std::vector<float> vcoef;               // [n_distinct][8]  distinct coefficient rows, c * 2^107 in tap order
-    std::vector<unsigned char> vidx;        // [dh]             coefficient row of each output row
-    std::vector<unsigned short> vyend;      // [sh + VT + 1]    see SlabVClass
+    std::vector<float> vcoef;               // [n_distinct][VT] distinct coefficient rows, c * 2^107 in tap order
+    std::vector<unsigned short> vidx;       // [dh]             coefficient row of each output row
+    std::vector<unsigned short> vyend;      // [sh + VT + 1]    see SlabLaunchParams
+    size_t pool_words() const { return vcoef.size() + (vidx.size() + 1) / 2 + (vyend.size() + 1) / 2; }
 };
 
 struct SlabPlan {
@@ -599,21 +610,21 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         for (int y = 0; y < op.dh; ++y) vpos[y] = v.pos[y];
         // vertical tables for the kernel parameters: distinct coefficient rows, a row index per output row, and per
         // source row the number of output rows whose VT-row window [pos, pos + VT) ends at or before it
-        if (op.dh > kSlabMaxRows || op.sh + VT + 1 > kSlabMaxRows) { err = "plane taller than the slab kernel's tables"; delete sp; return nullptr; }
+        if (op.dh > 65535) { err = "plane taller than the slab kernel's tables"; delete sp; return nullptr; }
         so.vtable = op.vtable;
         so.vidx.resize(op.dh);
         for (int y = 0; y < op.dh; ++y) {
             float row[8] = {0, 0, 0, 0, 0, 0, 0, 0};
             for (int j = 0; j < v.taps; ++j) row[j] = std::ldexp(static_cast<float>(v.coef[static_cast<size_t>(y) * v.taps + j]), 107);
             int id = -1;
-            for (size_t k = 0; k + 8 <= so.vcoef.size() && id < 0; k += 8)
-                if (memcmp(&so.vcoef[k], row, sizeof row) == 0) id = static_cast<int>(k / 8);
+            for (size_t k = 0; k + VT <= so.vcoef.size() && id < 0; k += VT)
+                if (memcmp(&so.vcoef[k], row, VT * sizeof(float)) == 0) id = static_cast<int>(k / VT);
             if (id < 0) {
-                id = static_cast<int>(so.vcoef.size() / 8);
-                if (id >= kSlabMaxDistinct) { err = "too many distinct vertical coefficient rows (not a repeating ratio)"; delete sp; return nullptr; }
-                so.vcoef.insert(so.vcoef.end(), row, row + 8);
+                id = static_cast<int>(so.vcoef.size() / VT);
+                so.vcoef.insert(so.vcoef.end(), row, row + VT);
+                if (so.vcoef.size() > static_cast<size_t>(kSlabPoolWords)) { err = "vertical tables do not fit in the kernel parameters"; delete sp; return nullptr; }
             }
-            so.vidx[y] = static_cast<unsigned char>(id);
+            so.vidx[y] = static_cast<unsigned short>(id);
         }
         so.vyend.assign(op.sh + VT + 1, static_cast<unsigned short>(op.dh));
         {
@@ -629,6 +640,17 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         sp->ops.push_back(so);
     }
     if (sp->ops.empty()) { err = "nothing to scale"; delete sp; return nullptr; }
+    {
+        // the vertical tables of all planes (one set per distinct table) must fit in the parameter pool together
+        size_t words = 0;
+        std::vector<int> seen;
+        for (const SlabOp &so : sp->ops) {
+            if (std::find(seen.begin(), seen.end(), so.vtable) != seen.end()) continue;
+            seen.push_back(so.vtable);
+            words += so.pool_words();
+        }
+        if (seen.size() > 2 || words > static_cast<size_t>(kSlabPoolWords)) { err = "vertical tables do not fit in the kernel parameters"; delete sp; return nullptr; }
+    }
     if (cudaMalloc(&sp->blob, blob.size()) != cudaSuccess ||
         cudaMemcpy(sp->blob, blob.data(), blob.size(), cudaMemcpyHostToDevice) != cudaSuccess) {
         err = "device allocation for the slab tables failed";
@@ -692,6 +714,7 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
         }
         int items = 0;
         int n_classes = 0, class_vtable[2] = {-1, -1};
+        size_t pool_used = 0;
         for (size_t j : members) {
             const SlabOp &so = p->ops[j];
             const PlaneOp &op = plan.ops[so.op_index];
@@ -717,9 +740,16 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
                 cls = n_classes++;
                 class_vtable[cls] = so.vtable;
                 SlabVClass &vc = lp.vc[cls];
-                memcpy(vc.coef, so.vcoef.data(), so.vcoef.size() * sizeof(float));
-                memcpy(vc.idx, so.vidx.data(), so.vidx.size());
-                memcpy(vc.yend, so.vyend.data(), so.vyend.size() * sizeof(unsigned short));
+                if (pool_used + so.pool_words() > static_cast<size_t>(kSlabPoolWords)) return -1;
+                vc.coef_off = static_cast<int>(pool_used);
+                memcpy(lp.pool + pool_used, so.vcoef.data(), so.vcoef.size() * sizeof(float));
+                pool_used += so.vcoef.size();
+                vc.idx_off = static_cast<int>(pool_used);
+                memcpy(lp.pool + pool_used, so.vidx.data(), so.vidx.size() * sizeof(unsigned short));
+                pool_used += (so.vidx.size() + 1) / 2;
+                vc.yend_off = static_cast<int>(pool_used);
+                memcpy(lp.pool + pool_used, so.vyend.data(), so.vyend.size() * sizeof(unsigned short));
+                pool_used += (so.vyend.size() + 1) / 2;
             }
             q.vclass = cls;
             q.src_lo = s.base - op.src_offset;

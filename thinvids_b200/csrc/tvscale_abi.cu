@@ -106,7 +106,7 @@ bool fused_prefers_two_pass(const tvs_ctx *c) {
 bool use_stream_path(const tvs_ctx *c) { return c->streaming && (c->forced_path == 2 || c->forced_path < 0); }
 bool use_slab_path(const tvs_ctx *c) {
     if (use_stream_path(c)) return false;
-    return c->slab && c->forced_path == 3;   // not yet the automatic choice: see DESIGN.md
+    return c->slab && (c->forced_path == 3 || c->forced_path < 0);
 }
 bool use_fused_path(const tvs_ctx *c) {
     if (use_stream_path(c) || use_slab_path(c)) return false;
