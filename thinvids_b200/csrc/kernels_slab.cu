@@ -35,7 +35,6 @@
 namespace tvs {
 namespace {
 
-constexpr int kSlabW = 128;        // output columns per slab: lane * 4 + k
 constexpr int kSlabThreads = 32;   // one warp
 constexpr int kBlockRows = 4;      // source rows staged and converted together
 constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the warp prefetches kRawBlocks - 1 blocks ahead
@@ -48,12 +47,12 @@ struct SlabOpParams {
     const uint8_t *src; ptrdiff_t src_pitch, src_fstride; int src_xstep;
     uint8_t *dst; ptrdiff_t dst_pitch, dst_fstride; int dst_xstep;
     int sw, sh, dw, dh;
-    int n_groups;          // groups of 4 output columns
-    int n_slabs;           // ceil(dw / 128)
+    int n_groups;          // groups of C adjacent output columns (one group per lane)
+    int n_slabs;           // ceil(dw / (32 * C))
     int chunk_rows;        // output rows per work item
     int n_chunks;          // ceil(dh / chunk_rows)
     int item_begin;        // first item of this plane inside a frame's item list
-    const float *hdense;   // [n_groups][4][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
+    const float *hdense;   // [n_groups][C][SPAN]  c * 2^-(23+hshift), zero outside a column's own window
     const int *hbase;      // [n_groups]           first source column of the group's span
     const int *vpos;       // [dh + 1]             first source row of each output row (one padding entry)
     int vclass;            // which SlabVClass of the launch holds this plane's vertical tables
@@ -64,6 +63,7 @@ struct SlabOpParams {
     int src_mode;          // kSrcU8 / kSrcU8Pair / kSrcU16 / kSrcU16Pair
     int src_shift;         // P010: the 10 bits sit 6 places up in the word
     int dst_shift, dither_xoff;
+    const unsigned char *win_aligned;   // [n_slabs] every lane's window starts a multiple of 4 samples after the slab's first one
 };
 
 // Vertical tables of one plane geometry (luma, or the two chroma planes), held in the kernel parameters: the constant
@@ -165,19 +165,42 @@ __device__ __forceinline__ void slab_prefetch_block(const SlabStage &st, int row
 __device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
                                                    unsigned mis0, unsigned pmod, int row0, int lane) {
     const int total = kBlockRows * words_per_row;
+    // `S` may sit a few floats off its natural alignment (see the aligned-window path of the horizontal pass): vector
+    // stores only when the destination of every word is aligned for them
+    const unsigned s_mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(S)) & 15u;
     if (src_mode == kSrcU8) {                       // 4 samples per word
-#pragma unroll 1
-        for (int i = lane; i < total; i += 32) {
-            const unsigned v = raw[i];
-            reinterpret_cast<float4 *>(S)[i] = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
-                                                           byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+        if (s_mis == 0) {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = raw[i];
+                reinterpret_cast<float4 *>(S)[i] = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
+                                                               byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+            }
+        } else {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = raw[i];
+                float *o = S + 4 * i;
+                o[0] = byte_to_float(v, 0x7540u); o[1] = byte_to_float(v, 0x7541u);
+                o[2] = byte_to_float(v, 0x7542u); o[3] = byte_to_float(v, 0x7543u);
+            }
         }
     } else if (src_mode == kSrcU16) {               // two 16-bit samples per word, centred on 512
         const unsigned keep = 0xffffu >> src_shift;
-#pragma unroll 1
-        for (int i = lane; i < total; i += 32) {
-            const unsigned v = (raw[i] >> src_shift) & (keep | (keep << 16));   // P010: integer shift first, as libswscale does
-            reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7410u) - 512.0f, byte_to_float(v, 0x7432u) - 512.0f);
+        const unsigned mask = keep | (keep << 16);  // P010: integer shift first, as libswscale does; planar words pass unchanged
+        if ((s_mis & 7u) == 0) {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = (raw[i] >> src_shift) & mask;
+                reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7410u) - 512.0f, byte_to_float(v, 0x7432u) - 512.0f);
+            }
+        } else {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = (raw[i] >> src_shift) & mask;
+                S[2 * i] = byte_to_float(v, 0x7410u) - 512.0f;
+                S[2 * i + 1] = byte_to_float(v, 0x7432u) - 512.0f;
+            }
         }
     } else {
         // interleaved chroma: which byte / half of a word belongs to this plane depends on the row's alignment
@@ -206,26 +229,26 @@ __device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S
 }
 
 // The register ring, passed by value to the (rare, out-of-line) exact path.
-template <int VT> struct SlabRing { float w[VT][4]; };
+template <int VT, int C> struct SlabRing { float w[VT][C]; };
 
 // Exact redo of the samples of one quad whose float residual sits inside the error band of a rounding boundary: the
 // intermediates are the bit patterns held in the ring, the coefficients the integer copy of the row's record.
-template <int VT, int OUT>
-__device__ __noinline__ uint2 slab_fixup(SlabRing<VT> ring, float4 g0, float4 g1, float v_thr, float r0, float r1, float r2, float r3,
-                                         int4 dither, int dst_shift, uint2 packed) {
+template <int VT, int C, int OUT>
+__device__ __noinline__ uint2 slab_fixup(SlabRing<VT, C> ring, float4 g0, float4 g1, float4 g2, float v_thr, float4 rr, int4 dither,
+                                         int dst_shift, uint2 packed) {
     unsigned word[2] = {packed.x, packed.y};
-    const float r[4] = {r0, r1, r2, r3};
+    const float r[4] = {rr.x, rr.y, rr.z, rr.w};
     const int d[4] = {dither.x, dither.y, dither.z, dither.w};
     int a[4] = {0, 0, 0, 0};
-    const float gf[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float gf[12] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w, g2.x, g2.y, g2.z, g2.w};
 #pragma unroll
     for (int s = 0; s < VT; ++s) {
         const int c = static_cast<int>(gf[s] * 0x1p-107f);   // the table holds c * 2^107, exactly
 #pragma unroll
-        for (int k = 0; k < 4; ++k) a[k] += subnormal_to_int(ring.w[s][k]) * c;
+        for (int k = 0; k < C; ++k) a[k] += subnormal_to_int(ring.w[s][k]) * c;
     }
 #pragma unroll
-    for (int k = 0; k < 4; ++k) {
+    for (int k = 0; k < C; ++k) {
         if (fabsf(r[k]) >= v_thr) {
             const int bias = OUT == kOutU8 ? (64 << 12) : OUT == kOutU8Dither ? (d[k] << 12) : (1 << 16);
             const unsigned v = static_cast<unsigned>(min(max((a[k] + bias) >> OutRule<OUT>::kShift, 0), OutRule<OUT>::kMax));
@@ -240,35 +263,65 @@ __device__ __noinline__ uint2 slab_fixup(SlabRing<VT> ring, float4 g0, float4 g1
     return make_uint2(word[0], word[1]);
 }
 
-// Quotient, residual and packing of one quad of float sums (scalar form of finish_quad).
-template <int OUT>
-__device__ __forceinline__ float slab_finish(const float (&a)[4], int dst_shift, unsigned (&word)[2], float (&r)[4]) {
+// Quotient, residual and packing of C float sums (scalar form of finish_quad).  8-bit samples land in the low C bytes
+// of word[0]; 10-bit samples two per word.
+template <int C, int OUT>
+__device__ __forceinline__ float slab_finish(const float (&a)[C], int dst_shift, unsigned (&word)[2], float (&r)[4]) {
     constexpr float kQ = OutRule<OUT>::kShift == 19 ? 0x1p-126f : 0x1p-124f;
     constexpr float kBack = OutRule<OUT>::kShift == 19 ? -0x1p126f : -0x1p124f;
-    float q[4];
+    float q[4] = {0.f, 0.f, 0.f, 0.f};
+    r[0] = r[1] = r[2] = r[3] = 0.f;
 #pragma unroll
-    for (int c = 0; c < 4; ++c) q[c] = a[c] * kQ;                    // round(acc / 2^shift) as a subnormal bit pattern
+    for (int c = 0; c < C; ++c) q[c] = a[c] * kQ;                    // round(acc / 2^shift) as a subnormal bit pattern
 #pragma unroll
-    for (int c = 0; c < 4; ++c) r[c] = fmaf(q[c], kBack, a[c]);     // exact residual
+    for (int c = 0; c < C; ++c) r[c] = fmaf(q[c], kBack, a[c]);     // exact residual
     if (OUT == kOutU10) {
         const float top = __int_as_float(1023);
         const unsigned b0 = __float_as_uint(fminf(fmaxf(q[0], 0.f), top)) << dst_shift;
         const unsigned b1 = __float_as_uint(fminf(fmaxf(q[1], 0.f), top)) << dst_shift;
-        const unsigned b2 = __float_as_uint(fminf(fmaxf(q[2], 0.f), top)) << dst_shift;
-        const unsigned b3 = __float_as_uint(fminf(fmaxf(q[3], 0.f), top)) << dst_shift;
         word[0] = __byte_perm(b0, b1, 0x5410);
-        word[1] = __byte_perm(b2, b3, 0x5410);
+        word[1] = 0;
+        if (C == 4) {
+            const unsigned b2 = __float_as_uint(fminf(fmaxf(q[2], 0.f), top)) << dst_shift;
+            const unsigned b3 = __float_as_uint(fminf(fmaxf(q[3], 0.f), top)) << dst_shift;
+            word[1] = __byte_perm(b2, b3, 0x5410);
+        }
     } else {
-        word[0] = pack_sat_u8(__float_as_int(q[3]), __float_as_int(q[2]), 0u);
+        word[0] = 0;
+        if (C == 4) word[0] = pack_sat_u8(__float_as_int(q[3]), __float_as_int(q[2]), 0u);
         word[0] = pack_sat_u8(__float_as_int(q[1]), __float_as_int(q[0]), word[0]);
         word[1] = 0;
     }
-    return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
+    if (C == 4) return fmaxf(fmaxf(fabsf(r[0]), fabsf(r[1])), fmaxf(fabsf(r[2]), fabsf(r[3])));
+    return fmaxf(fabsf(r[0]), fabsf(r[1]));
+}
+
+// C samples of one lane: one vector store (the caller has checked alignment and bounds), or bounds-checked element stores
+// with `xstep` bytes between samples.
+template <int C, int OUT>
+__device__ __forceinline__ void slab_store_fast(uint8_t *p, const unsigned (&word)[2]) {
+    if (OUT == kOutU10) {
+        if (C == 4) *reinterpret_cast<uint2 *>(p) = make_uint2(word[0], word[1]);
+        else *reinterpret_cast<unsigned *>(p) = word[0];
+    } else {
+        if (C == 4) *reinterpret_cast<unsigned *>(p) = word[0];
+        else *reinterpret_cast<unsigned short *>(p) = static_cast<unsigned short>(word[0]);
+    }
+}
+template <int C, int OUT>
+__device__ __forceinline__ void slab_store_slow(uint8_t *row, int x, int dw, int xstep, const unsigned (&word)[2]) {
+#pragma unroll
+    for (int k = 0; k < C; ++k) {
+        if (x + k >= dw) continue;
+        uint8_t *p = row + static_cast<ptrdiff_t>(x + k) * xstep;
+        if (OUT == kOutU10) *reinterpret_cast<uint16_t *>(p) = static_cast<uint16_t>(word[k >> 1] >> (16 * (k & 1)));
+        else *p = static_cast<uint8_t>(word[0] >> (8 * k));
+    }
 }
 
 // FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
 // vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
-template <int SPAN, int VT, int OUT, bool FAST>
+template <int C, int SPAN, int VT, int OUT, bool FAST>
 __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
     const SlabOpParams &op = P.op[it.oi];
     const float *v_coef = reinterpret_cast<const float *>(P.pool + P.vc[op.vclass].coef_off);
@@ -276,14 +329,16 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     const unsigned short *v_yend = reinterpret_cast<const unsigned short *>(P.pool + P.vc[op.vclass].yend_off) + it.r_begin;
 
     // ---- horizontal side: this lane's 4 output columns, dense coefficients over their common source span ----
-    const int g_first = it.slab * (kSlabW / 4);
+    constexpr int kSlabW = 32 * C;   // output columns per slab: lane * C + k
+    const int g_first = it.slab * 32;
     const int grp = min(g_first + lane, op.n_groups - 1);
-    float cd[4][SPAN];
+    float cd[C][SPAN];
     {
-        const float4 *src = reinterpret_cast<const float4 *>(op.hdense + static_cast<size_t>(grp) * (4 * SPAN));
+        static_assert((C * SPAN) % 4 == 0, "a lane's coefficients are read as 16-byte pieces");
+        const float4 *src = reinterpret_cast<const float4 *>(op.hdense + static_cast<size_t>(grp) * (C * SPAN));
         float *flat = &cd[0][0];
 #pragma unroll
-        for (int i = 0; i < SPAN; ++i) {
+        for (int i = 0; i < C * SPAN / 4; ++i) {
             const float4 v = __ldg(src + i);
             flat[4 * i] = v.x; flat[4 * i + 1] = v.y; flat[4 * i + 2] = v.z; flat[4 * i + 3] = v.w;
         }
@@ -299,7 +354,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     int hb;
     {
         const int c0 = __ldg(op.hbase + g_first);
-        const int g_last = min(g_first + kSlabW / 4 - 1, op.n_groups - 1);
+        const int g_last = min(g_first + 31, op.n_groups - 1);
         const int ncols = min(__ldg(op.hbase + g_last) + SPAN, op.sw) - c0;   // samples past the plane's width carry zero weight
         hb = __ldg(op.hbase + grp) - c0;
         st.last_byte = (ncols - 1) * xs + (src_mode >= kSrcU16 ? 1 : 0);
@@ -317,19 +372,27 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     const float h_addend = op.h_addend;
     const float t_max = __int_as_float(32767);
     const int block_chunks = kBlockRows * st.s_chunks;
+    // Aligned windows: when the lanes' windows start a multiple of 4 samples apart (exact 2:1, 4:1 ... down-scales, where
+    // scalar loads 4 words apart would be 4-way bank conflicts) and every row has the same alignment, the converted block is
+    // placed a few floats off so that each window starts on a 16-byte boundary and is read with 128-bit loads.
+    const bool aligned_win = C == 2 && pmod == 0 && (src_mode == kSrcU8 || src_mode == kSrcU16) && __ldg(op.win_aligned + it.slab) != 0;
+    if (aligned_win) S += (4 - static_cast<int>((mis0 >> mshift) & 3u)) & 3;
     const float *s_lane = S + hb;
 
     // ---- vertical side ----
-    const int x = it.slab * kSlabW + 4 * lane;
+    const int x = it.slab * kSlabW + C * lane;
     const int dw = op.dw, dst_xstep = op.dst_xstep, dst_shift = op.dst_shift;
     const int dst_pitch = static_cast<int>(op.dst_pitch);
     uint8_t *drow = op.dst + it.f * op.dst_fstride + static_cast<ptrdiff_t>(it.ya) * dst_pitch;
     if (FAST) drow += static_cast<ptrdiff_t>(x) * (OUT == kOutU10 ? 2 : 1);    // this lane's first sample of the row
     const float v_thr = op.v_thr, v_init = op.v_init;
     const int dcol = (x + op.dither_xoff) & 7;
-    SlabRing<VT> ring;
+    SlabRing<VT, C> ring;
 #pragma unroll
-    for (int s = 0; s < VT; ++s) ring.w[s][0] = ring.w[s][1] = ring.w[s][2] = ring.w[s][3] = 0.f;
+    for (int s = 0; s < VT; ++s) {
+#pragma unroll
+        for (int c = 0; c < C; ++c) ring.w[s][c] = 0.f;
+    }
     int y = it.ya;
     const int yb = it.yb;
 
@@ -343,64 +406,76 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 #pragma unroll
         for (int s = 0; s + 1 < VT; ++s) {
 #pragma unroll
-            for (int c = 0; c < 4; ++c) ring.w[s][c] = ring.w[s + 1][c];
+            for (int c = 0; c < C; ++c) ring.w[s][c] = ring.w[s + 1][c];
         }
-        float (&o)[4] = ring.w[VT - 1];
+        float (&o)[C] = ring.w[VT - 1];
         if (row < rows_real) {
             const float *win = sp + (mis >> mshift);
-            float px[SPAN];
+            float px[(SPAN + 3) & ~3];
+            if (C == 2 && aligned_win) {
 #pragma unroll
-            for (int i = 0; i < SPAN; ++i) px[i] = win[i];
-            float t[4];
+                for (int i = 0; i < (SPAN + 3) / 4; ++i) {
+                    const float4 v = reinterpret_cast<const float4 *>(win)[i];
+                    px[4 * i] = v.x; px[4 * i + 1] = v.y; px[4 * i + 2] = v.z; px[4 * i + 3] = v.w;
+                }
+            } else {
 #pragma unroll
-            for (int c = 0; c < 4; ++c) t[c] = px[0] * cd[c][0];
+                for (int i = 0; i < SPAN; ++i) px[i] = win[i];
+            }
+            float t[C];
+#pragma unroll
+            for (int c = 0; c < C; ++c) t[c] = px[0] * cd[c][0];
 #pragma unroll
             for (int i = 1; i < SPAN; ++i) {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
+                for (int c = 0; c < C; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
             }
             // floor(sum >> hshift) lands on the subnormal grid (one multiplication rounded toward minus infinity; for
             // samples centred on 512 the offset is an integer on that grid, so adding it afterwards is exact), clamped
             // above like libswscale's int16 store
 #pragma unroll
-            for (int c = 0; c < 4; ++c) o[c] = fminf(__fmul_rd(t[c], 0x1p-126f) + h_addend, t_max);
+            for (int c = 0; c < C; ++c) o[c] = fminf(__fmul_rd(t[c], 0x1p-126f) + h_addend, t_max);
         } else {
-            o[0] = o[1] = o[2] = o[3] = 0.f;   // a row below the plane: zero weight in every window that reaches it
+#pragma unroll
+            for (int c = 0; c < C; ++c) o[c] = 0.f;   // a row below the plane: zero weight in every window that reaches it
         }
         mis = (mis + pmod) & 15u;
         ++row;
         const int y_stop = min(static_cast<int>(v_yend[row - 1]), yb);   // rows complete now that this source row is in
         while (y < y_stop) {
             const float *gp = v_coef + static_cast<int>(v_idx[y]) * VT;
-            float g[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+            float g[12] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll
             for (int s = 0; s < VT; ++s) g[s] = gp[s];
-            float a[4];
+            float a[C];
             int4 dither = make_int4(0, 0, 0, 0);
             if (OUT == kOutU8Dither) {
                 const int *tab = kDither128i[y & 7];
                 dither = make_int4(tab[dcol], tab[(dcol + 1) & 7], tab[(dcol + 2) & 7], tab[(dcol + 3) & 7]);
+                const int dv[4] = {dither.x, dither.y, dither.z, dither.w};
                 // (d - 64) * 4096 * 2^-42: the rounding quotient already adds 64 << 12
-                a[0] = fmaf(static_cast<float>(dither.x - 64), 0x1p-30f, v_init); a[1] = fmaf(static_cast<float>(dither.y - 64), 0x1p-30f, v_init);
-                a[2] = fmaf(static_cast<float>(dither.z - 64), 0x1p-30f, v_init); a[3] = fmaf(static_cast<float>(dither.w - 64), 0x1p-30f, v_init);
+#pragma unroll
+                for (int c = 0; c < C; ++c) a[c] = fmaf(static_cast<float>(dv[c] - 64), 0x1p-30f, v_init);
             } else {
-                a[0] = a[1] = a[2] = a[3] = v_init;
+#pragma unroll
+                for (int c = 0; c < C; ++c) a[c] = v_init;
             }
 #pragma unroll
             for (int s = 0; s < VT; ++s) {
 #pragma unroll
-                for (int c = 0; c < 4; ++c) a[c] = fmaf(ring.w[s][c], g[s], a[c]);
+                for (int c = 0; c < C; ++c) a[c] = fmaf(ring.w[s][c], g[s], a[c]);
             }
             unsigned word[2];
             float r[4];
-            const float worst = slab_finish<OUT>(a, dst_shift, word, r);
+            const float worst = slab_finish<C, OUT>(a, dst_shift, word, r);
             if (worst >= v_thr) {
-                const uint2 fx = slab_fixup<VT, OUT>(ring, make_float4(g[0], g[1], g[2], g[3]), make_float4(g[4], g[5], g[6], g[7]), v_thr,
-                                                     r[0], r[1], r[2], r[3], dither, dst_shift, make_uint2(word[0], word[1]));
+                const uint2 fx = slab_fixup<VT, C, OUT>(ring, make_float4(g[0], g[1], g[2], g[3]), make_float4(g[4], g[5], g[6], g[7]),
+                                                        make_float4(g[8], g[9], g[10], g[11]), v_thr, make_float4(r[0], r[1], r[2], r[3]),
+                                                        dither, dst_shift, make_uint2(word[0], word[1]));
                 word[0] = fx.x; word[1] = fx.y;
             }
-            if (FAST) store_quad_fast<OUT>(drow, 0, word);
-            else store_quad_slow<OUT>(drow, x, dw, dst_xstep, word);
+            if (FAST) slab_store_fast<C, OUT>(drow, word);
+            else slab_store_slow<C, OUT>(drow, x, dw, dst_xstep, word);
             drow += dst_pitch;
             ++y;
         }
@@ -435,11 +510,12 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 
 // Resident warps per SM the register budget is set for: 21 (80 registers) for short filters, 18 (96 registers) once the
 // horizontal coefficients and the vertical window together need more (measured: profiles/r02_slab_history.md).
-template <int SPAN, int VT> struct SlabBudget { static constexpr int kMinCtas = (SPAN >= 8 && VT >= 6) ? 18 : TVS_SLAB_MIN_CTAS; };
+template <int C, int SPAN, int VT> struct SlabBudget { static constexpr int kMinCtas = SPAN + VT >= 26 ? 16 : C * (SPAN + VT) >= 52 ? 18 : TVS_SLAB_MIN_CTAS; };
 
-template <int SPAN, int VT, int OUT>
-__global__ void __launch_bounds__(kSlabThreads, SlabBudget<SPAN, VT>::kMinCtas)
+template <int C, int SPAN, int VT, int OUT>
+__global__ void __launch_bounds__(kSlabThreads, SlabBudget<C, SPAN, VT>::kMinCtas)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
+    constexpr int kSlabW = 32 * C;
     extern __shared__ __align__(16) float smem[];
     float *S = smem;                                                       // [kBlockRows][raw_pitch] floats at most, + a zero tail
     const int s_floats = kBlockRows * P.raw_pitch + 32;
@@ -454,20 +530,23 @@ slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     for (int item = blockIdx.x; item < P.n_items; item += gridDim.x) {
         const SlabItem it = decode_item(P, item, VT);
         const SlabOpParams &op = P.op[it.oi];
-        constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = 4 * kSample - 1;
+        constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = C * kSample - 1;
         const uintptr_t d0 = reinterpret_cast<uintptr_t>(op.dst + it.f * op.dst_fstride) + static_cast<uintptr_t>(it.slab * kSlabW) * kSample;
         const bool fast = op.dst_xstep == kSample && (op.dst_pitch & kAlign) == 0 && (d0 & kAlign) == 0 && (it.slab + 1) * kSlabW <= op.dw;
-        if (fast) slab_run_item<SPAN, VT, OUT, true>(P, it, S, RAW, lane);
-        else slab_run_item<SPAN, VT, OUT, false>(P, it, S, RAW, lane);
+        if (fast) slab_run_item<C, SPAN, VT, OUT, true>(P, it, S, RAW, lane);
+        else slab_run_item<C, SPAN, VT, OUT, false>(P, it, S, RAW, lane);
         __syncwarp();
     }
 }
 
 using SlabKernelFn = void (*)(const SlabLaunchParams);
-struct SlabInstance { int span, vt; SlabKernelFn fn[3]; };   // one kernel per output rule
-#define TVS_SLAB_INST(S, V) {S, V, {slab_scale_kernel<S, V, kOutU8>, slab_scale_kernel<S, V, kOutU8Dither>, slab_scale_kernel<S, V, kOutU10>}}
+// `cols` adjacent output columns per lane (a slab is 32 * cols columns wide): 4 wherever the dense horizontal window of
+// four neighbours stays short (up-scales, mild down-scales), 2 for stronger down-scales, whose windows are long and far apart.
+struct SlabInstance { int cols, span, vt; SlabKernelFn fn[3]; };   // one kernel per output rule
+#define TVS_SLAB_INST(C, S, V) {C, S, V, {slab_scale_kernel<C, S, V, kOutU8>, slab_scale_kernel<C, S, V, kOutU8Dither>, slab_scale_kernel<C, S, V, kOutU10>}}
 const SlabInstance kSlabInstances[] = {
-    TVS_SLAB_INST(4, 2), TVS_SLAB_INST(6, 4), TVS_SLAB_INST(8, 4), TVS_SLAB_INST(8, 6), TVS_SLAB_INST(12, 6), TVS_SLAB_INST(12, 8),
+    TVS_SLAB_INST(4, 4, 2), TVS_SLAB_INST(4, 6, 4), TVS_SLAB_INST(4, 8, 4), TVS_SLAB_INST(4, 8, 6), TVS_SLAB_INST(4, 12, 6), TVS_SLAB_INST(4, 12, 8),
+    TVS_SLAB_INST(2, 6, 4), TVS_SLAB_INST(2, 8, 6), TVS_SLAB_INST(2, 10, 8), TVS_SLAB_INST(2, 12, 10), TVS_SLAB_INST(2, 14, 12),
 };
 #undef TVS_SLAB_INST
 
@@ -486,6 +565,7 @@ struct SlabOp {
     int n_groups = 0, n_slabs = 0;
     int s_pitch = 0, raw_pitch = 0;
     float v_thr = 0, v_init = 0, h_addend = 0;
+    size_t win_aligned_off = 0;
     size_t hdense_off = 0, hbase_off = 0, vpos_off = 0;
     int vtable = 0;                         // which vertical table of the context (2 luma, 3 chroma): planes that share it share a class
     std::vector<float> vcoef;               // [n_distinct][VT] distinct coefficient rows, c * 2^107 in tap order
@@ -542,9 +622,8 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         if (static_cast<long long>(op.sh) * op.sw * op.src_xstep >= (1LL << 30)) { err = "plane too large for 32-bit offsets"; delete sp; return nullptr; }
         const int src_mode = wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
         const int out_mode = op.rule == kOut10 ? kOutU10 : op.rule == kOut8Dither ? kOutU8Dither : kOutU8;
-        // the walk is driven by source rows: consecutive output rows must start at the same source row or the next one
         for (int y = 1; y < op.dh; ++y)
-            if (v.pos[y] < v.pos[y - 1] || v.pos[y] > v.pos[y - 1] + 1) { err = "plane is shrunk vertically"; delete sp; return nullptr; }
+            if (v.pos[y] < v.pos[y - 1]) { err = "vertical positions go backwards"; delete sp; return nullptr; }
         // float exactness of the horizontal sum (see the tile kernel)
         long long worst_abs = 0;
         for (int x = 0; x < op.dw; ++x) {
@@ -554,19 +633,21 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             worst_abs = std::max(worst_abs, a);
         }
         if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete sp; return nullptr; }
-        const int n_groups = (op.dw + 3) / 4;
-        int span = 0;
-        for (int g = 0; g < n_groups; ++g) {
-            const int xa = g * 4, xb = std::min(xa + 4, op.dw) - 1;
-            span = std::max(span, h.pos[xb] + h.taps - h.pos[xa]);
-        }
+        // smallest instance whose dense window covers every group of `cols` neighbouring columns and whose vertical
+        // window covers the taps; four columns per lane are preferred (less staging and bookkeeping per sample)
         int inst = -1;
         for (size_t i = 0; i < sizeof(kSlabInstances) / sizeof(kSlabInstances[0]); ++i) {
-            if (kSlabInstances[i].span < span || kSlabInstances[i].vt < v.taps) continue;
-            if (inst < 0 || kSlabInstances[i].span + kSlabInstances[i].vt < kSlabInstances[inst].span + kSlabInstances[inst].vt) inst = static_cast<int>(i);
+            const int cols = kSlabInstances[i].cols;
+            if (kSlabInstances[i].vt < v.taps) continue;
+            int span = 0;
+            for (int xa = 0; xa < op.dw; xa += cols) span = std::max(span, h.pos[std::min(xa + cols, op.dw) - 1] + h.taps - h.pos[xa]);
+            if (kSlabInstances[i].span < span) continue;
+            auto cost = [](const SlabInstance &k) { return (k.cols == 4 ? 0 : 1000) + k.cols * (k.span + k.vt); };
+            if (inst < 0 || cost(kSlabInstances[i]) < cost(kSlabInstances[inst])) inst = static_cast<int>(i);
         }
         if (inst < 0) { err = "no slab kernel instance for this filter size"; delete sp; return nullptr; }
-        const int SPAN = kSlabInstances[inst].span, VT = kSlabInstances[inst].vt;
+        const int C = kSlabInstances[inst].cols, SPAN = kSlabInstances[inst].span, VT = kSlabInstances[inst].vt;
+        const int n_groups = (op.dw + C - 1) / C;
         const VerticalFloatRule vrule = slab_vertical_rule(v, VT, out_mode == kOutU10, out_mode == kOutU8Dither);
         if (!vrule.ok) { err = "vertical error bound too large"; delete sp; return nullptr; }
 
@@ -576,29 +657,32 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         so.out_mode = out_mode;
         so.src_mode = src_mode;
         so.n_groups = n_groups;
-        so.n_slabs = (op.dw + kSlabW - 1) / kSlabW;
+        so.n_slabs = (op.dw + 32 * C - 1) / (32 * C);
         so.v_thr = vrule.thr;
         so.v_init = vrule.init;
         so.h_addend = wide_src ? std::ldexp(16384.0f, -149) : 0.0f;   // (512 << 14) >> 9, as a subnormal
 
-        std::vector<float> hdense(static_cast<size_t>(n_groups) * 4 * SPAN, 0.0f);
+        std::vector<float> hdense(static_cast<size_t>(n_groups) * C * SPAN, 0.0f);
         std::vector<int> hbase(n_groups);
         for (int g = 0; g < n_groups; ++g) {
-            const int xa = g * 4;
+            const int xa = g * C;
             hbase[g] = h.pos[xa];
-            for (int k = 0; k < 4 && xa + k < op.dw; ++k) {
+            for (int k = 0; k < C && xa + k < op.dw; ++k) {
                 const int x = xa + k;
                 for (int j = 0; j < h.taps; ++j) {
                     const int c = h.coef[static_cast<size_t>(x) * h.taps + j];
                     // scaled so that one FMA by 2^-126 lands floor(sum >> hshift) on the subnormal grid
-                    if (c) hdense[(static_cast<size_t>(g) * 4 + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -(23 + op.hshift));
+                    if (c) hdense[(static_cast<size_t>(g) * C + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -(23 + op.hshift));
                 }
             }
         }
+        std::vector<unsigned char> win_aligned(so.n_slabs, 1);
+        for (int g = 0; g < n_groups; ++g)
+            if ((hbase[g] - hbase[g / 32 * 32]) % 4 != 0) win_aligned[g / 32] = 0;
         // widest slab footprint -> staged row sizes (worst alignment)
         int ncols_max = 0;
         for (int s = 0; s < so.n_slabs; ++s) {
-            const int ga = s * (kSlabW / 4), gb = std::min(ga + kSlabW / 4 - 1, n_groups - 1);
+            const int ga = s * 32, gb = std::min(ga + 31, n_groups - 1);
             ncols_max = std::max(ncols_max, std::min(hbase[gb] + SPAN, op.sw) - hbase[ga]);
         }
         const int s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
@@ -614,7 +698,7 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         so.vtable = op.vtable;
         so.vidx.resize(op.dh);
         for (int y = 0; y < op.dh; ++y) {
-            float row[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+            float row[12] = {0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};   // VT <= 12
             for (int j = 0; j < v.taps; ++j) row[j] = std::ldexp(static_cast<float>(v.coef[static_cast<size_t>(y) * v.taps + j]), 107);
             int id = -1;
             for (size_t k = 0; k + VT <= so.vcoef.size() && id < 0; k += VT)
@@ -635,6 +719,7 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             }
         }
         so.hdense_off = slab_append(blob, hdense);
+        so.win_aligned_off = slab_append(blob, win_aligned);
         so.hbase_off = slab_append(blob, hbase);
         so.vpos_off = slab_append(blob, vpos);
         sp->ops.push_back(so);
@@ -757,6 +842,7 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
             q.v_thr = so.v_thr; q.v_init = so.v_init; q.h_addend = so.h_addend;
             q.src_mode = so.src_mode; q.src_shift = op.src_shift;
             q.dst_shift = op.dst_shift; q.dither_xoff = op.dither_xoff;
+            q.win_aligned = p->blob + so.win_aligned_off;
             lp.raw_pitch = std::max(lp.raw_pitch, so.raw_pitch);   // every plane of the launch stages the launch's chunk count per row
         }
         lp.chunk_magic = static_cast<unsigned>((0x100000000ULL + (lp.raw_pitch >> 4) - 1) / (lp.raw_pitch >> 4));

@@ -103,7 +103,17 @@ bool fused_prefers_two_pass(const tvs_ctx *c) {
     return c->fused_narrow ? fused_plan_prefers_two_pass_w128(c->fused) : fused_plan_prefers_two_pass_w256(c->fused);
 }
 // forced_path: -1 automatic, 0 fused tile kernel, 1 two-pass kernels, 2 streaming kernel, 3 slab kernel
-bool use_stream_path(const tvs_ctx *c) { return c->streaming && (c->forced_path == 2 || c->forced_path < 0); }
+// Vertical down-scales: the streaming kernel's raw-byte pass wins on 8-bit sources, the slab kernel on 16-bit planar
+// ones (measured: 4K yuv420p10le -> 1080p lanczos 37.8 K vs 29.5 K frames/s, profiles/r02_slab_history.md).
+bool slab_beats_stream(const tvs_ctx *c) {
+    if (!c->slab) return false;
+    for (const PlaneOp &op : c->plan.ops)
+        if (op.kind == kOpScale && !(op.src_bits > 8 && op.src_xstep == 2)) return false;
+    return true;
+}
+bool use_stream_path(const tvs_ctx *c) {
+    return c->streaming && (c->forced_path == 2 || (c->forced_path < 0 && !slab_beats_stream(c)));
+}
 bool use_slab_path(const tvs_ctx *c) {
     if (use_stream_path(c)) return false;
     return c->slab && (c->forced_path == 3 || c->forced_path < 0);
