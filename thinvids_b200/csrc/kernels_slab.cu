@@ -442,6 +442,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
         mis = (mis + pmod) & 15u;
         ++row;
         const int y_stop = min(static_cast<int>(v_yend[row - 1]), yb);   // rows complete now that this source row is in
+#pragma unroll 1
         while (y < y_stop) {
             const float *gp = v_coef + static_cast<int>(v_idx[y]) * VT;
             float g[12] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
