@@ -126,12 +126,24 @@ struct SlabStage {
     unsigned chunk_magic;
 };
 
+// A chunk at the edge of the plane: 4-byte words that each contain at least one needed byte, zeros elsewhere.  Rare, and
+// kept out of line so that the staging loop stays short (the hot code of this kernel has to fit the instruction cache).
+__device__ __noinline__ void slab_prefetch_edge(uint4 *dst, const uint8_t *g, int first, int last_byte) {
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
+        if (first + 4 * k <= last_byte && first + 4 * k + 3 >= 0) cp_async4(d, g + 4 * k);
+        else *d = 0u;
+    }
+}
+
 // Start the asynchronous copy of raw source rows [row0, row0 + kBlockRows) of the slab's footprint (rows counted from
 // the item's first source row) into `raw_block` ([kBlockRows][s_chunks] 16-byte chunks).  Rows are read as aligned
 // chunks starting at the chunk that holds the row's first sample, so byte i of a footprint row lands at position
 // mis + i of the staged row, mis (0..15) being the misalignment of the row's first byte; any pitch works.  A chunk that
 // would reach outside the plane is fetched as 4-byte words that each contain at least one needed byte; chunks and words
 // past the end of the row, and rows below the plane, are zeroed.
+template <int C>
 __device__ __forceinline__ void slab_prefetch_block(const SlabStage &st, int row0, uint4 *raw_block, int lane) {
     const int total = kBlockRows * st.s_chunks;
     const unsigned lo_mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(st.lo)) & 15u;
@@ -148,13 +160,15 @@ __device__ __forceinline__ void slab_prefetch_block(const SlabStage &st, int row
             *dst = make_uint4(0u, 0u, 0u, 0u);
         } else if (go >= 0 && go + 16 <= st.extent) {
             cp_async16(dst, st.lo + go);
-        } else {
+        } else if (C == 2) {
 #pragma unroll
             for (int k = 0; k < 4; ++k) {
                 unsigned *d = reinterpret_cast<unsigned *>(dst) + k;
                 if (first + 4 * k <= st.last_byte && first + 4 * k + 3 >= 0) cp_async4(d, st.lo + go + 4 * k);
                 else *d = 0u;
             }
+        } else {
+            slab_prefetch_edge(dst, st.lo + go, first, st.last_byte);
         }
     }
 }
@@ -162,8 +176,8 @@ __device__ __forceinline__ void slab_prefetch_block(const SlabStage &st, int row
 // Raw words of one staged block -> exact float samples.  The converted block mirrors the raw block: raw word i becomes
 // floats [i * n, (i + 1) * n) with n = 4 / (bytes between samples), so sample j of a footprint row sits at float index
 // (mis >> log2(bytes between samples)) + j of its converted row whatever the alignment.
-__device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
-                                                   unsigned mis0, unsigned pmod, int row0, int lane) {
+__device__ __forceinline__ void slab_convert_block_impl(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
+                                                        unsigned mis0, unsigned pmod, int row0, int lane) {
     const int total = kBlockRows * words_per_row;
     // `S` may sit a few floats off its natural alignment (see the aligned-window path of the horizontal pass): vector
     // stores only when the destination of every word is aligned for them
@@ -225,6 +239,33 @@ __device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S
                 }
             }
         }
+    }
+}
+
+__device__ __noinline__ void slab_convert_block_general(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
+                                                        unsigned mis0, unsigned pmod, int row0, int lane) {
+    slab_convert_block_impl(raw, S, words_per_row, src_mode, src_shift, mis0, pmod, row0, lane);
+}
+
+// What is inline here is hot code, and the hot code of this kernel has to stay small (profiles/r02_slab_history.md).
+// The 4-column instances (up-scales, mostly of 8-bit material) keep only the conversion of 8-bit planar sources into a
+// naturally aligned block inline and call the rest; the 2-column instances (down-scales, where 10-bit 4K sources are
+// the heavy case and a call in the block loop costs registers) inline everything.
+template <int C>
+__device__ __forceinline__ void slab_convert_block(const unsigned *raw, float *S, int words_per_row, int src_mode, int src_shift,
+                                                   unsigned mis0, unsigned pmod, int row0, int lane) {
+    if (C == 2) {
+        slab_convert_block_impl(raw, S, words_per_row, src_mode, src_shift, mis0, pmod, row0, lane);
+    } else if (src_mode == kSrcU8 && (static_cast<unsigned>(reinterpret_cast<uintptr_t>(S)) & 15u) == 0) {
+        const int total = kBlockRows * words_per_row;
+#pragma unroll 2
+        for (int i = lane; i < total; i += 32) {
+            const unsigned v = raw[i];
+            reinterpret_cast<float4 *>(S)[i] = make_float4(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7541u),
+                                                           byte_to_float(v, 0x7542u), byte_to_float(v, 0x7543u));
+        }
+    } else {
+        slab_convert_block_general(raw, S, words_per_row, src_mode, src_shift, mis0, pmod, row0, lane);
     }
 }
 
@@ -485,18 +526,18 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     // prologue: the first kRawBlocks - 1 blocks are on their way before anything is converted
 #pragma unroll 1
     for (int b = 0; b < kRawBlocks - 1; ++b) {
-        if (b < n_blocks) slab_prefetch_block(st, b * kBlockRows, RAW + b * block_chunks, lane);
+        if (b < n_blocks) slab_prefetch_block<C>(st, b * kBlockRows, RAW + b * block_chunks, lane);
         cp_async_commit();
     }
 #pragma unroll 1
     for (int b = 0; b < n_blocks; ++b) {
         cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
         __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
-        slab_convert_block(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
+        slab_convert_block<C>(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
                            src_shift, mis0, pmod, b * kBlockRows, lane);
         __syncwarp();                              // S is complete; the raw block is free again
         if (b + kRawBlocks - 1 < n_blocks)
-            slab_prefetch_block(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
+            slab_prefetch_block<C>(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
         cp_async_commit();
 
         const int rows_here = min(kBlockRows, rows_total - row);
