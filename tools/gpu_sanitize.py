@@ -25,7 +25,7 @@ bad = 0
 for sf, sw, sh, df, dw, dh, alg in cases:
     src = [F.random_frame(sf, sw, sh, 9), F.random_frame(sf, sw, sh, 10)]
     want = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(fr) for fr in src]
-    for path in ("auto", "two-pass", "fused", "stream"):
+    for path in ("auto", "two-pass", "fused", "stream", "slab"):
         with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
             try:
                 s.set_path(path)
