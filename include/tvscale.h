@@ -172,7 +172,9 @@ TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size
  *   TVS_INFO_PATH             0 = fused tile kernel, 1 = two-pass kernels through device scratch,
  *                             2 = same-size repack only, 3 = streaming (line-buffer) kernel for vertical down-scales,
  *                             4 = box-filter kernel (exact 2:1 area on 8-bit planes),
- *                             5 = slab kernel (warp-specialised row streaming for vertical up-scales).
+ *                             5 = slab kernel (one autonomous warp per 128-column slab),
+ *                             6 = cascade: two inner contexts, src -> tmp -> dst, as libswscale does for filters that reach
+ *                                 170 taps (extreme down-scales); each stage picks its own kernel.
  *                             Shapes that fall back to 1 (two-pass): rgb24 sources, filters wider than the fused /
  *                             streaming instances cover (more than 24 horizontal or 12 vertical taps), tables that fail the
  *                             FP32 exactness preconditions, and footprints that do not fit in shared memory.

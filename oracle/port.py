@@ -36,6 +36,8 @@ class PortScaler:
         self.dst = (dst_w, dst_h, dst_fmt)
         cp = (ctypes.c_int * 4)(*chr_pos) if chr_pos is not None else None
         self._ctx = self._lib.tvo_create(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, cp)
+        if not self._ctx:
+            raise ValueError("libswscale refuses this conversion (a cascade whose source is not 4x larger than its destination)")
 
     def table(self, which: int):
         """(int16 coefficients [n, taps], int32 positions [n]) of table 0 hLum, 1 hChr, 2 vLum, 3 vChr."""

@@ -42,6 +42,14 @@ typedef struct {
     int rgb_half;       /* FMT_RGB24 source: chroma is made at half width */
     uint16_t *rgb[3];   /* FMT_RGB24 source: the input stage's Y, U, V lines for the frame being scaled */
     o_filter hl, hc, vl, vc;
+    /* Cascade (libswscale utils.c, sws_init_context's RETCODE_USE_CASCADE branch): with accurate_rnd a filter that, padded
+     * to the table alignment of the x86 build (4 taps horizontally, 2 vertically), reaches 256 * 16 / 24 = 171 taps is not
+     * run; the context becomes two contexts, src -> tmp -> dst, with tmp a yuv420p frame of int(sqrt(srcW * dstW)) x
+     * int(sqrt(srcH * dstH)).  The two inner contexts take the library's DEFAULT chroma positions whatever the outer
+     * context was given (pinned against the genuine library, tests/test_oracle.py). */
+    void *cascade[2];
+    uint8_t *tmp[3];
+    int tmp_stride[3];
 } o_ctx;
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
@@ -219,6 +227,17 @@ static int local_pos(int p, int sub)
 
 static int step16(int s, int d) { return (int)((((int64_t)s << 16) + (d >> 1)) / d); }
 
+void tvo_destroy(void *p);
+
+/* RETCODE_USE_CASCADE of initFilter, for flags that include SWS_ACCURATE_RND on an x86 build: filterAlign is 4 for the
+ * horizontal tables and 2 for the vertical ones, the limit MAX_FILTER_SIZE * 16 / APCK_SIZE = 256 * 16 / 24. */
+int tvo_needs_cascade(int h_lum_taps, int h_chr_taps, int v_lum_taps, int v_chr_taps)
+{
+    const int limit = 256 * 16 / 24;   /* 170 in integer arithmetic: a padded filter size >= 170 cascades */
+    return ((h_lum_taps + 3) & ~3) >= limit || ((h_chr_taps + 3) & ~3) >= limit ||
+           ((v_lum_taps + 1) & ~1) >= limit || ((v_chr_taps + 1) & ~1) >= limit;
+}
+
 /* chr_pos: {src_h, src_v, dst_h, dst_v}, -513 = library default; may be NULL. */
 void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, const int *chr_pos)
 {
@@ -247,6 +266,18 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
     make_filter(&c->vl, step16(sh, dh), sh, dh, 1 << 12, alg, local_pos(-513, 0), local_pos(-513, 0));
     make_filter(&c->vc, step16(c->csh, c->cdh), c->csh, c->cdh, 1 << 12, alg,
                 local_pos(chr_pos[1], 1), local_pos(chr_pos[3], 1));
+    if (tvo_needs_cascade(c->hl.taps, c->hc.taps, c->vl.taps, c->vc.taps)) {
+        const int tw = (int)sqrt((double)sw * dw), th = (int)sqrt((double)sh * dh);
+        if ((int64_t)sw * sh <= 4LL * dw * dh) { tvo_destroy(c); return NULL; }   /* the library gives up here (EINVAL) */
+        c->cascade[0] = tvo_create(sw, sh, sfmt, tw, th, FMT_YUV420P, alg, NULL);
+        c->cascade[1] = tvo_create(tw, th, FMT_YUV420P, dw, dh, dfmt, alg, NULL);
+        if (!c->cascade[0] || !c->cascade[1]) { tvo_destroy(c); return NULL; }
+        const int cw = (tw + 1) >> 1, ch = (th + 1) >> 1;
+        c->tmp_stride[0] = tw; c->tmp_stride[1] = c->tmp_stride[2] = cw;
+        c->tmp[0] = (uint8_t *)malloc((size_t)tw * th);
+        c->tmp[1] = (uint8_t *)malloc((size_t)cw * ch);
+        c->tmp[2] = (uint8_t *)malloc((size_t)cw * ch);
+    }
     return c;
 }
 
@@ -256,6 +287,8 @@ void tvo_destroy(void *p)
     if (!c) return;
     o_filter *fs[4] = { &c->hl, &c->hc, &c->vl, &c->vc };
     for (int i = 0; i < 4; i++) { free(fs[i]->f); free(fs[i]->pos); }
+    for (int i = 0; i < 2; i++) if (c->cascade[i]) tvo_destroy(c->cascade[i]);
+    for (int i = 0; i < 3; i++) free(c->tmp[i]);
     free(c);
 }
 
@@ -460,6 +493,12 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
 int tvo_scale(void *p, const uint8_t *const src[], const int sstride[], uint8_t *const dst[], const int dstride[])
 {
     o_ctx *c = (o_ctx *)p;
+    if (c->cascade[0]) {
+        uint8_t *const tmp[3] = { c->tmp[0], c->tmp[1], c->tmp[2] };
+        if (tvo_scale(c->cascade[0], src, sstride, tmp, c->tmp_stride) < 0) return -1;
+        const uint8_t *const tsrc[3] = { c->tmp[0], c->tmp[1], c->tmp[2] };
+        return tvo_scale(c->cascade[1], tsrc, c->tmp_stride, dst, dstride) < 0 ? -1 : c->dh;
+    }
     if (c->sfmt == FMT_RGB24) {
         /* even widths only: with an odd width the library's half-width chroma reads one pixel past the row */
         if ((c->sw & 1) || fmt_bits(c->dfmt) < 8 || c->dfmt == FMT_RGB24) return -1;

@@ -143,3 +143,42 @@ def test_port_equals_genuine_library_with_explicit_chroma_siting():
         b = port.PortScaler(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, chr_pos=cp).scale(src)
         for x, y in zip(a, b):
             assert np.array_equal(x, y), cp
+
+
+@needs_ref
+def test_port_cascade_equals_genuine_library():
+    """libswscale's cascade (filters that reach 170 taps after padding): boundary cases on both axes, every format,
+    explicit chroma sitings (which the inner contexts ignore), and the refusal when the source is under 4x the destination."""
+    rnd = random.Random(5)
+    cases = [(0, 0, 399, 133, 9, 133, 4, None), (0, 3, 399, 133, 9, 133, 4, None), (0, 0, 16, 399, 16, 9, 4, None),
+             (2, 1, 800, 64, 12, 40, 0x200, None), (1, 0, 1000, 50, 20, 60, 4, None), (0, 0, 380, 16, 9, 16, 4, None),
+             (0, 0, 390, 16, 9, 16, 4, None), (0, 0, 16, 380, 16, 9, 4, None), (0, 0, 16, 384, 16, 9, 4, None), (0, 0, 16, 388, 16, 9, 4, None),
+             (0, 0, 16, 392, 16, 9, 4, None), (3, 2, 2000, 40, 16, 50, 0x200, None), (0, 0, 4000, 8, 8, 8, 0x200, None),
+             (0, 0, 399, 133, 9, 133, 4, (0, 128, 0, 128)), (0, 1, 399, 133, 9, 133, 4, (256, 128, 0, 0))]
+    for _ in range(20):
+        sf, df = rnd.randrange(4), rnd.randrange(4)
+        sw, dw, sh, dh = rnd.randrange(300, 1500), rnd.randrange(2, 16), rnd.randrange(8, 40), rnd.randrange(8, 60)
+        if rnd.random() < 0.5:
+            sw, dw, sh, dh = sh, dh, sw, dw
+        cases.append((sf, df, sw, sh, dw, dh, rnd.choice([4, 0x200, 2, 0x20]), None))
+    compared = 0
+    for sf, df, sw, sh, dw, dh, alg, cp in cases:
+        src = F.random_frame(sf, sw, sh, 91)
+        try:
+            ref = ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp)
+        except Exception:
+            with pytest.raises(ValueError):
+                port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp)
+            continue
+        a = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        b = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        ref.scale_into(src, a)
+        port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale_into(src, b)
+        compared += 1
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), (sf, df, sw, sh, dw, dh, hex(alg), cp)
+    assert compared >= 25
+    with pytest.raises(Exception):
+        ref_swscale.RefScaler(700, 16, 0, 4, 800, 0, 4)
+    with pytest.raises(ValueError):
+        port.PortScaler(700, 16, 0, 4, 800, 0, 4)

@@ -91,11 +91,6 @@ def test_random_shapes_against_oracle():
         src = F.random_frame(sf, sw, sh, 1000 + i)
         want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
         make_checker(sw, sh, sf, dw, dh, df, alg).scale_into(src, want)
-        try:
-            Scaler(sw, sh, sf, dw, dh, df, alg).close()
-        except tv_lib.TvscaleError as e:
-            assert "cascades" in str(e), e     # 171 taps or more: refused, never scaled differently from the library
-            continue
         for path in PATHS:
             got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
             with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
@@ -104,6 +99,50 @@ def test_random_shapes_against_oracle():
                 s.scale(src, got)
             for k, (a, b) in enumerate(zip(got, want)):
                 assert np.array_equal(a, b), (i, path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
+
+
+CASCADE_CASES = [(0, 0, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 3, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 0, 16, 399, 16, 9, F.SWS_BICUBIC),
+                 (2, 1, 800, 64, 12, 40, F.SWS_LANCZOS), (1, 0, 1000, 50, 20, 60, F.SWS_BICUBIC), (3, 2, 2000, 40, 16, 50, F.SWS_LANCZOS),
+                 (0, 0, 16, 380, 16, 9, F.SWS_BICUBIC), (0, 0, 16, 384, 16, 9, F.SWS_BICUBIC), (0, 1, 4000, 8, 8, 8, F.SWS_LANCZOS)]
+
+
+def test_cascaded_contexts_against_oracle():
+    """Filters that reach 170 taps (extreme down-scales): libswscale runs two contexts through a yuv420p intermediate of
+    sqrt sizes; so does tvs_create (TVS_INFO_PATH 6).  The port's cascade is pinned to the genuine library in
+    tests/test_oracle.py; here the GPU against the genuine library when it is there, else the port."""
+    import torch
+    from oracle import port, ref_swscale
+    from thinvids_b200.swscale import Scaler
+    make_checker = ref_swscale.RefScaler if ref_swscale.available() else port.PortScaler
+    for sf, df, sw, sh, dw, dh, alg in CASCADE_CASES:
+        frames = [F.random_frame(sf, sw, sh, 300 + i) for i in range(3)]
+        ck = make_checker(sw, sh, sf, dw, dh, df, alg)
+        want = []
+        for fr in frames:
+            w = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+            ck.scale_into(fr, w)
+            want.append(w)
+        with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+            expect_cascade = (sw, sh, dw, dh) != (16, 380, 16, 9)   # 167 taps stay under the limit, 169 (384 -> 9) pad to 170
+            assert (s.path == "cascade") == expect_cascade, (s.path, sw, sh, dw, dh)
+            got_host = [s.scale(fr) for fr in frames]
+            d_src = torch.from_numpy(s.src_layout.pack(frames)).cuda()
+            d_dst = torch.zeros((3, s.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+            s.scale_packed_device(d_src, d_dst)
+            torch.cuda.synchronize()
+            got_dev = s.dst_layout.unpack(d_dst.cpu().numpy())
+        for g in (got_host, got_dev):
+            for fr_g, fr_w in zip(g, want):
+                for a, b in zip(fr_g, fr_w):
+                    assert np.array_equal(a, b), (sf, df, sw, sh, dw, dh, hex(alg))
+
+
+def test_cascade_that_libswscale_refuses_is_refused():
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler
+    with pytest.raises(tv_lib.TvscaleError) as e:      # 700 -> 4 needs a cascade, but the source is not 4x the destination in area
+        Scaler(700, 16, "yuv420p", 4, 800, "yuv420p", "bicubic")
+    assert "refuses" in str(e.value)
 
 
 def test_unscaled_all_format_pairs_against_oracle():
@@ -301,8 +340,8 @@ def test_error_paths():
         Scaler(64, 64, 9, 32, 32, 0, F.SWS_BICUBIC)            # unknown format
     with pytest.raises(tv_lib.TvscaleError):
         Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC | F.SWS_LANCZOS)  # two algorithms
-    with pytest.raises(tv_lib.TvscaleError):
-        Scaler(4000, 64, 0, 8, 64, 0, F.SWS_LANCZOS)           # would need cascaded contexts
+    with pytest.raises(tv_lib.TvscaleError, match="refuses"):
+        Scaler(4000, 8, 0, 8, 1200, 0, F.SWS_LANCZOS)          # needs a cascade libswscale itself refuses (source < 4x destination)
     with pytest.raises(tv_lib.TvscaleError):
         Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC, device=99)
     with Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC) as s:

@@ -168,7 +168,13 @@ bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, i
         }
         kept = std::max(kept, live);
     }
-    if (kept > 256) return false;  // libswscale would cascade two contexts here; not supported
+    if (kept > 256) {   // far past the size at which libswscale cascades two contexts: report the size, build nothing
+        out.length = dst_len;
+        out.taps = kept;
+        out.coef.clear();
+        out.pos.clear();
+        return false;
+    }
 
     const int taps = kept;
     out.length = dst_len;

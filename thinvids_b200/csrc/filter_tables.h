@@ -30,7 +30,8 @@ int axis_position(int siting, int subsample_log2);
 
 // Build one table.  `one` is 1<<14 for horizontal and 1<<12 for vertical tables.
 // Returns false for arguments the scaler cannot handle (non-positive sizes, unknown algorithm,
-// or a kernel wider than 256 taps, where libswscale would switch to cascaded contexts).
+// or a kernel wider than 256 taps: `out.taps` then holds the size and no coefficients - libswscale cascades two
+// contexts long before that, and so does tvs_create).
 bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, int one, int src_pos, int dst_pos);
 
 }  // namespace tvs

@@ -94,6 +94,11 @@ struct tvs_ctx {
     uint8_t *stage_dst[kSlots] = {nullptr, nullptr, nullptr};
     size_t stage_src_bytes = 0, stage_dst_bytes = 0;
     long long launches = 0;
+    // Cascade (libswscale's RETCODE_USE_CASCADE): the conversion runs as two contexts, src -> tmp -> dst, tmp being
+    // yuv420p frames of int(sqrt(srcW * dstW)) x int(sqrt(srcH * dstH)) in a device buffer of `cascade_chunk` frames.
+    tvs_ctx *cascade[2] = {nullptr, nullptr};
+    uint8_t *cascade_tmp = nullptr;
+    int cascade_w = 0, cascade_h = 0, cascade_chunk = 0;
 };
 
 namespace {
@@ -430,6 +435,27 @@ int static_mid_for_device(int device, int16_t **out) {
 // a bounded number of frames at a time, and then through the same launches as planar sources.
 int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], const ptrdiff_t sf[3],
                   void *const dst[3], const ptrdiff_t dp[3], const ptrdiff_t df[3], int n_frames, cudaStream_t stream) {
+    if (c->cascade[0]) {
+        // src -> tmp -> dst, a bounded number of frames at a time through the context's intermediate frames
+        const int tw = c->cascade_w, th = c->cascade_h, cw = (tw + 1) / 2, ch = (th + 1) / 2;
+        const size_t tframe = static_cast<size_t>(tw) * th + 2 * static_cast<size_t>(cw) * ch;
+        void *tplanes[3] = {c->cascade_tmp, c->cascade_tmp + static_cast<size_t>(tw) * th,
+                            c->cascade_tmp + static_cast<size_t>(tw) * th + static_cast<size_t>(cw) * ch};
+        const ptrdiff_t tpitch[3] = {tw, cw, cw};
+        const ptrdiff_t tfs[3] = {static_cast<ptrdiff_t>(tframe), static_cast<ptrdiff_t>(tframe), static_cast<ptrdiff_t>(tframe)};
+        for (int f0 = 0; f0 < n_frames; f0 += c->cascade_chunk) {
+            const int nf = std::min(c->cascade_chunk, n_frames - f0);
+            const void *s3[3] = {nullptr, nullptr, nullptr};
+            void *d3[3] = {nullptr, nullptr, nullptr};
+            for (int i = 0; i < c->sfi.planes; ++i) s3[i] = static_cast<const uint8_t *>(src[i]) + static_cast<ptrdiff_t>(f0) * sf[i];
+            for (int i = 0; i < c->dfi.planes; ++i) d3[i] = static_cast<uint8_t *>(dst[i]) + static_cast<ptrdiff_t>(f0) * df[i];
+            const long long before = c->cascade[0]->launches + c->cascade[1]->launches;
+            if (int rc = enqueue_batch(c->cascade[0], s3, sp, sf, tplanes, tpitch, tfs, nf, stream)) return rc;
+            if (int rc = enqueue_batch(c->cascade[1], tplanes, tpitch, tfs, d3, dp, df, nf, stream)) return rc;
+            c->launches += c->cascade[0]->launches + c->cascade[1]->launches - before;
+        }
+        return 0;
+    }
     if (!c->sfi.rgb) return enqueue_planar(c, src, sp, sf, dst, dp, df, n_frames, stream);
     const size_t y_bytes = static_cast<size_t>(c->src_w) * c->src_h * 2, c_bytes = static_cast<size_t>(c->rgb_cw) * c->src_h * 2;
     const size_t per_frame = y_bytes + 2 * c_bytes;
@@ -564,24 +590,46 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     }
     const Algorithm a = static_cast<Algorithm>(alg);
     const int luma = axis_position(TVS_CHR_POS_DEFAULT, 0);
-    const bool ok = build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma) &&
-                    build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], src_hsub), axis_position(chr_pos[2], 1)) &&
-                    build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma) &&
-                    build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], src_vsub), axis_position(chr_pos[3], 1));
-    if (!ok) {
-        fail(-ENOSYS, "%dx%d -> %dx%d needs a filter wider than 256 taps (libswscale would cascade); not supported",
-             src_w, src_h, dst_w, dst_h);
-        delete c;
-        return nullptr;
+    const bool built[4] = {
+        build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma),
+        build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], src_hsub), axis_position(chr_pos[2], 1)),
+        build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma),
+        build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], src_vsub), axis_position(chr_pos[3], 1))};
+    for (int i = 0; i < 4; ++i) {
+        if (!built[i] && c->host_tables[i].taps <= 256) {   // (a table wider than 256 taps is the cascade's business, below)
+            fail(-EINVAL, "cannot build the filter tables for %dx%d -> %dx%d", src_w, src_h, dst_w, dst_h);
+            delete c;
+            return nullptr;
+        }
     }
-    // With accurate_rnd libswscale switches to two cascaded contexts once a filter, padded to the x86 build's table
-    // alignment (4 taps horizontally, 2 vertically), reaches 256 * 16 / 24 = 171 taps (RETCODE_USE_CASCADE).
-    if (((c->host_tables[0].taps + 3) & ~3) >= 171 || ((c->host_tables[1].taps + 3) & ~3) >= 171 ||
-        ((c->host_tables[2].taps + 1) & ~1) >= 171 || ((c->host_tables[3].taps + 1) & ~1) >= 171) {
-        fail(-ENOSYS, "%dx%d -> %dx%d needs a filter of 171 taps or more, where libswscale cascades two contexts; not supported",
-             src_w, src_h, dst_w, dst_h);
-        delete c;
-        return nullptr;
+    // With accurate_rnd libswscale does not run a filter that, padded to the x86 build's table alignment (4 taps
+    // horizontally, 2 vertically), reaches 256 * 16 / 24 = 170 taps (initFilter's RETCODE_USE_CASCADE): the context
+    // becomes two, src -> tmp -> dst, with tmp a yuv420p frame of int(sqrt(srcW * dstW)) x int(sqrt(srcH * dstH)) and both
+    // inner contexts at the library's default chroma positions (oracle/swscale_port.c, pinned against the genuine library).
+    if (((c->host_tables[0].taps + 3) & ~3) >= 170 || ((c->host_tables[1].taps + 3) & ~3) >= 170 ||
+        ((c->host_tables[2].taps + 1) & ~1) >= 170 || ((c->host_tables[3].taps + 1) & ~1) >= 170) {
+        if (static_cast<long long>(src_w) * src_h <= 4LL * dst_w * dst_h) {
+            fail(-EINVAL, "%dx%d -> %dx%d: libswscale refuses this conversion (it would cascade, and the source is not four times the destination)",
+                 src_w, src_h, dst_w, dst_h);
+            delete c;
+            return nullptr;
+        }
+        c->cascade_w = static_cast<int>(std::sqrt(static_cast<double>(src_w) * dst_w));
+        c->cascade_h = static_cast<int>(std::sqrt(static_cast<double>(src_h) * dst_h));
+        c->cascade[0] = tvs_create(device, src_w, src_h, src_fmt, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, flags, nullptr);
+        c->cascade[1] = c->cascade[0] ? tvs_create(device, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, dst_w, dst_h, dst_fmt, flags, nullptr) : nullptr;
+        const size_t tframe = static_cast<size_t>(c->cascade_w) * c->cascade_h +
+                              2 * static_cast<size_t>((c->cascade_w + 1) / 2) * ((c->cascade_h + 1) / 2);
+        c->cascade_chunk = static_cast<int>(std::min<size_t>(65535, std::max<size_t>(1, (static_cast<size_t>(64) << 20) / tframe)));
+        if (!c->cascade[0] || !c->cascade[1] ||
+            cudaMalloc(&c->cascade_tmp, tframe * static_cast<size_t>(c->cascade_chunk)) != cudaSuccess) {
+            const std::string why = g_last_error;
+            cudaGetLastError();
+            tvs_destroy(c);
+            fail(-EIO, "cascaded context: %s", why.empty() ? "device allocation failed" : why.c_str());
+            return nullptr;
+        }
+        return c;
     }
     build_plan(c);
     if (upload_tables(c) != 0) {
@@ -620,6 +668,9 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
 
 void tvs_destroy(tvs_ctx *c) {
     if (!c) return;
+    cudaSetDevice(c->device);
+    for (int i = 0; i < 2; ++i) if (c->cascade[i]) tvs_destroy(c->cascade[i]);
+    if (c->cascade_tmp) cudaFree(c->cascade_tmp);
     cudaSetDevice(c->device);
     if (c->fused) { if (c->fused_narrow) fused_plan_destroy_w128(c->fused); else fused_plan_destroy_w256(c->fused); }
     if (c->streaming) stream_plan_destroy(c->streaming);
@@ -800,11 +851,13 @@ long long tvs_info(const tvs_ctx *c, int what) {
     switch (what) {
     case TVS_INFO_KERNEL_LAUNCHES: return c->launches;
     case TVS_INFO_PATH:
+        if (c->cascade[0]) return 6;
         if (!c->plan.any_scale) return 2;
         if (c->box2 && c->forced_path < 0) return 4;
         return use_stream_path(c) ? 3 : use_slab_path(c) ? 5 : use_fused_path(c) ? 0 : 1;
     case TVS_INFO_SCRATCH_BYTES:
-        return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + tvs_ctx::kSlots * (c->stage_src_bytes + c->stage_dst_bytes));
+        return static_cast<long long>(c->mid_capacity_elems * sizeof(int16_t) + tvs_ctx::kSlots * (c->stage_src_bytes + c->stage_dst_bytes)) +
+               (c->cascade[0] ? tvs_info(c->cascade[0], what) + tvs_info(c->cascade[1], what) : 0);
     case TVS_INFO_SRC_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->sfi, c->src_w, c->src_h));
     case TVS_INFO_DST_FRAME_BYTES: return static_cast<long long>(tight_frame_bytes(c->dfi, c->dst_w, c->dst_h));
     default: return fail(-EINVAL, "unknown info key %d", what);
@@ -813,6 +866,14 @@ long long tvs_info(const tvs_ctx *c, int what) {
 
 int tvs_set_path(tvs_ctx *c, int path) {
     if (!c || path < -1 || path > 3) return fail(-EINVAL, "bad path");
+    if (c->cascade[0]) {
+        // both stages take the request, or neither does
+        if (tvs_set_path(c->cascade[0], path) == 0 && tvs_set_path(c->cascade[1], path) == 0) return 0;
+        const std::string why = g_last_error;
+        tvs_set_path(c->cascade[0], -1);
+        tvs_set_path(c->cascade[1], -1);
+        return fail(-ENOSYS, "cascaded context: %s", why.c_str());
+    }
     if (path == 3 && c->plan.any_scale && !c->slab) return fail(-ENOSYS, "this shape is not supported by the slab kernel");
     if (path == 0 && c->plan.any_scale && !c->fused) return fail(-ENOSYS, "this shape is not supported by the fused kernel");
     if (path == 2 && c->plan.any_scale && !c->streaming) return fail(-ENOSYS, "this shape is not supported by the streaming kernel");
@@ -826,6 +887,7 @@ int tvs_scale_batch_static(tvs_ctx *c, const void *const src[3], const ptrdiff_t
     if (!c) return fail(-EINVAL, "NULL context");
     if (n_frames < 0 || n_frames > 65535) return fail(-EINVAL, "n_frames must be 0..65535");
     if (c->sfi.rgb) return fail(-ENOSYS, "rgb24 sources need the context's input-stage buffer; use tvs_scale_batch");
+    if (c->cascade[0]) return fail(-ENOSYS, "a cascaded context needs its intermediate frames; use tvs_scale_batch");
     if (int rc = check_planes(c->sfi, c->src_w, c->src_h, src, src_pitch, "src")) return rc;
     if (int rc = check_planes(c->dfi, c->dst_w, c->dst_h, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
     const Plan &plan = c->plan;

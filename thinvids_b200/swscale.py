@@ -100,7 +100,7 @@ class Scaler:
 
     @property
     def path(self) -> str:
-        return ("fused", "two-pass", "repack", "stream", "box2", "slab")[self.info(_lib.INFO_PATH)]
+        return ("fused", "two-pass", "repack", "stream", "box2", "slab", "cascade")[self.info(_lib.INFO_PATH)]
 
     def set_path(self, path) -> None:
         code = {"auto": -1, "fused": 0, "two-pass": 1, "stream": 2, "slab": 3}.get(path, path)
