@@ -144,6 +144,28 @@ TVS_API int tvs_scale_batch_static(tvs_ctx *ctx,
                     int n_frames, void *stream);
 
 /*
+ * Replaces ffmpeg's `bwdif=mode=send_frame:parity=auto:deint=all` (libavfilter; the filter the reference puts in front of
+ * `scale` on its DVD path: worker/tasks.py:62-63,446-447, tools/upscale_benchmark.py:128-132).  PARITY UNPINNED: there is no
+ * libavfilter in the build image to compare with; the kernel follows the published algorithm and is tested against a
+ * numpy restatement of it (oracle/bwdif_port.py) and against its invariants.  The `encode` task keeps ffmpeg's own
+ * bwdif in its decode child unless asked otherwise.
+ *
+ * `src` / `dst`: planar 4:2:0 frames (TVS_FMT_YUV420P or TVS_FMT_YUV420P10LE), `n_frames` of them in stream order, same
+ * plane / pitch / frame-stride meaning as tvs_scale_batch.  Frame i is interpolated from frames i - 1, i, i + 1.  `tff`:
+ * the frames are top-field-first (the top field is kept), else bottom-field-first.  `flags`: TVS_BWDIF_STREAM_START =
+ * frame 0 is the first frame of the stream (it has no predecessor and gets the intra filter), otherwise frame 0 is only
+ * context for frame 1 and is not written; TVS_BWDIF_STREAM_END likewise for the last frame.  A stream is processed in
+ * batches by repeating one frame of context on either side.  Returns the number of frames written, or a negative code.
+ * tvs_bwdif_host is the same on tightly packed host frames (synchronous, allocates its device staging).
+ */
+enum { TVS_BWDIF_STREAM_START = 1, TVS_BWDIF_STREAM_END = 2 };
+TVS_API int tvs_bwdif_batch(int device, int fmt, int width, int height,
+                    const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
+                    void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
+                    int n_frames, int tff, int flags, void *stream);
+TVS_API int tvs_bwdif_host(int device, int fmt, int width, int height, const void *src, void *dst, int n_frames, int tff, int flags);
+
+/*
  * No counterpart in libswscale (which works on pageable memory): page-locked host buffers for tvs_scale_host().
  * Frames read into / written from such a buffer cross PCIe without the driver's intermediate staging copy and let the
  * host entry point overlap its copies with its kernels.  thinvids_b200/worker.py reads the decoder's raw video into a

@@ -14,7 +14,7 @@ import sys
 PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libtvscale.so")
-SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused_w256.cu", "kernels_fused_w128.cu", "kernels_stream.cu", "kernels_slab.cu", "tvscale_abi.cu"]
+SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused_w256.cu", "kernels_fused_w128.cu", "kernels_stream.cu", "kernels_slab.cu", "kernels_bwdif.cu", "tvscale_abi.cu"]
 HEADERS = ["filter_tables.h", "tvs_internal.h", "kernels_fused_impl.cuh", "scale_device.cuh", os.path.join("..", "..", "include", "tvscale.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "--fmad=true"]

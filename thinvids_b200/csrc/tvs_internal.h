@@ -183,6 +183,11 @@ void stream_plan_destroy(StreamPlan *p);
 int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_views[], const SampleView dst_views[], int n_frames,
                   cudaStream_t stream);
 
+// ---- bwdif de-interlacer (kernels_bwdif.cu): one plane of a batch; returns kernels launched or -1 ----
+int launch_bwdif_plane(const uint8_t *src, ptrdiff_t src_pitch, ptrdiff_t src_fstride, uint8_t *dst, ptrdiff_t dst_pitch,
+                       ptrdiff_t dst_fstride, int w, int h, int depth, int n_frames, int tff, bool stream_start, bool stream_end,
+                       cudaStream_t stream);
+
 // ---- slab kernel (kernels_slab.cu): warp-specialised row streaming for planes that are not shrunk vertically ----
 struct SlabPlan;  // opaque, owned by the context
 SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int device, std::string &err);

@@ -881,6 +881,62 @@ int tvs_set_path(tvs_ctx *c, int path) {
     return 0;
 }
 
+int tvs_bwdif_batch(int device, int fmt, int width, int height, const void *const src[3], const ptrdiff_t src_pitch[3],
+                    const ptrdiff_t src_frame_stride[3], void *const dst[3], const ptrdiff_t dst_pitch[3],
+                    const ptrdiff_t dst_frame_stride[3], int n_frames, int tff, int flags, void *stream) {
+    FormatInfo fi;
+    if (!format_info(fmt, fi) || fi.semi || fi.rgb) return fail(-EINVAL, "bwdif takes planar 4:2:0 frames (yuv420p, yuv420p10le)");
+    if (width < 1 || height < 1 || n_frames < 1) return fail(-EINVAL, "bad size or frame count");
+    if (int rc = check_planes(fi, width, height, src, src_pitch, "src")) return rc;
+    if (int rc = check_planes(fi, width, height, reinterpret_cast<const void *const *>(dst), dst_pitch, "dst")) return rc;
+    TVS_CUDA(cudaSetDevice(device), "cudaSetDevice");
+    const int cw = (width + 1) / 2, ch = (height + 1) / 2;
+    int written = 0;
+    for (int pl = 0; pl < 3; ++pl) {
+        const int rc = launch_bwdif_plane(static_cast<const uint8_t *>(src[pl]), src_pitch[pl], src_frame_stride[pl],
+                                          static_cast<uint8_t *>(dst[pl]), dst_pitch[pl], dst_frame_stride[pl], pl ? cw : width,
+                                          pl ? ch : height, fi.bits, n_frames, tff, (flags & TVS_BWDIF_STREAM_START) != 0,
+                                          (flags & TVS_BWDIF_STREAM_END) != 0, static_cast<cudaStream_t>(stream));
+        if (rc < 0) return cuda_fail(cudaGetLastError(), "bwdif kernel launch");
+    }
+    written = n_frames - ((flags & TVS_BWDIF_STREAM_START) ? 0 : 1) - ((flags & TVS_BWDIF_STREAM_END) ? 0 : 1);
+    return written < 0 ? 0 : written;
+}
+
+int tvs_bwdif_host(int device, int fmt, int width, int height, const void *src, void *dst, int n_frames, int tff, int flags) {
+    FormatInfo fi;
+    if (!format_info(fmt, fi) || fi.semi || fi.rgb) return fail(-EINVAL, "bwdif takes planar 4:2:0 frames (yuv420p, yuv420p10le)");
+    if (width < 1 || height < 1 || n_frames < 1 || !src || !dst) return fail(-EINVAL, "bad arguments");
+    TVS_CUDA(cudaSetDevice(device), "cudaSetDevice");
+    const size_t frame = tight_frame_bytes(fi, width, height);
+    const int cw = (width + 1) / 2, ch = (height + 1) / 2;
+    uint8_t *d_src = nullptr, *d_dst = nullptr;
+    if (cudaMalloc(&d_src, frame * n_frames) != cudaSuccess || cudaMalloc(&d_dst, frame * n_frames) != cudaSuccess) {
+        const cudaError_t e = cudaGetLastError();
+        if (d_src) cudaFree(d_src);
+        return cuda_fail(e, "cudaMalloc(bwdif staging)");
+    }
+    int rc = 0;
+    cudaError_t e = cudaMemcpy(d_src, src, frame * n_frames, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        const size_t y = static_cast<size_t>(width) * height * fi.bytes, c = static_cast<size_t>(cw) * ch * fi.bytes;
+        const void *sp[3] = {d_src, d_src + y, d_src + y + c};
+        void *dp[3] = {d_dst, d_dst + y, d_dst + y + c};
+        const ptrdiff_t pitch[3] = {static_cast<ptrdiff_t>(width) * fi.bytes, static_cast<ptrdiff_t>(cw) * fi.bytes, static_cast<ptrdiff_t>(cw) * fi.bytes};
+        const ptrdiff_t fs[3] = {static_cast<ptrdiff_t>(frame), static_cast<ptrdiff_t>(frame), static_cast<ptrdiff_t>(frame)};
+        rc = tvs_bwdif_batch(device, fmt, width, height, sp, pitch, fs, dp, pitch, fs, n_frames, tff, flags, nullptr);
+        if (rc >= 0) {
+            // frames that are context only are not written on the device; hand back only the written range
+            const int first = (flags & TVS_BWDIF_STREAM_START) ? 0 : 1;
+            if (rc > 0) e = cudaMemcpy(static_cast<uint8_t *>(dst) + first * frame, d_dst + first * frame, frame * rc, cudaMemcpyDeviceToHost);
+        }
+    }
+    cudaFree(d_src);
+    cudaFree(d_dst);
+    if (e != cudaSuccess) return cuda_fail(e, "bwdif copies");
+    return rc;
+}
+
 int tvs_scale_batch_static(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pitch[3], const ptrdiff_t src_frame_stride[3],
                            void *const dst[3], const ptrdiff_t dst_pitch[3], const ptrdiff_t dst_frame_stride[3],
                            int n_frames, void *stream) {

@@ -10,7 +10,7 @@ LIB_PATH = os.path.join(_PKG, "libtvscale.so")
 
 # Every symbol include/tvscale.h declares; tests check the built library exports each one.
 EXPORTS = ("tvs_create", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tvs_scale_batch_static", "tvs_filter_table",
-           "tvs_context_table", "tvs_info", "tvs_set_path", "tvs_last_error", "tvs_version", "tvs_host_alloc", "tvs_host_free")
+           "tvs_context_table", "tvs_info", "tvs_set_path", "tvs_last_error", "tvs_version", "tvs_host_alloc", "tvs_host_free", "tvs_bwdif_batch", "tvs_bwdif_host")
 
 STATIC_SCRATCH_BYTES = 32 << 20   # TVS_STATIC_SCRATCH_BYTES
 INFO_KERNEL_LAUNCHES, INFO_PATH, INFO_SCRATCH_BYTES, INFO_SRC_FRAME_BYTES, INFO_DST_FRAME_BYTES = range(5)
@@ -55,6 +55,10 @@ def load() -> ctypes.CDLL:
     lib.tvs_host_alloc.argtypes = [Z]
     lib.tvs_host_free.restype = None
     lib.tvs_host_free.argtypes = [P]
+    lib.tvs_bwdif_batch.restype = I
+    lib.tvs_bwdif_batch.argtypes = [I, I, I, I, P, P, P, P, P, P, I, I, I, P]
+    lib.tvs_bwdif_host.restype = I
+    lib.tvs_bwdif_host.argtypes = [I, I, I, I, P, P, I, I, I]
     lib.tvs_last_error.restype = ctypes.c_char_p
     lib.tvs_version.restype = ctypes.c_char_p
     _lib = lib

@@ -195,9 +195,39 @@ def _scale_stream_pinned(scaler, frames_in: BinaryIO, frames_out: BinaryIO, src_
     return n_frames, aborted
 
 
+class _GpuDeinterlacedReader:
+    """File-like view of a raw video stream with bwdif applied on the GPU (thinvids_b200.deinterlace; parity unpinned):
+    what the scaler reads when the job's graph de-interlaces and nothing upstream has done it."""
+
+    def __init__(self, stream: BinaryIO, width: int, height: int, fmt: str, tff: bool, device: int, batch_frames: int):
+        from .deinterlace import BwdifStream
+        self._in, self._frame = stream, F.frame_bytes(F.FMT_BY_NAME[fmt], width, height)
+        self._batch = max(2, batch_frames)
+        self._bw = BwdifStream(width, height, fmt, tff, device)
+        self._buf, self._eof = b"", False
+
+    def read(self, n: int = -1) -> bytes:
+        while not self._eof and (n < 0 or len(self._buf) < n):
+            raw = bytearray(self._frame * self._batch)
+            got = _readinto_exact(self._in, memoryview(raw))
+            if got % self._frame:
+                raise EOFError(f"raw video stream ended inside a frame ({got % self._frame} of {self._frame} bytes)")
+            if got:
+                out = self._bw.push(np.frombuffer(raw, dtype=np.uint8, count=got).reshape(-1, self._frame))
+                self._buf += out.tobytes()
+            if got < len(raw):
+                self._eof = True
+                self._buf += self._bw.flush().tobytes()
+        if n < 0:
+            n = len(self._buf)
+        out, self._buf = self._buf[:n], self._buf[n:]
+        return out
+
+
 def encode_part(job: Mapping, idx: int, frames_in: BinaryIO, frames_out: BinaryIO, *, src_w: int, src_h: int,
                 src_fmt: str = "yuv420p", device: int = 0, hooks: Optional[EncodeHooks] = None, batch_frames: int = 64,
-                deinterlaced_upstream: bool = False, scaler_factory: Optional[Callable[[ScaleStage, int], object]] = None) -> dict:
+                deinterlaced_upstream: bool = False, scaler_factory: Optional[Callable[[ScaleStage, int], object]] = None,
+                gpu_deinterlace: bool = False, tff: bool = True) -> dict:
     """Scale one segment's decoded frames as the job's filter text says.  `job` is the job hash (the fields
     `_effective_target_height_for_job` and `encode` read: target_height, software_encode, filename, source_codec,
     source_resolution).  `scaler_factory(stage, device)` exists for tests of the control flow; the default builds the
@@ -210,13 +240,16 @@ def encode_part(job: Mapping, idx: int, frames_in: BinaryIO, frames_out: BinaryI
         vf = encode_filtergraph(job)
         try:
             # VAAPI text ends in format=nv12,hwupload; the libx264 text names no format and x264 takes yuv420p
-            stage = ScaleStage.from_filtergraph(vf, src_w, src_h, src_fmt, deinterlaced_upstream=deinterlaced_upstream,
+            stage = ScaleStage.from_filtergraph(vf, src_w, src_h, src_fmt, deinterlaced_upstream=deinterlaced_upstream or gpu_deinterlace,
                                                 default_dst_fmt="yuv420p" if int(job.get("software_encode") or 0) else None)
         except FilterGraphError as e:
             return {"status": "FAILED", "reason": f"part {idx} ({stage_name}): {e}", "stage": stage_name}
         hooks.heartbeat("encode_start")
         if hooks.is_halted():
             return {"status": "ABORTED"}
+        if stage.deinterlace and gpu_deinterlace and not deinterlaced_upstream:
+            # the graph asks for bwdif and nothing upstream has run it: run it here, on the GPU, ahead of the scaler
+            frames_in = _GpuDeinterlacedReader(frames_in, src_w, src_h, src_fmt, tff, device, batch_frames)
 
         src_layout = PackedLayout(F.FMT_BY_NAME[stage.src_fmt], stage.src_w, stage.src_h)
         n_frames = 0
@@ -296,6 +329,8 @@ class EncodeEnv:
     device: int = 0
     batch_frames: int = 32
     scaler_factory: Optional[Callable[[ScaleStage, int], object]] = None
+    gpu_deinterlace: bool = False    # run the graph's bwdif on the GPU (parity unpinned) instead of in the decode child
+    top_field_first: bool = True     # field order handed to the GPU de-interlacer (raw video carries no flags)
     last_commands: dict = field(default_factory=dict)     # the two argv lists of the last part, for logs and tests
 
 
@@ -310,7 +345,7 @@ def configure(env: EncodeEnv) -> None:
 
 def build_commands(job: Mapping, in_path: str, out_path: str, stage: ScaleStage, fps: float, *, v_sel: int = 0, a_sel: int = 0,
                    source_path: Optional[str] = None, source_start_s: Optional[float] = None,
-                   source_duration_s: Optional[float] = None) -> tuple:
+                   source_duration_s: Optional[float] = None, deinterlace_in_decoder: bool = True) -> tuple:
     """The reference's single ffmpeg command (worker/tasks.py:1558-1586) cut in two around the scaler.
 
     decode:  same `*input_args`, the selected video stream only, `-vf setpts=PTS-STARTPTS[,bwdif=...]` (the part of the
@@ -331,7 +366,8 @@ def build_commands(job: Mapping, in_path: str, out_path: str, stage: ScaleStage,
         video_sel = f"0:v:{int(v_sel)}"
         audio_map = ["-map", f"1:a:{int(a_sel)}?"]
         extra_maps = ["-sn", "-dn", "-map_metadata", "-1", "-map_chapters", "-1"]
-    upstream = [f for f in parse_filtergraph(encode_filtergraph(job)) if f.name in ("setpts", "bwdif")]
+    upstream = [f for f in parse_filtergraph(encode_filtergraph(job))
+                if f.name == "setpts" or (f.name == "bwdif" and deinterlace_in_decoder)]
     upstream_text = ",".join(_filter_text(f) for f in upstream)
     decode = [*_FFMPEG_HEAD, *input_args, "-map", video_sel, "-an", "-sn", "-dn", "-vf", upstream_text,
               "-f", "rawvideo", "-pix_fmt", stage.src_fmt, "pipe:1"]
@@ -408,7 +444,8 @@ def encode(job_id: str, idx: int, master_host: str, v_sel: int = 0, a_sel: int =
         except FilterGraphError as e:
             return _fail(str(e), stage_name)
         decode_cmd, encode_cmd = build_commands(job, in_path, out_path, stage, fps, v_sel=v_sel, a_sel=a_sel, source_path=source_path,
-                                                source_start_s=source_start_s, source_duration_s=source_duration_s)
+                                                source_start_s=source_start_s, source_duration_s=source_duration_s,
+                                                deinterlace_in_decoder=not env.gpu_deinterlace)
         env.last_commands = {"decode": decode_cmd, "encode": encode_cmd}
         env.heartbeat(job_id, "encode_start", force=True, note=f"part={idx}")
         if env.is_halted(job_id):
@@ -437,7 +474,8 @@ def encode(job_id: str, idx: int, master_host: str, v_sel: int = 0, a_sel: int =
         hooks = EncodeHooks(is_halted=lambda: env.is_halted(job_id),
                             heartbeat=lambda st: env.heartbeat(job_id, st, note=f"part={idx}"))
         res = encode_part(job, idx, pr_dec.stdout, pr_enc.stdin, src_w=src_w, src_h=src_h, src_fmt=src_fmt, device=env.device,
-                          hooks=hooks, batch_frames=env.batch_frames, deinterlaced_upstream=True, scaler_factory=env.scaler_factory)
+                          hooks=hooks, batch_frames=env.batch_frames, deinterlaced_upstream=not env.gpu_deinterlace,
+                          scaler_factory=env.scaler_factory, gpu_deinterlace=env.gpu_deinterlace, tff=env.top_field_first)
         try:
             pr_enc.stdin.close()
         except Exception:
