@@ -238,6 +238,25 @@ int tvo_needs_cascade(int h_lum_taps, int h_chr_taps, int v_lum_taps, int v_chr_
            ((v_lum_taps + 1) & ~1) >= limit || ((v_chr_taps + 1) & ~1) >= limit;
 }
 
+void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, const int *chr_pos);
+/* Turn `c` into a cascade when one of its filters is too long (see o_ctx); 0 = fine, -1 = libswscale refuses. */
+static int tvo_setup_cascade(o_ctx *c)
+{
+    const int sw = c->sw, sh = c->sh, dw = c->dw, dh = c->dh, sfmt = c->sfmt, dfmt = c->dfmt, alg = c->alg;
+    if (!tvo_needs_cascade(c->hl.taps, c->hc.taps, c->vl.taps, c->vc.taps)) return 0;
+    const int tw = (int)sqrt((double)sw * dw), th = (int)sqrt((double)sh * dh);
+    if ((int64_t)sw * sh <= 4LL * dw * dh) return -1;   /* the library gives up here (EINVAL) */
+    c->cascade[0] = tvo_create(sw, sh, sfmt, tw, th, FMT_YUV420P, alg, NULL);
+    c->cascade[1] = tvo_create(tw, th, FMT_YUV420P, dw, dh, dfmt, alg, NULL);
+    if (!c->cascade[0] || !c->cascade[1]) return -1;
+    const int cw = (tw + 1) >> 1, ch = (th + 1) >> 1;
+    c->tmp_stride[0] = tw; c->tmp_stride[1] = c->tmp_stride[2] = cw;
+    c->tmp[0] = (uint8_t *)malloc((size_t)tw * th);
+    c->tmp[1] = (uint8_t *)malloc((size_t)cw * ch);
+    c->tmp[2] = (uint8_t *)malloc((size_t)cw * ch);
+    return 0;
+}
+
 /* chr_pos: {src_h, src_v, dst_h, dst_v}, -513 = library default; may be NULL. */
 void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, const int *chr_pos)
 {
@@ -258,6 +277,7 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
                     local_pos(chr_pos[0], c->rgb_half ? 1 : 0), local_pos(chr_pos[2], 1));
         make_filter(&c->vl, step16(sh, dh), sh, dh, 1 << 12, alg, local_pos(-513, 0), local_pos(-513, 0));
         make_filter(&c->vc, step16(c->csh, c->cdh), c->csh, c->cdh, 1 << 12, alg, local_pos(chr_pos[1], 0), local_pos(chr_pos[3], 1));
+        if (tvo_setup_cascade(c)) { tvo_destroy(c); return NULL; }
         return c;
     }
     make_filter(&c->hl, step16(sw, dw), sw, dw, 1 << 14, alg, local_pos(-513, 0), local_pos(-513, 0));
@@ -266,18 +286,7 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
     make_filter(&c->vl, step16(sh, dh), sh, dh, 1 << 12, alg, local_pos(-513, 0), local_pos(-513, 0));
     make_filter(&c->vc, step16(c->csh, c->cdh), c->csh, c->cdh, 1 << 12, alg,
                 local_pos(chr_pos[1], 1), local_pos(chr_pos[3], 1));
-    if (tvo_needs_cascade(c->hl.taps, c->hc.taps, c->vl.taps, c->vc.taps)) {
-        const int tw = (int)sqrt((double)sw * dw), th = (int)sqrt((double)sh * dh);
-        if ((int64_t)sw * sh <= 4LL * dw * dh) { tvo_destroy(c); return NULL; }   /* the library gives up here (EINVAL) */
-        c->cascade[0] = tvo_create(sw, sh, sfmt, tw, th, FMT_YUV420P, alg, NULL);
-        c->cascade[1] = tvo_create(tw, th, FMT_YUV420P, dw, dh, dfmt, alg, NULL);
-        if (!c->cascade[0] || !c->cascade[1]) { tvo_destroy(c); return NULL; }
-        const int cw = (tw + 1) >> 1, ch = (th + 1) >> 1;
-        c->tmp_stride[0] = tw; c->tmp_stride[1] = c->tmp_stride[2] = cw;
-        c->tmp[0] = (uint8_t *)malloc((size_t)tw * th);
-        c->tmp[1] = (uint8_t *)malloc((size_t)cw * ch);
-        c->tmp[2] = (uint8_t *)malloc((size_t)cw * ch);
-    }
+    if (tvo_setup_cascade(c)) { tvo_destroy(c); return NULL; }
     return c;
 }
 

@@ -154,7 +154,10 @@ def test_port_cascade_equals_genuine_library():
              (2, 1, 800, 64, 12, 40, 0x200, None), (1, 0, 1000, 50, 20, 60, 4, None), (0, 0, 380, 16, 9, 16, 4, None),
              (0, 0, 390, 16, 9, 16, 4, None), (0, 0, 16, 380, 16, 9, 4, None), (0, 0, 16, 384, 16, 9, 4, None), (0, 0, 16, 388, 16, 9, 4, None),
              (0, 0, 16, 392, 16, 9, 4, None), (3, 2, 2000, 40, 16, 50, 0x200, None), (0, 0, 4000, 8, 8, 8, 0x200, None),
-             (0, 0, 399, 133, 9, 133, 4, (0, 128, 0, 128)), (0, 1, 399, 133, 9, 133, 4, (256, 128, 0, 0))]
+             (0, 0, 399, 133, 9, 133, 4, (0, 128, 0, 128)), (0, 1, 399, 133, 9, 133, 4, (256, 128, 0, 0)),
+             # rgb24 sources cascade like any other (found by tools/gpu_fuzz.py: the port used to skip the check for them)
+             (4, 1, 306, 172, 114, 3, 2, None), (4, 3, 134, 199, 122, 2, 4, None), (4, 3, 234, 148, 6, 395, 0x200, None),
+             (4, 2, 52, 192, 100, 5, 4, None), (4, 0, 332, 222, 3, 216, 4, None), (4, 0, 700, 16, 4, 800, 4, None)]
     for _ in range(20):
         sf, df = rnd.randrange(4), rnd.randrange(4)
         sw, dw, sh, dh = rnd.randrange(300, 1500), rnd.randrange(2, 16), rnd.randrange(8, 40), rnd.randrange(8, 60)
@@ -172,7 +175,10 @@ def test_port_cascade_equals_genuine_library():
             continue
         a = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
         b = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
-        ref.scale_into(src, a)
+        if sf == 4:
+            a = ref.scale(src)       # padded buffers for the library's rgb24 input stage
+        else:
+            ref.scale_into(src, a)
         port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale_into(src, b)
         compared += 1
         for x, y in zip(a, b):

@@ -101,9 +101,36 @@ def test_random_shapes_against_oracle():
                 assert np.array_equal(a, b), (i, path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
 
 
+def test_planes_one_or_two_columns_wide_on_every_path():
+    """2- and 3-pixel-wide frames (chroma planes of one column): found by tools/gpu_fuzz.py, where the slab kernel staged
+    a row in a single 16-byte chunk and its 32-bit reciprocal of the chunk count overflowed."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    cases = [(0, 2, 135, 0, 457, 44, F.SWS_AREA), (0, 2, 14, 1, 2, 7, F.SWS_AREA), (0, 2, 290, 0, 2, 145, F.SWS_AREA),
+             (1, 2, 35, 2, 2, 17, F.SWS_BICUBIC), (1, 3, 281, 0, 2, 140, F.SWS_BILINEAR), (0, 2, 14, 0, 2, 7, F.SWS_AREA),
+             (0, 2, 64, 0, 2, 32, F.SWS_BICUBIC), (0, 2, 20, 0, 3, 50, F.SWS_LANCZOS), (3, 2, 40, 2, 2, 90, F.SWS_BICUBIC),
+             (2, 3, 33, 1, 2, 16, F.SWS_LANCZOS)]
+    ran = {p: 0 for p in PATHS}
+    for sf, sw, sh, df, dw, dh, alg in cases:
+        src = F.random_frame(sf, sw, sh, 5)
+        want = port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(src)
+        for path in PATHS:
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                if not _use_path(s, path):
+                    continue
+                got = s.scale(src)
+            ran[path] += 1
+            for k, (a, b) in enumerate(zip(got, want)):
+                assert np.array_equal(a, b), (path, sf, sw, sh, df, dw, dh, hex(alg), k)
+    assert ran["slab"] >= 6 and ran["auto"] == len(cases), ran
+
+
 CASCADE_CASES = [(0, 0, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 3, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 0, 16, 399, 16, 9, F.SWS_BICUBIC),
                  (2, 1, 800, 64, 12, 40, F.SWS_LANCZOS), (1, 0, 1000, 50, 20, 60, F.SWS_BICUBIC), (3, 2, 2000, 40, 16, 50, F.SWS_LANCZOS),
-                 (0, 0, 16, 380, 16, 9, F.SWS_BICUBIC), (0, 0, 16, 384, 16, 9, F.SWS_BICUBIC), (0, 1, 4000, 8, 8, 8, F.SWS_LANCZOS)]
+                 (0, 0, 16, 380, 16, 9, F.SWS_BICUBIC), (0, 0, 16, 384, 16, 9, F.SWS_BICUBIC), (0, 1, 4000, 8, 8, 8, F.SWS_LANCZOS),
+                 # rgb24 sources (tools/gpu_fuzz.py, round 2)
+                 (4, 1, 306, 172, 114, 3, F.SWS_BILINEAR), (4, 3, 134, 199, 122, 2, F.SWS_BICUBIC), (4, 3, 234, 148, 6, 395, F.SWS_LANCZOS),
+                 (4, 2, 52, 192, 100, 5, F.SWS_BICUBIC), (4, 0, 332, 222, 3, 216, F.SWS_BICUBIC)]
 
 
 def test_cascaded_contexts_against_oracle():
@@ -119,6 +146,9 @@ def test_cascaded_contexts_against_oracle():
         ck = make_checker(sw, sh, sf, dw, dh, df, alg)
         want = []
         for fr in frames:
+            if sf == 4:      # the genuine library's rgb24 input stage wants padded rows: scale() provides them
+                want.append(ck.scale(fr))
+                continue
             w = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
             ck.scale_into(fr, w)
             want.append(w)

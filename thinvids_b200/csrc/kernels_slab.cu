@@ -727,7 +727,9 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             const int ga = s * 32, gb = std::min(ga + 31, n_groups - 1);
             ncols_max = std::max(ncols_max, std::min(hbase[gb] + SPAN, op.sw) - hbase[ga]);
         }
-        const int s_chunks = (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1;
+        // at least two chunks: the kernel divides by the chunk count with a 32-bit reciprocal, and ceil(2^32 / 1) does not fit
+        // (found by tools/gpu_fuzz.py on one-column chroma planes, whose rows all landed in row 0 of the block)
+        const int s_chunks = std::max(2, (15 + (ncols_max - 1) * op.src_xstep + sample_bytes - 1) / 16 + 1);
         so.raw_pitch = 16 * s_chunks;
         // a converted row holds (16 / spacing) samples per chunk, and a lane's window may start up to SPAN short of its end
         so.s_pitch = ((s_chunks * (16 / op.src_xstep) + SPAN + 3) & ~3) + 4;
