@@ -49,8 +49,11 @@ enum {
     TVS_FMT_NV12        = 1, /* AV_PIX_FMT_NV12         planes Y, UV interleaved  8 bit  */
     TVS_FMT_YUV420P10LE = 2, /* AV_PIX_FMT_YUV420P10LE  planes Y, U, V            10 bit in the low bits of LE16  */
     TVS_FMT_P010LE      = 3, /* AV_PIX_FMT_P010LE       planes Y, UV interleaved  10 bit in the high bits of LE16 */
-    TVS_FMT_RGB24       = 4  /* AV_PIX_FMT_RGB24        one plane of R, G, B bytes; SOURCE only, even widths (what
+    TVS_FMT_RGB24       = 4, /* AV_PIX_FMT_RGB24        one plane of R, G, B bytes; SOURCE only, even widths (what
                                 tools/upscale_benchmark.py:159-182 feeds its lanczos stage); BT.601 limited-range output */
+    TVS_FMT_YUVJ420P    = 5  /* AV_PIX_FMT_YUVJ420P     yuv420p holding full-range (JPEG) samples: what ffmpeg's decoders hand
+                                the scale filter for MJPEG and most phone / camera H.264.  As source it implies
+                                TVS_SRC_FULL_RANGE, as destination TVS_DST_FULL_RANGE (libswscale's handle_jpeg) */
 };
 
 /* Scaler flags: numerically equal to libswscale's SWS_* so ffmpeg `flags=` values pass through. */
@@ -60,7 +63,14 @@ enum {
     TVS_AREA         = 0x20,
     TVS_LANCZOS      = 0x200,  /* tools/upscale_benchmark.py:163,182 */
     TVS_ACCURATE_RND = 0x40000,/* accepted; results are always accurate_rnd+bitexact */
-    TVS_BITEXACT     = 0x80000
+    TVS_BITEXACT     = 0x80000,
+    /* Sample ranges: libswscale's src_range / dst_range options (what vf_scale's in_range / out_range, or the frame's own
+     * colour range, set).  Not SWS_* bits.  When exactly one is set, the 15-bit intermediate is converted between full
+     * (JPEG) and limited (MPEG) range after the horizontal pass, with libswscale 9.1's constants and rounding (restated in
+     * oracle/swscale_port.c, checked against the genuine library); such contexts run on the integer two-pass kernels.
+     * A context that cascades (TVS_INFO_PATH 6) converts no range - neither does libswscale.  -ENOSYS for rgb24 sources. */
+    TVS_SRC_FULL_RANGE = 0x10000000,
+    TVS_DST_FULL_RANGE = 0x20000000
 };
 
 /* Chroma siting sentinel: "use libswscale's default" (centre), as sws_getContext does. */

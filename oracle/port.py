@@ -23,6 +23,8 @@ def _load():
         lib.tvo_destroy.argtypes = [ctypes.c_void_p]
         lib.tvo_scale.restype = ctypes.c_int
         lib.tvo_scale.argtypes = [ctypes.c_void_p] * 5
+        lib.tvo_set_ranges.restype = ctypes.c_int
+        lib.tvo_set_ranges.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_int]
         lib.tvo_table.restype = ctypes.c_int
         lib.tvo_table.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p]
         _lib = lib
@@ -30,7 +32,7 @@ def _load():
 
 
 class PortScaler:
-    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None):
+    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, ranges=None):
         self._lib = _load()
         self.src = (src_w, src_h, src_fmt)
         self.dst = (dst_w, dst_h, dst_fmt)
@@ -38,6 +40,8 @@ class PortScaler:
         self._ctx = self._lib.tvo_create(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, cp)
         if not self._ctx:
             raise ValueError("libswscale refuses this conversion (a cascade whose source is not 4x larger than its destination)")
+        if ranges is not None and self._lib.tvo_set_ranges(self._ctx, int(ranges[0]), int(ranges[1])) < 0:
+            raise NotImplementedError("range conversion is not restated for RGB sources")
 
     def table(self, which: int):
         """(int16 coefficients [n, taps], int32 positions [n]) of table 0 hLum, 1 hChr, 2 vLum, 3 vChr."""

@@ -80,7 +80,7 @@ def force_plain_c(on: bool = True) -> None:
 class RefScaler:
     """One SwsContext.  Not safe for concurrent ``scale`` calls (same rule as libswscale)."""
 
-    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, bitexact=True):
+    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, bitexact=True, ranges=None):
         avu, sws = _load()
         self._sws = sws
         self.src = (src_w, src_h, src_fmt)
@@ -88,6 +88,8 @@ class RefScaler:
         sf = avu.av_get_pix_fmt(_PIXFMT_NAMES[src_fmt])
         df = avu.av_get_pix_fmt(_PIXFMT_NAMES[dst_fmt])
         flags = alg | (0x40000 | 0x80000 if bitexact else 0)
+        if ranges is not None and chr_pos is None:
+            chr_pos = (-513, -513, -513, -513)
         if chr_pos is None:
             self._ctx = sws.sws_getContext(src_w, src_h, sf, dst_w, dst_h, df, flags, None, None, None)
         else:
@@ -95,6 +97,8 @@ class RefScaler:
             opts = {b"srcw": src_w, b"srch": src_h, b"dstw": dst_w, b"dsth": dst_h, b"src_format": sf,
                     b"dst_format": df, b"sws_flags": flags, b"src_h_chr_pos": chr_pos[0],
                     b"src_v_chr_pos": chr_pos[1], b"dst_h_chr_pos": chr_pos[2], b"dst_v_chr_pos": chr_pos[3]}
+            if ranges is not None:      # (src_range, dst_range), 1 = full (JPEG) range: what vf_scale's in_range / out_range set
+                opts[b"src_range"], opts[b"dst_range"] = int(ranges[0]), int(ranges[1])
             for k, v in opts.items():
                 if avu.av_opt_set_int(self._ctx, k, v, 0) < 0:
                     raise RuntimeError(f"av_opt_set_int({k!r}) failed")

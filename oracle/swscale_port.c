@@ -50,6 +50,14 @@ typedef struct {
     void *cascade[2];
     uint8_t *tmp[3];
     int tmp_stride[3];
+    /* Range conversion (swscale_internal.h lumConvertRange / chrConvertRange, FFmpeg >= 7.1 form): applied to the
+     * 15-bit intermediate right after the horizontal pass when source and destination ranges differ,
+     *   t' = min((t * coeff + offset) >> 14, 32767).
+     * Constants as ff_sws_init_range_convert derives them from the DESTINATION bit depth; the form and the values were
+     * checked against the genuine library by tools/fit_range_convert.py (unique coeff, offset inside a 60-wide window). */
+    int range_convert;            /* 0 none, 1 full -> limited, 2 limited -> full */
+    int rc_coeff[2];              /* luma, chroma */
+    int64_t rc_offset[2];
 } o_ctx;
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
@@ -257,6 +265,42 @@ static int tvo_setup_cascade(o_ctx *c)
     return 0;
 }
 
+static void solve_range(int src_min, int src_max, int dst_min, int dst_max, int src_shift, int mult_shift, int *coeff, int64_t *offset)
+{
+    const int total = mult_shift + src_shift;
+    const uint64_t q = ((uint64_t)(dst_max - dst_min) << total) / (uint64_t)(src_max - src_min);
+    *coeff = (int)((q + ((1u << src_shift) - 1)) >> src_shift);           /* AV_CEIL_RSHIFT */
+    *offset = ((int64_t)dst_max << total) - ((int64_t)src_max << src_shift) * *coeff + (1 << (mult_shift - 1));
+}
+
+/* src_full / dst_full: 1 = full (JPEG) range, 0 = limited (MPEG) range: libswscale's src_range / dst_range options, which
+ * ffmpeg's scale filter sets from in_range / out_range or the frame's colour range, and which the deprecated yuvj420p
+ * pixel format implies.  Returns 0, or -1 where this restatement was not checked (RGB sources). */
+int tvo_set_ranges(void *p, int src_full, int dst_full)
+{
+    o_ctx *c = (o_ctx *)p;
+    c->range_convert = 0;
+    if (!!src_full == !!dst_full) return 0;
+    /* a cascade's two inner contexts are created with the default ranges, so the library converts nothing there
+     * (pinned against it in tests/test_oracle.py) */
+    if (c->cascade[0]) return 0;
+    if (c->sfmt == FMT_RGB24) return -1;
+    const int depth = fmt_bits(c->dfmt);
+    const int src_shift = 15 - depth, mult_shift = 14;
+    const int mpeg_min = 16 << (depth - 8), mpeg_max_lum = 235 << (depth - 8), mpeg_max_chr = 240 << (depth - 8);
+    const int jpeg_max = (1 << depth) - 1;
+    if (src_full) {
+        c->range_convert = 1;
+        solve_range(0, jpeg_max, mpeg_min, mpeg_max_lum, src_shift, mult_shift, &c->rc_coeff[0], &c->rc_offset[0]);
+        solve_range(0, jpeg_max, mpeg_min, mpeg_max_chr, src_shift, mult_shift, &c->rc_coeff[1], &c->rc_offset[1]);
+    } else {
+        c->range_convert = 2;
+        solve_range(mpeg_min, mpeg_max_lum, 0, jpeg_max, src_shift, mult_shift, &c->rc_coeff[0], &c->rc_offset[0]);
+        solve_range(mpeg_min, mpeg_max_chr, 0, jpeg_max, src_shift, mult_shift, &c->rc_coeff[1], &c->rc_offset[1]);
+    }
+    return 0;
+}
+
 /* chr_pos: {src_h, src_v, dst_h, dst_v}, -513 = library default; may be NULL. */
 void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, const int *chr_pos)
 {
@@ -377,7 +421,12 @@ static int scale_plane(const o_ctx *c, const uint8_t *const src[], const int sst
                 acc += src_sample(c, src, sstride, pl, r, sx) * f[j];
             }
             acc >>= hshift;
-            mid[(size_t)r * dw + x] = (int16_t)(acc > 32767 ? 32767 : acc);
+            if (acc > 32767) acc = 32767;
+            if (c->range_convert) {
+                const int64_t v = ((int64_t)acc * c->rc_coeff[pl ? 1 : 0] + c->rc_offset[pl ? 1 : 0]) >> 14;
+                acc = (int32_t)(v > 32767 ? 32767 : v);
+            }
+            mid[(size_t)r * dw + x] = (int16_t)acc;
         }
     }
     for (int y = 0; y < dh; y++) {
@@ -522,14 +571,14 @@ int tvo_scale(void *p, const uint8_t *const src[], const int sstride[], uint8_t 
     /* planar -> p010le at equal size: libswscale's converter writes floor(w/2) chroma pairs, so
      * with an odd width the last pair of every chroma row is left untouched. */
     const int cdw_full = c->cdw;
-    if (same && c->dfmt == FMT_P010 && !fmt_semi(c->sfmt)) c->cdw = c->dw >> 1;
+    if (same && !c->range_convert && c->dfmt == FMT_P010 && !fmt_semi(c->sfmt)) c->cdw = c->dw >> 1;
     int rc = c->dh;
-    if (same && unscaled_rule(c, 0) == 4) {
+    if (same && !c->range_convert && unscaled_rule(c, 0) == 4) {
         copy_stored_p010_to_nv12(c, src, sstride, dst, dstride, 0);
         copy_stored_p010_to_nv12(c, src, sstride, dst, dstride, 1);
     } else {
         for (int pl = 0; pl < 3; pl++) {
-            int rule = same ? unscaled_rule(c, pl) : 0;
+            int rule = same && !c->range_convert ? unscaled_rule(c, pl) : 0;   /* a range change always runs the generic scaler */
             if (rule == 1) copy_plane(c, src, sstride, dst, dstride, pl);
             else if (rule == 2) copy_plane_10to8(c, src, sstride, dst, dstride, pl);
             else if (scale_plane(c, src, sstride, dst, dstride, pl)) rc = -1;

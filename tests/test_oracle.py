@@ -188,3 +188,43 @@ def test_port_cascade_equals_genuine_library():
         ref_swscale.RefScaler(700, 16, 0, 4, 800, 0, 4)
     with pytest.raises(ValueError):
         port.PortScaler(700, 16, 0, 4, 800, 0, 4)
+
+
+@needs_ref
+def test_port_range_conversion_equals_genuine_library():
+    """Full <-> limited range (yuvj420p sources, ffmpeg's in_range / out_range): the conversion of the 15-bit intermediate
+    with libswscale 9.1's constants, for every format pair (the constants follow the destination depth), scaled and
+    same-size, three input statistics.  tools/fit_range_convert.py shows how the form and the constants were found."""
+    rnd = random.Random(3)
+    cases = []
+    for sf in range(4):
+        for df in range(4):
+            for rg in ((1, 0), (0, 1)):
+                cases += [(sf, df, 64, 48, 64, 48, 4, rg), (sf, df, 67, 35, 67, 35, 4, rg), (sf, df, 64, 48, 96, 48, 0x200, rg),
+                          (sf, df, 64, 48, 64, 30, 2, rg)]
+    for _ in range(60):
+        cases.append((rnd.randrange(4), rnd.randrange(4), rnd.randrange(2, 300), rnd.randrange(2, 200), rnd.randrange(2, 400),
+                      rnd.randrange(2, 300), rnd.choice([2, 4, 0x20, 0x200]), rnd.choice([(1, 0), (0, 1)])))
+    cases.append((0, 0, 64, 48, 128, 96, 4, (1, 1)))     # equal ranges: nothing to convert
+    for n, (sf, df, sw, sh, dw, dh, alg, rg) in enumerate(cases):
+        hi = 255 if sf < 2 else 1023
+        rng = np.random.default_rng(n)
+        src = []
+        for rows, cols in F.plane_shapes(sf, sw, sh):
+            kind = n % 3
+            pl = (rng.integers(0, hi + 1, (rows, cols)) if kind == 0 else rng.integers(0, 2, (rows, cols)) * hi if kind == 1
+                  else np.add.outer(np.arange(rows) * 3, np.arange(cols) * 2) % (hi + 1)).astype(F.sample_dtype(sf))
+            src.append(pl << 6 if sf == 3 else pl)
+        a = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        b = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg, ranges=rg).scale_into(src, a)
+        port.PortScaler(sw, sh, sf, dw, dh, df, alg, ranges=rg).scale_into(src, b)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), (sf, df, sw, sh, dw, dh, hex(alg), rg)
+    # a cascaded context converts no range (its inner contexts are created with the defaults)
+    src = F.random_frame(0, 399, 133, 1)
+    plain = ref_swscale.RefScaler(399, 133, 0, 9, 133, 0, 4).scale(src)
+    for rg in ((1, 0), (0, 1)):
+        for got in (ref_swscale.RefScaler(399, 133, 0, 9, 133, 0, 4, ranges=rg).scale(src), port.PortScaler(399, 133, 0, 9, 133, 0, 4, ranges=rg).scale(src)):
+            for x, y in zip(got, plain):
+                assert np.array_equal(x, y), rg

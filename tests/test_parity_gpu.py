@@ -125,6 +125,68 @@ def test_planes_one_or_two_columns_wide_on_every_path():
     assert ran["slab"] >= 6 and ran["auto"] == len(cases), ran
 
 
+def test_range_conversion_against_oracle():
+    """Full <-> limited range (TVS_SRC_FULL_RANGE / TVS_DST_FULL_RANGE, the yuvj420p format code): every format pair, scaled
+    and same-size, through tvs_scale_host; checker = the genuine library when present, else the port pinned to it."""
+    from oracle import port, ref_swscale
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler
+    make_checker = ref_swscale.RefScaler if ref_swscale.available() else port.PortScaler
+    rnd = random.Random(11)
+    cases = []
+    for sf in range(4):
+        for df in range(4):
+            for rg in ((1, 0), (0, 1)):
+                cases += [(sf, df, 64, 48, 64, 48, F.SWS_BICUBIC, rg), (sf, df, 67, 35, 67, 35, F.SWS_BICUBIC, rg),
+                          (sf, df, 64, 48, 96, 48, F.SWS_LANCZOS, rg), (sf, df, 130, 96, 64, 30, F.SWS_AREA, rg)]
+    for _ in range(40):
+        cases.append((rnd.randrange(4), rnd.randrange(4), rnd.randrange(2, 300), rnd.randrange(2, 200), rnd.randrange(2, 400),
+                      rnd.randrange(2, 300), rnd.choice([2, 4, 0x20, 0x200]), rnd.choice([(1, 0), (0, 1)])))
+    names = {0: "limited", 1: "full"}
+    for n, (sf, df, sw, sh, dw, dh, alg, rg) in enumerate(cases):
+        src = F.random_frame(sf, sw, sh, 900 + n) if n % 2 else F.pattern_frame(sf, sw, sh, "checker")
+        want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+        try:
+            make_checker(sw, sh, sf, dw, dh, df, alg, ranges=rg).scale_into(src, want)
+        except (RuntimeError, ValueError):      # a cascade libswscale refuses
+            with pytest.raises(tv_lib.TvscaleError):
+                Scaler(sw, sh, sf, dw, dh, df, alg, src_range=names[rg[0]], dst_range=names[rg[1]])
+            continue
+        with Scaler(sw, sh, sf, dw, dh, df, alg, src_range=names[rg[0]], dst_range=names[rg[1]]) as s:
+            assert s.path in ("two-pass", "cascade"), s.path
+            got = s.scale(src)
+            if s.path == "two-pass":
+                with pytest.raises(tv_lib.TvscaleError):
+                    s.set_path("fused")
+        for k, (a, b) in enumerate(zip(got, want)):
+            assert np.array_equal(a, b), (sf, df, sw, sh, dw, dh, hex(alg), rg, k, int((a != b).sum()))
+    # the "J" format code through the C ABI is yuv420p + full range on that side; equal ranges convert nothing
+    src = F.random_frame(0, 320, 240, 5)
+    want = make_checker(320, 240, 0, 480, 270, 1, F.SWS_BICUBIC, ranges=(1, 0)).scale(src)
+    with Scaler(320, 240, "yuvj420p", 480, 270, "nv12", "bicubic") as s:
+        got = s.scale(src)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+    lib = tv_lib.load()
+    ctx = lib.tvs_create(0, 320, 240, tv_lib.FMT_YUVJ420P, 480, 270, 1, F.SWS_BICUBIC, None)
+    assert ctx, tv_lib.last_error()
+    assert lib.tvs_info(ctx, tv_lib.INFO_PATH) == 1      # two-pass
+    lib.tvs_destroy(ctx)
+    with Scaler(320, 240, "yuvj420p", 480, 270, "yuvj420p", "bicubic") as s, Scaler(320, 240, "yuv420p", 480, 270, "yuv420p", "bicubic") as p:
+        assert s.path == p.path != "two-pass"
+        for a, b in zip(s.scale(src), p.scale(src)):
+            assert np.array_equal(a, b)
+    # a cascade converts no range, as in libswscale
+    src = F.random_frame(0, 399, 133, 1)
+    want = make_checker(399, 133, 0, 9, 133, 0, F.SWS_BICUBIC, ranges=(1, 0)).scale(src)
+    with Scaler(399, 133, "yuvj420p", 9, 133, "yuv420p", "bicubic") as s:
+        assert s.path == "cascade"
+        for a, b in zip(s.scale(src), want):
+            assert np.array_equal(a, b)
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 48, "rgb24", 128, 96, "yuv420p", "bicubic", dst_range="full")
+
+
 CASCADE_CASES = [(0, 0, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 3, 399, 133, 9, 133, F.SWS_BICUBIC), (0, 0, 16, 399, 16, 9, F.SWS_BICUBIC),
                  (2, 1, 800, 64, 12, 40, F.SWS_LANCZOS), (1, 0, 1000, 50, 20, 60, F.SWS_BICUBIC), (3, 2, 2000, 40, 16, 50, F.SWS_LANCZOS),
                  (0, 0, 16, 380, 16, 9, F.SWS_BICUBIC), (0, 0, 16, 384, 16, 9, F.SWS_BICUBIC), (0, 1, 4000, 8, 8, 8, F.SWS_LANCZOS),

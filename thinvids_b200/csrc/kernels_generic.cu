@@ -29,7 +29,7 @@ template <typename SrcT>
 __global__ void __launch_bounds__(256)
 hpass_generic_kernel(const uint8_t *__restrict__ src, ptrdiff_t pitch, ptrdiff_t frame_stride, int xstep, int src_shift,
                      int sw, int dw, const int16_t *__restrict__ coef, const int32_t *__restrict__ pos, int taps,
-                     int hshift, int16_t *__restrict__ mid, size_t mid_frame_stride, int sh) {
+                     int hshift, int16_t *__restrict__ mid, size_t mid_frame_stride, int sh, int rc_coeff, int rc_offset) {
     const int x = blockIdx.x * blockDim.x + threadIdx.x;
     const int r = blockIdx.y;
     const int f = blockIdx.z;
@@ -41,8 +41,9 @@ hpass_generic_kernel(const uint8_t *__restrict__ src, ptrdiff_t pitch, ptrdiff_t
     int acc = 0;
 #pragma unroll 4
     for (int j = 0; j < n; ++j, p += xstep) acc += (load_sample<SrcT>(p) >> src_shift) * c[j];
-    acc >>= hshift;
-    mid[f * mid_frame_stride + static_cast<size_t>(r) * dw + x] = static_cast<int16_t>(min(acc, 32767));
+    acc = min(acc >> hshift, 32767);
+    if (rc_coeff) acc = min((acc * rc_coeff + rc_offset) >> 14, 32767);   // full <-> limited range (lumConvertRange / chrConvertRange)
+    mid[f * mid_frame_stride + static_cast<size_t>(r) * dw + x] = static_cast<int16_t>(acc);
 }
 
 // One thread per output sample.
@@ -424,10 +425,10 @@ int launch_hpass_generic(const PlaneOp &op, const SampleView &src, const DeviceT
     int16_t *m = mid + op.mid_offset;
     if (op.src_bits == 8)
         hpass_generic_kernel<uint8_t><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep,
-            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh);
+            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh, op.rc_coeff, op.rc_offset);
     else
         hpass_generic_kernel<uint16_t><<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, src.xstep,
-            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh);
+            op.src_shift, op.sw, op.dw, h.coef, h.pos, h.taps, op.hshift, m, mid_frame_stride, op.sh, op.rc_coeff, op.rc_offset);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

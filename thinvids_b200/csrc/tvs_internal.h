@@ -61,6 +61,7 @@ struct PlaneOp {
     int hshift = 7;                        // right shift after the horizontal sum
     OutputRule rule = kOut8;
     int dither_xoff = 0;                   // 3 for the V component when dithering
+    int rc_coeff = 0, rc_offset = 0;       // range conversion of the intermediate: t' = min((t * rc_coeff + rc_offset) >> 14, 32767); 0 = none
     int raw_tail_from = -1;                // kOpDither2 only: columns >= this use the un-shifted P010 word
     size_t mid_offset = 0;                 // element offset of this plane's intermediate inside a frame's scratch block
 };

@@ -67,6 +67,10 @@ size_t tight_frame_bytes(const FormatInfo &fi, int w, int h) {
 struct tvs_ctx {
     int device = 0;
     int src_w = 0, src_h = 0, dst_w = 0, dst_h = 0, src_fmt = 0, dst_fmt = 0, flags = 0;
+    // Range conversion (libswscale's lumConvertRange / chrConvertRange on the 15-bit intermediate): 0 none, 1 full ->
+    // limited, 2 limited -> full.  Constants {luma, chroma} as ff_sws_init_range_convert derives them (oracle/swscale_port.c).
+    int range_convert = 0;
+    int rc_coeff[2] = {0, 0}, rc_offset[2] = {0, 0};
     FormatInfo sfi{}, dfi{};
     AxisTable host_tables[4];
     DeviceTable dev_tables[4];
@@ -156,7 +160,7 @@ void build_plan(tvs_ctx *c) {
     const FormatInfo &s = c->sfi, &d = c->dfi;
     const int sw = c->src_w, sh = c->src_h, dw = c->dst_w, dh = c->dst_h;
     const int csw = (sw + 1) / 2, csh = (sh + 1) / 2, cdw = (dw + 1) / 2, cdh = (dh + 1) / 2;
-    const bool same = sw == dw && sh == dh;
+    const bool same = sw == dw && sh == dh && !c->range_convert;   // a range change always runs the scaler proper, as in libswscale
 
     auto logical_op = [&](int pl, PlaneOpKind kind) {
         PlaneOp op;
@@ -169,6 +173,7 @@ void build_plan(tvs_ctx *c) {
         op.hshift = s.bits == 8 ? 7 : s.bits - 1;
         op.rule = d.bits > 8 ? kOut10 : (s.bits > 8 ? kOut8Dither : kOut8);
         op.dither_xoff = pl == 2 ? 3 : 0;
+        if (c->range_convert) { op.rc_coeff = c->rc_coeff[pl ? 1 : 0]; op.rc_offset = c->rc_offset[pl ? 1 : 0]; }
         // Note: libswscale's same-size planar -> P010 converter writes only floor(w/2) chroma pairs and
         // leaves the last pair of an odd-width frame untouched; we write all ceil(w/2) pairs (the value the
         // scaler proper would produce), so every destination byte is defined.
@@ -521,6 +526,11 @@ void tvs_host_free(void *p) {
 
 tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt, int flags,
                     const int chr_pos[4]) {
+    // The deprecated "J" format is yuv420p carrying full-range samples (libswscale's handle_jpeg)
+    bool src_full = (flags & TVS_SRC_FULL_RANGE) != 0, dst_full = (flags & TVS_DST_FULL_RANGE) != 0;
+    if (src_fmt == TVS_FMT_YUVJ420P) { src_fmt = TVS_FMT_YUV420P; src_full = true; }
+    if (dst_fmt == TVS_FMT_YUVJ420P) { dst_fmt = TVS_FMT_YUV420P; dst_full = true; }
+    flags &= ~(TVS_SRC_FULL_RANGE | TVS_DST_FULL_RANGE);
     FormatInfo sfi, dfi;
     if (!format_info(src_fmt, sfi) || !format_info(dst_fmt, dfi)) {
         fail(-EINVAL, "unsupported pixel format (src %d, dst %d)", src_fmt, dst_fmt);
@@ -532,6 +542,12 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     }
     if (dfi.rgb) {
         fail(-ENOSYS, "rgb24 is supported as a source format only");
+        return nullptr;
+    }
+    if (sfi.rgb && src_full != dst_full) {
+        // rgb24 is full range by nature and the input stage's table already produces limited-range YUV; what libswscale does
+        // with an explicit destination range there has not been restated
+        fail(-ENOSYS, "range flags are not implemented for rgb24 sources");
         return nullptr;
     }
     if (sfi.rgb && (src_w & 1)) {
@@ -574,6 +590,24 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     c->src_w = src_w; c->src_h = src_h; c->dst_w = dst_w; c->dst_h = dst_h;
     c->src_fmt = src_fmt; c->dst_fmt = dst_fmt; c->flags = flags;
     c->sfi = sfi; c->dfi = dfi;
+    if (src_full != dst_full) {
+        // ff_sws_init_range_convert: the constants follow the DESTINATION depth; t' = min((t * coeff + offset) >> 14, 32767)
+        const int depth = dfi.bits, src_shift = 15 - depth, total = 14 + src_shift;
+        const long long mpeg_min = 16LL << (depth - 8), mpeg_lum = 235LL << (depth - 8), mpeg_chr = 240LL << (depth - 8), jpeg_max = (1LL << depth) - 1;
+        auto solve = [&](long long smin, long long smax, long long dmin, long long dmax, int &coeff, int &offset) {
+            const unsigned long long q = (static_cast<unsigned long long>(dmax - dmin) << total) / static_cast<unsigned long long>(smax - smin);
+            coeff = static_cast<int>((q + ((1ULL << src_shift) - 1)) >> src_shift);
+            offset = static_cast<int>((dmax << total) - (smax << src_shift) * coeff + (1 << 13));
+        };
+        c->range_convert = src_full ? 1 : 2;
+        if (src_full) {
+            solve(0, jpeg_max, mpeg_min, mpeg_lum, c->rc_coeff[0], c->rc_offset[0]);
+            solve(0, jpeg_max, mpeg_min, mpeg_chr, c->rc_coeff[1], c->rc_offset[1]);
+        } else {
+            solve(mpeg_min, mpeg_lum, 0, jpeg_max, c->rc_coeff[0], c->rc_offset[0]);
+            solve(mpeg_min, mpeg_chr, 0, jpeg_max, c->rc_coeff[1], c->rc_offset[1]);
+        }
+    }
     static const int centred[4] = {TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT, TVS_CHR_POS_DEFAULT};
     if (!chr_pos) chr_pos = centred;
     int csw = (src_w + 1) / 2, csh = (src_h + 1) / 2;
@@ -614,6 +648,9 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
             delete c;
             return nullptr;
         }
+        // (the two inner contexts are created with the default ranges, so a cascade converts no range: libswscale's behaviour,
+        // pinned in tests/test_oracle.py)
+        c->range_convert = 0;
         c->cascade_w = static_cast<int>(std::sqrt(static_cast<double>(src_w) * dst_w));
         c->cascade_h = static_cast<int>(std::sqrt(static_cast<double>(src_h) * dst_h));
         c->cascade[0] = tvs_create(device, src_w, src_h, src_fmt, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, flags, nullptr);
@@ -644,12 +681,14 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
                 if (t.pos[i] != 2 * i || t.coef[2 * i] != one / 2 || t.coef[2 * i + 1] != one / 2) return false;
             return true;
         };
-        bool ok = c->plan.any_scale && sfi.bits == 8 && dfi.bits == 8 && src_w == 2 * dst_w && src_h == 2 * dst_h &&
+        bool ok = c->plan.any_scale && !c->range_convert && sfi.bits == 8 && dfi.bits == 8 && src_w == 2 * dst_w && src_h == 2 * dst_h &&
                   (src_w % 4) == 0 && (src_h % 4) == 0 && sfi.semi == dfi.semi;
         for (int i = 0; ok && i < 4; ++i) ok = is_box(c->host_tables[i], i < 2 ? 1 << 14 : 1 << 12);
         c->box2 = ok;
     }
-    if (c->plan.any_scale && !sfi.rgb) {   // RGB sources run on the integer two-pass kernels (15-bit samples: see 4.4 in DESIGN.md)
+    // RGB sources run on the integer two-pass kernels (15-bit samples: see 4.4 in DESIGN.md), and so do range changes (the
+    // conversion is an integer multiply-add on the intermediate, wider than the float kernels keep exact)
+    if (c->plan.any_scale && !sfi.rgb && !c->range_convert) {
         std::string why;
         // Down-scales stage a wide source footprint and do better with 128-column tiles; up-scales amortise the
         // vertical pass over 256 columns.  If the preferred build cannot take the shape, try the other one;

@@ -69,11 +69,23 @@ class PackedLayout:
 class Scaler:
     """One scaling context on one GPU (the SwsContext of this package)."""
 
-    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags=F.SWS_BICUBIC, chr_pos=None, device=0):
+    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags=F.SWS_BICUBIC, chr_pos=None, device=0,
+                 src_range=None, dst_range=None):
+        """`src_range` / `dst_range`: "full" (JPEG) or "limited" (MPEG, the default), ffmpeg's in_range / out_range.  The
+        deprecated format name "yuvj420p" is yuv420p with full range on that side (include/tvscale.h TVS_FMT_YUVJ420P)."""
         self._lib = _lib.load()
+        if src_fmt == "yuvj420p":
+            src_fmt, src_range = "yuv420p", "full"
+        if dst_fmt == "yuvj420p":
+            dst_fmt, dst_range = "yuv420p", "full"
         self.src_fmt, self.dst_fmt = F.fmt_code(src_fmt), F.fmt_code(dst_fmt)
         self.src_w, self.src_h, self.dst_w, self.dst_h = src_w, src_h, dst_w, dst_h
         self.flags = F.ALG_BY_NAME[flags] if isinstance(flags, str) else int(flags)
+        for side, bit in ((src_range, _lib.SRC_FULL_RANGE), (dst_range, _lib.DST_FULL_RANGE)):
+            if side not in (None, "limited", "mpeg", "tv", "full", "jpeg", "pc", 0, 1):
+                raise ValueError(f"unknown range {side!r}")
+            if side in ("full", "jpeg", "pc", 1):
+                self.flags |= bit
         self.device = device
         cp = (ctypes.c_int * 4)(*chr_pos) if chr_pos is not None else None
         self._ctx = self._lib.tvs_create(device, src_w, src_h, self.src_fmt, dst_w, dst_h, self.dst_fmt, self.flags, cp)
