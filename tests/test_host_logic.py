@@ -79,6 +79,23 @@ def test_scale_stage_rejects_what_it_cannot_do():
             fg.ScaleStage.from_filtergraph(bad, 1920, 1080)
 
 
+def test_scale_stage_ranges():
+    """yuvj420p sources are full-range yuv420p; scale keeps the range unless out_range= changes it (vf_scale)."""
+    st = fg.ScaleStage.from_filtergraph("setpts=PTS-STARTPTS,scale=-2:1080,format=nv12,hwupload", 720, 480, "yuvj420p")
+    assert (st.src_fmt, st.src_range, st.dst_fmt, st.dst_range) == ("yuv420p", "full", "nv12", "full")
+    assert st.src_raw_args == ["-pix_fmt", "yuvj420p"] and st.dst_raw_args == ["-color_range", "pc", "-pix_fmt", "nv12"]
+    st = fg.ScaleStage.from_filtergraph("scale=-2:720:out_range=tv", 1920, 1080, "yuvj420p")
+    assert (st.src_range, st.dst_range, st.dst_fmt) == ("full", "limited", "yuv420p") and st.dst_raw_args == ["-pix_fmt", "yuv420p"]
+    st = fg.ScaleStage.from_filtergraph("scale=-2:720:in_range=limited:out_range=full,format=yuvj420p", 1920, 1080)
+    assert (st.src_range, st.dst_range, st.dst_fmt) == ("limited", "full", "yuv420p")
+    assert not fg.ScaleStage.from_filtergraph("scale=out_range=pc", 64, 48).is_identity     # same size, but a range change
+    assert fg.ScaleStage.from_filtergraph("setpts=PTS-STARTPTS", 64, 48, "yuvj420p").is_identity
+    with pytest.raises(fg.FilterGraphError):
+        fg.ScaleStage.from_filtergraph("scale=-2:720:out_range=bogus", 1920, 1080)
+    with pytest.raises(fg.FilterGraphError):
+        fg.ScaleStage.from_filtergraph("scale=-2:720:out_range=full,format=yuv420p", 1920, 1080, "rgb24")
+
+
 def test_shard_segments_is_a_partition():
     for n in (0, 1, 7, 64):
         for world in (1, 2, 4, 8):

@@ -179,7 +179,7 @@ class _FakeProc:
         self.terminated = True
 
 
-def _task_env(tmp_path, job, data, w, h, rc_enc=0, halted=lambda job_id: False, make_output=True):
+def _task_env(tmp_path, job, data, w, h, rc_enc=0, halted=lambda job_id: False, make_output=True, pix_fmt="yuv420p"):
     from thinvids_b200 import worker
     procs, beats, fields = [], [], {}
     sink = io.BytesIO()
@@ -197,7 +197,7 @@ def _task_env(tmp_path, job, data, w, h, rc_enc=0, halted=lambda job_id: False, 
         return pr
 
     uploads = []
-    env = worker.EncodeEnv(job_fields=lambda job_id: job, probe=lambda path: (w, h, "yuv420p", 24.0),
+    env = worker.EncodeEnv(job_fields=lambda job_id: job, probe=lambda path: (w, h, pix_fmt, 24.0),
                            set_job_fields=lambda job_id, m: fields.update(m), is_halted=halted,
                            heartbeat=lambda job_id, stage, force=False, note="": beats.append(stage),
                            base_dir=lambda job_id: str(tmp_path / job_id), popen=popen, scaler_factory=_StandIn,
@@ -249,6 +249,21 @@ def test_encode_task_software_dvd_branch_deinterlaces_in_the_decode_child(tmp_pa
     assert tail[6:] == ["-map", "0:v:0", "-map", "1:a:2?", "-sn", "-dn", "-map_metadata", "-1", "-map_chapters", "-1",
                         "-c:v", "libx264", "-preset", "veryfast", "-crf", "23", "-c:a", "aac", "-ac", "2", "-b:a", "192k",
                         enc[-1]]
+
+
+def test_encode_task_keeps_full_range_sources_full_range(tmp_path):
+    """Phone / camera H.264 and MJPEG decode as yuvj420p.  The reference's scale filter keeps the range (no out_range=), so
+    both children are told the frames are full range and the scaler converts nothing (worker/tasks.py:62-65,1565-1580)."""
+    from thinvids_b200 import worker
+    _, data = _raw(F.YUV420P, 720, 480, 2)
+    for soft, want_dst in (("1", ["-pix_fmt", "yuvj420p"]), ("0", ["-color_range", "pc", "-pix_fmt", "nv12"])):
+        env, procs, *_ = _task_env(tmp_path, {"target_height": "1080", "software_encode": soft}, data, 720, 480, pix_fmt="yuvj420p")
+        res = worker.encode("job9", 1, "http://master:8000")
+        assert res == {"status": "COMPLETED", "idx": 1}
+        dec, enc = procs[0].argv, procs[1].argv
+        assert dec[dec.index("rawvideo") + 1:] == ["-pix_fmt", "yuvj420p", "pipe:1"]
+        at = enc.index("rawvideo") + 1
+        assert enc[at:at + len(want_dst)] == want_dst and enc[at + len(want_dst)] == "-s"
 
 
 def test_encode_task_status_dicts(tmp_path):

@@ -136,6 +136,9 @@ def parse_filtergraph(text: str) -> list[FilterSpec]:
 _SCALE_FLAG_NAMES = {"bilinear": F.SWS_BILINEAR, "bicubic": F.SWS_BICUBIC, "area": F.SWS_AREA, "lanczos": F.SWS_LANCZOS,
                      "accurate_rnd": F.SWS_ACCURATE_RND, "bitexact": F.SWS_BITEXACT}
 _PASSTHROUGH = {"setpts", "hwupload", "null", "fps"}   # no pixel work in this stage
+# scale's in_range / out_range values (libavfilter/vf_scale.c): None = keep what the frames carry
+_RANGE_NAMES = {"auto": None, "unknown": None, "full": "full", "jpeg": "full", "pc": "full",
+                "limited": "limited", "mpeg": "limited", "tv": "limited"}
 
 
 def _eval_dim(expr: str, other: int, src_this: int, src_other: int) -> int:
@@ -166,11 +169,19 @@ class ScaleStage:
     flags: int
     deinterlace: bool       # the graph contains bwdif (must happen upstream)
     hwupload: bool          # the graph hands frames to a hardware encoder
+    # Sample ranges, "limited" (MPEG) or "full" (JPEG).  ffmpeg's decoders announce full-range 4:2:0 as yuvj420p (MJPEG, most
+    # phone and camera H.264); the scale filter keeps the input's range unless out_range= says otherwise, so the usual
+    # full-range part passes through with no conversion and comes out full range.
+    src_range: str = "limited"
+    dst_range: str = "limited"
 
     @classmethod
     def from_filtergraph(cls, text: str, src_w: int, src_h: int, src_fmt: str = "yuv420p", *,
                          deinterlaced_upstream: bool = False, default_dst_fmt: str | None = None) -> "ScaleStage":
         dst_w, dst_h, flags = src_w, src_h, F.SWS_BICUBIC
+        src_range, dst_range = "limited", None
+        if src_fmt == "yuvj420p":
+            src_fmt, src_range = "yuv420p", "full"
         dst_fmt = default_dst_fmt or src_fmt
         deint = hwup = False
         seen_scale = False
@@ -197,8 +208,18 @@ class ScaleStage:
                         flags |= _SCALE_FLAG_NAMES[name]
                     if not flags & (F.SWS_BILINEAR | F.SWS_BICUBIC | F.SWS_AREA | F.SWS_LANCZOS):
                         flags |= F.SWS_BICUBIC
+                for key in ("in_range", "out_range"):
+                    val = f.kwargs.get(key, "auto")
+                    if val not in _RANGE_NAMES:
+                        raise FilterGraphError(f"scale {key}={val!r} is not supported")
+                    if _RANGE_NAMES[val] and key == "in_range":
+                        src_range = _RANGE_NAMES[val]
+                    elif _RANGE_NAMES[val]:
+                        dst_range = _RANGE_NAMES[val]
             elif f.name == "format":
                 fmt = f.kwargs.get("pix_fmts", f.args[0] if f.args else "")
+                if fmt == "yuvj420p":
+                    fmt, dst_range = "yuv420p", "full"
                 if fmt not in F.FMT_BY_NAME or F.FMT_BY_NAME[fmt] in F.SOURCE_ONLY_FORMATS:
                     ok = sorted(n for n, c in F.FMT_BY_NAME.items() if c not in F.SOURCE_ONLY_FORMATS)
                     raise FilterGraphError(f"format={fmt!r}: only {ok} are supported")
@@ -217,13 +238,33 @@ class ScaleStage:
         if F.FMT_BY_NAME[dst_fmt] in F.SOURCE_ONLY_FORMATS:
             # tools/upscale_benchmark.py:163,182 always names the output format after its rgb24 input
             raise FilterGraphError(f"a {src_fmt} source needs an explicit format= (yuv420p, nv12, ...) after scale")
-        return cls(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, deint, hwup)
+        if src_range != (dst_range or src_range) and F.FMT_BY_NAME[src_fmt] in F.SOURCE_ONLY_FORMATS:
+            raise FilterGraphError("range conversion is not supported for rgb24 sources")
+        return cls(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, deint, hwup, src_range, dst_range or src_range)
 
     @property
     def is_identity(self) -> bool:
-        return (self.src_w, self.src_h, self.src_fmt) == (self.dst_w, self.dst_h, self.dst_fmt)
+        return (self.src_w, self.src_h, self.src_fmt, self.src_range) == (self.dst_w, self.dst_h, self.dst_fmt, self.dst_range)
+
+    @staticmethod
+    def _raw_args(fmt: str, rng: str) -> list:
+        if rng != "full":
+            return ["-pix_fmt", fmt]
+        # full range: 8-bit planar 4:2:0 has its own name in ffmpeg; every other layout carries the range as an option
+        return ["-pix_fmt", "yuvj420p"] if fmt == "yuv420p" else ["-color_range", "pc", "-pix_fmt", fmt]
+
+    @property
+    def src_raw_args(self) -> list:
+        """ffmpeg arguments that describe the raw frames entering the stage (decode child's output)."""
+        return self._raw_args(self.src_fmt, self.src_range)
+
+    @property
+    def dst_raw_args(self) -> list:
+        """ffmpeg arguments that describe the raw frames leaving the stage (encode child's input)."""
+        return self._raw_args(self.dst_fmt, self.dst_range)
 
     def make_scaler(self, device: int = 0):
         """The CUDA context for this stage (thinvids_b200.swscale.Scaler)."""
         from .swscale import Scaler
-        return Scaler(self.src_w, self.src_h, self.src_fmt, self.dst_w, self.dst_h, self.dst_fmt, self.flags, device=device)
+        return Scaler(self.src_w, self.src_h, self.src_fmt, self.dst_w, self.dst_h, self.dst_fmt, self.flags, device=device,
+                      src_range=self.src_range, dst_range=self.dst_range)

@@ -249,7 +249,7 @@ def encode_part(job: Mapping, idx: int, frames_in: BinaryIO, frames_out: BinaryI
             return {"status": "ABORTED"}
         if stage.deinterlace and gpu_deinterlace and not deinterlaced_upstream:
             # the graph asks for bwdif and nothing upstream has run it: run it here, on the GPU, ahead of the scaler
-            frames_in = _GpuDeinterlacedReader(frames_in, src_w, src_h, src_fmt, tff, device, batch_frames)
+            frames_in = _GpuDeinterlacedReader(frames_in, src_w, src_h, stage.src_fmt, tff, device, batch_frames)
 
         src_layout = PackedLayout(F.FMT_BY_NAME[stage.src_fmt], stage.src_w, stage.src_h)
         n_frames = 0
@@ -370,8 +370,8 @@ def build_commands(job: Mapping, in_path: str, out_path: str, stage: ScaleStage,
                 if f.name == "setpts" or (f.name == "bwdif" and deinterlace_in_decoder)]
     upstream_text = ",".join(_filter_text(f) for f in upstream)
     decode = [*_FFMPEG_HEAD, *input_args, "-map", video_sel, "-an", "-sn", "-dn", "-vf", upstream_text,
-              "-f", "rawvideo", "-pix_fmt", stage.src_fmt, "pipe:1"]
-    raw_in = ["-f", "rawvideo", "-pix_fmt", stage.dst_fmt, "-s", f"{stage.dst_w}x{stage.dst_h}", "-r", f"{fps:.6f}", "-i", "pipe:0"]
+              "-f", "rawvideo", *stage.src_raw_args, "pipe:1"]
+    raw_in = ["-f", "rawvideo", *stage.dst_raw_args, "-s", f"{stage.dst_w}x{stage.dst_h}", "-r", f"{fps:.6f}", "-i", "pipe:0"]
     if int(job.get("software_encode") or 0):
         encode = [*_FFMPEG_HEAD, "-y", "-progress", "pipe:2", *raw_in, *input_args, "-map", "0:v:0", *audio_map, *extra_maps,
                   "-c:v", "libx264", "-preset", "veryfast", "-crf", "23", *AUDIO_ARGS.split(), out_path]
