@@ -391,33 +391,43 @@ def test_full_size_batch_properties():
 
 
 def test_rgb24_sources_against_oracle():
-    """packed RGB frames in (input stage on the GPU, then the integer two-pass kernels), every
-    destination format, both chroma input widths, host planes and packed device batches."""
+    """packed RGB frames in (input stage on the GPU, then the slab kernel's split-sample horizontal pass
+    where it takes the shape, else the integer two-pass kernels; both are run), every destination format, both chroma input
+    widths, host planes and packed device batches, noise and two-level inputs (the worst case for the 15-bit sums)."""
     import torch
     from oracle import port
     from thinvids_b200.swscale import Scaler
     rnd = random.Random(77)
     algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
-    for i in range(40):
+    seen = set()
+    for i in range(48):
         sw, sh = 2 * rnd.randrange(1, 120), rnd.randrange(2, 140)
         dw, dh = (sw, sh) if rnd.random() < 0.15 else (rnd.randrange(2, 400), rnd.randrange(2, 300))
+        if i >= 40:
+            sw, sh, dw, dh = [(720, 480, 1920, 1080), (1440, 960, 1920, 1080), (2880, 1920, 1920, 1080), (640, 360, 1280, 720)][i % 4]
         alg, df = rnd.choice(algs), rnd.randrange(4)
         frames = [F.random_frame(F.RGB24, sw, sh, 900 + 3 * i + k) for k in range(3)]
+        if i % 3 == 1:     # only 0 and 255
+            frames = [[(p > 127).astype(np.uint8) * 255 for p in fr] for fr in frames]
         ref = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg)
         want = [ref.scale(fr) for fr in frames]
-        with Scaler(sw, sh, F.RGB24, dw, dh, df, alg) as s:
-            assert s.path == "two-pass"
-            got = s.scale(frames[0])
-            d_src = torch.from_numpy(s.src_layout.pack(frames)).cuda()
-            d_dst = torch.zeros((3, s.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
-            s.scale_packed_device(d_src, d_dst)
-            torch.cuda.synchronize()
-            got_batch = s.dst_layout.unpack(d_dst.cpu().numpy())
-        for a, b in zip(got, want[0]):
-            assert np.array_equal(a, b), (sw, sh, dw, dh, df, hex(alg))
-        for g, w in zip(got_batch, want):
-            for a, b in zip(g, w):
-                assert np.array_equal(a, b), (sw, sh, dw, dh, df, hex(alg), "batch")
+        for path in ("auto", "two-pass"):
+            with Scaler(sw, sh, F.RGB24, dw, dh, df, alg) as s:
+                s.set_path(path)
+                assert s.path in ("slab", "two-pass", "cascade"), s.path
+                seen.add(s.path)
+                got = s.scale(frames[0])
+                d_src = torch.from_numpy(s.src_layout.pack(frames)).cuda()
+                d_dst = torch.zeros((3, s.dst_layout.frame_bytes), dtype=torch.uint8, device="cuda")
+                s.scale_packed_device(d_src, d_dst)
+                torch.cuda.synchronize()
+                got_batch = s.dst_layout.unpack(d_dst.cpu().numpy())
+            for a, b in zip(got, want[0]):
+                assert np.array_equal(a, b), (path, sw, sh, dw, dh, df, hex(alg))
+            for g, w in zip(got_batch, want):
+                for a, b in zip(g, w):
+                    assert np.array_equal(a, b), (path, sw, sh, dw, dh, df, hex(alg), "batch")
+    assert {"slab", "two-pass"} <= seen, seen
 
 
 def test_error_paths():

@@ -39,6 +39,11 @@ constexpr int kSlabThreads = 32;   // one warp
 constexpr int kBlockRows = 4;      // source rows staged and converted together
 constexpr int kRawBlocks = 4;      // raw staging ring in blocks: the warp prefetches kRawBlocks - 1 blocks ahead
 constexpr int kMaxSlabOps = 3;
+// A fifth source mode, of this kernel only: 16-bit samples of up to 15 significant bits (the planes libswscale's RGB input
+// stage makes).  Sample x coefficient no longer fits a float exactly, so each sample is staged as two floats, its low
+// byte and its high byte, and the horizontal sum runs once over each (see the WIDE horizontal pass).
+constexpr int kSrcU16Split = 4;
+constexpr float kWideMagic = 0x1.8p-5f;   // 1.5 * 2^23 in units of the scaled coefficients (2^-28): the floor-by-addition constant
 #ifndef TVS_SLAB_MIN_CTAS
 #define TVS_SLAB_MIN_CTAS 21
 #endif
@@ -216,6 +221,23 @@ __device__ __forceinline__ void slab_convert_block_impl(const unsigned *raw, flo
                 S[2 * i + 1] = byte_to_float(v, 0x7432u) - 512.0f;
             }
         }
+    } else if (src_mode == kSrcU16Split) {          // two 16-bit samples per word -> low bytes in S, high bytes in the block behind it
+        float *hi = S + kBlockRows * (2 * words_per_row);
+        if ((s_mis & 7u) == 0) {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = raw[i];
+                reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7542u));
+                reinterpret_cast<float2 *>(hi)[i] = make_float2(byte_to_float(v, 0x7541u), byte_to_float(v, 0x7543u));
+            }
+        } else {
+#pragma unroll 2
+            for (int i = lane; i < total; i += 32) {
+                const unsigned v = raw[i];
+                S[2 * i] = byte_to_float(v, 0x7540u); S[2 * i + 1] = byte_to_float(v, 0x7542u);
+                hi[2 * i] = byte_to_float(v, 0x7541u); hi[2 * i + 1] = byte_to_float(v, 0x7543u);
+            }
+        }
     } else {
         // interleaved chroma: which byte / half of a word belongs to this plane depends on the row's alignment
 #pragma unroll 1
@@ -362,7 +384,12 @@ __device__ __forceinline__ void slab_store_slow(uint8_t *row, int x, int dw, int
 
 // FAST: the slab is full width, samples are back to back and every row of it starts on a store-sized boundary: one
 // vector store per lane and row.  Otherwise bounds-checked element stores (partial slabs, interleaved chroma, odd pitches).
-template <int C, int SPAN, int VT, int OUT, bool FAST>
+// WIDE: the source is staged as low and high bytes (kSrcU16Split).  With coefficients c scaled by 2^-28 the pass forms
+// A = sum(high * c) and B = sum(low * c), both exact, and needs floor((256 A + B) >> 13) = floor((A + floor(B / 256)) / 32):
+// floor(B / 256) comes from one FMA rounded down onto 1.5 * 2^23 (where floats are integers), the A chain starts at minus
+// that constant so that the two add up exactly, and the last division is the usual multiplication rounded down onto the
+// subnormal grid.
+template <int C, int SPAN, int VT, int OUT, bool FAST, bool WIDE>
 __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
     const SlabOpParams &op = P.op[it.oi];
     const float *v_coef = reinterpret_cast<const float *>(P.pool + P.vc[op.vclass].coef_off);
@@ -416,7 +443,9 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     // Aligned windows: when the lanes' windows start a multiple of 4 samples apart (exact 2:1, 4:1 ... down-scales, where
     // scalar loads 4 words apart would be 4-way bank conflicts) and every row has the same alignment, the converted block is
     // placed a few floats off so that each window starts on a 16-byte boundary and is read with 128-bit loads.
-    const bool aligned_win = C == 2 && pmod == 0 && (src_mode == kSrcU8 || src_mode == kSrcU16) && __ldg(op.win_aligned + it.slab) != 0;
+    const bool aligned_win = C == 2 && pmod == 0 && (src_mode == kSrcU8 || src_mode == kSrcU16 || src_mode == kSrcU16Split) &&
+                             __ldg(op.win_aligned + it.slab) != 0;
+    const int hi_off = kBlockRows * s_pitch;   // WIDE: the high bytes of a converted block sit this far behind the low bytes
     if (aligned_win) S += (4 - static_cast<int>((mis0 >> mshift) & 3u)) & 3;
     const float *s_lane = S + hb;
 
@@ -470,6 +499,29 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
             for (int i = 1; i < SPAN; ++i) {
 #pragma unroll
                 for (int c = 0; c < C; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
+            }
+            if (WIDE) {
+                // t holds B (low bytes); now A over the high bytes, started at minus the magic constant
+                if (C == 2 && aligned_win) {
+#pragma unroll
+                    for (int i = 0; i < (SPAN + 3) / 4; ++i) {
+                        const float4 v = reinterpret_cast<const float4 *>(win + hi_off)[i];
+                        px[4 * i] = v.x; px[4 * i + 1] = v.y; px[4 * i + 2] = v.z; px[4 * i + 3] = v.w;
+                    }
+                } else {
+#pragma unroll
+                    for (int i = 0; i < SPAN; ++i) px[i] = win[hi_off + i];
+                }
+                float ta[C];
+#pragma unroll
+                for (int c = 0; c < C; ++c) ta[c] = fmaf(px[0], cd[c][0], -kWideMagic);
+#pragma unroll
+                for (int i = 1; i < SPAN; ++i) {
+#pragma unroll
+                    for (int c = 0; c < C; ++c) ta[c] = fmaf(px[i], cd[c][i], ta[c]);
+                }
+#pragma unroll
+                for (int c = 0; c < C; ++c) t[c] = __fmaf_rd(t[c], 0x1p-8f, kWideMagic) + ta[c];
             }
             // floor(sum >> hshift) lands on the subnormal grid (one multiplication rounded toward minus infinity; for
             // samples centred on 512 the offset is an integer on that grid, so adding it afterwards is exact), clamped
@@ -554,7 +606,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 // horizontal coefficients and the vertical window together need more (measured: profiles/r02_slab_history.md).
 template <int C, int SPAN, int VT> struct SlabBudget { static constexpr int kMinCtas = SPAN + VT >= 26 ? 16 : C * (SPAN + VT) >= 52 ? 18 : TVS_SLAB_MIN_CTAS; };
 
-template <int C, int SPAN, int VT, int OUT>
+template <int C, int SPAN, int VT, int OUT, bool WIDE>
 __global__ void __launch_bounds__(kSlabThreads, SlabBudget<C, SPAN, VT>::kMinCtas)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     constexpr int kSlabW = 32 * C;
@@ -575,8 +627,8 @@ slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
         constexpr int kSample = OUT == kOutU10 ? 2 : 1, kAlign = C * kSample - 1;
         const uintptr_t d0 = reinterpret_cast<uintptr_t>(op.dst + it.f * op.dst_fstride) + static_cast<uintptr_t>(it.slab * kSlabW) * kSample;
         const bool fast = op.dst_xstep == kSample && (op.dst_pitch & kAlign) == 0 && (d0 & kAlign) == 0 && (it.slab + 1) * kSlabW <= op.dw;
-        if (fast) slab_run_item<C, SPAN, VT, OUT, true>(P, it, S, RAW, lane);
-        else slab_run_item<C, SPAN, VT, OUT, false>(P, it, S, RAW, lane);
+        if (fast) slab_run_item<C, SPAN, VT, OUT, true, WIDE>(P, it, S, RAW, lane);
+        else slab_run_item<C, SPAN, VT, OUT, false, WIDE>(P, it, S, RAW, lane);
         __syncwarp();
     }
 }
@@ -584,8 +636,9 @@ slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
 using SlabKernelFn = void (*)(const SlabLaunchParams);
 // `cols` adjacent output columns per lane (a slab is 32 * cols columns wide): 4 wherever the dense horizontal window of
 // four neighbours stays short (up-scales, mild down-scales), 2 for stronger down-scales, whose windows are long and far apart.
-struct SlabInstance { int cols, span, vt; SlabKernelFn fn[3]; };   // one kernel per output rule
-#define TVS_SLAB_INST(C, S, V) {C, S, V, {slab_scale_kernel<C, S, V, kOutU8>, slab_scale_kernel<C, S, V, kOutU8Dither>, slab_scale_kernel<C, S, V, kOutU10>}}
+struct SlabInstance { int cols, span, vt; SlabKernelFn fn[3], fn_wide[3]; };   // one kernel per output rule (wide sources are never dithered)
+#define TVS_SLAB_INST(C, S, V) {C, S, V, {slab_scale_kernel<C, S, V, kOutU8, false>, slab_scale_kernel<C, S, V, kOutU8Dither, false>, slab_scale_kernel<C, S, V, kOutU10, false>}, \
+                                {slab_scale_kernel<C, S, V, kOutU8, true>, nullptr, slab_scale_kernel<C, S, V, kOutU10, true>}}
 const SlabInstance kSlabInstances[] = {
     TVS_SLAB_INST(4, 4, 2), TVS_SLAB_INST(4, 6, 4), TVS_SLAB_INST(4, 8, 4), TVS_SLAB_INST(4, 8, 6), TVS_SLAB_INST(4, 12, 6), TVS_SLAB_INST(4, 12, 8),
     TVS_SLAB_INST(2, 6, 4), TVS_SLAB_INST(2, 8, 6), TVS_SLAB_INST(2, 10, 8), TVS_SLAB_INST(2, 12, 10), TVS_SLAB_INST(2, 14, 12),
@@ -660,9 +713,10 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         const bool wide_src = op.src_bits > 8;
         const int sample_bytes = wide_src ? 2 : 1;
         if (op.src_xstep != sample_bytes && op.src_xstep != 2 * sample_bytes) { err = "unexpected sample spacing"; delete sp; return nullptr; }
-        if (op.src_bits > 10) { err = "samples wider than 10 bits"; delete sp; return nullptr; }
+        const bool split = op.src_bits == 16 && op.src_xstep == 2 && op.rule != kOut8Dither;   // the RGB input stage's 15-bit planes
+        if (op.src_bits > 10 && !split) { err = "samples wider than 10 bits"; delete sp; return nullptr; }
         if (static_cast<long long>(op.sh) * op.sw * op.src_xstep >= (1LL << 30)) { err = "plane too large for 32-bit offsets"; delete sp; return nullptr; }
-        const int src_mode = wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
+        const int src_mode = split ? kSrcU16Split : wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
         const int out_mode = op.rule == kOut10 ? kOutU10 : op.rule == kOut8Dither ? kOutU8Dither : kOutU8;
         for (int y = 1; y < op.dh; ++y)
             if (v.pos[y] < v.pos[y - 1]) { err = "vertical positions go backwards"; delete sp; return nullptr; }
@@ -674,7 +728,12 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             if (s != (1 << 14)) { err = "horizontal row does not sum to one"; delete sp; return nullptr; }
             worst_abs = std::max(worst_abs, a);
         }
-        if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete sp; return nullptr; }
+        if (split) {
+            // low bytes: |B| <= 255 * worst_abs; high bytes (<= 127) on top of the 1.5 * 2^23 start value
+            if (op.hshift != 13 || 255 * worst_abs >= (1LL << 24) || 127 * worst_abs + (3LL << 22) + 255 * worst_abs / 256 + 1 >= (1LL << 24)) {
+                err = "horizontal sum not exact in fp32"; delete sp; return nullptr;
+            }
+        } else if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete sp; return nullptr; }
         // smallest instance whose dense window covers every group of `cols` neighbouring columns and whose vertical
         // window covers the taps; four columns per lane are preferred (less staging and bookkeeping per sample)
         int inst = -1;
@@ -702,7 +761,8 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         so.n_slabs = (op.dw + 32 * C - 1) / (32 * C);
         so.v_thr = vrule.thr;
         so.v_init = vrule.init;
-        so.h_addend = wide_src ? std::ldexp(16384.0f, -149) : 0.0f;   // (512 << 14) >> 9, as a subnormal
+        so.h_addend = wide_src && !split ? std::ldexp(16384.0f, -149) : 0.0f;   // (512 << 14) >> 9, as a subnormal
+        const int coef_shift = split ? op.hshift - 8 : op.hshift;   // split samples: the high byte already carries a factor 256
 
         std::vector<float> hdense(static_cast<size_t>(n_groups) * C * SPAN, 0.0f);
         std::vector<int> hbase(n_groups);
@@ -714,7 +774,7 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
                 for (int j = 0; j < h.taps; ++j) {
                     const int c = h.coef[static_cast<size_t>(x) * h.taps + j];
                     // scaled so that one FMA by 2^-126 lands floor(sum >> hshift) on the subnormal grid
-                    if (c) hdense[(static_cast<size_t>(g) * C + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -(23 + op.hshift));
+                    if (c) hdense[(static_cast<size_t>(g) * C + k) * SPAN + (h.pos[x] - hbase[g] + j)] = std::ldexp(static_cast<float>(c), -(23 + coef_shift));
                 }
             }
         }
@@ -808,13 +868,16 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
         SlabLaunchParams lp{};
         std::vector<size_t> members;
         for (size_t j = i; j < p->ops.size() && members.size() < kMaxSlabOps; ++j)
-            if (!done[j] && p->ops[j].instance == p->ops[i].instance && p->ops[j].out_mode == p->ops[i].out_mode) { done[j] = true; members.push_back(j); }
+            if (!done[j] && p->ops[j].instance == p->ops[i].instance && p->ops[j].out_mode == p->ops[i].out_mode &&
+                (p->ops[j].src_mode == kSrcU16Split) == (p->ops[i].src_mode == kSrcU16Split)) { done[j] = true; members.push_back(j); }
         // Row chunks: every item should cost about the same (all slabs are 128 columns wide, so cost ~ output rows) and
         // there should be several items per resident CTA; a chunk is never shorter than 64 rows (ring warm-up, tables).
         int min_dh = 1 << 30;
         for (size_t j : members) min_dh = std::min(min_dh, plan.ops[p->ops[j].op_index].dh);
         int chunk_rows = std::max(64, std::min(min_dh, 1024));
-        const SlabKernelFn fn = kSlabInstances[p->ops[i].instance].fn[p->ops[i].out_mode];
+        const SlabInstance &inst = kSlabInstances[p->ops[i].instance];
+        const SlabKernelFn fn = p->ops[i].src_mode == kSrcU16Split ? inst.fn_wide[p->ops[i].out_mode] : inst.fn[p->ops[i].out_mode];
+        if (!fn) return -1;
         size_t smem = 0;
         {
             int raw_pitch = 0;

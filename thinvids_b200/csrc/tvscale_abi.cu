@@ -686,8 +686,8 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         for (int i = 0; ok && i < 4; ++i) ok = is_box(c->host_tables[i], i < 2 ? 1 << 14 : 1 << 12);
         c->box2 = ok;
     }
-    // RGB sources run on the integer two-pass kernels (15-bit samples: see 4.4 in DESIGN.md), and so do range changes (the
-    // conversion is an integer multiply-add on the intermediate, wider than the float kernels keep exact)
+    // Range changes run on the integer two-pass kernels (the conversion is an integer multiply-add on the intermediate, wider
+    // than the float kernels keep exact); RGB sources on the slab kernel's split-sample pass, else on the two-pass kernels
     if (c->plan.any_scale && !sfi.rgb && !c->range_convert) {
         std::string why;
         // Down-scales stage a wide source footprint and do better with 128-column tiles; up-scales amortise the
@@ -701,6 +701,11 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
                                        : fused_plan_create_w256(c->plan, c->host_tables, device, why);
             if (c->fused) break;
         }
+    }
+    if (c->plan.any_scale && sfi.rgb) {
+        // the input stage's 15-bit planes go through the slab kernel's split-sample horizontal pass when it takes the shape
+        std::string why;
+        c->slab = slab_plan_create(c->plan, c->host_tables, device, why);
     }
     return c;
 }

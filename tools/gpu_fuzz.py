@@ -96,6 +96,8 @@ def main():
     t0, n, bad = time.time(), 0, 0
     while time.time() - t0 < budget:
         sf = rnd.choice([0, 0, 1, 2, 3, 4])
+        if os.environ.get("FUZZ_SF"):   # one source format only, e.g. 4 = rgb24
+            sf = int(os.environ["FUZZ_SF"])
         df = rnd.randrange(4)
         huge = bool(os.environ.get("FUZZ_HUGE"))   # up to 4K frames, every case large
         big = huge or rnd.random() < 0.25
