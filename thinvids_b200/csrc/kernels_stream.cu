@@ -219,8 +219,11 @@ __device__ __forceinline__ int dp2a_hi(unsigned pixels, int coef_pair, int acc) 
 // aligned relative to each other skip the float conversion altogether: the pass reads the raw staged words and does
 // two taps per IDP.2A, with each column's 16-bit coefficients pre-placed at the byte positions of its window inside NW
 // consecutive words (the placement depends only on the column and on the strip's alignment, not on the row).
+// Resident CTAs the register budget is set for (measured, one B200): the raw-byte instances gain 6-11 % at 6 CTAs
+// (80 registers) over 4 (128), the float instances are best at 5 (96 registers).
+constexpr int stream_min_ctas(int nw) { return nw > 0 ? 6 : 5; }
 template <int HT, int VT, int OUT, int NW>
-__global__ void __launch_bounds__(kSThreads, 4)
+__global__ void __launch_bounds__(kSThreads, stream_min_ctas(NW))
 stream_scale_kernel(const __grid_constant__ StreamLaunchParams P) {
     extern __shared__ __align__(16) float smem[];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -728,6 +731,13 @@ int stream_launch(const StreamPlan *p, const Plan &plan, const SampleView src_vi
         const size_t smem = static_cast<size_t>(m_floats + s_floats + 2 * raw_words) * 4;
         if (smem > 200 * 1024) return -2;
         const dim3 grid(strips, n_frames);
+        {
+            // room for the CTAs the register budget allows, no more: the rest of the 256 KB stays L1 for the tables
+            const size_t want = static_cast<size_t>(stream_min_ctas(kStreamInstances[chosen[i]].nw)) * (smem + 1024);
+            const int pct = static_cast<int>((want * 100 + (228 << 10) - 1) / (228 << 10));
+            cudaFuncSetAttribute(reinterpret_cast<const void *>(kStreamInstances[chosen[i]].fn[p->ops[i].out_mode]),
+                                 cudaFuncAttributePreferredSharedMemoryCarveout, std::min(100, std::max(pct, 15)));
+        }
         kStreamInstances[chosen[i]].fn[p->ops[i].out_mode]<<<grid, kSThreads, smem, stream>>>(lp);
         if (cudaPeekAtLastError() != cudaSuccess) return -1;
         ++launched;
