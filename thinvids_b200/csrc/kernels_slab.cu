@@ -221,23 +221,6 @@ __device__ __forceinline__ void slab_convert_block_impl(const unsigned *raw, flo
                 S[2 * i + 1] = byte_to_float(v, 0x7432u) - 512.0f;
             }
         }
-    } else if (src_mode == kSrcU16Split) {          // two 16-bit samples per word -> low bytes in S, high bytes in the block behind it
-        float *hi = S + kBlockRows * (2 * words_per_row);
-        if ((s_mis & 7u) == 0) {
-#pragma unroll 2
-            for (int i = lane; i < total; i += 32) {
-                const unsigned v = raw[i];
-                reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7542u));
-                reinterpret_cast<float2 *>(hi)[i] = make_float2(byte_to_float(v, 0x7541u), byte_to_float(v, 0x7543u));
-            }
-        } else {
-#pragma unroll 2
-            for (int i = lane; i < total; i += 32) {
-                const unsigned v = raw[i];
-                S[2 * i] = byte_to_float(v, 0x7540u); S[2 * i + 1] = byte_to_float(v, 0x7542u);
-                hi[2 * i] = byte_to_float(v, 0x7541u); hi[2 * i + 1] = byte_to_float(v, 0x7543u);
-            }
-        }
     } else {
         // interleaved chroma: which byte / half of a word belongs to this plane depends on the row's alignment
 #pragma unroll 1
@@ -260,6 +243,29 @@ __device__ __forceinline__ void slab_convert_block_impl(const unsigned *raw, flo
                     out[w] = byte_to_float(v, sel) - 512.0f;
                 }
             }
+        }
+    }
+}
+
+// kSrcU16Split (WIDE instances only; kept apart so that the other instances' code is untouched by it): two 16-bit samples
+// per word -> low bytes in S, high bytes in the block behind it.
+__device__ __forceinline__ void slab_convert_block_split(const unsigned *raw, float *S, int words_per_row, int lane) {
+    const int total = kBlockRows * words_per_row;
+    const unsigned s_mis = static_cast<unsigned>(reinterpret_cast<uintptr_t>(S)) & 15u;
+    float *hi = S + kBlockRows * (2 * words_per_row);
+    if ((s_mis & 7u) == 0) {
+#pragma unroll 2
+        for (int i = lane; i < total; i += 32) {
+            const unsigned v = raw[i];
+            reinterpret_cast<float2 *>(S)[i] = make_float2(byte_to_float(v, 0x7540u), byte_to_float(v, 0x7542u));
+            reinterpret_cast<float2 *>(hi)[i] = make_float2(byte_to_float(v, 0x7541u), byte_to_float(v, 0x7543u));
+        }
+    } else {
+#pragma unroll 2
+        for (int i = lane; i < total; i += 32) {
+            const unsigned v = raw[i];
+            S[2 * i] = byte_to_float(v, 0x7540u); S[2 * i + 1] = byte_to_float(v, 0x7542u);
+            hi[2 * i] = byte_to_float(v, 0x7541u); hi[2 * i + 1] = byte_to_float(v, 0x7543u);
         }
     }
 }
@@ -443,9 +449,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     // Aligned windows: when the lanes' windows start a multiple of 4 samples apart (exact 2:1, 4:1 ... down-scales, where
     // scalar loads 4 words apart would be 4-way bank conflicts) and every row has the same alignment, the converted block is
     // placed a few floats off so that each window starts on a 16-byte boundary and is read with 128-bit loads.
-    const bool aligned_win = C == 2 && pmod == 0 && (src_mode == kSrcU8 || src_mode == kSrcU16 || src_mode == kSrcU16Split) &&
-                             __ldg(op.win_aligned + it.slab) != 0;
-    const int hi_off = kBlockRows * s_pitch;   // WIDE: the high bytes of a converted block sit this far behind the low bytes
+    const bool aligned_win = C == 2 && pmod == 0 && (src_mode == kSrcU8 || src_mode == (WIDE ? kSrcU16Split : kSrcU16)) && __ldg(op.win_aligned + it.slab) != 0;
     if (aligned_win) S += (4 - static_cast<int>((mis0 >> mshift) & 3u)) & 3;
     const float *s_lane = S + hb;
 
@@ -500,8 +504,9 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 #pragma unroll
                 for (int c = 0; c < C; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
             }
-            if (WIDE) {
+            if constexpr (WIDE) {
                 // t holds B (low bytes); now A over the high bytes, started at minus the magic constant
+                const int hi_off = kBlockRows * s_pitch;   // the high bytes of a converted block sit this far behind the low bytes
                 if (C == 2 && aligned_win) {
 #pragma unroll
                     for (int i = 0; i < (SPAN + 3) / 4; ++i) {
@@ -585,8 +590,11 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     for (int b = 0; b < n_blocks; ++b) {
         cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
         __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
-        slab_convert_block<C>(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
-                           src_shift, mis0, pmod, b * kBlockRows, lane);
+        if constexpr (WIDE)
+            slab_convert_block_split(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, lane);
+        else
+            slab_convert_block<C>(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
+                               src_shift, mis0, pmod, b * kBlockRows, lane);
         __syncwarp();                              // S is complete; the raw block is free again
         if (b + kRawBlocks - 1 < n_blocks)
             slab_prefetch_block<C>(st, (b + kRawBlocks - 1) * kBlockRows, RAW + ((b + kRawBlocks - 1) % kRawBlocks) * block_chunks, lane);
