@@ -305,6 +305,28 @@ def test_chroma_siting_against_oracle():
             assert np.array_equal(a, b), cp
 
 
+def test_p010_padding_bits_are_ignored_on_every_path():
+    """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
+    (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    rng = np.random.default_rng(4)
+    for sw, sh, dw, dh, df, alg in [(320, 180, 640, 360, 3, F.SWS_LANCZOS), (640, 360, 320, 180, 1, F.SWS_BICUBIC), (322, 182, 200, 300, 0, F.SWS_BILINEAR),
+                                    (640, 360, 320, 180, 3, F.SWS_AREA), (256, 128, 256, 128, 1, F.SWS_BICUBIC), (1280, 720, 640, 360, 2, F.SWS_LANCZOS)]:
+        clean = F.random_frame(F.P010LE, sw, sh, 31)
+        dirty = [p | rng.integers(0, 64, p.shape, dtype=np.uint16) for p in clean]
+        want = port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(clean)
+        for x, y in zip(port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(dirty), want):
+            assert np.array_equal(x, y)
+        for path in PATHS:
+            with Scaler(sw, sh, F.P010LE, dw, dh, df, alg) as s:
+                if not _use_path(s, path):
+                    continue
+                got = s.scale(dirty)
+            for k, (a, b) in enumerate(zip(got, want)):
+                assert np.array_equal(a, b), (path, sw, sh, dw, dh, df, hex(alg), k, int((a != b).sum()))
+
+
 def test_pitched_and_strided_device_surfaces():
     """NVDEC-style pitched planes (pitch > row, odd pitches too) through tvs_scale_batch directly."""
     import torch

@@ -564,6 +564,7 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
             const int rstep = kThreads >> clog;
             const int src_mode = op.src_mode;
             const float sscale = op.src_scale;
+            const unsigned keep16 = sscale < 1.0f ? 0xFFC0FFC0u : 0xFFFFFFFFu;   // P010: drop whatever sits in the six padding bits, as libswscale's shift does
             // a thread converts the chunks it prefetched: byte p of a staged row is sample p / spacing of S
             for (int ch = tid & cmask; ch < s_chunks; ch += 1 << clog) {
                 int row = tid >> clog;
@@ -591,7 +592,8 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                 } else if (src_mode == kSrcU16) {      // eight 16-bit samples per chunk, centred on 512
                     float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + 2 * ch;
                     for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
-                        const uint4 v = *rw;
+                        uint4 v = *rw;
+                        v.x &= keep16; v.y &= keep16; v.z &= keep16; v.w &= keep16;
                         out[0] = make_float4(fmaf(byte_to_float(v.x, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.x, 0x7432u), sscale, -512.0f),
                                              fmaf(byte_to_float(v.y, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.y, 0x7432u), sscale, -512.0f));
                         out[1] = make_float4(fmaf(byte_to_float(v.z, 0x7410u), sscale, -512.0f), fmaf(byte_to_float(v.z, 0x7432u), sscale, -512.0f),
@@ -601,7 +603,8 @@ fused_scale_kernel(const __grid_constant__ FusedLaunchParams P) {
                     float4 *out = reinterpret_cast<float4 *>(S + row * s_pitch) + ch;
                     for (; row < nrows; row += rstep, rw += rstep * s_chunks, out += rstep * (s_pitch / 4)) {
                         const unsigned sel = ((mis0 + row * pmod) & 2u) ? 0x7432u : 0x7410u;
-                        const uint4 v = *rw;
+                        uint4 v = *rw;
+                        v.x &= keep16; v.y &= keep16; v.z &= keep16; v.w &= keep16;
                         *out = make_float4(fmaf(byte_to_float(v.x, sel), sscale, -512.0f), fmaf(byte_to_float(v.y, sel), sscale, -512.0f),
                                            fmaf(byte_to_float(v.z, sel), sscale, -512.0f), fmaf(byte_to_float(v.w, sel), sscale, -512.0f));
                     }

@@ -159,8 +159,12 @@ __device__ __forceinline__ void convert_block(const StreamOpParams &op, const un
         const int step_rows = op.pf_step_rows, step_chunks = op.pf_step_chunks;
         int row = static_cast<int>(__umulhi(static_cast<unsigned>(tid), op.chunk_magic));
         int ch = tid - row * s_chunks;
+        // P010 keeps its 10 bits in the top of the word: whatever a decoder left in the six bits below is dropped first, as
+        // libswscale's integer shift drops it (sscale < 1 marks that layout)
+        const unsigned keep = sscale < 1.0f ? 0xFFC0FFC0u : 0xFFFFFFFFu;
         for (int idx = tid; idx < total; idx += kSThreads) {
-            const uint4 v = reinterpret_cast<const uint4 *>(raw)[idx];
+            uint4 v = reinterpret_cast<const uint4 *>(raw)[idx];
+            v.x &= keep; v.y &= keep; v.z &= keep; v.w &= keep;
             float *srow = S + row * s_pitch;
             if (src_mode == kSrcU16 && op.s_split) {   // eight samples per chunk, even and odd positions apart
                 reinterpret_cast<float4 *>(srow)[ch] = make_float4(wide_to_float(v.x, 0x7410u, sscale, bias), wide_to_float(v.y, 0x7410u, sscale, bias),
