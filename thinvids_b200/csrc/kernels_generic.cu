@@ -475,7 +475,13 @@ inline bool aligned_for(const void *p, ptrdiff_t pitch, ptrdiff_t frame, int n_f
 }
 }  // namespace
 
-int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream) {
+int launch_copy_rows(const SampleView &src_in, const SampleView &dst_in, int row_bytes, int rows, int n_frames, cudaStream_t stream) {
+    SampleView src = src_in, dst = dst_in;
+    // Tightly packed planes (what a rawvideo pipe delivers) are one long row: 854-wide frames then copy with 16-byte vectors
+    // although their rows are only 2-byte aligned.
+    if (rows > 1 && src.pitch == row_bytes && dst.pitch == row_bytes && static_cast<long long>(row_bytes) * rows < (1LL << 30)) {
+        row_bytes *= rows; rows = 1; src.pitch = dst.pitch = 0;
+    }
     const int v = aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 16) && aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16) ? 16
                 : aligned_for(src.base, src.pitch, src.frame_stride, n_frames, 4) && aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 4) ? 4 : 1;
     const int slots = row_bytes / v + (row_bytes % v ? 1 : 0);
@@ -486,8 +492,13 @@ int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 
-int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,
+int launch_interleave(const SampleView &u_in, const SampleView &v_in, const SampleView &dst_in, int sample_bytes, int w, int rows, int n_frames,
                       cudaStream_t stream) {
+    SampleView u = u_in, v = v_in, dst = dst_in;
+    if (rows > 1 && u.pitch == static_cast<ptrdiff_t>(w) * sample_bytes && v.pitch == u.pitch && dst.pitch == 2 * u.pitch &&
+        static_cast<long long>(w) * rows < (1LL << 29)) {   // tightly packed planes: one long row (see launch_copy_rows)
+        w *= rows; rows = 1; u.pitch = v.pitch = dst.pitch = 0;
+    }
     const bool vec = aligned_for(u.base, u.pitch, u.frame_stride, n_frames, 8) && aligned_for(v.base, v.pitch, v.frame_stride, n_frames, 8) &&
                      aligned_for(dst.base, dst.pitch, dst.frame_stride, n_frames, 16);
     const int per = vec ? 8 / sample_bytes : 1;
