@@ -305,6 +305,32 @@ def test_chroma_siting_against_oracle():
             assert np.array_equal(a, b), cp
 
 
+def test_strong_down_scales_on_every_path():
+    """13- to 20-tap filters (4K -> 576p / 480p bicubic at 3.75:1 and 4.5:1, lanczos at 3:1).  Filters past 12 vertical taps
+    run on the two-pass kernels: 16- and 20-tap streaming instances were built and measured (8-bit 4K -> 480p 28.4 K -> 31.3 K
+    frames/s, 10-bit 27.6 K -> 14.4 K) and not kept."""
+    from oracle import port, ref_swscale
+    from thinvids_b200.swscale import Scaler
+    make_checker = ref_swscale.RefScaler if ref_swscale.available() else port.PortScaler
+    seen = set()
+    for sf, df, sw, sh, dw, dh, alg in [(0, 1, 900, 508, 200, 113, F.SWS_BICUBIC), (0, 0, 960, 540, 256, 144, F.SWS_BICUBIC),
+                                        (1, 1, 960, 540, 214, 120, F.SWS_BICUBIC), (2, 1, 900, 508, 200, 113, F.SWS_BICUBIC),
+                                        (0, 0, 600, 300, 200, 100, F.SWS_LANCZOS), (3, 3, 768, 432, 204, 116, F.SWS_BICUBIC),
+                                        (0, 1, 3840, 2160, 854, 480, F.SWS_BICUBIC)]:
+        src = F.random_frame(sf, sw, sh, 77)
+        want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+        make_checker(sw, sh, sf, dw, dh, df, alg).scale_into(src, want)
+        for path in PATHS:
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                if not _use_path(s, path):
+                    continue
+                got = s.scale(src)
+                seen.add(s.path)
+            for k, (a, b) in enumerate(zip(got, want)):
+                assert np.array_equal(a, b), (path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
+    assert "two-pass" in seen, seen
+
+
 def test_p010_padding_bits_are_ignored_on_every_path():
     """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
     (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""
