@@ -21,6 +21,34 @@ from dataclasses import dataclass
 from typing import Callable, Sequence
 
 
+def bind_to_gpu_cpus(device: int) -> str:
+    """Restrict the calling process to the CPUs next to GPU `device` (NVML's ideal affinity), so that the pinned staging
+    buffers it allocates afterwards land on that GPU's NUMA node and its copies do not cross the socket interconnect.
+    One consumer per GPU should call this before it allocates anything; with a single consumer it is not needed.
+    Returns a short description of what was done ("" when NVML or the topology is not available: nothing is changed)."""
+    import os
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        visible = os.environ.get("CUDA_VISIBLE_DEVICES", "")
+        index = device
+        if visible:
+            entry = visible.split(",")[device].strip()
+            if not entry.isdigit():
+                return ""        # UUID lists: leave the affinity alone
+            index = int(entry)
+        handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(handle, (os.cpu_count() + 63) // 64)
+        cpus = {64 * i + b for i, w in enumerate(words) for b in range(64) if (int(w) >> b) & 1}
+        cpus &= os.sched_getaffinity(0)
+        if not cpus:
+            return ""
+        os.sched_setaffinity(0, cpus)
+        return f"{len(cpus)} CPUs local to GPU {index}"
+    except Exception:
+        return ""
+
+
 def shard_segments(n_segments: int, rank: int, world: int) -> list[int]:
     """Segment i goes to GPU i mod world — the same striping the reference gets from its shared queue."""
     if world < 1 or not 0 <= rank < world:
