@@ -54,9 +54,10 @@ enum {
                                 as they are, the float kernels here assume 10 bits */
     TVS_FMT_RGB24       = 4, /* AV_PIX_FMT_RGB24        one plane of R, G, B bytes; SOURCE only, even widths (what
                                 tools/upscale_benchmark.py:159-182 feeds its lanczos stage); BT.601 limited-range output */
-    TVS_FMT_YUVJ420P    = 5  /* AV_PIX_FMT_YUVJ420P     yuv420p holding full-range (JPEG) samples: what ffmpeg's decoders hand
+    TVS_FMT_YUVJ420P    = 5, /* AV_PIX_FMT_YUVJ420P     yuv420p holding full-range (JPEG) samples: what ffmpeg's decoders hand
                                 the scale filter for MJPEG and most phone / camera H.264.  As source it implies
                                 TVS_SRC_FULL_RANGE, as destination TVS_DST_FULL_RANGE (libswscale's handle_jpeg) */
+    TVS_FMT_BGR24       = 6  /* AV_PIX_FMT_BGR24        as TVS_FMT_RGB24 with B, G, R byte order (OpenCV's frames); SOURCE only */
 };
 
 /* Scaler flags: numerically equal to libswscale's SWS_* so ffmpeg `flags=` values pass through. */

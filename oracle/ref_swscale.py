@@ -16,7 +16,7 @@ import numpy as np
 
 from . import build as _build
 
-_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24"}
+_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24"}
 _libs = None
 
 
@@ -116,8 +116,8 @@ class RefScaler:
 
     def scale(self, src_planes):
         from thinvids_b200.frames import alloc_frame, plane_shapes, sample_dtype
-        if self.src[2] == 4:
-            # rgb24: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
+        if self.src[2] in (4, 6):
+            # rgb24 / bgr24: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
             # give it padded buffers and crop
             h, row = src_planes[0].shape
             pad = np.zeros((h + 2, row + 64), dtype=np.uint8)

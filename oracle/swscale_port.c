@@ -26,7 +26,8 @@
 #include <stdlib.h>
 #include <string.h>
 
-enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */ };
+enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */, FMT_BGR24 = 6 /* source only */ };
+static int fmt_rgb(int f) { return f == FMT_RGB24 || f == FMT_BGR24; }
 enum { ALG_BILINEAR = 2, ALG_BICUBIC = 4, ALG_AREA = 0x20, ALG_LANCZOS = 0x200 };
 
 typedef struct {
@@ -62,7 +63,7 @@ typedef struct {
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
 static int64_t iabs64(int64_t v) { return v < 0 ? -v : v; }
-static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24) ? 8 : 10; }
+static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24 || f == FMT_BGR24) ? 8 : 10; }
 static int fmt_semi(int f) { return f == FMT_NV12 || f == FMT_P010; }
 
 /* SURVEY.md A.2 — coefficient table for one axis. */
@@ -284,7 +285,7 @@ int tvo_set_ranges(void *p, int src_full, int dst_full)
     /* a cascade's two inner contexts are created with the default ranges, so the library converts nothing there
      * (pinned against it in tests/test_oracle.py) */
     if (c->cascade[0]) return 0;
-    if (c->sfmt == FMT_RGB24) return -1;
+    if (fmt_rgb(c->sfmt)) return -1;
     const int depth = fmt_bits(c->dfmt);
     const int src_shift = 15 - depth, mult_shift = 14;
     const int mpeg_min = 16 << (depth - 8), mpeg_max_lum = 235 << (depth - 8), mpeg_max_chr = 240 << (depth - 8);
@@ -309,7 +310,7 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
     o_ctx *c = (o_ctx *)calloc(1, sizeof(*c));
     c->sw = sw; c->sh = sh; c->dw = dw; c->dh = dh; c->sfmt = sfmt; c->dfmt = dfmt; c->alg = alg;
     c->csw = (sw + 1) >> 1; c->csh = (sh + 1) >> 1; c->cdw = (dw + 1) >> 1; c->cdh = (dh + 1) >> 1;
-    if (sfmt == FMT_RGB24) {
+    if (fmt_rgb(sfmt)) {
         /* RGB has no chroma planes of its own: the input stage makes them, at full height and -- unless the
          * destination chroma is wider than half the source -- at half width (rgb24ToUV_half_c, the sum of two
          * pixels); both cases sit at libswscale's default (centred) positions. */
@@ -365,7 +366,7 @@ static const uint8_t D128[8][8] = {
 static inline int src_sample(const o_ctx *c, const uint8_t *const src[], const int stride[], int pl, int r, int x)
 {
     switch (c->sfmt) {
-    case FMT_RGB24: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
+    case FMT_RGB24: case FMT_BGR24: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
     case FMT_YUV420P: return src[pl][(size_t)r * stride[pl] + x];
     case FMT_NV12:
         return pl == 0 ? src[0][(size_t)r * stride[0] + x] : src[1][(size_t)r * stride[1] + 2 * x + (pl - 1)];
@@ -407,7 +408,7 @@ static int scale_plane(const o_ctx *c, const uint8_t *const src[], const int sst
     const int dw = pl ? c->cdw : c->dw, dh = pl ? c->cdh : c->dh;
     const int sbits = fmt_bits(c->sfmt), dbits = fmt_bits(c->dfmt);
     /* RGB input reaches the scaler as 14/15-bit lines (srcBpc = 16) and hScale16To15 then shifts by 13 */
-    const int hshift = c->sfmt == FMT_RGB24 ? 13 : sbits == 8 ? 7 : sbits - 1;
+    const int hshift = fmt_rgb(c->sfmt) ? 13 : sbits == 8 ? 7 : sbits - 1;
     int16_t *mid = (int16_t *)malloc((size_t)sh * dw * sizeof(int16_t));
     if (!mid) return -1;
 
@@ -528,10 +529,11 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
         c->rgb[pl] = (uint16_t *)malloc((size_t)c->sh * (pl ? c->csw : c->sw) * sizeof(uint16_t));
         if (!c->rgb[pl]) return -1;
     }
+    const int ro = c->sfmt == FMT_BGR24 ? 2 : 0, bo = 2 - ro;   /* bgr24ToY_c / bgr24ToUV*_c: the same sums with R and B swapped in memory */
     for (int r = 0; r < c->sh; r++) {
         const uint8_t *row = rgb + (size_t)r * stride;
         for (int x = 0; x < c->sw; x++) {
-            const int R = row[3 * x], G = row[3 * x + 1], B = row[3 * x + 2];
+            const int R = row[3 * x + ro], G = row[3 * x + 1], B = row[3 * x + bo];
             c->rgb[0][(size_t)r * c->sw + x] = (uint16_t)((RY * R + GY * G + BY * B + (32 << 14) + (1 << 8)) >> 9);
             if (!c->rgb_half) {
                 c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (256 << 14) + (1 << 8)) >> 9);
@@ -540,7 +542,7 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
         }
         if (c->rgb_half)
             for (int x = 0; x < c->csw; x++) {
-                const int R = row[6 * x] + row[6 * x + 3], G = row[6 * x + 1] + row[6 * x + 4], B = row[6 * x + 2] + row[6 * x + 5];
+                const int R = row[6 * x + ro] + row[6 * x + 3 + ro], G = row[6 * x + 1] + row[6 * x + 4], B = row[6 * x + bo] + row[6 * x + 3 + bo];
                 c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (256 << 15) + (1 << 9)) >> 10);
                 c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)((RV * R + GV * G + BV * B + (256 << 15) + (1 << 9)) >> 10);
             }
@@ -557,9 +559,9 @@ int tvo_scale(void *p, const uint8_t *const src[], const int sstride[], uint8_t 
         const uint8_t *const tsrc[3] = { c->tmp[0], c->tmp[1], c->tmp[2] };
         return tvo_scale(c->cascade[1], tsrc, c->tmp_stride, dst, dstride) < 0 ? -1 : c->dh;
     }
-    if (c->sfmt == FMT_RGB24) {
+    if (fmt_rgb(c->sfmt)) {
         /* even widths only: with an odd width the library's half-width chroma reads one pixel past the row */
-        if ((c->sw & 1) || fmt_bits(c->dfmt) < 8 || c->dfmt == FMT_RGB24) return -1;
+        if ((c->sw & 1) || fmt_bits(c->dfmt) < 8 || fmt_rgb(c->dfmt)) return -1;
         int rc = c->dh;
         if (rgb_input_stage(c, src[0], sstride[0])) rc = -1;
         for (int pl = 0; pl < 3 && rc >= 0; pl++)

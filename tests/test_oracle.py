@@ -114,11 +114,12 @@ def test_port_equals_genuine_library_rgb24_sources():
         dw, dh = (sw, sh) if rnd.random() < 0.15 else (rnd.randrange(2, 240), rnd.randrange(2, 160))
         alg, df = rnd.choice(algs), rnd.randrange(4)
         cp = rnd.choice([None, None, (0, -513, 0, -513), (0, 128, 0, 128), (64, 192, 0, 64)])   # explicit chroma siting too
-        src = F.random_frame(F.RGB24, sw, sh, 500 + i)
-        want = ref_swscale.RefScaler(sw, sh, F.RGB24, dw, dh, df, alg, chr_pos=cp).scale(src)
-        got = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg, chr_pos=cp).scale(src)
+        sf = F.BGR24 if i % 3 == 2 else F.RGB24       # bgr24 (OpenCV's order): the same input stage with R and B swapped in memory
+        src = F.random_frame(sf, sw, sh, 500 + i)
+        want = ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale(src)
+        got = port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale(src)
         for x, y in zip(got, want):
-            assert np.array_equal(x, y), (sw, sh, dw, dh, df, hex(alg))
+            assert np.array_equal(x, y), (sf, sw, sh, dw, dh, df, hex(alg))
 
 
 @needs_ref

@@ -454,13 +454,14 @@ def test_rgb24_sources_against_oracle():
         if i >= 40:
             sw, sh, dw, dh = [(720, 480, 1920, 1080), (1440, 960, 1920, 1080), (2880, 1920, 1920, 1080), (640, 360, 1280, 720)][i % 4]
         alg, df = rnd.choice(algs), rnd.randrange(4)
-        frames = [F.random_frame(F.RGB24, sw, sh, 900 + 3 * i + k) for k in range(3)]
+        sf = F.BGR24 if i % 4 == 3 else F.RGB24
+        frames = [F.random_frame(sf, sw, sh, 900 + 3 * i + k) for k in range(3)]
         if i % 3 == 1:     # only 0 and 255
             frames = [[(p > 127).astype(np.uint8) * 255 for p in fr] for fr in frames]
-        ref = port.PortScaler(sw, sh, F.RGB24, dw, dh, df, alg)
+        ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg)
         want = [ref.scale(fr) for fr in frames]
         for path in ("auto", "two-pass"):
-            with Scaler(sw, sh, F.RGB24, dw, dh, df, alg) as s:
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
                 s.set_path(path)
                 assert s.path in ("slab", "two-pass", "cascade"), s.path
                 seen.add(s.path)
@@ -471,7 +472,7 @@ def test_rgb24_sources_against_oracle():
                 torch.cuda.synchronize()
                 got_batch = s.dst_layout.unpack(d_dst.cpu().numpy())
             for a, b in zip(got, want[0]):
-                assert np.array_equal(a, b), (path, sw, sh, dw, dh, df, hex(alg))
+                assert np.array_equal(a, b), (path, sf, sw, sh, dw, dh, df, hex(alg))
             for g, w in zip(got_batch, want):
                 for a, b in zip(g, w):
                     assert np.array_equal(a, b), (path, sw, sh, dw, dh, df, hex(alg), "batch")
@@ -484,7 +485,7 @@ def test_error_paths():
     from thinvids_b200.swscale import Scaler, PtrArr3, DiffArr3
     with pytest.raises(tv_lib.TvscaleError, match="even width"):
         Scaler(63, 64, F.RGB24, 32, 32, 0, F.SWS_BICUBIC)      # libswscale itself over-reads odd-width RGB rows
-    with pytest.raises(tv_lib.TvscaleError, match="source format only"):
+    with pytest.raises(tv_lib.TvscaleError, match="source formats only"):
         Scaler(64, 64, 0, 32, 32, F.RGB24, F.SWS_BICUBIC)
     with pytest.raises(tv_lib.TvscaleError):
         Scaler(64, 64, 9, 32, 32, 0, F.SWS_BICUBIC)            # unknown format

@@ -273,7 +273,7 @@ dither128_interleave_kernel(const uint8_t *__restrict__ u, const uint8_t *__rest
 // rgb24ToUV_half_c; RGB2YUV_SHIFT = 15, default BT.601 limited-range table).  One thread per pixel pair.
 __global__ void __launch_bounds__(256)
 rgb_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *__restrict__ planes,
-                 size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half) {
+                 size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half, int bgr) {
     constexpr int RY = 8414, GY = 16519, BY = 3208, RU = -4865, GU = -9528, BU = 14392, RV = 14392, GV = -12061, BV = -2332;
     const int pairs = w >> 1;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -281,7 +281,8 @@ rgb_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t fra
     if (y >= h) return;
     const int f = blockIdx.z;
     const uint8_t *p = rgb + f * frame_stride + y * pitch + 6 * i;
-    const int r0 = p[0], g0 = p[1], b0 = p[2], r1 = p[3], g1 = p[4], b1 = p[5];
+    const int ro = bgr ? 2 : 0, bo = 2 - ro;   // bgr24: the same sums with R and B swapped in memory (bgr24ToY_c, bgr24ToUV*_c)
+    const int r0 = p[ro], g0 = p[1], b0 = p[bo], r1 = p[3 + ro], g1 = p[4], b1 = p[3 + bo];
     uint8_t *out = planes + f * planes_frame_stride;
     uint16_t *yrow = reinterpret_cast<uint16_t *>(out) + static_cast<size_t>(y) * w + 2 * i;
     yrow[0] = static_cast<uint16_t>((RY * r0 + GY * g0 + BY * b0 + (32 << 14) + (1 << 8)) >> 9);
@@ -548,11 +549,11 @@ int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const Sa
 }
 
 int launch_rgb_input(const uint8_t *rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *planes, size_t planes_frame_stride,
-                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, int n_frames, cudaStream_t stream) {
+                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, bool bgr, int n_frames, cudaStream_t stream) {
     const unsigned total = static_cast<unsigned>(w / 2) * h;
     const dim3 grid((total + 255) / 256, 1, n_frames);
     rgb_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
-                                               half ? 1 : 0);
+                                               half ? 1 : 0, bgr ? 1 : 0);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

@@ -43,6 +43,7 @@ struct FormatInfo {
     bool semi;      // chroma interleaved in one plane
     int planes;     // stored planes
     bool rgb;       // one plane of packed R, G, B bytes (source only)
+    bool bgr = false;   // ... stored B, G, R
 };
 
 bool format_info(int fmt, FormatInfo &fi) {
@@ -52,6 +53,7 @@ bool format_info(int fmt, FormatInfo &fi) {
     case TVS_FMT_YUV420P10LE: fi = {10, 2, 0, false, 3, false}; return true;
     case TVS_FMT_P010LE: fi = {10, 2, 6, true, 2, false}; return true;
     case TVS_FMT_RGB24: fi = {8, 1, 0, false, 1, true}; return true;
+    case TVS_FMT_BGR24: fi = {8, 1, 0, false, 1, true, true}; return true;
     default: return false;
     }
 }
@@ -478,7 +480,7 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk)) {
         const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
         if (launch_rgb_input(static_cast<const uint8_t *>(src[0]) + static_cast<ptrdiff_t>(f0) * sf[0], sp[0], sf[0], c->rgb_planes, per_frame,
-                             y_bytes, c_bytes, c->src_w, c->src_h, c->rgb_half, nf, stream) < 0)
+                             y_bytes, c_bytes, c->src_w, c->src_h, c->rgb_half, c->sfi.bgr, nf, stream) < 0)
             return cuda_fail(cudaGetLastError(), "rgb input kernel launch");
         ++c->launches;
         void *vdst[3] = {nullptr, nullptr, nullptr};
@@ -541,7 +543,7 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         return nullptr;
     }
     if (dfi.rgb) {
-        fail(-ENOSYS, "rgb24 is supported as a source format only");
+        fail(-ENOSYS, "rgb24 / bgr24 are supported as source formats only");
         return nullptr;
     }
     if (sfi.rgb && src_full != dst_full) {
@@ -552,7 +554,7 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     }
     if (sfi.rgb && (src_w & 1)) {
         // libswscale's half-width chroma input (rgb24ToUV_half_c) reads a pixel past the row when the width is odd
-        fail(-EINVAL, "rgb24 sources need an even width (got %d)", src_w);
+        fail(-EINVAL, "rgb24 / bgr24 sources need an even width (got %d)", src_w);
         return nullptr;
     }
     const int alg_bits = flags & (TVS_BILINEAR | TVS_BICUBIC | TVS_AREA | TVS_LANCZOS);

@@ -14,7 +14,7 @@ EXPORTS = ("tvs_create", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tv
 
 STATIC_SCRATCH_BYTES = 32 << 20   # TVS_STATIC_SCRATCH_BYTES
 INFO_KERNEL_LAUNCHES, INFO_PATH, INFO_SCRATCH_BYTES, INFO_SRC_FRAME_BYTES, INFO_DST_FRAME_BYTES = range(5)
-FMT_YUVJ420P = 5                                         # TVS_FMT_YUVJ420P
+FMT_YUVJ420P = 5                                         # TVS_FMT_YUVJ420P (frames.BGR24 = 6 is TVS_FMT_BGR24)
 SRC_FULL_RANGE, DST_FULL_RANGE = 0x10000000, 0x20000000  # TVS_SRC_FULL_RANGE, TVS_DST_FULL_RANGE
 
 _lib = None

@@ -95,7 +95,7 @@ def main():
     algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
     t0, n, bad = time.time(), 0, 0
     while time.time() - t0 < budget:
-        sf = rnd.choice([0, 0, 1, 2, 3, 4])
+        sf = rnd.choice([0, 0, 1, 2, 3, 4])   # (FUZZ_SF=6 for bgr24)
         if os.environ.get("FUZZ_SF"):   # one source format only, e.g. 4 = rgb24
             sf = int(os.environ["FUZZ_SF"])
         df = rnd.randrange(4)
@@ -103,7 +103,7 @@ def main():
         big = huge or rnd.random() < 0.25
         sw, sh = (rnd.randrange(200, 3850 if huge else 1930), rnd.randrange(100, 2170 if huge else 1090)) if big \
             else (rnd.randrange(2, 400), rnd.randrange(2, 300))
-        if sf == 4:
+        if sf in (4, 6):
             sw += sw & 1
         mode = rnd.random()
         if mode < 0.15:
