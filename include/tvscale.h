@@ -93,6 +93,13 @@ typedef struct tvs_ctx tvs_ctx;
 TVS_API tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt,
                     int flags, const int chr_pos[4]);
 
+/* tvs_create with libswscale's two scaler parameters (sws_getContext's `param`, ffmpeg's scale=...:param0=..:param1=..):
+ * bicubic B = param[0], C = param[1] (defaults 0 and 0.6); lanczos lobes = param[0] (default 3, at least 1).  An entry equal to
+ * TVS_PARAM_DEFAULT (= SWS_PARAM_DEFAULT), or param == NULL, selects the default.  The other algorithms ignore them. */
+#define TVS_PARAM_DEFAULT 123456.0
+TVS_API tvs_ctx *tvs_create_ex(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt,
+                               int flags, const int chr_pos[4], const double param[2]);
+
 /* Replaces sws_freeContext(). */
 TVS_API void tvs_destroy(tvs_ctx *ctx);
 

@@ -20,6 +20,8 @@ def _load():
         lib = ctypes.CDLL(_build.build_port())
         lib.tvo_create.restype = ctypes.c_void_p
         lib.tvo_create.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p]
+        lib.tvo_create_ex.restype = ctypes.c_void_p
+        lib.tvo_create_ex.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p, ctypes.c_void_p]
         lib.tvo_destroy.argtypes = [ctypes.c_void_p]
         lib.tvo_scale.restype = ctypes.c_int
         lib.tvo_scale.argtypes = [ctypes.c_void_p] * 5
@@ -32,12 +34,15 @@ def _load():
 
 
 class PortScaler:
-    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, ranges=None):
+    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, ranges=None, params=None):
         self._lib = _load()
         self.src = (src_w, src_h, src_fmt)
         self.dst = (dst_w, dst_h, dst_fmt)
         cp = (ctypes.c_int * 4)(*chr_pos) if chr_pos is not None else None
-        self._ctx = self._lib.tvo_create(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, cp)
+        pr = None
+        if params is not None:      # (param0, param1) of ffmpeg's scale filter; None = the algorithm's default
+            pr = (ctypes.c_double * 2)(*[123456.0 if v is None else float(v) for v in params])
+        self._ctx = self._lib.tvo_create_ex(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, cp, pr)
         if not self._ctx:
             raise ValueError("libswscale refuses this conversion (a cascade whose source is not 4x larger than its destination)")
         if ranges is not None and self._lib.tvo_set_ranges(self._ctx, int(ranges[0]), int(ranges[1])) < 0:

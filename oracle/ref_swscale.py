@@ -45,6 +45,8 @@ def _load():
     avu.av_force_cpu_flags.argtypes = [ctypes.c_int]
     avu.av_opt_set_int.restype = ctypes.c_int
     avu.av_opt_set_int.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_int64, ctypes.c_int]
+    avu.av_opt_set_double.restype = ctypes.c_int
+    avu.av_opt_set_double.argtypes = [ctypes.c_void_p, ctypes.c_char_p, ctypes.c_double, ctypes.c_int]
     sws.sws_getContext.restype = ctypes.c_void_p
     sws.sws_getContext.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p] * 3
     sws.sws_alloc_context.restype = ctypes.c_void_p
@@ -80,7 +82,7 @@ def force_plain_c(on: bool = True) -> None:
 class RefScaler:
     """One SwsContext.  Not safe for concurrent ``scale`` calls (same rule as libswscale)."""
 
-    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, bitexact=True, ranges=None):
+    def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, alg, chr_pos=None, bitexact=True, ranges=None, params=None):
         avu, sws = _load()
         self._sws = sws
         self.src = (src_w, src_h, src_fmt)
@@ -88,7 +90,7 @@ class RefScaler:
         sf = avu.av_get_pix_fmt(_PIXFMT_NAMES[src_fmt])
         df = avu.av_get_pix_fmt(_PIXFMT_NAMES[dst_fmt])
         flags = alg | (0x40000 | 0x80000 if bitexact else 0)
-        if ranges is not None and chr_pos is None:
+        if (ranges is not None or params is not None) and chr_pos is None:
             chr_pos = (-513, -513, -513, -513)
         if chr_pos is None:
             self._ctx = sws.sws_getContext(src_w, src_h, sf, dst_w, dst_h, df, flags, None, None, None)
@@ -102,6 +104,9 @@ class RefScaler:
             for k, v in opts.items():
                 if avu.av_opt_set_int(self._ctx, k, v, 0) < 0:
                     raise RuntimeError(f"av_opt_set_int({k!r}) failed")
+            for k, v in zip((b"param0", b"param1"), params or ()):      # vf_scale's param0 / param1
+                if v is not None and avu.av_opt_set_double(self._ctx, k, float(v), 0) < 0:
+                    raise RuntimeError(f"av_opt_set_double({k!r}) failed")
             if sws.sws_init_context(self._ctx, None, None) < 0:
                 raise RuntimeError("sws_init_context failed")
         if not self._ctx:

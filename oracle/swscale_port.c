@@ -67,6 +67,11 @@ static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == F
 static int fmt_semi(int f) { return f == FMT_NV12 || f == FMT_P010; }
 
 /* SURVEY.md A.2 — coefficient table for one axis. */
+/* libswscale's SWS_PARAM_DEFAULT: "use the algorithm's own default" for a scaler parameter (vf_scale's param0 / param1):
+ * bicubic B = param[0] (0), C = param[1] (0.6); lanczos lobes = param[0] (3), support ceil(2 * lobes). */
+#define PARAM_DEFAULT 123456.0
+static double g_param[2] = { PARAM_DEFAULT, PARAM_DEFAULT };   /* set around tvo_create_ex; the port is single-threaded test code */
+
 static int make_filter(o_filter *out, int inc, int src_len, int dst_len, int one, int alg,
                        int src_pos, int dst_pos)
 {
@@ -97,7 +102,7 @@ static int make_filter(o_filter *out, int inc, int src_len, int dst_len, int one
             centre += inc;
         }
     } else {
-        int support = alg == ALG_BICUBIC ? 4 : alg == ALG_LANCZOS ? 6 : alg == ALG_AREA ? 1 : 2;
+        int support = alg == ALG_BICUBIC ? 4 : alg == ALG_LANCZOS ? (g_param[0] != PARAM_DEFAULT ? (int)ceil(2 * g_param[0]) : 6) : alg == ALG_AREA ? 1 : 2;
         if (inc <= 0x10000) taps = 1 + support;
         else taps = 1 + (int)(((int64_t)support * src_len + dst_len - 1) / dst_len);
         if (taps > src_len - 2) taps = src_len - 2;
@@ -113,7 +118,8 @@ static int make_filter(o_filter *out, int inc, int src_len, int dst_len, int one
                 if (inc > 0x10000) d = d * dst_len / src_len;
                 double fd = (double)d * (1.0 / (1 << 30));
                 if (alg == ALG_BICUBIC) {
-                    const int64_t B = 0, C = (int64_t)(0.6 * (1 << 24));
+                    const int64_t B = (int64_t)((g_param[0] != PARAM_DEFAULT ? g_param[0] : 0) * (1 << 24));
+                    const int64_t C = (int64_t)((g_param[1] != PARAM_DEFAULT ? g_param[1] : 0.6) * (1 << 24));
                     if (d >= ((int64_t)1 << 31)) {
                         c = 0;
                     } else {
@@ -135,7 +141,7 @@ static int make_filter(o_filter *out, int inc, int src_len, int dst_len, int one
                     else c = 0;
                     c *= fone >> 46;
                 } else if (alg == ALG_LANCZOS) {
-                    const double p = 3.0;
+                    const double p = g_param[0] != PARAM_DEFAULT ? g_param[0] : 3.0;
                     double v = d ? sin(fd * M_PI) * sin(fd * M_PI / p) / (fd * fd * M_PI * M_PI / p) : 1.0;
                     c = (int64_t)(v * (double)fone);
                     if (fd > p) c = 0;
@@ -332,6 +338,15 @@ void *tvo_create(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, co
     make_filter(&c->vc, step16(c->csh, c->cdh), c->csh, c->cdh, 1 << 12, alg,
                 local_pos(chr_pos[1], 1), local_pos(chr_pos[3], 1));
     if (tvo_setup_cascade(c)) { tvo_destroy(c); return NULL; }
+    return c;
+}
+
+/* tvo_create with scaler parameters (NULL = defaults); a cascade's inner contexts inherit them, as in libswscale. */
+void *tvo_create_ex(int sw, int sh, int sfmt, int dw, int dh, int dfmt, int alg, const int *chr_pos, const double *param)
+{
+    if (param) { g_param[0] = param[0]; g_param[1] = param[1]; }
+    void *c = tvo_create(sw, sh, sfmt, dw, dh, dfmt, alg, chr_pos);
+    g_param[0] = g_param[1] = PARAM_DEFAULT;
     return c;
 }
 

@@ -79,6 +79,15 @@ def test_scale_stage_rejects_what_it_cannot_do():
             fg.ScaleStage.from_filtergraph(bad, 1920, 1080)
 
 
+def test_scale_stage_params():
+    st = fg.ScaleStage.from_filtergraph("scale=-2:720:flags=bicubic:param0=0.333:param1=0.25", 1920, 1080)
+    assert st.params == (0.333, 0.25) and st.flags == F.SWS_BICUBIC
+    assert fg.ScaleStage.from_filtergraph("scale=-2:720:flags=lanczos:param0=4", 1920, 1080).params == (4.0, None)
+    assert fg.ScaleStage.from_filtergraph("scale=-2:720", 1920, 1080).params == (None, None)
+    with pytest.raises(fg.FilterGraphError):
+        fg.ScaleStage.from_filtergraph("scale=-2:720:param0=abc", 1920, 1080)
+
+
 def test_scale_stage_ranges():
     """yuvj420p sources are full-range yuv420p; scale keeps the range unless out_range= changes it (vf_scale)."""
     st = fg.ScaleStage.from_filtergraph("setpts=PTS-STARTPTS,scale=-2:1080,format=nv12,hwupload", 720, 480, "yuvj420p")

@@ -229,3 +229,31 @@ def test_port_range_conversion_equals_genuine_library():
         for got in (ref_swscale.RefScaler(399, 133, 0, 9, 133, 0, 4, ranges=rg).scale(src), port.PortScaler(399, 133, 0, 9, 133, 0, 4, ranges=rg).scale(src)):
             for x, y in zip(got, plain):
                 assert np.array_equal(x, y), rg
+
+
+@needs_ref
+def test_port_scaler_params_equal_genuine_library():
+    """ffmpeg's scale=...:param0=..:param1=.. (sws_getContext's `param`): bicubic B / C and the lanczos lobe count, which
+    also sets the filter's support; a cascade hands them to its inner contexts."""
+    rnd = random.Random(4)
+    cases = []
+    for _ in range(40):
+        alg = rnd.choice([4, 0x200])
+        pr = rnd.choice([(0, 0.5), (1 / 3, 1 / 3), (1, 0), (0, 0.75), (0.2, None), (None, 0.3), (0, 1)]) if alg == 4 else \
+            rnd.choice([(2, None), (4, None), (2.5, None), (5, None), (1, None), (3, None)])
+        cases.append((rnd.randrange(4), rnd.randrange(4), rnd.randrange(8, 300), rnd.randrange(8, 200), rnd.randrange(8, 400),
+                      rnd.randrange(8, 300), alg, pr))
+    cases.append((0, 0, 700, 64, 12, 40, 0x200, (5, None)))      # cascades
+    cases.append((0, 1, 64, 48, 128, 96, 2, (0.7, 0.1)))          # bilinear ignores them
+    for n, (sf, df, sw, sh, dw, dh, alg, pr) in enumerate(cases):
+        src = F.random_frame(sf, sw, sh, n)
+        a = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        b = [np.full_like(p, 77) for p in F.alloc_frame(df, dw, dh)]
+        ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg, params=pr).scale_into(src, a)
+        port.PortScaler(sw, sh, sf, dw, dh, df, alg, params=pr).scale_into(src, b)
+        for x, y in zip(a, b):
+            assert np.array_equal(x, y), (sf, df, sw, sh, dw, dh, hex(alg), pr)
+    src = F.random_frame(0, 64, 48, 1)
+    plain = port.PortScaler(64, 48, 0, 128, 96, 0, 4).scale(src)
+    assert not np.array_equal(plain[0], port.PortScaler(64, 48, 0, 128, 96, 0, 4, params=(1, 0)).scale(src)[0])
+    assert np.array_equal(plain[0], port.PortScaler(64, 48, 0, 128, 96, 0, 4, params=(None, None)).scale(src)[0])

@@ -331,6 +331,34 @@ def test_strong_down_scales_on_every_path():
     assert "two-pass" in seen, seen
 
 
+def test_scaler_params_against_oracle():
+    """tvs_create_ex: bicubic B / C and lanczos lobes (ffmpeg's param0 / param1) on every kernel path that takes the shape."""
+    from oracle import port, ref_swscale
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler
+    make_checker = ref_swscale.RefScaler if ref_swscale.available() else port.PortScaler
+    cases = [(0, 1, 320, 180, 640, 360, 4, (1 / 3, 1 / 3)), (0, 0, 640, 360, 320, 180, 4, (1, 0)), (2, 2, 320, 180, 480, 270, 4, (0, 0.75)),
+             (0, 0, 320, 180, 640, 360, 0x200, (2, None)), (1, 1, 640, 360, 426, 240, 0x200, (4, None)), (3, 1, 320, 180, 500, 300, 0x200, (2.5, None)),
+             (0, 0, 720, 480, 1920, 1080, 0x200, (5, None)), (4, 0, 320, 180, 640, 360, 4, (0, 0.5)), (0, 1, 700, 64, 12, 40, 0x200, (5, None)),
+             (0, 3, 200, 120, 200, 120, 4, (0.2, 0.4))]
+    for sf, df, sw, sh, dw, dh, alg, pr in cases:
+        src = F.random_frame(sf, sw, sh, 7)
+        want = make_checker(sw, sh, sf, dw, dh, df, alg, params=pr).scale(src)
+        for path in PATHS:
+            with Scaler(sw, sh, sf, dw, dh, df, alg, params=pr) as s:
+                if not _use_path(s, path):
+                    continue
+                got = s.scale(src)
+            for k, (a, b) in enumerate(zip(got, want)):
+                if k == 1 and df == 3 and (sw, sh) == (dw, dh) and sw % 2:
+                    continue
+                assert np.array_equal(a, b), (path, sf, df, sw, sh, dw, dh, hex(alg), pr, k, int((a != b).sum()))
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 48, 0, 128, 96, 0, 0x200, params=(0.5, None))      # lanczos with less than one lobe
+    with pytest.raises(tv_lib.TvscaleError):
+        Scaler(64, 48, 0, 128, 96, 0, 4, params=(float("nan"), None))
+
+
 def test_p010_padding_bits_are_ignored_on_every_path():
     """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
     (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""

@@ -27,11 +27,13 @@ struct KernelEval {
     Algorithm alg;
     i64 unity;
     int inc;
+    double p0, p1;   // libswscale's scaler parameters (kParamDefault = the algorithm's own default)
 
     i64 operator()(i64 d) const {
         switch (alg) {
         case kBicubic: {
-            const i64 b = 0, c = static_cast<i64>(0.6 * (1 << 24));
+            const i64 b = static_cast<i64>((p0 != kParamDefault ? p0 : 0.0) * (1 << 24));
+            const i64 c = static_cast<i64>((p1 != kParamDefault ? p1 : 0.6) * (1 << 24));
             const i64 q30 = 1LL << 30, q24 = 1LL << 24;
             i64 w = 0;
             if (d < (1LL << 31)) {
@@ -54,7 +56,7 @@ struct KernelEval {
             return w * (unity >> 46);
         }
         case kLanczos: {
-            const double lobes = 3.0;
+            const double lobes = p0 != kParamDefault ? p0 : 3.0;
             const double x = static_cast<double>(d) * (1.0 / (1 << 30));
             if (x > lobes) return 0;
             const double v = d ? std::sin(x * kPi) * std::sin(x * kPi / lobes) / (x * x * kPi * kPi / lobes) : 1.0;
@@ -68,10 +70,10 @@ struct KernelEval {
     }
 };
 
-int kernel_support(Algorithm alg) {
+int kernel_support(Algorithm alg, double p0) {
     switch (alg) {
     case kBicubic: return 4;
-    case kLanczos: return 6;
+    case kLanczos: return p0 != kParamDefault ? static_cast<int>(std::ceil(2 * p0)) : 6;
     case kArea: return 1;
     default: return 2;
     }
@@ -94,7 +96,8 @@ int axis_position(int siting, int subsample_log2) {
     return (siting + 128) >> subsample_log2;
 }
 
-bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, int one, int src_pos, int dst_pos) {
+bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, int one, int src_pos, int dst_pos, const double *param) {
+    const double p0 = param ? param[0] : kParamDefault, p1 = param ? param[1] : kParamDefault;
     if (src_len <= 0 || dst_len <= 0) return false;
     if (alg != kBilinear && alg != kBicubic && alg != kArea && alg != kLanczos) return false;
 
@@ -125,12 +128,12 @@ bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, i
             }
         }
     } else {
-        const int support = kernel_support(alg);
+        const int support = kernel_support(alg, p0);
         width = enlarging ? 1 + support
                           : 1 + static_cast<int>((static_cast<i64>(support) * src_len + dst_len - 1) / dst_len);
         width = std::max(std::min(width, src_len - 2), 1);
         raw.assign(static_cast<size_t>(dst_len) * width, 0);
-        const KernelEval weight{alg, unity, inc};
+        const KernelEval weight{alg, unity, inc, p0, p1};
         // centre carries 17 fractional bits here
         i64 centre = ((static_cast<i64>(dst_pos) * inc) >> 7) - ((static_cast<i64>(src_pos) * kOne16) >> 7);
         for (int i = 0; i < dst_len; ++i, centre += 2LL * inc) {

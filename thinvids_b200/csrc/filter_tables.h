@@ -32,6 +32,9 @@ int axis_position(int siting, int subsample_log2);
 // Returns false for arguments the scaler cannot handle (non-positive sizes, unknown algorithm,
 // or a kernel wider than 256 taps: `out.taps` then holds the size and no coefficients - libswscale cascades two
 // contexts long before that, and so does tvs_create).
-bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, int one, int src_pos, int dst_pos);
+// `param`: libswscale's two scaler parameters (ffmpeg's param0 / param1: bicubic B and C, lanczos lobes), or nullptr;
+// a value of kParamDefault (SWS_PARAM_DEFAULT) means the algorithm's own default (B 0, C 0.6; 3 lobes).
+constexpr double kParamDefault = 123456.0;
+bool build_axis_table(AxisTable &out, int src_len, int dst_len, Algorithm alg, int one, int src_pos, int dst_pos, const double *param = nullptr);
 
 }  // namespace tvs

@@ -528,6 +528,20 @@ void tvs_host_free(void *p) {
 
 tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt, int flags,
                     const int chr_pos[4]) {
+    return tvs_create_ex(device, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, chr_pos, nullptr);
+}
+
+tvs_ctx *tvs_create_ex(int device, int src_w, int src_h, int src_fmt, int dst_w, int dst_h, int dst_fmt, int flags,
+                       const int chr_pos[4], const double param[2]) {
+    if (param && (!(param[0] == param[0]) || !(param[1] == param[1]) || (param[0] != TVS_PARAM_DEFAULT && std::fabs(param[0]) > 64) ||
+                  (param[1] != TVS_PARAM_DEFAULT && std::fabs(param[1]) > 64))) {
+        fail(-EINVAL, "scaler parameters out of range");
+        return nullptr;
+    }
+    if (param && (flags & TVS_LANCZOS) && param[0] != TVS_PARAM_DEFAULT && param[0] < 1.0) {
+        fail(-EINVAL, "lanczos needs at least one lobe (param0 = %g)", param[0]);
+        return nullptr;
+    }
     // The deprecated "J" format is yuv420p carrying full-range samples (libswscale's handle_jpeg)
     bool src_full = (flags & TVS_SRC_FULL_RANGE) != 0, dst_full = (flags & TVS_DST_FULL_RANGE) != 0;
     if (src_fmt == TVS_FMT_YUVJ420P) { src_fmt = TVS_FMT_YUV420P; src_full = true; }
@@ -627,10 +641,10 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
     const Algorithm a = static_cast<Algorithm>(alg);
     const int luma = axis_position(TVS_CHR_POS_DEFAULT, 0);
     const bool built[4] = {
-        build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma),
-        build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], src_hsub), axis_position(chr_pos[2], 1)),
-        build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma),
-        build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], src_vsub), axis_position(chr_pos[3], 1))};
+        build_axis_table(c->host_tables[0], src_w, dst_w, a, 1 << 14, luma, luma, param),
+        build_axis_table(c->host_tables[1], csw, cdw, a, 1 << 14, axis_position(chr_pos[0], src_hsub), axis_position(chr_pos[2], 1), param),
+        build_axis_table(c->host_tables[2], src_h, dst_h, a, 1 << 12, luma, luma, param),
+        build_axis_table(c->host_tables[3], csh, cdh, a, 1 << 12, axis_position(chr_pos[1], src_vsub), axis_position(chr_pos[3], 1), param)};
     for (int i = 0; i < 4; ++i) {
         if (!built[i] && c->host_tables[i].taps <= 256) {   // (a table wider than 256 taps is the cascade's business, below)
             fail(-EINVAL, "cannot build the filter tables for %dx%d -> %dx%d", src_w, src_h, dst_w, dst_h);
@@ -655,8 +669,8 @@ tvs_ctx *tvs_create(int device, int src_w, int src_h, int src_fmt, int dst_w, in
         c->range_convert = 0;
         c->cascade_w = static_cast<int>(std::sqrt(static_cast<double>(src_w) * dst_w));
         c->cascade_h = static_cast<int>(std::sqrt(static_cast<double>(src_h) * dst_h));
-        c->cascade[0] = tvs_create(device, src_w, src_h, src_fmt, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, flags, nullptr);
-        c->cascade[1] = c->cascade[0] ? tvs_create(device, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, dst_w, dst_h, dst_fmt, flags, nullptr) : nullptr;
+        c->cascade[0] = tvs_create_ex(device, src_w, src_h, src_fmt, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, flags, nullptr, param);
+        c->cascade[1] = c->cascade[0] ? tvs_create_ex(device, c->cascade_w, c->cascade_h, TVS_FMT_YUV420P, dst_w, dst_h, dst_fmt, flags, nullptr, param) : nullptr;
         const size_t tframe = static_cast<size_t>(c->cascade_w) * c->cascade_h +
                               2 * static_cast<size_t>((c->cascade_w + 1) / 2) * ((c->cascade_h + 1) / 2);
         c->cascade_chunk = static_cast<int>(std::min<size_t>(65535, std::max<size_t>(1, (static_cast<size_t>(64) << 20) / tframe)));

@@ -174,12 +174,14 @@ class ScaleStage:
     # full-range part passes through with no conversion and comes out full range.
     src_range: str = "limited"
     dst_range: str = "limited"
+    params: tuple = (None, None)   # scale's param0 / param1 (bicubic B and C, lanczos lobes); None = the algorithm's default
 
     @classmethod
     def from_filtergraph(cls, text: str, src_w: int, src_h: int, src_fmt: str = "yuv420p", *,
                          deinterlaced_upstream: bool = False, default_dst_fmt: str | None = None) -> "ScaleStage":
         dst_w, dst_h, flags = src_w, src_h, F.SWS_BICUBIC
         src_range, dst_range = "limited", None
+        params = [None, None]
         if src_fmt == "yuvj420p":
             src_fmt, src_range = "yuv420p", "full"
         dst_fmt = default_dst_fmt or src_fmt
@@ -208,6 +210,12 @@ class ScaleStage:
                         flags |= _SCALE_FLAG_NAMES[name]
                     if not flags & (F.SWS_BILINEAR | F.SWS_BICUBIC | F.SWS_AREA | F.SWS_LANCZOS):
                         flags |= F.SWS_BICUBIC
+                for k, key in enumerate(("param0", "param1")):
+                    if key in f.kwargs:
+                        try:
+                            params[k] = float(f.kwargs[key])
+                        except ValueError:
+                            raise FilterGraphError(f"scale {key}={f.kwargs[key]!r} is not a number") from None
                 for key in ("in_range", "out_range"):
                     val = f.kwargs.get(key, "auto")
                     if val not in _RANGE_NAMES:
@@ -240,7 +248,7 @@ class ScaleStage:
             raise FilterGraphError(f"a {src_fmt} source needs an explicit format= (yuv420p, nv12, ...) after scale")
         if src_range != (dst_range or src_range) and F.FMT_BY_NAME[src_fmt] in F.SOURCE_ONLY_FORMATS:
             raise FilterGraphError("range conversion is not supported for rgb24 sources")
-        return cls(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, deint, hwup, src_range, dst_range or src_range)
+        return cls(src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags, deint, hwup, src_range, dst_range or src_range, tuple(params))
 
     @property
     def is_identity(self) -> bool:
@@ -267,4 +275,4 @@ class ScaleStage:
         """The CUDA context for this stage (thinvids_b200.swscale.Scaler)."""
         from .swscale import Scaler
         return Scaler(self.src_w, self.src_h, self.src_fmt, self.dst_w, self.dst_h, self.dst_fmt, self.flags, device=device,
-                      src_range=self.src_range, dst_range=self.dst_range)
+                      src_range=self.src_range, dst_range=self.dst_range, params=self.params)

@@ -9,11 +9,12 @@ _PKG = os.path.dirname(os.path.abspath(__file__))
 LIB_PATH = os.path.join(_PKG, "libtvscale.so")
 
 # Every symbol include/tvscale.h declares; tests check the built library exports each one.
-EXPORTS = ("tvs_create", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tvs_scale_batch_static", "tvs_filter_table",
+EXPORTS = ("tvs_create", "tvs_create_ex", "tvs_destroy", "tvs_scale_batch", "tvs_scale_host", "tvs_scale_batch_static", "tvs_filter_table",
            "tvs_context_table", "tvs_info", "tvs_set_path", "tvs_last_error", "tvs_version", "tvs_host_alloc", "tvs_host_free", "tvs_bwdif_batch", "tvs_bwdif_host")
 
 STATIC_SCRATCH_BYTES = 32 << 20   # TVS_STATIC_SCRATCH_BYTES
 INFO_KERNEL_LAUNCHES, INFO_PATH, INFO_SCRATCH_BYTES, INFO_SRC_FRAME_BYTES, INFO_DST_FRAME_BYTES = range(5)
+PARAM_DEFAULT = 123456.0                                 # TVS_PARAM_DEFAULT
 FMT_YUVJ420P = 5                                         # TVS_FMT_YUVJ420P (frames.BGR24 = 6 is TVS_FMT_BGR24)
 SRC_FULL_RANGE, DST_FULL_RANGE = 0x10000000, 0x20000000  # TVS_SRC_FULL_RANGE, TVS_DST_FULL_RANGE
 
@@ -37,6 +38,8 @@ def load() -> ctypes.CDLL:
     P, I, Z = ctypes.c_void_p, ctypes.c_int, ctypes.c_size_t
     lib.tvs_create.restype = P
     lib.tvs_create.argtypes = [I] * 8 + [P]
+    lib.tvs_create_ex.restype = P
+    lib.tvs_create_ex.argtypes = [I] * 8 + [P, P]
     lib.tvs_destroy.restype = None
     lib.tvs_destroy.argtypes = [P]
     lib.tvs_scale_batch.restype = I

@@ -70,9 +70,10 @@ class Scaler:
     """One scaling context on one GPU (the SwsContext of this package)."""
 
     def __init__(self, src_w, src_h, src_fmt, dst_w, dst_h, dst_fmt, flags=F.SWS_BICUBIC, chr_pos=None, device=0,
-                 src_range=None, dst_range=None):
+                 src_range=None, dst_range=None, params=None):
         """`src_range` / `dst_range`: "full" (JPEG) or "limited" (MPEG, the default), ffmpeg's in_range / out_range.  The
-        deprecated format name "yuvj420p" is yuv420p with full range on that side (include/tvscale.h TVS_FMT_YUVJ420P)."""
+        deprecated format name "yuvj420p" is yuv420p with full range on that side (include/tvscale.h TVS_FMT_YUVJ420P).
+        `params`: (param0, param1) of ffmpeg's scale filter - bicubic B and C, lanczos lobes - None entries = defaults."""
         self._lib = _lib.load()
         if src_fmt == "yuvj420p":
             src_fmt, src_range = "yuv420p", "full"
@@ -88,7 +89,10 @@ class Scaler:
                 self.flags |= bit
         self.device = device
         cp = (ctypes.c_int * 4)(*chr_pos) if chr_pos is not None else None
-        self._ctx = self._lib.tvs_create(device, src_w, src_h, self.src_fmt, dst_w, dst_h, self.dst_fmt, self.flags, cp)
+        pr = None
+        if params is not None and any(v is not None for v in params):
+            pr = (ctypes.c_double * 2)(*[_lib.PARAM_DEFAULT if v is None else float(v) for v in (tuple(params) + (None, None))[:2]])
+        self._ctx = self._lib.tvs_create_ex(device, src_w, src_h, self.src_fmt, dst_w, dst_h, self.dst_fmt, self.flags, cp, pr)
         if not self._ctx:
             raise _lib.TvscaleError(-1, _lib.last_error())
         self.src_layout = PackedLayout(self.src_fmt, src_w, src_h)
