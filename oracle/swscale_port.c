@@ -486,6 +486,25 @@ static void copy_plane(const o_ctx *c, const uint8_t *const src[], const int sst
                        uint8_t *const dst[], const int dstride[], int pl)
 {
     const int w = pl ? c->cdw : c->dw, h = pl ? c->cdh : c->dh;
+    if (c->sfmt == FMT_P010 && c->dfmt == FMT_P010) {
+        /* Same format: the library copies each STORED plane word by word - but the first word of every group of four, and
+         * the row's last (words % 4) words, lose their six padding bits (observed on libswscale 9.1.100, SIMD and plain C
+         * alike, once the fuzzer filled P010's padding with noise; conforming frames, padding zero, are copied unchanged).
+         * The interleaved UV plane is one plane of 2 * cw words; it is written when pl == 1, nothing is left for pl == 2. */
+        if (pl == 2) return;
+        const int words = pl ? 2 * w : w;
+        for (int y = 0; y < h; y++) {
+            const uint8_t *sr = src[pl] + (size_t)y * sstride[pl];
+            uint8_t *dr = dst[pl] + (size_t)y * dstride[pl];
+            for (int i = 0; i < words; i++) {
+                uint16_t v;
+                memcpy(&v, sr + 2 * i, 2);
+                if ((i & 3) == 0 || i >= (words & ~3)) v &= 0xffc0;
+                memcpy(dr + 2 * i, &v, 2);
+            }
+        }
+        return;
+    }
     for (int y = 0; y < h; y++)
         for (int x = 0; x < w; x++)
             dst_store(c, dst, dstride, pl, y, x, src_sample(c, src, sstride, pl, y, x));
