@@ -49,9 +49,9 @@ enum {
     TVS_FMT_NV12        = 1, /* AV_PIX_FMT_NV12         planes Y, UV interleaved  8 bit  */
     TVS_FMT_YUV420P10LE = 2, /* AV_PIX_FMT_YUV420P10LE  planes Y, U, V            10 bit in the low bits of LE16  */
     TVS_FMT_P010LE      = 3, /* AV_PIX_FMT_P010LE       planes Y, UV interleaved  10 bit in the high bits of LE16; as a source the
-                                six bits below may hold anything (they are shifted away, as in libswscale; only the same-size
-                                p010le -> p010le copy keeps them: all of them here, while libswscale clears those of every
-                                fourth word and of the row tail - identical for frames whose padding is zero).  Samples of
+                                six bits below may hold anything (they are shifted away, as in libswscale; the same-size
+                                p010le -> p010le copy keeps them except in every fourth word and the row tail, as libswscale's
+                                does).  Samples of
                                 TVS_FMT_YUV420P10LE sources must not exceed 1023: libswscale feeds larger words to its filters
                                 as they are, the float kernels here assume 10 bits */
     TVS_FMT_RGB24       = 4, /* AV_PIX_FMT_RGB24        one plane of R, G, B bytes; SOURCE only, even widths (what

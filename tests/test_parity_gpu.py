@@ -365,13 +365,14 @@ def test_p010_padding_bits_are_ignored_on_every_path():
     from oracle import port
     from thinvids_b200.swscale import Scaler
     rng = np.random.default_rng(4)
-    for sw, sh, dw, dh, df, alg in [(320, 180, 640, 360, 3, F.SWS_LANCZOS), (640, 360, 320, 180, 1, F.SWS_BICUBIC), (322, 182, 200, 300, 0, F.SWS_BILINEAR),
+    for sw, sh, dw, dh, df, alg in [(79, 97, 79, 97, 3, F.SWS_BICUBIC), (80, 96, 80, 96, 3, F.SWS_BICUBIC), (320, 180, 640, 360, 3, F.SWS_LANCZOS), (640, 360, 320, 180, 1, F.SWS_BICUBIC), (322, 182, 200, 300, 0, F.SWS_BILINEAR),
                                     (640, 360, 320, 180, 3, F.SWS_AREA), (256, 128, 256, 128, 1, F.SWS_BICUBIC), (1280, 720, 640, 360, 2, F.SWS_LANCZOS)]:
         clean = F.random_frame(F.P010LE, sw, sh, 31)
         dirty = [p | rng.integers(0, 64, p.shape, dtype=np.uint16) for p in clean]
-        want = port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(clean)
-        for x, y in zip(port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(dirty), want):
-            assert np.array_equal(x, y)
+        want = port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(dirty)
+        if (sw, sh, df) != (dw, dh, 3):      # (the same-size p010le -> p010le copy is the one place where padding survives)
+            for x, y in zip(port.PortScaler(sw, sh, F.P010LE, dw, dh, df, alg).scale(clean), want):
+                assert np.array_equal(x, y)
         for path in PATHS:
             with Scaler(sw, sh, F.P010LE, dw, dh, df, alg) as s:
                 if not _use_path(s, path):

@@ -476,6 +476,34 @@ inline bool aligned_for(const void *p, ptrdiff_t pitch, ptrdiff_t frame, int n_f
 }
 }  // namespace
 
+// libswscale's same-size p010le -> p010le copy (see copy_plane in oracle/swscale_port.c): the stored words are copied, but
+// the first word of every group of four and the row's last (words % 4) words lose their six padding bits.  One thread per
+// group of four words; a no-op conversion nobody should need fast.
+__global__ void __launch_bounds__(256)
+p010_copy_kernel(const uint8_t *__restrict__ src, ptrdiff_t spitch, ptrdiff_t sframe, uint8_t *__restrict__ dst, ptrdiff_t dpitch,
+                 ptrdiff_t dframe, int words, int rows) {
+    const int groups = (words + 3) >> 2;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / groups, g = idx - y * groups;
+    if (y >= rows) return;
+    const uint16_t *s = reinterpret_cast<const uint16_t *>(src + blockIdx.z * sframe + y * spitch);
+    uint16_t *d = reinterpret_cast<uint16_t *>(dst + blockIdx.z * dframe + y * dpitch);
+    for (int k = 0; k < 4; ++k) {
+        const int i = 4 * g + k;
+        if (i >= words) break;
+        uint16_t v = s[i];
+        if (k == 0 || i >= (words & ~3)) v &= 0xffc0;
+        d[i] = v;
+    }
+}
+
+int launch_p010_copy(const SampleView &src, const SampleView &dst, int words, int rows, int n_frames, cudaStream_t stream) {
+    const unsigned total = static_cast<unsigned>((words + 3) / 4) * rows;
+    const dim3 grid((total + 255) / 256, 1, n_frames);
+    p010_copy_kernel<<<grid, 256, 0, stream>>>(src.base, src.pitch, src.frame_stride, dst.base, dst.pitch, dst.frame_stride, words, rows);
+    return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
+}
+
 int launch_copy_rows(const SampleView &src_in, const SampleView &dst_in, int row_bytes, int rows, int n_frames, cudaStream_t stream) {
     SampleView src = src_in, dst = dst_in;
     // Tightly packed planes (what a rawvideo pipe delivers) are one long row: 854-wide frames then copy with 16-byte vectors

@@ -145,6 +145,7 @@ int launch_vpass_generic(const PlaneOp &op, const SampleView &dst, const DeviceT
 int launch_repack(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);
 // memcpy-class special cases of the same-size converters
 int launch_copy_rows(const SampleView &src, const SampleView &dst, int row_bytes, int rows, int n_frames, cudaStream_t stream);
+int launch_p010_copy(const SampleView &src, const SampleView &dst, int words, int rows, int n_frames, cudaStream_t stream);
 // vector forms of kOpDither2 (contiguous 16-bit plane -> byte plane; planar U + V -> interleaved bytes); they return 0
 // without launching when the surfaces are not aligned for them
 int launch_dither2_rows(const PlaneOp &op, const SampleView &src, const SampleView &dst, int n_frames, cudaStream_t stream);

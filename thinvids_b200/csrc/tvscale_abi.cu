@@ -319,15 +319,18 @@ int enqueue_planar(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], 
         int rc;
         const int bytes = op.src_bits > 8 ? 2 : 1;
         const bool plain = op.kind == kOpCopy && op.src_bits == op.dst_bits && op.src_shift == op.dst_shift;
+        const bool p010_both = plain && op.src_shift == 6 && op.src_bits == 10;   // p010le -> p010le: the library's copy has a quirk
         if (plain && op.src_xstep == bytes && op.dst_xstep == bytes) {
-            rc = launch_copy_rows(sv[i], dv[i], op.dw * bytes, op.dh, n_frames, stream);                 // plane -> plane
+            rc = p010_both ? launch_p010_copy(sv[i], dv[i], op.dw, op.dh, n_frames, stream)
+                           : launch_copy_rows(sv[i], dv[i], op.dw * bytes, op.dh, n_frames, stream);     // plane -> plane
         } else if (plain && op.src_xstep == bytes && op.dst_xstep == 2 * bytes && op.dst_offset == 0 && i + 1 < plan.ops.size() &&
                    plan.ops[i + 1].kind == kOpCopy && plan.ops[i + 1].dst_plane == op.dst_plane && plan.ops[i + 1].src_xstep == bytes) {
             rc = launch_interleave(sv[i], sv[i + 1], dv[i], bytes, op.dw, op.dh, n_frames, stream);       // U, V -> UV
             ++i;                                                                                          // consumed the V op too
         } else if (plain && op.src_xstep == 2 * bytes && op.dst_xstep == 2 * bytes && op.src_offset == 0 && op.dst_offset == 0 &&
                    i + 1 < plan.ops.size() && plan.ops[i + 1].src_plane == op.src_plane && plan.ops[i + 1].dst_plane == op.dst_plane) {
-            rc = launch_copy_rows(sv[i], dv[i], 2 * op.dw * bytes, op.dh, n_frames, stream);              // UV -> UV as one byte plane
+            rc = p010_both ? launch_p010_copy(sv[i], dv[i], 2 * op.dw, op.dh, n_frames, stream)
+                           : launch_copy_rows(sv[i], dv[i], 2 * op.dw * bytes, op.dh, n_frames, stream);  // UV -> UV as one byte plane
             ++i;
         } else {
             rc = 0;

@@ -126,9 +126,7 @@ def main():
         if n < int(os.environ.get("FUZZ_SKIP", "0")):   # fast-forward the case stream
             n += 1
             continue
-        # (the same-size p010le -> p010le copy is the one place where the padding survives, in the library with a quirk the
-        # product does not copy: include/tvscale.h; conforming frames there)
-        src = make_input(sf, sw, sh, kind, n, dirty_padding=not (sf == 3 and df == 3 and (sw, sh) == (dw, dh)))
+        src = make_input(sf, sw, sh, kind, n)
         try:
             ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=chr_pos)
             want = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
