@@ -359,6 +359,24 @@ def test_scaler_params_against_oracle():
         Scaler(64, 48, 0, 128, 96, 0, 4, params=(float("nan"), None))
 
 
+def test_extreme_geometries_against_oracle():
+    """The ends of the size range tvs_create accepts (1 .. 32768 per axis): 8K frames, planes a few rows or columns thick but
+    tens of thousands long, one-pixel frames, and the largest width at equal size."""
+    from oracle import port
+    from thinvids_b200.swscale import Scaler
+    cases = [(0, 0, 7680, 4320, 3840, 2160, F.SWS_BICUBIC), (2, 2, 4096, 2176, 1920, 1080, F.SWS_LANCZOS), (0, 1, 16384, 16, 8192, 16, F.SWS_BICUBIC),
+             (0, 0, 16, 8192, 16, 4096, F.SWS_AREA), (1, 1, 32768, 2, 32768, 2, F.SWS_BICUBIC), (0, 0, 1, 1, 1, 1, F.SWS_BICUBIC),
+             (0, 1, 1, 1, 5, 7, F.SWS_BILINEAR), (3, 0, 2, 32768, 2, 1000, F.SWS_BILINEAR), (0, 0, 24, 10, 32768, 10, F.SWS_LANCZOS)]
+    for sf, df, sw, sh, dw, dh, alg in cases:
+        src = F.random_frame(sf, sw, sh, 3)
+        want = port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(src)
+        with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+            got = s.scale(src)
+            path = s.path
+        for k, (a, b) in enumerate(zip(got, want)):
+            assert np.array_equal(a, b), (path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
+
+
 def test_p010_padding_bits_are_ignored_on_every_path():
     """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
     (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""
