@@ -101,3 +101,23 @@ def test_scaled_width_matches_reference_shapes():
     assert F.CONFIGS["C1"].algorithmic_bytes == 3628800
     assert F.CONFIGS["C2"].algorithmic_bytes == 15552000
     assert F.CONFIGS["C4"].algorithmic_bytes == 31104000
+
+
+def test_libswscale_api_shim_loads_and_exports_the_trio():
+    """thinvids_b200/libswscale_tvs.so: sws_getContext / sws_scale / sws_freeContext on top of libtvscale (no compute here)."""
+    import ctypes
+    import os
+    from thinvids_b200 import build as tv_build
+    tv_build.build()
+    if not os.path.exists(tv_build.SHIM_LIB):
+        tv_build.build_shim()
+    shim = ctypes.CDLL(tv_build.SHIM_LIB)
+    for name in ("sws_getContext", "sws_scale", "sws_freeContext", "tvs_shim_map_pix_fmt"):
+        assert hasattr(shim, name), name
+    shim.sws_getContext.restype = ctypes.c_void_p
+    shim.sws_getContext.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p] * 3
+    assert not shim.sws_getContext(64, 48, 9999, 32, 24, 0, 4, None, None, None)      # unknown pixel format: NULL, like libswscale
+    assert not shim.sws_getContext(64, 48, 0, 32, 24, 0, 4, ctypes.c_void_p(1), None, None)   # source filters are not supported
+    assert shim.tvs_shim_map_pix_fmt(9999, 0) == 0
+    shim.sws_freeContext.argtypes = [ctypes.c_void_p]
+    shim.sws_freeContext(None)

@@ -377,6 +377,43 @@ def test_extreme_geometries_against_oracle():
             assert np.array_equal(a, b), (path, sf, df, sw, sh, dw, dh, hex(alg), k, int((a != b).sum()))
 
 
+def test_libswscale_api_shim_against_the_genuine_library():
+    """sws_getContext / sws_scale / sws_freeContext of thinvids_b200/libswscale_tvs.so called exactly as the genuine library is
+    called (same AVPixelFormat values, plane pointer and int stride arrays, slice arguments), outputs compared byte for byte."""
+    import ctypes
+    from oracle import ref_swscale
+    from thinvids_b200 import build as tv_build
+    if not ref_swscale.available():
+        pytest.skip("needs the genuine library's AVPixelFormat values")
+    avu, _ = ref_swscale._load()
+    shim = ctypes.CDLL(tv_build.SHIM_LIB)
+    shim.sws_getContext.restype = ctypes.c_void_p
+    shim.sws_getContext.argtypes = [ctypes.c_int] * 7 + [ctypes.c_void_p] * 3
+    shim.sws_scale.restype = ctypes.c_int
+    shim.sws_scale.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int, ctypes.c_int, ctypes.c_void_p, ctypes.c_void_p]
+    shim.sws_freeContext.argtypes = [ctypes.c_void_p]
+    names = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24"}
+    for sf, df, sw, sh, dw, dh, alg in [(0, 1, 720, 480, 1620, 1080, 4), (0, 0, 320, 240, 480, 270, 0x200), (1, 1, 640, 360, 320, 180, 0x20),
+                                        (2, 3, 322, 182, 200, 300, 2), (3, 1, 256, 128, 256, 128, 4), (4, 0, 320, 180, 640, 360, 0x200),
+                                        (6, 1, 320, 180, 200, 100, 4), (0, 1, 854, 480, 854, 480, 4)]:
+        src = F.random_frame(sf, sw, sh, 21)
+        want = ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg).scale(src)
+        ctx = shim.sws_getContext(sw, sh, avu.av_get_pix_fmt(names[sf]), dw, dh, avu.av_get_pix_fmt(names[df]), alg | 0x40000 | 0x80000, None, None, None)
+        assert ctx
+        got = [np.full_like(p, 0x5a) for p in F.alloc_frame(df, dw, dh)]
+        sp = (ctypes.c_void_p * 4)(*([p.ctypes.data for p in src] + [None] * (4 - len(src))))
+        ss = (ctypes.c_int * 4)(*([p.strides[0] for p in src] + [0] * (4 - len(src))))
+        dp = (ctypes.c_void_p * 4)(*([p.ctypes.data for p in got] + [None] * (4 - len(got))))
+        ds = (ctypes.c_int * 4)(*([p.strides[0] for p in got] + [0] * (4 - len(got))))
+        assert shim.sws_scale(ctx, sp, ss, 0, sh, dp, ds) == dh
+        assert shim.sws_scale(ctx, sp, ss, 0, sh // 2, dp, ds) < 0          # slices are refused, not approximated
+        shim.sws_freeContext(ctx)
+        for k, (a, b) in enumerate(zip(got, want)):
+            if k == 1 and df == 3 and (sw, sh) == (dw, dh) and sw % 2:
+                a, b = a[:, :-2], b[:, :-2]
+            assert np.array_equal(a, b), (sf, df, sw, sh, dw, dh, hex(alg), k)
+
+
 def test_p010_padding_bits_are_ignored_on_every_path():
     """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
     (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""

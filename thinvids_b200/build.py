@@ -15,7 +15,7 @@ PKG = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(PKG, "csrc")
 LIB = os.path.join(PKG, "libtvscale.so")
 SOURCES = ["filter_tables.cpp", "kernels_generic.cu", "kernels_fused_w256.cu", "kernels_fused_w128.cu", "kernels_stream.cu", "kernels_slab.cu", "kernels_bwdif.cu", "tvscale_abi.cu"]
-HEADERS = ["filter_tables.h", "tvs_internal.h", "kernels_fused_impl.cuh", "scale_device.cuh", os.path.join("..", "..", "include", "tvscale.h")]
+HEADERS = ["swscale_shim.cpp", "filter_tables.h", "tvs_internal.h", "kernels_fused_impl.cuh", "scale_device.cuh", os.path.join("..", "..", "include", "tvscale.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17",
               "-Xcompiler", "-fPIC,-ffp-contract=off,-fvisibility=hidden", "--fmad=true"]
 NVCC_FLAGS += os.environ.get("TVS_NVCC_EXTRA", "").split()   # experiments, e.g. -DTVS_HALVES=1
@@ -29,7 +29,7 @@ def _nvcc() -> str:
 
 
 def needs_build() -> bool:
-    if not os.path.exists(LIB):
+    if not os.path.exists(LIB) or not os.path.exists(os.path.join(PKG, "libswscale_tvs.so")):
         return True
     t = os.path.getmtime(LIB)
     deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS] + [os.path.abspath(__file__)]
@@ -66,7 +66,22 @@ def build(force: bool = False, verbose: bool = False) -> str:
     subprocess.check_call([_nvcc(), "-shared", "-o", tmp, *objs, "-gencode", "arch=compute_100a,code=sm_100a",
                            "-cudart", "static"])
     os.replace(tmp, LIB)
+    build_shim()
     return LIB
+
+
+SHIM_LIB = os.path.join(PKG, "libswscale_tvs.so")
+
+
+def build_shim() -> str:
+    """libswscale's sws_getContext / sws_scale / sws_freeContext on top of libtvscale.so (csrc/swscale_shim.cpp): a small
+    host-only library that finds libtvscale.so next to itself."""
+    src = os.path.join(CSRC, "swscale_shim.cpp")
+    tmp = SHIM_LIB + ".tmp.%d" % os.getpid()
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-fvisibility=hidden", "-o", tmp, src,
+                           "-L" + PKG, "-l:libtvscale.so", "-Wl,-rpath,$ORIGIN"])
+    os.replace(tmp, SHIM_LIB)
+    return SHIM_LIB
 
 
 if __name__ == "__main__":
