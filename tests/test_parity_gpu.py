@@ -414,6 +414,50 @@ def test_libswscale_api_shim_against_the_genuine_library():
             assert np.array_equal(a, b), (sf, df, sw, sh, dw, dh, hex(alg), k)
 
 
+def test_contexts_on_concurrent_host_threads():
+    """Several host threads, each with its own context (the SegmentFarm form: ctypes drops the GIL inside the C ABI), scaling
+    different shapes at the same time on one GPU: every result still equals the oracle's, and a failing call in one thread
+    leaves its own error text in that thread only."""
+    import threading
+    from oracle import port
+    from thinvids_b200 import lib as tv_lib
+    from thinvids_b200.swscale import Scaler
+    jobs = [(0, 1, 720, 480, 1620, 1080, F.SWS_BICUBIC), (0, 0, 640, 360, 320, 180, F.SWS_LANCZOS), (2, 3, 320, 180, 480, 270, F.SWS_BICUBIC),
+            (4, 0, 320, 180, 640, 360, F.SWS_LANCZOS), (1, 1, 640, 360, 640, 360, F.SWS_BICUBIC), (3, 1, 640, 360, 320, 180, F.SWS_AREA)]
+    wants = [port.PortScaler(sw, sh, sf, dw, dh, df, alg).scale(F.random_frame(sf, sw, sh, 40 + i))
+             for i, (sf, df, sw, sh, dw, dh, alg) in enumerate(jobs)]
+    problems = []
+
+    def work(i):
+        sf, df, sw, sh, dw, dh, alg = jobs[i]
+        src = F.random_frame(sf, sw, sh, 40 + i)
+        try:
+            with Scaler(sw, sh, sf, dw, dh, df, alg) as s:
+                for rep in range(6):
+                    got = s.scale(src)
+                    if not all(np.array_equal(a, b) for a, b in zip(got, wants[i])):
+                        problems.append(("pixels", i, rep))
+                if i == 0:
+                    try:
+                        s.set_path("stream")        # an up-scale has no streaming plan: this thread's error, nobody else's
+                        problems.append(("no error", i))
+                    except tv_lib.TvscaleError:
+                        pass
+                    if not tv_lib.last_error():
+                        problems.append(("error text lost", i))
+                elif tv_lib.last_error() and "stream" in tv_lib.last_error():
+                    problems.append(("foreign error text", i, tv_lib.last_error()))
+        except Exception as e:      # noqa: BLE001 - reported through the list
+            problems.append(("exception", i, repr(e)))
+
+    threads = [threading.Thread(target=work, args=(i,)) for i in range(len(jobs))]
+    for t in threads:
+        t.start()
+    for t in threads:
+        t.join()
+    assert not problems, problems
+
+
 def test_p010_padding_bits_are_ignored_on_every_path():
     """P010 keeps 10 bits in the top of a 16-bit word; decoders do not promise zeros below.  libswscale shifts them away
     (p010LEToY_c / p010LEToUV_c), so every kernel path must give the same bytes whatever sits there."""
