@@ -59,7 +59,9 @@ enum {
     TVS_FMT_YUVJ420P    = 5, /* AV_PIX_FMT_YUVJ420P     yuv420p holding full-range (JPEG) samples: what ffmpeg's decoders hand
                                 the scale filter for MJPEG and most phone / camera H.264.  As source it implies
                                 TVS_SRC_FULL_RANGE, as destination TVS_DST_FULL_RANGE (libswscale's handle_jpeg) */
-    TVS_FMT_BGR24       = 6  /* AV_PIX_FMT_BGR24        as TVS_FMT_RGB24 with B, G, R byte order (OpenCV's frames); SOURCE only */
+    TVS_FMT_BGR24       = 6, /* AV_PIX_FMT_BGR24        as TVS_FMT_RGB24 with B, G, R byte order (OpenCV's frames); SOURCE only */
+    TVS_FMT_RGB48LE     = 7, /* AV_PIX_FMT_RGB48LE      R, G, B of 16 bits each, little-endian; SOURCE only, even widths */
+    TVS_FMT_RGB48BE     = 8  /* AV_PIX_FMT_RGB48BE      the same big-endian (what ffmpeg decodes a 16-bit PNG to); SOURCE only */
 };
 
 /* Scaler flags: numerically equal to libswscale's SWS_* so ffmpeg `flags=` values pass through. */

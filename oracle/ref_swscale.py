@@ -16,7 +16,7 @@ import numpy as np
 
 from . import build as _build
 
-_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24"}
+_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24", 7: b"rgb48le", 8: b"rgb48be"}
 _libs = None
 
 
@@ -121,11 +121,11 @@ class RefScaler:
 
     def scale(self, src_planes):
         from thinvids_b200.frames import alloc_frame, plane_shapes, sample_dtype
-        if self.src[2] in (4, 6):
-            # rgb24 / bgr24: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
+        if self.src[2] in (4, 6, 7, 8):
+            # packed RGB sources: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
             # give it padded buffers and crop
             h, row = src_planes[0].shape
-            pad = np.zeros((h + 2, row + 64), dtype=np.uint8)
+            pad = np.zeros((h + 2, row + 64), dtype=src_planes[0].dtype)
             pad[:h, :row] = src_planes[0]
             shapes = plane_shapes(self.dst[2], self.dst[0], self.dst[1])
             big = [np.zeros((r + 2, c + 64), dtype=sample_dtype(self.dst[2])) for r, c in shapes]

@@ -26,8 +26,10 @@
 #include <stdlib.h>
 #include <string.h>
 
-enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */, FMT_BGR24 = 6 /* source only */ };
-static int fmt_rgb(int f) { return f == FMT_RGB24 || f == FMT_BGR24; }
+enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */, FMT_BGR24 = 6 /* source only */,
+       FMT_RGB48LE = 7, FMT_RGB48BE = 8 /* 16 bits per component, source only */ };
+static int fmt_rgb48(int f) { return f == FMT_RGB48LE || f == FMT_RGB48BE; }
+static int fmt_rgb(int f) { return f == FMT_RGB24 || f == FMT_BGR24 || f == FMT_RGB48LE || f == FMT_RGB48BE; }
 enum { ALG_BILINEAR = 2, ALG_BICUBIC = 4, ALG_AREA = 0x20, ALG_LANCZOS = 0x200 };
 
 typedef struct {
@@ -63,7 +65,7 @@ typedef struct {
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
 static int64_t iabs64(int64_t v) { return v < 0 ? -v : v; }
-static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24 || f == FMT_BGR24) ? 8 : 10; }
+static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24 || f == FMT_BGR24) ? 8 : (f == FMT_RGB48LE || f == FMT_RGB48BE) ? 16 : 10; }
 static int fmt_semi(int f) { return f == FMT_NV12 || f == FMT_P010; }
 
 /* SURVEY.md A.2 — coefficient table for one axis. */
@@ -381,7 +383,7 @@ static const uint8_t D128[8][8] = {
 static inline int src_sample(const o_ctx *c, const uint8_t *const src[], const int stride[], int pl, int r, int x)
 {
     switch (c->sfmt) {
-    case FMT_RGB24: case FMT_BGR24: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
+    case FMT_RGB24: case FMT_BGR24: case FMT_RGB48LE: case FMT_RGB48BE: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
     case FMT_YUV420P: return src[pl][(size_t)r * stride[pl] + x];
     case FMT_NV12:
         return pl == 0 ? src[0][(size_t)r * stride[0] + x] : src[1][(size_t)r * stride[1] + 2 * x + (pl - 1)];
@@ -423,7 +425,8 @@ static int scale_plane(const o_ctx *c, const uint8_t *const src[], const int sst
     const int dw = pl ? c->cdw : c->dw, dh = pl ? c->cdh : c->dh;
     const int sbits = fmt_bits(c->sfmt), dbits = fmt_bits(c->dfmt);
     /* RGB input reaches the scaler as 14/15-bit lines (srcBpc = 16) and hScale16To15 then shifts by 13 */
-    const int hshift = fmt_rgb(c->sfmt) ? 13 : sbits == 8 ? 7 : sbits - 1;
+    /* ... and 16-bit RGB as 16-bit lines, shifted by 15 (hScale16To15_c: depth - 1) */
+    const int hshift = fmt_rgb48(c->sfmt) ? 15 : fmt_rgb(c->sfmt) ? 13 : sbits == 8 ? 7 : sbits - 1;
     int16_t *mid = (int16_t *)malloc((size_t)sh * dw * sizeof(int16_t));
     if (!mid) return -1;
 
@@ -562,6 +565,32 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
     for (int pl = 0; pl < 3; pl++) {
         c->rgb[pl] = (uint16_t *)malloc((size_t)c->sh * (pl ? c->csw : c->sw) * sizeof(uint16_t));
         if (!c->rgb[pl]) return -1;
+    }
+    if (fmt_rgb48(c->sfmt)) {
+        /* rgb48ToY_c / rgb48ToUV_c / rgb48ToUV_half_c: 16-bit components (either byte order), RGB2YUV_SHIFT = 15, the result
+         * a full 16-bit line; the half-width chroma averages two pixels with rounding first */
+        const int be = c->sfmt == FMT_RGB48BE;
+        for (int r = 0; r < c->sh; r++) {
+            const uint8_t *row = rgb + (size_t)r * stride;
+#define PX16(i) (be ? (unsigned)(row[2 * (i)] << 8 | row[2 * (i) + 1]) : (unsigned)(row[2 * (i) + 1] << 8 | row[2 * (i)]))
+            for (int x = 0; x < c->sw; x++) {
+                const unsigned R = PX16(3 * x), G = PX16(3 * x + 1), B = PX16(3 * x + 2);
+                c->rgb[0][(size_t)r * c->sw + x] = (uint16_t)(((int)(RY * R + GY * G + BY * B) + (0x2001 << 14)) >> 15);
+                if (!c->rgb_half) {
+                    c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)(((int)(RU * (int)R + GU * (int)G + BU * (int)B) + (0x10001 << 14)) >> 15);
+                    c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)(((int)(RV * (int)R + GV * (int)G + BV * (int)B) + (0x10001 << 14)) >> 15);
+                }
+            }
+            if (c->rgb_half)
+                for (int x = 0; x < c->csw; x++) {
+                    const int R = (int)((PX16(6 * x) + PX16(6 * x + 3) + 1) >> 1), G = (int)((PX16(6 * x + 1) + PX16(6 * x + 4) + 1) >> 1),
+                              B = (int)((PX16(6 * x + 2) + PX16(6 * x + 5) + 1) >> 1);
+                    c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (0x10001 << 14)) >> 15);
+                    c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)((RV * R + GV * G + BV * B + (0x10001 << 14)) >> 15);
+                }
+#undef PX16
+        }
+        return 0;
     }
     const int ro = c->sfmt == FMT_BGR24 ? 2 : 0, bo = 2 - ro;   /* bgr24ToY_c / bgr24ToUV*_c: the same sums with R and B swapped in memory */
     for (int r = 0; r < c->sh; r++) {

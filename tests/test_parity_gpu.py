@@ -582,10 +582,11 @@ def test_rgb24_sources_against_oracle():
         if i >= 40:
             sw, sh, dw, dh = [(720, 480, 1920, 1080), (1440, 960, 1920, 1080), (2880, 1920, 1920, 1080), (640, 360, 1280, 720)][i % 4]
         alg, df = rnd.choice(algs), rnd.randrange(4)
-        sf = F.BGR24 if i % 4 == 3 else F.RGB24
+        sf = (F.RGB24, F.RGB48LE, F.RGB24, F.BGR24, F.RGB24, F.RGB48BE)[i % 6]
         frames = [F.random_frame(sf, sw, sh, 900 + 3 * i + k) for k in range(3)]
-        if i % 3 == 1:     # only 0 and 255
-            frames = [[(p > 127).astype(np.uint8) * 255 for p in fr] for fr in frames]
+        if i % 3 == 1:     # only 0 and the maximum
+            hi = 65535 if F.bit_depth(sf) == 16 else 255
+            frames = [[((p > hi // 2) * hi).astype(p.dtype) for p in fr] for fr in frames]
         ref = port.PortScaler(sw, sh, sf, dw, dh, df, alg)
         want = [ref.scale(fr) for fr in frames]
         for path in ("auto", "two-pass"):

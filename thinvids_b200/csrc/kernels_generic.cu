@@ -301,6 +301,40 @@ rgb_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t fra
     }
 }
 
+// The same stage for 16-bit components (rgb48le / rgb48be; input.c: rgb48ToY_c, rgb48ToUV_c, rgb48ToUV_half_c): full 16-bit
+// lines, one rounding constant, and the half-width chroma averages its two pixels (with rounding) before the sum.
+__global__ void __launch_bounds__(256)
+rgb48_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *__restrict__ planes,
+                   size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half, int be) {
+    constexpr int RY = 8414, GY = 16519, BY = 3208, RU = -4865, GU = -9528, BU = 14392, RV = 14392, GV = -12061, BV = -2332;
+    const int pairs = w >> 1;
+    const int idx = blockIdx.x * blockDim.x + threadIdx.x;
+    const int y = idx / pairs, i = idx - y * pairs;
+    if (y >= h) return;
+    const int f = blockIdx.z;
+    const uint8_t *p = rgb + f * frame_stride + y * pitch + 12 * i;
+    int c[6];
+#pragma unroll
+    for (int k = 0; k < 6; ++k) c[k] = be ? (p[2 * k] << 8 | p[2 * k + 1]) : (p[2 * k + 1] << 8 | p[2 * k]);
+    uint8_t *out = planes + f * planes_frame_stride;
+    uint16_t *yrow = reinterpret_cast<uint16_t *>(out) + static_cast<size_t>(y) * w + 2 * i;
+    // (at most 28141 * 65535 + (0x2001 << 14) < 2^31: int arithmetic, as in libswscale)
+    yrow[0] = static_cast<uint16_t>((RY * c[0] + GY * c[1] + BY * c[2] + (0x2001 << 14)) >> 15);
+    yrow[1] = static_cast<uint16_t>((RY * c[3] + GY * c[4] + BY * c[5] + (0x2001 << 14)) >> 15);
+    uint16_t *u = reinterpret_cast<uint16_t *>(out + u_offset), *v = reinterpret_cast<uint16_t *>(out + u_offset + c_plane_bytes);
+    if (half) {
+        const int r = (c[0] + c[3] + 1) >> 1, g = (c[1] + c[4] + 1) >> 1, b = (c[2] + c[5] + 1) >> 1;
+        u[static_cast<size_t>(y) * pairs + i] = static_cast<uint16_t>((RU * r + GU * g + BU * b + (0x10001 << 14)) >> 15);
+        v[static_cast<size_t>(y) * pairs + i] = static_cast<uint16_t>((RV * r + GV * g + BV * b + (0x10001 << 14)) >> 15);
+    } else {
+        const size_t o = static_cast<size_t>(y) * w + 2 * i;
+        u[o] = static_cast<uint16_t>((RU * c[0] + GU * c[1] + BU * c[2] + (0x10001 << 14)) >> 15);
+        u[o + 1] = static_cast<uint16_t>((RU * c[3] + GU * c[4] + BU * c[5] + (0x10001 << 14)) >> 15);
+        v[o] = static_cast<uint16_t>((RV * c[0] + GV * c[1] + BV * c[2] + (0x10001 << 14)) >> 15);
+        v[o + 1] = static_cast<uint16_t>((RV * c[3] + GV * c[4] + BV * c[5] + (0x10001 << 14)) >> 15);
+    }
+}
+
 // ---- memcpy-class fast paths of the same-size converters (the DVD production shape: yuv420p -> nv12 at equal size,
 // worker/tasks.py:62-63) -------------------------------------------------------------------------------------------
 // Plain 2-D copy of `row_bytes` per row.  V = bytes per thread access (16, 4 or 1), chosen by the launcher from the
@@ -577,11 +611,15 @@ int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const Sa
 }
 
 int launch_rgb_input(const uint8_t *rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *planes, size_t planes_frame_stride,
-                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, bool bgr, int n_frames, cudaStream_t stream) {
+                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, bool bgr, int wide, int n_frames, cudaStream_t stream) {
     const unsigned total = static_cast<unsigned>(w / 2) * h;
     const dim3 grid((total + 255) / 256, 1, n_frames);
-    rgb_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
-                                               half ? 1 : 0, bgr ? 1 : 0);
+    if (wide)   // 1 = rgb48le, 2 = rgb48be
+        rgb48_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
+                                                     half ? 1 : 0, wide == 2 ? 1 : 0);
+    else
+        rgb_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
+                                                   half ? 1 : 0, bgr ? 1 : 0);
     return cudaPeekAtLastError() == cudaSuccess ? 1 : -1;
 }
 

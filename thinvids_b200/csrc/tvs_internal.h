@@ -157,7 +157,7 @@ int launch_dither128_interleave(const PlaneOp &op, const SampleView &u, const Sa
 // libswscale's input stage for packed rgb24 (rgb24ToY_c, rgb24ToUV_c / rgb24ToUV_half_c, BT.601 limited range): per frame
 // `planes` receives Y [h][w], then U and V [h][cw] as uint16, cw = w / 2 (half) or w
 int launch_rgb_input(const uint8_t *rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *planes, size_t planes_frame_stride,
-                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, bool bgr, int n_frames, cudaStream_t stream);
+                     size_t u_offset_bytes, size_t c_plane_bytes, int w, int h, bool half, bool bgr, int wide, int n_frames, cudaStream_t stream);
 // exact 2:1 area down-scale of an 8-bit plane (pair = interleaved UV bytes)
 int launch_box2(const SampleView &src, const SampleView &dst, bool pair, int out_bytes, int rows, int n_frames, cudaStream_t stream);
 int launch_interleave(const SampleView &u, const SampleView &v, const SampleView &dst, int sample_bytes, int w, int rows, int n_frames,

@@ -44,6 +44,7 @@ struct FormatInfo {
     int planes;     // stored planes
     bool rgb;       // one plane of packed R, G, B bytes (source only)
     bool bgr = false;   // ... stored B, G, R
+    bool be = false;    // 16-bit components stored big-endian (rgb48be)
 };
 
 bool format_info(int fmt, FormatInfo &fi) {
@@ -54,12 +55,14 @@ bool format_info(int fmt, FormatInfo &fi) {
     case TVS_FMT_P010LE: fi = {10, 2, 6, true, 2, false}; return true;
     case TVS_FMT_RGB24: fi = {8, 1, 0, false, 1, true}; return true;
     case TVS_FMT_BGR24: fi = {8, 1, 0, false, 1, true, true}; return true;
+    case TVS_FMT_RGB48LE: fi = {16, 2, 0, false, 1, true, false, false}; return true;
+    case TVS_FMT_RGB48BE: fi = {16, 2, 0, false, 1, true, false, true}; return true;
     default: return false;
     }
 }
 
 size_t tight_frame_bytes(const FormatInfo &fi, int w, int h) {
-    if (fi.rgb) return static_cast<size_t>(3) * w * h;
+    if (fi.rgb) return static_cast<size_t>(3) * w * h * fi.bytes;
     const size_t cw = (w + 1) / 2, ch = (h + 1) / 2;
     return (static_cast<size_t>(w) * h + 2 * cw * ch) * fi.bytes;
 }
@@ -184,7 +187,8 @@ void build_plan(tvs_ctx *c) {
 
     if (s.rgb) {
         // The scaler sees the input stage's planar 16-bit lines (virtual planes 0..2 in c->rgb_planes): luma sw x sh,
-        // chroma rgb_cw x sh (never subsampled vertically), 14/15-bit values, horizontal shift 13, no ordered dither.
+        // chroma rgb_cw x sh (never subsampled vertically), 14/15-bit values, horizontal shift 13, no ordered dither; from
+        // 16-bit components (rgb48) full 16-bit values, shift 15, and the ordered dither of every source deeper than 8 bits.
         for (int pl = 0; pl < 3; ++pl) {
             PlaneOp op;
             op.kind = kOpScale;
@@ -193,9 +197,9 @@ void build_plan(tvs_ctx *c) {
             op.src_bits = 16; op.dst_bits = d.bits; op.src_shift = 0; op.dst_shift = d.shift;
             op.sw = pl ? c->rgb_cw : sw; op.sh = sh; op.dw = pl ? cdw : dw; op.dh = pl ? cdh : dh;
             op.htable = pl ? 1 : 0; op.vtable = pl ? 3 : 2;
-            op.hshift = 13;
-            op.rule = d.bits > 8 ? kOut10 : kOut8;
-            op.dither_xoff = 0;
+            op.hshift = s.bits == 16 ? 15 : 13;
+            op.rule = d.bits > 8 ? kOut10 : s.bits == 16 ? kOut8Dither : kOut8;
+            op.dither_xoff = s.bits == 16 && pl == 2 ? 3 : 0;
             p.ops.push_back(op);
         }
     } else if (same && s.bits == 10 && d.bits == 8 && s.semi && d.semi) {
@@ -267,7 +271,7 @@ int check_planes(const FormatInfo &fi, int w, int h, const void *const planes[3]
     const int cw = (w + 1) / 2;
     for (int i = 0; i < fi.planes; ++i) {
         if (!planes[i]) return fail(-EINVAL, "%s plane %d is NULL", side, i);
-        const ptrdiff_t row = fi.rgb ? 3 * static_cast<ptrdiff_t>(w) : static_cast<ptrdiff_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
+        const ptrdiff_t row = fi.rgb ? 3 * static_cast<ptrdiff_t>(w) * fi.bytes : static_cast<ptrdiff_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
         if (pitch[i] < row) return fail(-EINVAL, "%s pitch[%d]=%td is smaller than a row (%td bytes)", side, i, pitch[i], row);
         if (fi.bytes == 2 && ((reinterpret_cast<uintptr_t>(planes[i]) | static_cast<uintptr_t>(pitch[i])) & 1))
             return fail(-EINVAL, "%s plane %d: 16-bit samples need 2-byte aligned pointer and pitch", side, i);
@@ -483,7 +487,7 @@ int enqueue_batch(tvs_ctx *c, const void *const src[3], const ptrdiff_t sp[3], c
     for (int f0 = 0; f0 < n_frames; f0 += static_cast<int>(chunk)) {
         const int nf = std::min<int>(static_cast<int>(chunk), n_frames - f0);
         if (launch_rgb_input(static_cast<const uint8_t *>(src[0]) + static_cast<ptrdiff_t>(f0) * sf[0], sp[0], sf[0], c->rgb_planes, per_frame,
-                             y_bytes, c_bytes, c->src_w, c->src_h, c->rgb_half, c->sfi.bgr, nf, stream) < 0)
+                             y_bytes, c_bytes, c->src_w, c->src_h, c->rgb_half, c->sfi.bgr, c->sfi.bits == 16 ? (c->sfi.be ? 2 : 1) : 0, nf, stream) < 0)
             return cuda_fail(cudaGetLastError(), "rgb input kernel launch");
         ++c->launches;
         void *vdst[3] = {nullptr, nullptr, nullptr};
@@ -560,18 +564,18 @@ tvs_ctx *tvs_create_ex(int device, int src_w, int src_h, int src_fmt, int dst_w,
         return nullptr;
     }
     if (dfi.rgb) {
-        fail(-ENOSYS, "rgb24 / bgr24 are supported as source formats only");
+        fail(-ENOSYS, "packed RGB formats are supported as source formats only");
         return nullptr;
     }
     if (sfi.rgb && src_full != dst_full) {
         // rgb24 is full range by nature and the input stage's table already produces limited-range YUV; what libswscale does
         // with an explicit destination range there has not been restated
-        fail(-ENOSYS, "range flags are not implemented for rgb24 sources");
+        fail(-ENOSYS, "range flags are not implemented for packed RGB sources");
         return nullptr;
     }
     if (sfi.rgb && (src_w & 1)) {
         // libswscale's half-width chroma input (rgb24ToUV_half_c) reads a pixel past the row when the width is odd
-        fail(-EINVAL, "rgb24 / bgr24 sources need an even width (got %d)", src_w);
+        fail(-EINVAL, "packed RGB sources need an even width (got %d)", src_w);
         return nullptr;
     }
     const int alg_bits = flags & (TVS_BILINEAR | TVS_BICUBIC | TVS_AREA | TVS_LANCZOS);
@@ -781,7 +785,7 @@ int tvs_scale_host(tvs_ctx *c, const void *const src[3], const ptrdiff_t src_pit
     const int cw_s = (c->src_w + 1) / 2, ch_s = (c->src_h + 1) / 2, cw_d = (c->dst_w + 1) / 2, ch_d = (c->dst_h + 1) / 2;
     auto plane_rows = [](int i, int h, int ch) { return i == 0 ? h : ch; };
     auto plane_row_bytes = [](const FormatInfo &fi, int i, int w, int cw) {
-        if (fi.rgb) return static_cast<size_t>(3) * w;
+        if (fi.rgb) return static_cast<size_t>(3) * w * fi.bytes;
         return static_cast<size_t>(i == 0 ? w : (fi.semi ? 2 * cw : cw)) * fi.bytes;
     };
     const size_t sframe = tight_frame_bytes(c->sfi, c->src_w, c->src_h);

@@ -18,9 +18,10 @@ import numpy as np
 
 # Pixel-format codes of the C ABI (include/tvscale.h).
 YUV420P, NV12, YUV420P10LE, P010LE, RGB24 = 0, 1, 2, 3, 4
+RGB48LE, RGB48BE = 7, 8   # 16 bits per component, either byte order (16-bit PNGs decode as rgb48be)
 BGR24 = 6   # (5 is the C ABI's yuvj420p, which the Python layer spells as yuv420p + full range)
-FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE, "rgb24": RGB24, "bgr24": BGR24}
-SOURCE_ONLY_FORMATS = {RGB24, BGR24}
+FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE, "rgb24": RGB24, "bgr24": BGR24, "rgb48le": RGB48LE, "rgb48be": RGB48BE}
+SOURCE_ONLY_FORMATS = {RGB24, BGR24, RGB48LE, RGB48BE}
 NAME_BY_FMT = {v: k for k, v in FMT_BY_NAME.items()}
 
 # Scaler algorithm flags, numerically equal to libswscale's SWS_* values.
@@ -38,7 +39,8 @@ def is_semiplanar(fmt) -> bool:
 
 
 def bit_depth(fmt) -> int:
-    return 8 if fmt_code(fmt) in (YUV420P, NV12, RGB24, BGR24) else 10
+    code = fmt_code(fmt)
+    return 8 if code in (YUV420P, NV12, RGB24, BGR24) else 16 if code in (RGB48LE, RGB48BE) else 10
 
 
 def sample_dtype(fmt):
@@ -48,7 +50,7 @@ def sample_dtype(fmt):
 def plane_shapes(fmt, w: int, h: int):
     """(rows, cols-in-samples) of every stored plane of a tightly packed frame."""
     cw, ch = (w + 1) // 2, (h + 1) // 2
-    if fmt_code(fmt) in (RGB24, BGR24):
+    if fmt_code(fmt) in (RGB24, BGR24, RGB48LE, RGB48BE):
         return [(h, 3 * w)]          # one plane of R, G, B bytes
     if is_semiplanar(fmt):
         return [(h, w), (ch, 2 * cw)]
@@ -72,7 +74,7 @@ def random_frame(fmt, w: int, h: int, seed: int = 1234):
         if bit_depth(fmt) == 8:
             planes.append(rng.integers(0, 256, shape, dtype=np.uint8))
         else:
-            p = rng.integers(0, 1024, shape, dtype=np.uint16)
+            p = rng.integers(0, 65536 if bit_depth(fmt) == 16 else 1024, shape, dtype=np.uint16)
             planes.append(p << 6 if fmt_code(fmt) == P010LE else p)
     return planes
 

@@ -20,7 +20,7 @@ from thinvids_b200.swscale import Scaler  # noqa: E402
 
 def make_input(fmt, w, h, kind, seed, dirty_padding=True):
     rng = np.random.default_rng(seed)
-    hi = 255 if F.bit_depth(fmt) == 8 else 1023
+    hi = {8: 255, 10: 1023, 16: 65535}[F.bit_depth(fmt)]
     planes = []
     for rows, cols in F.plane_shapes(fmt, w, h):
         if kind == 0:
@@ -99,7 +99,7 @@ def main():
     algs = [F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS]
     t0, n, bad = time.time(), 0, 0
     while time.time() - t0 < budget:
-        sf = rnd.choice([0, 0, 1, 2, 3, 4])   # (FUZZ_SF=6 for bgr24)
+        sf = rnd.choice([0, 0, 1, 2, 3, 4])   # (FUZZ_SF=6 for bgr24, 7 / 8 for rgb48le / rgb48be)
         if os.environ.get("FUZZ_SF"):   # one source format only, e.g. 4 = rgb24
             sf = int(os.environ["FUZZ_SF"])
         df = rnd.randrange(4)
@@ -107,7 +107,7 @@ def main():
         big = huge or rnd.random() < 0.25
         sw, sh = (rnd.randrange(200, 3850 if huge else 1930), rnd.randrange(100, 2170 if huge else 1090)) if big \
             else (rnd.randrange(2, 400), rnd.randrange(2, 300))
-        if sf in (4, 6):
+        if sf in (4, 6, 7, 8):
             sw += sw & 1
         mode = rnd.random()
         if mode < 0.15:
