@@ -98,6 +98,14 @@ EXTRA_CASES = [
     ("rgb24", 722, 479, "p010le", 333, 777, "area", "seed:1234", None),
     ("rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", "pattern:checker", None),
     ("rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", "pattern:white", None),
+    # bgr24 (OpenCV's order) and 16-bit RGB (rgb48be is what a 16-bit PNG decodes to): round 2
+    ("bgr24", 720, 480, "nv12", 1620, 1080, "bicubic", "seed:1234", None),
+    ("bgr24", 1920, 1080, "yuv420p", 1280, 720, "lanczos", "seed:1234", None),
+    ("rgb48be", 720, 480, "yuv420p", 1920, 1080, "lanczos", "seed:1234", None),
+    ("rgb48be", 720, 480, "yuv420p", 1920, 1080, "lanczos", "seed:1235", None),
+    ("rgb48le", 1920, 1080, "nv12", 1280, 720, "bicubic", "seed:1234", None),
+    ("rgb48le", 640, 360, "yuv420p10le", 1280, 720, "bicubic", "seed:1234", None),
+    ("rgb48be", 722, 479, "p010le", 333, 777, "area", "seed:1234", None),
 ]
 
 # Small cases whose full output is stored (tests/golden/small_cases.npz).

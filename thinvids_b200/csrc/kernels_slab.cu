@@ -43,7 +43,11 @@ constexpr int kMaxSlabOps = 3;
 // stage makes).  Sample x coefficient no longer fits a float exactly, so each sample is staged as two floats, its low
 // byte and its high byte, and the horizontal sum runs once over each (see the WIDE horizontal pass).
 constexpr int kSrcU16Split = 4;
-constexpr float kWideMagic = 0x1.8p-5f;   // 1.5 * 2^23 in units of the scaled coefficients (2^-28): the floor-by-addition constant
+// The floor-by-addition constant M of the WIDE pass, in units of the scaled coefficients (2^-(23 + hshift - 8)).  M plus the
+// quotient floor(B / 256) must stay inside [2^23, 2^24), where a float's unit is 1, and the high-byte sum A started at -M must
+// stay below 2^24 in magnitude: 1.5 * 2^23 for the RGB24 stage's 15-bit samples (high byte <= 127, shift 13), 2^23 + 2^15 for
+// RGB48's 16-bit samples (high byte <= 255, shift 15); slab_plan_create checks both against the table's largest row.
+template <int WIDE> struct WideMagic { static constexpr float value = WIDE == 15 ? 0x1.01p-7f : 0x1.8p-5f; };
 #ifndef TVS_SLAB_MIN_CTAS
 #define TVS_SLAB_MIN_CTAS 21
 #endif
@@ -395,7 +399,7 @@ __device__ __forceinline__ void slab_store_slow(uint8_t *row, int x, int dw, int
 // floor(B / 256) comes from one FMA rounded down onto 1.5 * 2^23 (where floats are integers), the A chain starts at minus
 // that constant so that the two add up exactly, and the last division is the usual multiplication rounded down onto the
 // subnormal grid.
-template <int C, int SPAN, int VT, int OUT, bool FAST, bool WIDE>
+template <int C, int SPAN, int VT, int OUT, bool FAST, int WIDE>
 __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const SlabItem &it, float *S, uint4 *RAW, int lane) {
     const SlabOpParams &op = P.op[it.oi];
     const float *v_coef = reinterpret_cast<const float *>(P.pool + P.vc[op.vclass].coef_off);
@@ -504,7 +508,8 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 #pragma unroll
                 for (int c = 0; c < C; ++c) t[c] = fmaf(px[i], cd[c][i], t[c]);
             }
-            if constexpr (WIDE) {
+            if constexpr (WIDE != 0) {
+                constexpr float kWideMagic = WideMagic<WIDE>::value;
                 // t holds B (low bytes); now A over the high bytes, started at minus the magic constant
                 const int hi_off = kBlockRows * s_pitch;   // the high bytes of a converted block sit this far behind the low bytes
                 if (C == 2 && aligned_win) {
@@ -590,7 +595,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
     for (int b = 0; b < n_blocks; ++b) {
         cp_async_wait_pending<kRawBlocks - 2>();   // this lane's copies of block b have landed ...
         __syncwarp();                              // ... and so have everybody else's; the previous block's S reads are done
-        if constexpr (WIDE)
+        if constexpr (WIDE != 0)
             slab_convert_block_split(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, lane);
         else
             slab_convert_block<C>(reinterpret_cast<const unsigned *>(RAW + (b % kRawBlocks) * block_chunks), S, words_per_row, src_mode,
@@ -614,7 +619,7 @@ __device__ __forceinline__ void slab_run_item(const SlabLaunchParams &P, const S
 // horizontal coefficients and the vertical window together need more (measured: profiles/r02_slab_history.md).
 template <int C, int SPAN, int VT> struct SlabBudget { static constexpr int kMinCtas = SPAN + VT >= 26 ? 16 : C * (SPAN + VT) >= 52 ? 18 : TVS_SLAB_MIN_CTAS; };
 
-template <int C, int SPAN, int VT, int OUT, bool WIDE>
+template <int C, int SPAN, int VT, int OUT, int WIDE>
 __global__ void __launch_bounds__(kSlabThreads, SlabBudget<C, SPAN, VT>::kMinCtas)
 slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
     constexpr int kSlabW = 32 * C;
@@ -644,9 +649,11 @@ slab_scale_kernel(const __grid_constant__ SlabLaunchParams P) {
 using SlabKernelFn = void (*)(const SlabLaunchParams);
 // `cols` adjacent output columns per lane (a slab is 32 * cols columns wide): 4 wherever the dense horizontal window of
 // four neighbours stays short (up-scales, mild down-scales), 2 for stronger down-scales, whose windows are long and far apart.
-struct SlabInstance { int cols, span, vt; SlabKernelFn fn[3], fn_wide[3]; };   // one kernel per output rule (wide sources are never dithered)
-#define TVS_SLAB_INST(C, S, V) {C, S, V, {slab_scale_kernel<C, S, V, kOutU8, false>, slab_scale_kernel<C, S, V, kOutU8Dither, false>, slab_scale_kernel<C, S, V, kOutU10, false>}, \
-                                {slab_scale_kernel<C, S, V, kOutU8, true>, nullptr, slab_scale_kernel<C, S, V, kOutU10, true>}}
+// one kernel per output rule; fn_wide13: RGB24 / BGR24 planes (never dithered), fn_wide15: RGB48 planes (8-bit output is dithered)
+struct SlabInstance { int cols, span, vt; SlabKernelFn fn[3], fn_wide13[3], fn_wide15[3]; };
+#define TVS_SLAB_INST(C, S, V) {C, S, V, {slab_scale_kernel<C, S, V, kOutU8, 0>, slab_scale_kernel<C, S, V, kOutU8Dither, 0>, slab_scale_kernel<C, S, V, kOutU10, 0>}, \
+                                {slab_scale_kernel<C, S, V, kOutU8, 13>, nullptr, slab_scale_kernel<C, S, V, kOutU10, 13>}, \
+                                {nullptr, slab_scale_kernel<C, S, V, kOutU8Dither, 15>, slab_scale_kernel<C, S, V, kOutU10, 15>}}
 const SlabInstance kSlabInstances[] = {
     TVS_SLAB_INST(4, 4, 2), TVS_SLAB_INST(4, 6, 4), TVS_SLAB_INST(4, 8, 4), TVS_SLAB_INST(4, 8, 6), TVS_SLAB_INST(4, 12, 6), TVS_SLAB_INST(4, 12, 8),
     TVS_SLAB_INST(2, 6, 4), TVS_SLAB_INST(2, 8, 6), TVS_SLAB_INST(2, 10, 8), TVS_SLAB_INST(2, 12, 10), TVS_SLAB_INST(2, 14, 12),
@@ -721,7 +728,9 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
         const bool wide_src = op.src_bits > 8;
         const int sample_bytes = wide_src ? 2 : 1;
         if (op.src_xstep != sample_bytes && op.src_xstep != 2 * sample_bytes) { err = "unexpected sample spacing"; delete sp; return nullptr; }
-        const bool split = op.src_bits == 16 && op.src_xstep == 2 && op.rule != kOut8Dither;   // the RGB input stage's 15-bit planes
+        // the RGB input stages' planes: 15-bit samples shifted by 13 (rgb24 / bgr24), 16-bit samples shifted by 15 (rgb48)
+        const bool split = op.src_bits == 16 && op.src_xstep == 2 &&
+                           ((op.hshift == 13 && op.rule != kOut8Dither) || (op.hshift == 15 && op.rule != kOut8));
         if (op.src_bits > 10 && !split) { err = "samples wider than 10 bits"; delete sp; return nullptr; }
         if (static_cast<long long>(op.sh) * op.sw * op.src_xstep >= (1LL << 30)) { err = "plane too large for 32-bit offsets"; delete sp; return nullptr; }
         const int src_mode = split ? kSrcU16Split : wide_src ? (op.src_xstep == 2 ? kSrcU16 : kSrcU16Pair) : (op.src_xstep == 1 ? kSrcU8 : kSrcU8Pair);
@@ -737,8 +746,12 @@ SlabPlan *slab_plan_create(const Plan &plan, const AxisTable host_tables[4], int
             worst_abs = std::max(worst_abs, a);
         }
         if (split) {
-            // low bytes: |B| <= 255 * worst_abs; high bytes (<= 127) on top of the 1.5 * 2^23 start value
-            if (op.hshift != 13 || 255 * worst_abs >= (1LL << 24) || 127 * worst_abs + (3LL << 22) + 255 * worst_abs / 256 + 1 >= (1LL << 24)) {
+            // low bytes: |B| <= 255 * worst_abs, and M + floor(B / 256) must stay inside [2^23, 2^24); high bytes (<= hi_max) on
+            // top of the start value -M must stay below 2^24 (see WideMagic)
+            const long long hi_max = op.hshift == 15 ? 255 : 127, magic = op.hshift == 15 ? (1LL << 23) + (1LL << 15) : (3LL << 22);
+            const long long bq = 255 * worst_abs / 256 + 1;
+            if (255 * worst_abs >= (1LL << 24) || magic - bq < (1LL << 23) || magic + bq >= (1LL << 24) ||
+                hi_max * worst_abs + magic + bq >= (1LL << 24)) {
                 err = "horizontal sum not exact in fp32"; delete sp; return nullptr;
             }
         } else if ((wide_src ? 512 : 255) * worst_abs >= (1LL << 24)) { err = "horizontal sum not exact in fp32"; delete sp; return nullptr; }
@@ -884,7 +897,8 @@ int slab_launch(const SlabPlan *p, const Plan &plan, const SampleView src_views[
         for (size_t j : members) min_dh = std::min(min_dh, plan.ops[p->ops[j].op_index].dh);
         int chunk_rows = std::max(64, std::min(min_dh, 1024));
         const SlabInstance &inst = kSlabInstances[p->ops[i].instance];
-        const SlabKernelFn fn = p->ops[i].src_mode == kSrcU16Split ? inst.fn_wide[p->ops[i].out_mode] : inst.fn[p->ops[i].out_mode];
+        const SlabKernelFn fn = p->ops[i].src_mode != kSrcU16Split ? inst.fn[p->ops[i].out_mode]
+                              : plan.ops[p->ops[i].op_index].hshift == 15 ? inst.fn_wide15[p->ops[i].out_mode] : inst.fn_wide13[p->ops[i].out_mode];
         if (!fn) return -1;
         size_t smem = 0;
         {

@@ -169,6 +169,7 @@ EXTRA_CONFIGS = {
     "C4S": ScaleConfig("C4S", "p010le", 3840, 2160, "p010le", 1920, 1080, "lanczos", 64),      # C4 on NVDEC-style P010 surfaces
     "C4N": ScaleConfig("C4N", "p010le", 3840, 2160, "nv12", 1920, 1080, "bicubic", 64),        # 10-bit 4K source to the 8-bit 1080p target
     "RGB1": ScaleConfig("RGB1", "rgb24", 720, 480, "yuv420p", 1920, 1080, "lanczos", 120),   # upscale_benchmark.py's real input
+    "RGB2": ScaleConfig("RGB2", "rgb48be", 720, 480, "yuv420p", 1920, 1080, "lanczos", 120),  # the same from 16-bit PNG frames
     "C4P8": ScaleConfig("C4P8", "yuv420p", 3840, 2160, "yuv420p", 1920, 1080, "lanczos", 64),
 }
 CONFIGS.update(EXTRA_CONFIGS)
