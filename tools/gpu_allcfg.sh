@@ -1,6 +1,6 @@
 # one short device-resident bench line per config into gpurun_out/allcfg.jsonl (no CPU arm, no host copies)
 : > gpurun_out/allcfg.jsonl
-for c in ${CFGS:-C1 C2 C3 C4 C5 W1080 W720 W4K DVD480 HDR8 C4P8 C4S C4N RGB1}; do
+for c in ${CFGS:-C1 C2 C3 C4 C5 W1080 W720 W4K DVD480 HDR8 C4P8 C4S C4N RGB1 RGB2}; do
   python bench.py --config $c --steps ${STEPS:-10} --warmup 3 --no-cpu-baseline --no-e2e 2>gpurun_out/allcfg_err.log | tail -1 >> gpurun_out/allcfg.jsonl
 done
 python - <<'PY'
