@@ -1,5 +1,6 @@
-// Slab kernel: one autonomous warp per 128-column slab, for planes that are not shrunk vertically (the up-scales of
-// BASELINE.json: 480p -> 1080p, 1080p -> 4K, and the worker's 480p -> 1080p NV12 target).
+// Slab kernel: one autonomous warp per 128-column slab.  Runs the up-scales of BASELINE.json (480p -> 1080p, 1080p -> 4K),
+// the worker's 480p -> 1080p NV12 target, 16-bit planar down-scales (two columns per lane: 4K 10-bit -> 1080p) and, through
+// the split-sample (WIDE) instances, the 15- and 16-bit planes that the packed-RGB input stages produce.
 //
 // A CTA is ONE warp.  It owns a *slab* - 128 output columns of one plane of one frame, lane L the columns 4L .. 4L+3 - and
 // walks it from its first output row to its last, source row by source row:
