@@ -11,7 +11,8 @@
  *
  * Semantics.  Output bytes are identical to libswscale 9.1.100 run with
  * flags = alg | SWS_ACCURATE_RND | SWS_BITEXACT, for 4:2:0 8- and 10-bit planar and
- * semi-planar formats.  There is no CPU fallback: every pixel is produced by sm_100a CUDA kernels, and
+ * semi-planar formats, packed RGB sources, full <-> limited range conversion, scaler parameters and the cascade
+ * libswscale runs for extreme down-scales.  There is no CPU fallback: every pixel is produced by sm_100a CUDA kernels, and
  * every call fails with a negative code when no usable device is present.
  *
  * Conventions.  All functions return 0 (or a positive count where stated) on success and a negative
@@ -222,9 +223,10 @@ TVS_API int tvs_context_table(const tvs_ctx *ctx, int which, int16_t *coef, size
  *                             5 = slab kernel (one autonomous warp per 128-column slab),
  *                             6 = cascade: two inner contexts, src -> tmp -> dst, as libswscale does for filters that reach
  *                                 170 taps (extreme down-scales); each stage picks its own kernel.
- *                             Shapes that fall back to 1 (two-pass): rgb24 sources, filters wider than the fused /
- *                             streaming instances cover (more than 24 horizontal or 12 vertical taps), tables that fail the
- *                             FP32 exactness preconditions, and footprints that do not fit in shared memory.
+ *                             Shapes that fall back to 1 (two-pass): contexts that convert between full and limited
+ *                             range, filters wider than the slab / fused / streaming instances cover (more than 24
+ *                             horizontal or 12 vertical taps), tables that fail the FP32 exactness preconditions, and
+ *                             footprints that do not fit in shared memory.
  *   TVS_INFO_SCRATCH_BYTES    device scratch currently owned by the context
  *   TVS_INFO_SRC_FRAME_BYTES / TVS_INFO_DST_FRAME_BYTES   tightly packed frame sizes
  */
