@@ -62,7 +62,9 @@ enum {
                                 TVS_SRC_FULL_RANGE, as destination TVS_DST_FULL_RANGE (libswscale's handle_jpeg) */
     TVS_FMT_BGR24       = 6, /* AV_PIX_FMT_BGR24        as TVS_FMT_RGB24 with B, G, R byte order (OpenCV's frames); SOURCE only */
     TVS_FMT_RGB48LE     = 7, /* AV_PIX_FMT_RGB48LE      R, G, B of 16 bits each, little-endian; SOURCE only, even widths */
-    TVS_FMT_RGB48BE     = 8  /* AV_PIX_FMT_RGB48BE      the same big-endian (what ffmpeg decodes a 16-bit PNG to); SOURCE only */
+    TVS_FMT_RGB48BE     = 8, /* AV_PIX_FMT_RGB48BE      the same big-endian (what ffmpeg decodes a 16-bit PNG to); SOURCE only */
+    TVS_FMT_BGR48LE     = 9, /* AV_PIX_FMT_BGR48LE      B, G, R of 16 bits each (OpenCV's 16-bit frames); SOURCE only */
+    TVS_FMT_BGR48BE     = 10 /* AV_PIX_FMT_BGR48BE      SOURCE only */
 };
 
 /* Scaler flags: numerically equal to libswscale's SWS_* so ffmpeg `flags=` values pass through. */

@@ -16,7 +16,7 @@ import numpy as np
 
 from . import build as _build
 
-_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24", 7: b"rgb48le", 8: b"rgb48be"}
+_PIXFMT_NAMES = {0: b"yuv420p", 1: b"nv12", 2: b"yuv420p10le", 3: b"p010le", 4: b"rgb24", 6: b"bgr24", 7: b"rgb48le", 8: b"rgb48be", 9: b"bgr48le", 10: b"bgr48be"}
 _libs = None
 
 
@@ -121,7 +121,7 @@ class RefScaler:
 
     def scale(self, src_planes):
         from thinvids_b200.frames import alloc_frame, plane_shapes, sample_dtype
-        if self.src[2] in (4, 6, 7, 8):
+        if self.src[2] in (4, 6, 7, 8, 9, 10):
             # packed RGB sources: the library's SIMD input stage reads and its output stage writes a few bytes past tight rows, so
             # give it padded buffers and crop
             h, row = src_planes[0].shape

@@ -27,9 +27,9 @@
 #include <string.h>
 
 enum { FMT_YUV420P = 0, FMT_NV12 = 1, FMT_YUV420P10 = 2, FMT_P010 = 3, FMT_RGB24 = 4 /* source only */, FMT_BGR24 = 6 /* source only */,
-       FMT_RGB48LE = 7, FMT_RGB48BE = 8 /* 16 bits per component, source only */ };
-static int fmt_rgb48(int f) { return f == FMT_RGB48LE || f == FMT_RGB48BE; }
-static int fmt_rgb(int f) { return f == FMT_RGB24 || f == FMT_BGR24 || f == FMT_RGB48LE || f == FMT_RGB48BE; }
+       FMT_RGB48LE = 7, FMT_RGB48BE = 8, FMT_BGR48LE = 9, FMT_BGR48BE = 10 /* 16 bits per component, source only */ };
+static int fmt_rgb48(int f) { return f >= FMT_RGB48LE && f <= FMT_BGR48BE; }
+static int fmt_rgb(int f) { return f == FMT_RGB24 || f == FMT_BGR24 || fmt_rgb48(f); }
 enum { ALG_BILINEAR = 2, ALG_BICUBIC = 4, ALG_AREA = 0x20, ALG_LANCZOS = 0x200 };
 
 typedef struct {
@@ -65,7 +65,7 @@ typedef struct {
 
 static int ilog2(unsigned v) { int r = 0; while (v > 1) { v >>= 1; r++; } return r; }
 static int64_t iabs64(int64_t v) { return v < 0 ? -v : v; }
-static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24 || f == FMT_BGR24) ? 8 : (f == FMT_RGB48LE || f == FMT_RGB48BE) ? 16 : 10; }
+static int fmt_bits(int f) { return (f == FMT_YUV420P || f == FMT_NV12 || f == FMT_RGB24 || f == FMT_BGR24) ? 8 : (f >= FMT_RGB48LE && f <= FMT_BGR48BE) ? 16 : 10; }
 static int fmt_semi(int f) { return f == FMT_NV12 || f == FMT_P010; }
 
 /* SURVEY.md A.2 — coefficient table for one axis. */
@@ -383,7 +383,7 @@ static const uint8_t D128[8][8] = {
 static inline int src_sample(const o_ctx *c, const uint8_t *const src[], const int stride[], int pl, int r, int x)
 {
     switch (c->sfmt) {
-    case FMT_RGB24: case FMT_BGR24: case FMT_RGB48LE: case FMT_RGB48BE: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
+    case FMT_RGB24: case FMT_BGR24: case FMT_RGB48LE: case FMT_RGB48BE: case FMT_BGR48LE: case FMT_BGR48BE: return c->rgb[pl][(size_t)r * (pl ? c->csw : c->sw) + x];
     case FMT_YUV420P: return src[pl][(size_t)r * stride[pl] + x];
     case FMT_NV12:
         return pl == 0 ? src[0][(size_t)r * stride[0] + x] : src[1][(size_t)r * stride[1] + 2 * x + (pl - 1)];
@@ -569,12 +569,13 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
     if (fmt_rgb48(c->sfmt)) {
         /* rgb48ToY_c / rgb48ToUV_c / rgb48ToUV_half_c: 16-bit components (either byte order), RGB2YUV_SHIFT = 15, the result
          * a full 16-bit line; the half-width chroma averages two pixels with rounding first */
-        const int be = c->sfmt == FMT_RGB48BE;
+        const int be = c->sfmt == FMT_RGB48BE || c->sfmt == FMT_BGR48BE;
+        const int ro48 = (c->sfmt == FMT_BGR48LE || c->sfmt == FMT_BGR48BE) ? 2 : 0, bo48 = 2 - ro48;   /* bgr48: R and B swapped in memory */
         for (int r = 0; r < c->sh; r++) {
             const uint8_t *row = rgb + (size_t)r * stride;
 #define PX16(i) (be ? (unsigned)(row[2 * (i)] << 8 | row[2 * (i) + 1]) : (unsigned)(row[2 * (i) + 1] << 8 | row[2 * (i)]))
             for (int x = 0; x < c->sw; x++) {
-                const unsigned R = PX16(3 * x), G = PX16(3 * x + 1), B = PX16(3 * x + 2);
+                const unsigned R = PX16(3 * x + ro48), G = PX16(3 * x + 1), B = PX16(3 * x + bo48);
                 c->rgb[0][(size_t)r * c->sw + x] = (uint16_t)(((int)(RY * R + GY * G + BY * B) + (0x2001 << 14)) >> 15);
                 if (!c->rgb_half) {
                     c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)(((int)(RU * (int)R + GU * (int)G + BU * (int)B) + (0x10001 << 14)) >> 15);
@@ -583,8 +584,8 @@ static int rgb_input_stage(o_ctx *c, const uint8_t *rgb, int stride)
             }
             if (c->rgb_half)
                 for (int x = 0; x < c->csw; x++) {
-                    const int R = (int)((PX16(6 * x) + PX16(6 * x + 3) + 1) >> 1), G = (int)((PX16(6 * x + 1) + PX16(6 * x + 4) + 1) >> 1),
-                              B = (int)((PX16(6 * x + 2) + PX16(6 * x + 5) + 1) >> 1);
+                    const int R = (int)((PX16(6 * x + ro48) + PX16(6 * x + 3 + ro48) + 1) >> 1), G = (int)((PX16(6 * x + 1) + PX16(6 * x + 4) + 1) >> 1),
+                              B = (int)((PX16(6 * x + bo48) + PX16(6 * x + 3 + bo48) + 1) >> 1);
                     c->rgb[1][(size_t)r * c->csw + x] = (uint16_t)((RU * R + GU * G + BU * B + (0x10001 << 14)) >> 15);
                     c->rgb[2][(size_t)r * c->csw + x] = (uint16_t)((RV * R + GV * G + BV * B + (0x10001 << 14)) >> 15);
                 }

@@ -116,7 +116,7 @@ def test_port_equals_genuine_library_rgb24_sources():
         cp = rnd.choice([None, None, (0, -513, 0, -513), (0, 128, 0, 128), (64, 192, 0, 64)])   # explicit chroma siting too
         # bgr24 (OpenCV's order): the same input stage with R and B swapped in memory; rgb48le / rgb48be (16-bit PNGs): 16-bit
         # lines, shift 15, ordered dither on 8-bit output
-        sf = (F.RGB24, F.RGB48LE, F.BGR24, F.RGB24, F.RGB48BE, F.BGR24)[i % 6]
+        sf = (F.RGB24, F.RGB48LE, F.BGR24, F.BGR48LE, F.RGB48BE, F.BGR48BE)[i % 6]
         src = F.random_frame(sf, sw, sh, 500 + i)
         want = ref_swscale.RefScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale(src)
         got = port.PortScaler(sw, sh, sf, dw, dh, df, alg, chr_pos=cp).scale(src)

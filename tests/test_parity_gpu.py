@@ -582,7 +582,7 @@ def test_rgb24_sources_against_oracle():
         if i >= 40:
             sw, sh, dw, dh = [(720, 480, 1920, 1080), (1440, 960, 1920, 1080), (2880, 1920, 1920, 1080), (640, 360, 1280, 720)][i % 4]
         alg, df = rnd.choice(algs), rnd.randrange(4)
-        sf = (F.RGB24, F.RGB48LE, F.RGB24, F.BGR24, F.RGB24, F.RGB48BE)[i % 6]
+        sf = (F.RGB24, F.RGB48LE, F.BGR48BE, F.BGR24, F.RGB24, F.RGB48BE, F.BGR48LE, F.RGB24)[i % 8]
         frames = [F.random_frame(sf, sw, sh, 900 + 3 * i + k) for k in range(3)]
         if i % 3 == 1:     # only 0 and the maximum
             hi = 65535 if F.bit_depth(sf) == 16 else 255
@@ -617,7 +617,7 @@ def test_error_paths():
     with pytest.raises(tv_lib.TvscaleError, match="source formats only"):
         Scaler(64, 64, 0, 32, 32, F.RGB24, F.SWS_BICUBIC)
     with pytest.raises(tv_lib.TvscaleError):
-        Scaler(64, 64, 9, 32, 32, 0, F.SWS_BICUBIC)            # unknown format
+        Scaler(64, 64, 99, 32, 32, 0, F.SWS_BICUBIC)           # unknown format
     with pytest.raises(tv_lib.TvscaleError):
         Scaler(64, 64, 0, 32, 32, 0, F.SWS_BICUBIC | F.SWS_LANCZOS)  # two algorithms
     with pytest.raises(tv_lib.TvscaleError, match="refuses"):

@@ -305,7 +305,7 @@ rgb_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t fra
 // lines, one rounding constant, and the half-width chroma averages its two pixels (with rounding) before the sum.
 __global__ void __launch_bounds__(256)
 rgb48_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t frame_stride, uint8_t *__restrict__ planes,
-                   size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half, int be) {
+                   size_t planes_frame_stride, size_t u_offset, size_t c_plane_bytes, int w, int h, int half, int be, int bgr) {
     constexpr int RY = 8414, GY = 16519, BY = 3208, RU = -4865, GU = -9528, BU = 14392, RV = 14392, GV = -12061, BV = -2332;
     const int pairs = w >> 1;
     const int idx = blockIdx.x * blockDim.x + threadIdx.x;
@@ -316,6 +316,10 @@ rgb48_input_kernel(const uint8_t *__restrict__ rgb, ptrdiff_t pitch, ptrdiff_t f
     int c[6];
 #pragma unroll
     for (int k = 0; k < 6; ++k) c[k] = be ? (p[2 * k] << 8 | p[2 * k + 1]) : (p[2 * k + 1] << 8 | p[2 * k]);
+    if (bgr) {   // bgr48: R and B swapped in memory
+        int t = c[0]; c[0] = c[2]; c[2] = t;
+        t = c[3]; c[3] = c[5]; c[5] = t;
+    }
     uint8_t *out = planes + f * planes_frame_stride;
     uint16_t *yrow = reinterpret_cast<uint16_t *>(out) + static_cast<size_t>(y) * w + 2 * i;
     // (at most 28141 * 65535 + (0x2001 << 14) < 2^31: int arithmetic, as in libswscale)
@@ -616,7 +620,7 @@ int launch_rgb_input(const uint8_t *rgb, ptrdiff_t pitch, ptrdiff_t frame_stride
     const dim3 grid((total + 255) / 256, 1, n_frames);
     if (wide)   // 1 = rgb48le, 2 = rgb48be
         rgb48_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
-                                                     half ? 1 : 0, wide == 2 ? 1 : 0);
+                                                     half ? 1 : 0, wide == 2 ? 1 : 0, bgr ? 1 : 0);
     else
         rgb_input_kernel<<<grid, 256, 0, stream>>>(rgb, pitch, frame_stride, planes, planes_frame_stride, u_offset_bytes, c_plane_bytes, w, h,
                                                    half ? 1 : 0, bgr ? 1 : 0);

@@ -21,8 +21,9 @@ namespace {
 
 struct PixMap { int av, tvs; };
 PixMap g_map[16] = {{0, TVS_FMT_YUV420P}, {23, TVS_FMT_NV12}, {62, TVS_FMT_YUV420P10LE}, {158, TVS_FMT_P010LE},
-                    {2, TVS_FMT_RGB24},  {3, TVS_FMT_BGR24}, {12, TVS_FMT_YUVJ420P}, {35, TVS_FMT_RGB48LE}, {34, TVS_FMT_RGB48BE}};
-int g_map_n = 9;
+                    {2, TVS_FMT_RGB24},  {3, TVS_FMT_BGR24}, {12, TVS_FMT_YUVJ420P}, {35, TVS_FMT_RGB48LE}, {34, TVS_FMT_RGB48BE},
+                    {58, TVS_FMT_BGR48LE}, {57, TVS_FMT_BGR48BE}};
+int g_map_n = 11;
 
 int to_tvs(int av) {
     for (int i = 0; i < g_map_n; ++i)
@@ -33,7 +34,7 @@ int to_tvs(int av) {
 int planes_of(int tvs_fmt) {
     switch (tvs_fmt) {
     case TVS_FMT_NV12: case TVS_FMT_P010LE: return 2;
-    case TVS_FMT_RGB24: case TVS_FMT_BGR24: case TVS_FMT_RGB48LE: case TVS_FMT_RGB48BE: return 1;
+    case TVS_FMT_RGB24: case TVS_FMT_BGR24: case TVS_FMT_RGB48LE: case TVS_FMT_RGB48BE: case TVS_FMT_BGR48LE: case TVS_FMT_BGR48BE: return 1;
     default: return 3;
     }
 }

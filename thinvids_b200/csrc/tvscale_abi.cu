@@ -57,6 +57,8 @@ bool format_info(int fmt, FormatInfo &fi) {
     case TVS_FMT_BGR24: fi = {8, 1, 0, false, 1, true, true}; return true;
     case TVS_FMT_RGB48LE: fi = {16, 2, 0, false, 1, true, false, false}; return true;
     case TVS_FMT_RGB48BE: fi = {16, 2, 0, false, 1, true, false, true}; return true;
+    case TVS_FMT_BGR48LE: fi = {16, 2, 0, false, 1, true, true, false}; return true;
+    case TVS_FMT_BGR48BE: fi = {16, 2, 0, false, 1, true, true, true}; return true;
     default: return false;
     }
 }

@@ -18,10 +18,10 @@ import numpy as np
 
 # Pixel-format codes of the C ABI (include/tvscale.h).
 YUV420P, NV12, YUV420P10LE, P010LE, RGB24 = 0, 1, 2, 3, 4
-RGB48LE, RGB48BE = 7, 8   # 16 bits per component, either byte order (16-bit PNGs decode as rgb48be)
+RGB48LE, RGB48BE, BGR48LE, BGR48BE = 7, 8, 9, 10   # 16 bits per component (16-bit PNGs decode as rgb48be, OpenCV holds bgr48le)
 BGR24 = 6   # (5 is the C ABI's yuvj420p, which the Python layer spells as yuv420p + full range)
-FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE, "rgb24": RGB24, "bgr24": BGR24, "rgb48le": RGB48LE, "rgb48be": RGB48BE}
-SOURCE_ONLY_FORMATS = {RGB24, BGR24, RGB48LE, RGB48BE}
+FMT_BY_NAME = {"yuv420p": YUV420P, "nv12": NV12, "yuv420p10le": YUV420P10LE, "p010le": P010LE, "rgb24": RGB24, "bgr24": BGR24, "rgb48le": RGB48LE, "rgb48be": RGB48BE, "bgr48le": BGR48LE, "bgr48be": BGR48BE}
+SOURCE_ONLY_FORMATS = {RGB24, BGR24, RGB48LE, RGB48BE, BGR48LE, BGR48BE}
 NAME_BY_FMT = {v: k for k, v in FMT_BY_NAME.items()}
 
 # Scaler algorithm flags, numerically equal to libswscale's SWS_* values.
@@ -40,7 +40,7 @@ def is_semiplanar(fmt) -> bool:
 
 def bit_depth(fmt) -> int:
     code = fmt_code(fmt)
-    return 8 if code in (YUV420P, NV12, RGB24, BGR24) else 16 if code in (RGB48LE, RGB48BE) else 10
+    return 8 if code in (YUV420P, NV12, RGB24, BGR24) else 16 if code in (RGB48LE, RGB48BE, BGR48LE, BGR48BE) else 10
 
 
 def sample_dtype(fmt):
@@ -50,7 +50,7 @@ def sample_dtype(fmt):
 def plane_shapes(fmt, w: int, h: int):
     """(rows, cols-in-samples) of every stored plane of a tightly packed frame."""
     cw, ch = (w + 1) // 2, (h + 1) // 2
-    if fmt_code(fmt) in (RGB24, BGR24, RGB48LE, RGB48BE):
+    if fmt_code(fmt) in (RGB24, BGR24, RGB48LE, RGB48BE, BGR48LE, BGR48BE):
         return [(h, 3 * w)]          # one plane of R, G, B bytes
     if is_semiplanar(fmt):
         return [(h, w), (ch, 2 * cw)]

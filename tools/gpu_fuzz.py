@@ -107,7 +107,7 @@ def main():
         big = huge or rnd.random() < 0.25
         sw, sh = (rnd.randrange(200, 3850 if huge else 1930), rnd.randrange(100, 2170 if huge else 1090)) if big \
             else (rnd.randrange(2, 400), rnd.randrange(2, 300))
-        if sf in (4, 6, 7, 8):
+        if sf in (4, 6, 7, 8, 9, 10):
             sw += sw & 1
         mode = rnd.random()
         if mode < 0.15:
