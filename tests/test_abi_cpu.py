@@ -121,3 +121,24 @@ def test_libswscale_api_shim_loads_and_exports_the_trio():
     assert shim.tvs_shim_map_pix_fmt(9999, 0) == 0
     shim.sws_freeContext.argtypes = [ctypes.c_void_p]
     shim.sws_freeContext(None)
+
+
+def test_python_constants_match_the_header():
+    """Format codes, flag bits and info keys are spelled twice (include/tvscale.h, thinvids_b200/{frames,lib}.py): keep them equal."""
+    import os
+    import re
+    from thinvids_b200 import frames as F
+    from thinvids_b200 import lib as tv_lib
+    text = open(os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "include", "tvscale.h")).read()
+    vals = {m.group(1): int(m.group(2), 0) for m in re.finditer(r"\b(TVS_[A-Z0-9_]+)\s*=\s*(0x[0-9a-fA-F]+|\d+)", text)}
+    for name, code in (("YUV420P", F.YUV420P), ("NV12", F.NV12), ("YUV420P10LE", F.YUV420P10LE), ("P010LE", F.P010LE), ("RGB24", F.RGB24),
+                       ("YUVJ420P", tv_lib.FMT_YUVJ420P), ("BGR24", F.BGR24), ("RGB48LE", F.RGB48LE), ("RGB48BE", F.RGB48BE),
+                       ("BGR48LE", F.BGR48LE), ("BGR48BE", F.BGR48BE)):
+        assert vals["TVS_FMT_" + name] == code, name
+    assert (vals["TVS_BILINEAR"], vals["TVS_BICUBIC"], vals["TVS_AREA"], vals["TVS_LANCZOS"]) == (F.SWS_BILINEAR, F.SWS_BICUBIC, F.SWS_AREA, F.SWS_LANCZOS)
+    assert (vals["TVS_ACCURATE_RND"], vals["TVS_BITEXACT"]) == (F.SWS_ACCURATE_RND, F.SWS_BITEXACT)
+    assert (vals["TVS_SRC_FULL_RANGE"], vals["TVS_DST_FULL_RANGE"]) == (tv_lib.SRC_FULL_RANGE, tv_lib.DST_FULL_RANGE)
+    assert [vals[k] for k in ("TVS_INFO_KERNEL_LAUNCHES", "TVS_INFO_PATH", "TVS_INFO_SCRATCH_BYTES", "TVS_INFO_SRC_FRAME_BYTES",
+                              "TVS_INFO_DST_FRAME_BYTES")] == [tv_lib.INFO_KERNEL_LAUNCHES, tv_lib.INFO_PATH, tv_lib.INFO_SCRATCH_BYTES,
+                                                               tv_lib.INFO_SRC_FRAME_BYTES, tv_lib.INFO_DST_FRAME_BYTES]
+    assert float(re.search(r"#define TVS_PARAM_DEFAULT\s+([0-9.]+)", text).group(1)) == tv_lib.PARAM_DEFAULT
